@@ -1,0 +1,225 @@
+/*
+ * TEST INFRASTRUCTURE ONLY -- see oref.h.  Thin driver over the reference's own classes,
+ * following the head-less pattern of Client/HitTestDebugger.cpp:38-57,147-305.
+ */
+#include "oref.h"
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <Client/GameMap.h>
+#include <Client/SceneDefinition.h>
+#include <Core/Bitmap.h>
+#include <Core/Exception.h>
+#include <Core/MemoryStream.h>
+#include <Core/Settings.h>
+#include <Core/StdStream.h>
+#include <Draw/SWFeatureLevel.h>
+#include <Draw/SWMapRenderer.h>
+#include <Draw/SWPort.h>
+#include <Draw/SWRenderer.h>
+
+using namespace spades;
+
+/* SWMapRenderer::Line / LinePixel are private to SWMapRenderer.cpp (:70-105); the harness only
+   needs to read them, so it names layout-identical definitions here (8-byte pixel: combined,
+   depth; Line: vector, horizonDir, pitchTanMin, pitchScale, pitchTanMinI, pitchScaleI). */
+struct spades::draw::SWMapRenderer::LinePixel {
+	uint32_t combined;
+	float depth;
+};
+struct spades::draw::SWMapRenderer::Line {
+	std::vector<LinePixel> pixels;
+	Vector3 horizonDir;
+	float pitchTanMin;
+	float pitchScale;
+	int pitchTanMinI;
+	int pitchScaleI;
+};
+
+namespace {
+	thread_local std::string g_err;
+
+	class Port : public draw::SWPort {
+		Handle<Bitmap> bmp;
+
+	public:
+		Port(int w, int h) { bmp = Handle<Bitmap>::New(w, h); }
+		Bitmap &GetFramebuffer() override { return *bmp; }
+		void Swap() override {}
+	};
+
+	struct Renderer {
+		Handle<Port> port;
+		Handle<draw::SWRenderer> r;
+		int w, h;
+	};
+} // namespace
+
+extern "C" {
+
+const char *oref_variant(void) {
+#if ENABLE_SSE2
+	return "sse2";
+#else
+	return "ieee";
+#endif
+}
+
+const char *oref_last_error(void) { return g_err.c_str(); }
+
+void *oref_map_load_vxl(const char *path) {
+	try {
+		FILE *f = fopen(path, "rb");
+		if (!f) { g_err = std::string("cannot open ") + path; return nullptr; }
+		StdStream s(f, true);
+		return client::GameMap::Load(&s);
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+void *oref_map_load_vxl_mem(const void *data, size_t len) {
+	try {
+		MemoryStream s(reinterpret_cast<const char *>(data), len);
+		return client::GameMap::Load(&s);
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+void *oref_map_from_arrays(const uint64_t *solid, const uint32_t *color) {
+	auto *m = new client::GameMap();
+	std::memcpy(m->solidMap, solid, sizeof(m->solidMap));
+	std::memcpy(m->colorMap, color, sizeof(m->colorMap));
+	return m;
+}
+
+void oref_map_free(void *map) { reinterpret_cast<client::GameMap *>(map)->Release(); }
+
+void oref_map_get_arrays(void *map, uint64_t *solid, uint32_t *color) {
+	auto *m = reinterpret_cast<client::GameMap *>(map);
+	if (solid) std::memcpy(solid, m->solidMap, sizeof(m->solidMap));
+	if (color) std::memcpy(color, m->colorMap, sizeof(m->colorMap));
+}
+
+void oref_map_set(void *map, int x, int y, int z, int solid, uint32_t color) {
+	reinterpret_cast<client::GameMap *>(map)->Set(x, y, z, solid != 0, color);
+}
+
+void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps, oref_rayhit *out,
+                   size_t n, int threads) {
+	auto *m = reinterpret_cast<const client::GameMap *>(map);
+	if (threads < 1) threads = 1;
+#pragma omp parallel for num_threads(threads) schedule(static)
+	for (long long i = 0; i < (long long)n; i++) {
+		client::GameMap::RayCastResult res;
+		std::memset(&res, 0, sizeof(res)); /* hitBlock/normal stay 0 when maxSteps==0 */
+		res = m->CastRay2(MakeVector3(v0[i * 3], v0[i * 3 + 1], v0[i * 3 + 2]),
+		                  MakeVector3(dir[i * 3], dir[i * 3 + 1], dir[i * 3 + 2]), maxSteps);
+		oref_rayhit &o = out[i];
+		o.hit = res.hit; o.startSolid = res.startSolid; o.pad[0] = o.pad[1] = 0;
+		o.hitPos[0] = res.hitPos.x; o.hitPos[1] = res.hitPos.y; o.hitPos[2] = res.hitPos.z;
+		o.hitBlock[0] = res.hitBlock.x; o.hitBlock[1] = res.hitBlock.y; o.hitBlock[2] = res.hitBlock.z;
+		o.normal[0] = res.normal.x; o.normal[1] = res.normal.y; o.normal[2] = res.normal.z;
+	}
+}
+
+void oref_renderer_set_threads(int threads) {
+	Settings::ItemHandle h("r_swNumThreads", nullptr);
+	h = threads;
+}
+
+void *oref_renderer_create(int w, int h, int level, int threads) {
+	try {
+		oref_renderer_set_threads(threads);
+		auto *R = new Renderer();
+		R->w = w; R->h = h;
+		R->port = Handle<Port>::New(w, h);
+		if (level < 0)
+			R->r = Handle<draw::SWRenderer>::New(R->port.Cast<draw::SWPort>());
+		else
+			R->r = Handle<draw::SWRenderer>::New(R->port.Cast<draw::SWPort>(),
+			                                     static_cast<draw::SWFeatureLevel>(level));
+		R->r->Init();
+		return R;
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+int oref_renderer_level(void *r) {
+	return static_cast<int>(reinterpret_cast<Renderer *>(r)->r->featureLevel);
+}
+
+void oref_renderer_free(void *r) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	try { R->r->SetGameMap({}); R->r->Shutdown(); } catch (...) {}
+	delete R;
+}
+
+void oref_renderer_set_map(void *r, void *map) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	if (map) R->r->SetGameMap(*reinterpret_cast<client::GameMap *>(map));
+	else R->r->SetGameMap({});
+}
+
+void oref_renderer_set_fog(void *r, float cr, float cg, float cb, float dist) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	R->r->SetFogColor(MakeVector3(cr, cg, cb));
+	R->r->SetFogDistance(dist);
+}
+
+int oref_renderer_render(void *r, const oref_scene *s, uint32_t *bgrx, float *depth) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	try {
+		client::SceneDefinition def;
+		def.viewportLeft = def.viewportTop = 0;
+		def.viewportWidth = R->w; def.viewportHeight = R->h;
+		def.fovX = s->fovX; def.fovY = s->fovY;
+		def.viewOrigin = MakeVector3(s->origin[0], s->origin[1], s->origin[2]);
+		for (int i = 0; i < 3; i++)
+			def.viewAxis[i] = MakeVector3(s->axis[i][0], s->axis[i][1], s->axis[i][2]);
+		def.zNear = s->zNear; def.zFar = s->zFar;
+		def.skipWorld = false;
+		R->r->StartScene(def);
+		R->r->EndScene();
+		R->r->FrameDone();
+		size_t n = (size_t)R->w * R->h;
+		if (bgrx) std::memcpy(bgrx, R->port->GetFramebuffer().GetPixels(), n * 4);
+		if (depth) std::memcpy(depth, R->r->depthBuffer.data(), n * 4);
+		return 0;
+	} catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+
+int oref_renderer_rle(void *r, int x, int y, int8_t *out, int cap) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	auto *mr = R->r->mapRenderer.get();
+	if (!mr) return -1;
+	int idx = x + y * mr->w;
+	int len = (int)mr->rleLen[idx];
+	const int8_t *p = mr->rleHeap.Dereference<int8_t>(mr->rle[idx]);
+	if (len > cap) len = cap;
+	std::memcpy(out, p, len);
+	return len;
+}
+
+int oref_renderer_lines(void *r, int *lineRes) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	auto *mr = R->r->mapRenderer.get();
+	if (!mr) return -1;
+	if (lineRes) *lineRes = (int)mr->lineResolution;
+	return (int)mr->lines.size();
+}
+
+int oref_renderer_line(void *r, int i, uint32_t *combined, float *depth, float *misc, int32_t *misci) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	auto *mr = R->r->mapRenderer.get();
+	if (!mr || i < 0 || i >= (int)mr->lines.size()) return -1;
+	auto &l = mr->lines[i];
+	int n = (int)l.pixels.size();
+	for (int j = 0; j < n; j++) {
+		if (combined) combined[j] = l.pixels[j].combined;
+		if (depth) depth[j] = l.pixels[j].depth;
+	}
+	if (misc) { misc[0] = l.horizonDir.x; misc[1] = l.horizonDir.y; misc[2] = l.pitchTanMin; misc[3] = l.pitchScale; }
+	if (misci) { misci[0] = l.pitchTanMinI; misci[1] = l.pitchScaleI; }
+	return n;
+}
+
+} // extern "C"

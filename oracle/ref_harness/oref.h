@@ -1,0 +1,67 @@
+/*
+ * oref -- C entry points into the UNMODIFIED reference code (yvt/openspades), compiled in
+ * place from /root/reference by oracle/Makefile into oracle/_ref/liboref_{sse2,ieee}.so.
+ *
+ * TEST INFRASTRUCTURE ONLY: used by tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline / --impl reference legs as the checker and the timed CPU baseline.  Nothing
+ * in the product (openspades_b200/, include/) links, loads or calls it.
+ */
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OREF_API __attribute__((visibility("default")))
+
+/* Mirrors client::SceneDefinition's fields used by the terrain path (SceneDefinition.h:26-33). */
+typedef struct oref_scene {
+	float origin[3];
+	float axis[3][3]; /* viewAxis[0]=right, [1]=up, [2]=front */
+	float fovX, fovY;
+	float zNear, zFar;
+} oref_scene;
+
+/* Same field order/offsets as GameMap::RayCastResult (GameMap.h:150-156), 40 bytes. */
+typedef struct oref_rayhit {
+	uint8_t hit, startSolid, pad[2];
+	float hitPos[3];
+	int32_t hitBlock[3];
+	int32_t normal[3];
+} oref_rayhit;
+
+OREF_API const char *oref_variant(void); /* "sse2" or "ieee" (compile-time) */
+
+/* ---- GameMap ---- */
+OREF_API void *oref_map_load_vxl(const char *path);  /* GameMap::Load, GameMap.cpp:519 */
+OREF_API void *oref_map_load_vxl_mem(const void *data, size_t len);
+OREF_API void *oref_map_from_arrays(const uint64_t *solid /*[x][y]*/, const uint32_t *color /*[x][y][z]*/);
+OREF_API void oref_map_free(void *map);
+OREF_API void oref_map_get_arrays(void *map, uint64_t *solid, uint32_t *color);
+OREF_API void oref_map_set(void *map, int x, int y, int z, int solid, uint32_t color); /* GameMap::Set, notifies listeners */
+OREF_API void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps,
+                            oref_rayhit *out, size_t n, int threads); /* GameMap::CastRay2 */
+
+/* ---- SWRenderer ---- */
+/* level: -1 = DetectFeatureLevel(), else SWFeatureLevel enum value of this build */
+OREF_API void *oref_renderer_create(int w, int h, int level, int threads);
+OREF_API void oref_renderer_free(void *r);
+OREF_API int oref_renderer_level(void *r);
+OREF_API void oref_renderer_set_threads(int threads); /* cvar r_swNumThreads */
+OREF_API void oref_renderer_set_map(void *r, void *map);
+OREF_API void oref_renderer_set_fog(void *r, float cr, float cg, float cb, float dist);
+/* StartScene + EndScene + FrameDone; copies framebuffer (BGRX) and depth when non-NULL.
+   Returns 0, or -1 when the reference threw. */
+OREF_API int oref_renderer_render(void *r, const oref_scene *s, uint32_t *bgrx, float *depth);
+OREF_API const char *oref_last_error(void);
+/* raw RLE bytes of column (x,y) as SWMapRenderer stores them; returns length */
+OREF_API int oref_renderer_rle(void *r, int x, int y, int8_t *out, int cap);
+/* strip buffer of the last frame (for debugging parity): numLines, lineResolution */
+OREF_API int oref_renderer_lines(void *r, int *lineRes);
+OREF_API int oref_renderer_line(void *r, int i, uint32_t *combined, float *depth, float *misc /*horizX,horizY,pitchTanMin,pitchScale*/, int32_t *misci);
+
+#ifdef __cplusplus
+}
+#endif
