@@ -1,0 +1,116 @@
+/*
+ * osb200 -- C ABI of the B200-native voxel hot path for OpenSpades.
+ *
+ * The reference (yvt/openspades) has no FFI for this path: the software renderer is the C++
+ * class draw::SWRenderer behind client::IRenderer (Sources/Client/IRenderer.h:98-174,
+ * Sources/Draw/SWRenderer.h:48-219) and the ray query is the member GameMap::CastRay2
+ * (Sources/Client/GameMap.h:150-157).  This header is the boundary a maintainer binds instead:
+ * plain pointers and sizes, opaque context handle, int status (0 = ok, <0 = error, text via
+ * osb200_last_error()).  Each entry point names the reference interface it replaces.
+ * The host-side C++ class with SWRenderer's surface that sits on top of it is
+ * openspades_b200/host/B200Renderer.h; INTEGRATION.md shows the reference-side wiring.
+ *
+ * Every function requires a CUDA device (sm_100a).  There is no CPU fallback.
+ * A context is thread-compatible (one caller at a time), like SWRenderer itself.
+ */
+#ifndef OSB200_H
+#define OSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OSB200_API __attribute__((visibility("default")))
+
+#define OSB200_MAP_W 512 /* GameMap::DefaultWidth  (GameMap.h:45-49) */
+#define OSB200_MAP_H 512
+#define OSB200_MAP_D 64
+
+typedef struct osb200_ctx osb200_ctx;
+
+/* Which of the reference's numerically different builds of the SW path to reproduce
+ * (Sources/Draw/SWFeatureLevel.h:25-121). */
+enum osb200_numerics {
+	OSB200_NUM_IEEE = 0, /* SWFeatureLevel::None built without SSE: fastRcp = 1/x, scalar shading, truncating fog */
+	OSB200_NUM_SSE = 1,  /* SWFeatureLevel::SSE: rcpss/rsqrtss approximations, scalar shading, truncating fog */
+	OSB200_NUM_SSE2 = 2  /* SWFeatureLevel::SSE2 (the reference's default): rcpss/rsqrtss, SSE2 shading, rounding fog */
+};
+
+typedef struct osb200_opts {
+	int device;       /* CUDA device ordinal */
+	int numerics;     /* enum osb200_numerics */
+	int sw_threads;   /* emulated r_swNumThreads (SWRenderer.cpp:41): the reference's per-thread float
+	                     recurrences in RenderFinal / ApplyFog make the frame depend on it. 0 -> 4 */
+	int undersampling; /* r_swUndersampling (SWMapRenderer.cpp:37): 1, 2 or 4. 0 -> 1 */
+	int radiosity_mode; /* r_radiosity (GLSettings.cpp:60): 1 = sqrt-compressed, 2 = linear. 0 -> 1 */
+	/* rcpss / rsqrtss lookup tables for OSB200_NUM_SSE/SSE2: the result bits for every input whose
+	 * mantissa's top `rcp_bits` (`rsqrt_bits`) bits are i and whose exponent is 0 (rcp) or 0/1 (rsqrt,
+	 * 2 << rsqrt_bits entries, odd exponent second).  NULL -> osb200_create measures them itself on
+	 * this host with osb200_calibrate_sse (i.e. matches the reference SWRenderer run on this CPU);
+	 * pass tables to match another CPU.  Ignored in IEEE mode. */
+	const uint32_t *rcp_table;
+	int rcp_bits;
+	const uint32_t *rsqrt_table;
+	int rsqrt_bits;
+} osb200_opts;
+
+/* Fields of client::SceneDefinition the terrain path reads (Sources/Client/SceneDefinition.h:26-33). */
+typedef struct osb200_scene {
+	float origin[3];  /* viewOrigin */
+	float axis[3][3]; /* viewAxis[0] = right, [1] = up, [2] = front */
+	float fovX, fovY; /* radians */
+	float zNear, zFar;
+} osb200_scene;
+
+/* Same fields, order and offsets as GameMap::RayCastResult (GameMap.h:150-156); 40 bytes. */
+typedef struct osb200_rayhit {
+	uint8_t hit, startSolid, pad_[2];
+	float hitPos[3];
+	int32_t hitBlock[3];
+	int32_t normal[3];
+} osb200_rayhit;
+
+/* ---- lifetime / errors (replaces SWRenderer ctor/Init/Shutdown, SWRenderer.cpp:45-170) ---- */
+OSB200_API const char *osb200_last_error(void);
+OSB200_API int osb200_create(const osb200_opts *opts, osb200_ctx **out);
+OSB200_API void osb200_destroy(osb200_ctx *ctx);
+OSB200_API int osb200_sync(osb200_ctx *ctx);
+/* Measures the host CPU's RCPSS/RSQRTSS (SWFeatureLevel.h:89-116 fastRcp/fastRSqrt/fastDiv) into lookup
+ * tables of 1 << *rcp_bits and 2 << *rsqrt_bits entries (buffers sized for max_bits <= 16). */
+OSB200_API int osb200_calibrate_sse(uint32_t *rcp_table, int *rcp_bits, uint32_t *rsqrt_table,
+                                    int *rsqrt_bits, int max_bits);
+/* cudaStream_t the context launches on (for callers that time with events) */
+OSB200_API void *osb200_stream(osb200_ctx *ctx);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+OSB200_API uint64_t osb200_launch_count(osb200_ctx *ctx);
+
+/* ---- map residency (replaces SWRenderer::SetGameMap + SWMapRenderer ctor's RLE build,
+ *      SWRenderer.cpp:172-191, SWMapRenderer.cpp:107-203) ----
+ * solid: uint64[512][512] indexed [x][y], bit z set = solid (GameMap.h:160)
+ * color: uint32[512][512][64] indexed [x][y][z], 0xHHBBGGRR (GameMap.h:161)            */
+OSB200_API int osb200_map_upload(osb200_ctx *ctx, const uint64_t *solid, const uint32_t *color);
+/* replaces SWRenderer::GameMapChanged -> SWFlatMapRenderer::SetNeedsUpdate (SWRenderer.cpp:1148-1154,
+ * SWFlatMapRenderer.cpp:107-111): O(1), host-only. */
+OSB200_API int osb200_map_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
+/* replaces SWFlatMapRenderer::Update -> SWMapRenderer::UpdateRle x5 (SWFlatMapRenderer.cpp:52-92):
+ * re-packs and uploads only the dirty columns (and their 4 neighbours' derived data) from the
+ * caller's live arrays.  Returns the number of columns uploaded (>= 0) or < 0. */
+OSB200_API int osb200_map_flush(osb200_ctx *ctx, const uint64_t *solid, const uint32_t *color);
+/* read back the device-resident solid map ([x][y] order) -- test hook */
+OSB200_API int osb200_map_read_solid(osb200_ctx *ctx, uint64_t *solid);
+
+/* ---- GameMap::CastRay2 (GameMap.cpp:361-507), batched ----
+ * v0, dir: n x 3 floats; out: n records.  Host-pointer form copies in/out; the _device form takes
+ * device pointers and only enqueues on the context stream. */
+OSB200_API int osb200_castray2(osb200_ctx *ctx, const float *v0, const float *dir, int maxSteps,
+                               osb200_rayhit *out, size_t n);
+OSB200_API int osb200_castray2_device(osb200_ctx *ctx, const float *d_v0, const float *d_dir,
+                                      int maxSteps, osb200_rayhit *d_out, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OSB200_H */

@@ -1,0 +1,181 @@
+"""ctypes binding of the osb200 C ABI (include/osb200.h) -- used by tests/, bench.py and smoke().
+
+The product is the CUDA library; this file only marshals numpy / torch buffers into the plain
+pointers the C ABI takes.  Loading fails loudly when the library has not been built, and every
+compute call fails loudly (OsbError) when no CUDA device is present: there is no CPU fallback.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libosb200.so")
+
+NUM_IEEE, NUM_SSE, NUM_SSE2 = 0, 1, 2
+
+
+class OsbError(RuntimeError):
+    pass
+
+
+class Opts(ctypes.Structure):
+    _fields_ = [
+        ("device", ctypes.c_int),
+        ("numerics", ctypes.c_int),
+        ("sw_threads", ctypes.c_int),
+        ("undersampling", ctypes.c_int),
+        ("radiosity_mode", ctypes.c_int),
+        ("rcp_table", ctypes.c_void_p),
+        ("rcp_bits", ctypes.c_int),
+        ("rsqrt_table", ctypes.c_void_p),
+        ("rsqrt_bits", ctypes.c_int),
+    ]
+
+
+# numpy dtypes matching the C structs
+SCENE_DTYPE = np.dtype([("origin", "<f4", 3), ("axis", "<f4", (3, 3)), ("fovX", "<f4"), ("fovY", "<f4"),
+                        ("zNear", "<f4"), ("zFar", "<f4")])
+RAYHIT_DTYPE = np.dtype([("hit", "u1"), ("startSolid", "u1"), ("pad", "u1", 2), ("hitPos", "<f4", 3),
+                         ("hitBlock", "<i4", 3), ("normal", "<i4", 3)])
+assert SCENE_DTYPE.itemsize == 64 and RAYHIT_DTYPE.itemsize == 40
+
+_lib = None
+
+
+def load_library():
+    """dlopen libosb200.so; raises OsbError (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise OsbError(f"{LIB_PATH} not built: run `python -m openspades_b200.build` (needs nvcc); "
+                       "there is no CPU fallback")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, ci, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+    lib.osb200_last_error.restype = ctypes.c_char_p
+    lib.osb200_create.argtypes = [ctypes.POINTER(Opts), ctypes.POINTER(vp)]
+    lib.osb200_destroy.argtypes = [vp]
+    lib.osb200_destroy.restype = None
+    lib.osb200_sync.argtypes = [vp]
+    lib.osb200_stream.argtypes = [vp]
+    lib.osb200_stream.restype = vp
+    lib.osb200_launch_count.argtypes = [vp]
+    lib.osb200_launch_count.restype = ctypes.c_uint64
+    lib.osb200_map_upload.argtypes = [vp, vp, vp]
+    lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
+    lib.osb200_map_flush.argtypes = [vp, vp, vp]
+    lib.osb200_map_read_solid.argtypes = [vp, vp]
+    lib.osb200_castray2.argtypes = [vp, vp, vp, ci, vp, sz]
+    lib.osb200_castray2_device.argtypes = [vp, vp, vp, ci, vp, sz]
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):  # torch tensor (device or pinned host memory)
+        return a.data_ptr()
+    return a
+
+
+def calibrate_sse(max_bits=16):
+    """Host RCPSS/RSQRTSS tables (osb200_calibrate_sse). Pure host code; works without a GPU."""
+    lib = load_library()
+    lib.osb200_calibrate_sse.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int), ctypes.c_void_p,
+                                         ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    rcp = np.zeros(1 << max_bits, np.uint32)
+    rsq = np.zeros(2 << max_bits, np.uint32)
+    rb, sb = ctypes.c_int(0), ctypes.c_int(0)
+    rc = lib.osb200_calibrate_sse(rcp.ctypes.data, ctypes.byref(rb), rsq.ctypes.data, ctypes.byref(sb), max_bits)
+    if rc:
+        raise OsbError(lib.osb200_last_error().decode())
+    return rcp[: 1 << rb.value].copy(), rb.value, rsq[: 2 << sb.value].copy(), sb.value
+
+
+class Context:
+    """Owns one osb200_ctx (one GPU).  Mirrors the C ABI one to one."""
+
+    def __init__(self, device=0, numerics=NUM_SSE2, sw_threads=4, undersampling=1, radiosity_mode=1):
+        self._lib = load_library()
+        self._h = ctypes.c_void_p()
+        o = Opts(device=device, numerics=numerics, sw_threads=sw_threads, undersampling=undersampling,
+                 radiosity_mode=radiosity_mode, rcp_table=None, rcp_bits=0, rsqrt_table=None, rsqrt_bits=0)
+        rc = self._lib.osb200_create(ctypes.byref(o), ctypes.byref(self._h))
+        if rc:
+            raise OsbError(f"osb200_create failed ({rc}): {self._lib.osb200_last_error().decode()}")
+        self.device = device
+        self.numerics = numerics
+
+    def _check(self, rc):
+        if rc < 0:
+            raise OsbError(f"osb200 error {rc}: {self._lib.osb200_last_error().decode()}")
+        return rc
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.osb200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def stream(self):
+        return self._lib.osb200_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(self._lib.osb200_launch_count(self._h))
+
+    def sync(self):
+        self._check(self._lib.osb200_sync(self._h))
+
+    # ---- map ----
+    def map_upload(self, solid, color):
+        solid = np.ascontiguousarray(solid, np.uint64)
+        color = np.ascontiguousarray(color, np.uint32)
+        assert solid.shape == (512, 512) and color.shape == (512, 512, 64)
+        self._check(self._lib.osb200_map_upload(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def map_mark_dirty(self, x, y, z):
+        self._check(self._lib.osb200_map_mark_dirty(self._h, int(x), int(y), int(z)))
+
+    def map_flush(self, solid, color):
+        assert solid.dtype == np.uint64 and color.dtype == np.uint32
+        assert solid.flags.c_contiguous and color.flags.c_contiguous
+        return self._check(self._lib.osb200_map_flush(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def map_read_solid(self):
+        out = np.zeros((512, 512), np.uint64)
+        self._check(self._lib.osb200_map_read_solid(self._h, out.ctypes.data))
+        return out
+
+    # ---- GameMap::CastRay2 ----
+    def castray2(self, v0, dirs, max_steps):
+        """Host arrays in, host structured array (RAYHIT_DTYPE) out."""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n = v0.shape[0]
+        assert v0.shape == (n, 3) and dirs.shape == (n, 3)
+        out = np.zeros(n, RAYHIT_DTYPE)
+        self._check(self._lib.osb200_castray2(self._h, v0.ctypes.data, dirs.ctypes.data, int(max_steps),
+                                              out.ctypes.data, n))
+        return out
+
+    def castray2_device(self, d_v0, d_dir, max_steps, d_out, n):
+        """Device pointers (ints or torch CUDA tensors); enqueue only."""
+        self._check(self._lib.osb200_castray2_device(self._h, _ptr(d_v0), _ptr(d_dir), int(max_steps),
+                                                     _ptr(d_out), int(n)))

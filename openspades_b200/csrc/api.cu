@@ -1,0 +1,328 @@
+// Context lifetime, error reporting and map residency for the osb200 C ABI (include/osb200.h).
+//
+// Reference behaviour being replaced:
+//   SWRenderer::SetGameMap          Sources/Draw/SWRenderer.cpp:172-191
+//   SWMapRenderer ctor / BuildRle   Sources/Draw/SWMapRenderer.cpp:107-203   (the six z-lists are pure bit
+//       functions of a column's 64-bit mask and its neighbour's, so nothing is pre-built here: the
+//       line kernel derives them from the resident bitmap -- see terrain.cu)
+//   SWFlatMapRenderer dirty bitset  Sources/Draw/SWFlatMapRenderer.cpp:52-111
+#include "ctx.h"
+
+#include <cstdarg>
+#include <cstring>
+
+namespace osb {
+	static thread_local std::string g_err;
+	void set_error(const char *fmt, ...) {
+		char buf[1024];
+		va_list ap;
+		va_start(ap, fmt);
+		vsnprintf(buf, sizeof(buf), fmt, ap);
+		va_end(ap);
+		g_err = buf;
+	}
+	void terrain_destroy(osb200_ctx *ctx);   // terrain.cu
+	void radiosity_destroy(osb200_ctx *ctx); // radiosity.cu
+	void radiosity_map_replaced(osb200_ctx *ctx);
+	void radiosity_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
+} // namespace osb
+
+int osb200_ctx::ensure_scratch(size_t bytes) {
+	if (bytes <= d_scratch_bytes)
+		return 0;
+	if (d_scratch)
+		cudaFree(d_scratch);
+	d_scratch = nullptr;
+	d_scratch_bytes = 0;
+	size_t want = bytes + (bytes >> 2);
+	OSB_CUDA(cudaMalloc(&d_scratch, want));
+	d_scratch_bytes = want;
+	return 0;
+}
+
+int osb200_ctx::ensure_stage(size_t bytes) {
+	if (bytes <= h_stage_bytes && bytes <= d_stage_bytes)
+		return 0;
+	size_t want = bytes + (bytes >> 1) + 4096;
+	if (h_stage)
+		cudaFreeHost(h_stage);
+	if (d_stage)
+		cudaFree(d_stage);
+	h_stage = d_stage = nullptr;
+	h_stage_bytes = d_stage_bytes = 0;
+	OSB_CUDA(cudaMallocHost(&h_stage, want));
+	h_stage_bytes = want;
+	OSB_CUDA(cudaMalloc(&d_stage, want));
+	d_stage_bytes = want;
+	return 0;
+}
+
+// ---- kernels ----------------------------------------------------------------------------------
+
+// [x][y] (reference order) -> 4x4-tiled order.  One thread per column; colour rows are 256 B so
+// each thread moves 16 x uint4.
+__global__ void k_map_repack(const uint64_t *__restrict__ solidXY, const uint32_t *__restrict__ colorXYZ,
+                             uint64_t *__restrict__ solidT, uint32_t *__restrict__ colorT) {
+	int col = blockIdx.x * (blockDim.x >> 4) + (threadIdx.x >> 4); // 16 threads per column
+	int part = threadIdx.x & 15;
+	if (col >= OSB200_MAP_W * OSB200_MAP_H)
+		return;
+	int x = col >> 9, y = col & 511;
+	uint32_t t = osb::tiled_index(x, y);
+	if (part == 0)
+		solidT[t] = solidXY[col];
+	const uint4 *src = reinterpret_cast<const uint4 *>(colorXYZ + (size_t)col * 64);
+	uint4 *dst = reinterpret_cast<uint4 *>(colorT + (size_t)t * 64);
+	dst[part] = src[part];
+}
+
+struct DirtyColumn { // 272 B staging record of one edited column
+	uint32_t tiled;
+	uint32_t pad;
+	uint64_t solid;
+	uint32_t color[64];
+};
+
+__global__ void k_map_scatter(const DirtyColumn *__restrict__ recs, int n, uint64_t *__restrict__ solidT,
+                              uint32_t *__restrict__ colorT) {
+	int i = blockIdx.x * (blockDim.x >> 4) + (threadIdx.x >> 4);
+	int part = threadIdx.x & 15;
+	if (i >= n)
+		return;
+	const DirtyColumn &r = recs[i];
+	if (part == 0)
+		solidT[r.tiled] = r.solid;
+	const uint4 *src = reinterpret_cast<const uint4 *>(r.color);
+	reinterpret_cast<uint4 *>(colorT + (size_t)r.tiled * 64)[part] = src[part];
+}
+
+__global__ void k_map_untile_solid(const uint64_t *__restrict__ solidT, uint64_t *__restrict__ solidXY) {
+	int col = blockIdx.x * blockDim.x + threadIdx.x;
+	if (col < OSB200_MAP_W * OSB200_MAP_H)
+		solidXY[col] = solidT[osb::tiled_index(col >> 9, col & 511)];
+}
+
+// ---- C ABI ------------------------------------------------------------------------------------
+
+extern "C" {
+
+const char *osb200_last_error(void) { return osb::g_err.c_str(); }
+
+int osb200_create(const osb200_opts *opts, osb200_ctx **out) {
+	if (!opts || !out) {
+		osb::set_error("osb200_create: null argument");
+		return -1;
+	}
+	*out = nullptr;
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		// no CPU fallback: the product path fails loudly without a device
+		osb::set_error("osb200_create: no CUDA device available (%s); this library has no CPU fallback",
+		               e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+		return -3;
+	}
+	if (opts->device < 0 || opts->device >= ndev) {
+		osb::set_error("osb200_create: device %d out of range (0..%d)", opts->device, ndev - 1);
+		return -1;
+	}
+	if (opts->numerics < OSB200_NUM_IEEE || opts->numerics > OSB200_NUM_SSE2) {
+		osb::set_error("osb200_create: bad numerics mode %d", opts->numerics);
+		return -1;
+	}
+	std::vector<uint32_t> calRcp, calRsqrt;
+	const uint32_t *rcpTab = opts->rcp_table, *rsqrtTab = opts->rsqrt_table;
+	int rcpBits = opts->rcp_bits, rsqrtBits = opts->rsqrt_bits;
+	if (opts->numerics != OSB200_NUM_IEEE) {
+		if (!rcpTab || !rsqrtTab) {
+			// measure this host's RCPSS/RSQRTSS (the CPU the reference SWRenderer would run on)
+			calRcp.resize(1u << 16);
+			calRsqrt.resize(2u << 16);
+			int rc = osb200_calibrate_sse(calRcp.data(), &rcpBits, calRsqrt.data(), &rsqrtBits, 16);
+			if (rc)
+				return rc;
+			rcpTab = calRcp.data();
+			rsqrtTab = calRsqrt.data();
+		}
+		if (rcpBits < 1 || rcpBits > 16 || rsqrtBits < 1 || rsqrtBits > 16) {
+			osb::set_error("osb200_create: bad rcpss/rsqrtss table sizes");
+			return -1;
+		}
+	}
+	auto *c = new osb200_ctx();
+	c->opts = *opts;
+	if (c->opts.sw_threads <= 0)
+		c->opts.sw_threads = 4;
+	if (c->opts.sw_threads > 32)
+		c->opts.sw_threads = 32; // SWUtils.h:53
+	if (c->opts.undersampling != 2 && c->opts.undersampling != 4)
+		c->opts.undersampling = 1;
+	if (c->opts.radiosity_mode != 2)
+		c->opts.radiosity_mode = 1;
+	c->device = opts->device;
+	c->dirtyWords.assign(OSB200_MAP_W * OSB200_MAP_H / 32, 0);
+	auto fail = [&](int rc) {
+		osb200_destroy(c);
+		return rc;
+	};
+#define TRY(expr)                                                                                  \
+	do {                                                                                           \
+		cudaError_t e_ = (expr);                                                                   \
+		if (e_ != cudaSuccess) {                                                                   \
+			osb::set_error("%s failed: %s", #expr, cudaGetErrorString(e_));                        \
+			return fail(-2);                                                                       \
+		}                                                                                          \
+	} while (0)
+	TRY(cudaSetDevice(c->device));
+	cudaDeviceProp prop;
+	TRY(cudaGetDeviceProperties(&prop, c->device));
+	c->smCount = prop.multiProcessorCount;
+	TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	TRY(cudaMalloc(&c->d_solid, sizeof(uint64_t) * OSB200_MAP_W * OSB200_MAP_H));
+	TRY(cudaMalloc(&c->d_color, sizeof(uint32_t) * OSB200_MAP_W * OSB200_MAP_H * OSB200_MAP_D));
+	if (opts->numerics != OSB200_NUM_IEEE) {
+		c->rcpBits = rcpBits;
+		c->rsqrtBits = rsqrtBits;
+		size_t nr = (size_t)1 << c->rcpBits, ns = (size_t)2 << c->rsqrtBits;
+		TRY(cudaMalloc(&c->d_rcp, nr * 4));
+		TRY(cudaMalloc(&c->d_rsqrt, ns * 4));
+		TRY(cudaMemcpy(c->d_rcp, rcpTab, nr * 4, cudaMemcpyHostToDevice));
+		TRY(cudaMemcpy(c->d_rsqrt, rsqrtTab, ns * 4, cudaMemcpyHostToDevice));
+	}
+	c->opts.rcp_table = c->opts.rsqrt_table = nullptr; // caller's pointers are not retained
+#undef TRY
+	*out = c;
+	return 0;
+}
+
+void osb200_destroy(osb200_ctx *c) {
+	if (!c)
+		return;
+	cudaSetDevice(c->device);
+	if (c->stream)
+		cudaStreamSynchronize(c->stream);
+	osb::terrain_destroy(c);
+	osb::radiosity_destroy(c);
+	cudaFree(c->d_solid);
+	cudaFree(c->d_color);
+	cudaFree(c->d_rcp);
+	cudaFree(c->d_rsqrt);
+	cudaFree(c->d_scratch);
+	cudaFree(c->d_stage);
+	if (c->h_stage)
+		cudaFreeHost(c->h_stage);
+	if (c->stream)
+		cudaStreamDestroy(c->stream);
+	delete c;
+}
+
+int osb200_sync(osb200_ctx *c) {
+	if (!c)
+		return -1;
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+void *osb200_stream(osb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
+uint64_t osb200_launch_count(osb200_ctx *c) { return c ? c->launches : 0; }
+
+int osb200_map_upload(osb200_ctx *c, const uint64_t *solid, const uint32_t *color) {
+	if (!c || !solid || !color) {
+		osb::set_error("osb200_map_upload: null argument");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	const size_t ncol = (size_t)OSB200_MAP_W * OSB200_MAP_H;
+	const size_t sb = ncol * 8, cb = ncol * 64 * 4;
+	if (c->ensure_scratch(sb + cb))
+		return -2;
+	auto *dS = reinterpret_cast<uint64_t *>(c->d_scratch);
+	auto *dC = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(c->d_scratch) + sb);
+	OSB_CUDA(cudaMemcpyAsync(dS, solid, sb, cudaMemcpyHostToDevice, c->stream));
+	OSB_CUDA(cudaMemcpyAsync(dC, color, cb, cudaMemcpyHostToDevice, c->stream));
+	k_map_repack<<<(unsigned)(ncol / 16), 256, 0, c->stream>>>(dS, dC, c->d_solid, c->d_color);
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
+	c->anyDirty = false;
+	c->mapLoaded = true;
+	osb::radiosity_map_replaced(c);
+	return 0;
+}
+
+int osb200_map_mark_dirty(osb200_ctx *c, int x, int y, int z) {
+	if (!c || x < 0 || x >= OSB200_MAP_W || y < 0 || y >= OSB200_MAP_H) {
+		osb::set_error("osb200_map_mark_dirty: bad argument");
+		return -1;
+	}
+	c->dirtyWords[(x + y * OSB200_MAP_W) >> 5] |= 1u << (x & 31);
+	c->anyDirty = true;
+	osb::radiosity_mark_dirty(c, x, y, z);
+	return 0;
+}
+
+int osb200_map_flush(osb200_ctx *c, const uint64_t *solid, const uint32_t *color) {
+	if (!c || !solid || !color) {
+		osb::set_error("osb200_map_flush: null argument");
+		return -1;
+	}
+	if (!c->mapLoaded) {
+		osb::set_error("osb200_map_flush: no map uploaded");
+		return -1;
+	}
+	if (!c->anyDirty)
+		return 0;
+	OSB_CUDA(cudaSetDevice(c->device));
+	int n = 0;
+	for (uint32_t w : c->dirtyWords)
+		n += __builtin_popcount(w);
+	if (c->ensure_stage((size_t)n * sizeof(DirtyColumn)))
+		return -2;
+	// the staging buffer may still be read by the previous flush's copy
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	auto *recs = reinterpret_cast<DirtyColumn *>(c->h_stage);
+	int k = 0;
+	for (size_t wi = 0; wi < c->dirtyWords.size(); wi++) {
+		uint32_t w = c->dirtyWords[wi];
+		while (w) {
+			int b = __builtin_ctz(w);
+			w &= w - 1;
+			int lin = (int)wi * 32 + b; // x + y*512
+			int x = lin & 511, y = lin >> 9;
+			DirtyColumn &r = recs[k++];
+			r.tiled = osb::tiled_index(x, y);
+			r.pad = 0;
+			r.solid = solid[(size_t)x * 512 + y];
+			std::memcpy(r.color, color + ((size_t)x * 512 + y) * 64, 256);
+		}
+		c->dirtyWords[wi] = 0;
+	}
+	c->anyDirty = false;
+	OSB_CUDA(cudaMemcpyAsync(c->d_stage, recs, (size_t)n * sizeof(DirtyColumn), cudaMemcpyHostToDevice,
+	                         c->stream));
+	k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n,
+	                                                    c->d_solid, c->d_color);
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	return n;
+}
+
+int osb200_map_read_solid(osb200_ctx *c, uint64_t *solid) {
+	if (!c || !solid || !c->mapLoaded) {
+		osb::set_error("osb200_map_read_solid: bad argument or no map");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	const size_t ncol = (size_t)OSB200_MAP_W * OSB200_MAP_H;
+	if (c->ensure_scratch(ncol * 8))
+		return -2;
+	k_map_untile_solid<<<(unsigned)(ncol / 256), 256, 0, c->stream>>>(
+	  c->d_solid, reinterpret_cast<uint64_t *>(c->d_scratch));
+	c->launches++;
+	OSB_CUDA(cudaMemcpyAsync(solid, c->d_scratch, ncol * 8, cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+} // extern "C"

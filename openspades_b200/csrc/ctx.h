@@ -1,0 +1,73 @@
+// Internal state behind the opaque osb200_ctx handle (include/osb200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/osb200.h"
+
+namespace osb {
+
+	void set_error(const char *fmt, ...);
+
+#define OSB_CUDA(expr)                                                                             \
+	do {                                                                                           \
+		cudaError_t e_ = (expr);                                                                   \
+		if (e_ != cudaSuccess) {                                                                   \
+			osb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__,       \
+			               __LINE__);                                                              \
+			return -2;                                                                             \
+		}                                                                                          \
+	} while (0)
+
+	// The solid bitmap is stored in 4x4-column tiles of 128 B (one L1/L2 line) so that a ray or a
+	// DDA line walking in any horizontal direction stays ~4 steps inside one line, instead of the
+	// reference's x-major [x][y] order (GameMap.h:160) where every x-step is a 4 KiB jump.
+	__host__ __device__ inline uint32_t tiled_index(int x, int y) {
+		return ((uint32_t)(x >> 2) * 128u + (uint32_t)(y >> 2)) * 16u + (uint32_t)(x & 3) * 4u +
+		       (uint32_t)(y & 3);
+	}
+
+	struct Ctx;
+	struct TerrainState;   // terrain.cu
+	struct RadiosityState; // radiosity.cu
+} // namespace osb
+
+struct osb200_ctx {
+	osb200_opts opts{};
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	uint64_t launches = 0;
+	int smCount = 148;
+
+	// ---- resident map ----
+	bool mapLoaded = false;
+	uint64_t *d_solid = nullptr; // [tiled_index(x,y)] 2 MiB
+	uint32_t *d_color = nullptr; // [(tiled_index(x,y)) * 64 + z] 64 MiB, 0xHHBBGGRR as in GameMap
+	// dirty tracking (same 32-column words as SWFlatMapRenderer::updateMap, SWFlatMapRenderer.cpp:107-111)
+	std::vector<uint32_t> dirtyWords; // 512*512/32
+	bool anyDirty = false;
+	// pinned staging for dirty-column re-upload
+	void *h_stage = nullptr;
+	size_t h_stage_bytes = 0;
+	void *d_stage = nullptr;
+	size_t d_stage_bytes = 0;
+
+	// ---- SSE emulation tables (device copies; null in IEEE mode) ----
+	uint32_t *d_rcp = nullptr;
+	int rcpBits = 0;
+	uint32_t *d_rsqrt = nullptr;
+	int rsqrtBits = 0;
+
+	// ---- scratch for host-pointer convenience entry points ----
+	void *d_scratch = nullptr;
+	size_t d_scratch_bytes = 0;
+
+	osb::TerrainState *terrain = nullptr;
+	osb::RadiosityState *radiosity = nullptr;
+
+	int ensure_scratch(size_t bytes);
+	int ensure_stage(size_t bytes);
+};

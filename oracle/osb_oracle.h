@@ -1,0 +1,76 @@
+/*
+ * osb_oracle -- CPU restatement ("port") of the reference algorithms on the hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * --impl reference legs may load this; the product (openspades_b200/, include/) never does.
+ *
+ * Parity pinning: the reference (yvt/openspades) ships no tests, golden vectors or KATs for this
+ * path, so this restatement is pinned against the UNMODIFIED reference code
+ * itself, compiled in place into oracle/_ref/liboref_{sse2,ieee}.so (oracle/Makefile) and run on
+ * the same inputs: tests/test_oracle_vs_ref.py, plus the committed fixtures under tests/golden/
+ * that were generated from those libraries by tests/golden/make_golden.py.
+ *
+ * Every function cites the reference file:line it follows (paths relative to Sources/).
+ */
+#ifndef OSB_ORACLE_H
+#define OSB_ORACLE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orc_scene { /* same layout as osb200_scene / oref_scene */
+	float origin[3];
+	float axis[3][3];
+	float fovX, fovY;
+	float zNear, zFar;
+} orc_scene;
+
+typedef struct orc_rayhit { /* GameMap::RayCastResult, Client/GameMap.h:150-156 */
+	uint8_t hit, startSolid, pad[2];
+	float hitPos[3];
+	int32_t hitBlock[3];
+	int32_t normal[3];
+} orc_rayhit;
+
+enum { ORC_NUM_IEEE = 0, ORC_NUM_SSE = 1, ORC_NUM_SSE2 = 2 };
+
+/* map arrays everywhere: solid uint64[512][512] ([x][y]), color uint32[512][512][64] ([x][y][z]) */
+
+/* Client/GameMap.cpp:519-596 GameMap::Load.  Returns 0 or <0 on truncated input. */
+int orc_vxl_load(const uint8_t *data, size_t len, uint64_t *solid, uint32_t *color);
+
+/* Client/GameMap.cpp:361-507 GameMap::CastRay2 */
+void orc_castray2(const uint64_t *solid, const float *v0, const float *dir, int maxSteps, orc_rayhit *out,
+                  size_t n, int threads);
+
+/* Draw/SWMapRenderer.cpp:142-203 BuildRle: writes the byte image of the column's RLE record,
+ * returns its length (multiple of 4). out must hold >= 400 bytes. */
+int orc_build_rle(const uint64_t *solid, int x, int y, int8_t *out);
+
+/* Draw/SWRenderer.cpp:709-745 EndScene (clear, terrain, fog) for one view.
+ * numerics: ORC_NUM_*; threads = r_swNumThreads; under = r_swUndersampling clamp(1,2,4).
+ * bgrx/depth: w*h each; depth is read-modify (the reference never clears it). */
+int orc_render(const uint64_t *solid, const uint32_t *color, const orc_scene *scene, int w, int h,
+               const float fogColor[3], float fogDist, int numerics, int threads, int under,
+               uint32_t *bgrx, float *depth);
+/* strip buffer of the last orc_render on this thread (debug): returns numLines */
+int orc_last_lines(int *lineRes, const uint32_t **combined, const float **depth);
+
+/* Draw/GLMapShadowRenderer.cpp:177-218 GeneratePixel over the whole map: out uint32[y*512+x] */
+void orc_shadow_bitmap(const uint64_t *solid, const uint32_t *color, uint32_t *out);
+/* Draw/GLRadiosityRenderer.cpp:162-275 Evaluate: 12 floats (base,x,y,z as rgb each) */
+void orc_radiosity_evaluate(const uint32_t *bitmap, int x, int y, int z, float out[12]);
+/* Draw/GLRadiosityRenderer.cpp:456-515 EncodeValue (mode = r_radiosity) */
+uint32_t orc_radiosity_encode(const float v[3], int mode);
+/* Evaluate + EncodeValue over a box [x0,x1]x[y0,y1]x[z0,z1] (UpdateChunk :517-543 inner loop);
+ * f32 (12 floats/voxel) and enc (4 words/voxel: flat,x,y,z) are box-ordered [z][y][x]; either may be NULL */
+void orc_radiosity_box(const uint32_t *bitmap, int x0, int y0, int z0, int x1, int y1, int z1, int mode,
+                       float *f32, uint32_t *enc, int threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
