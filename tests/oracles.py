@@ -47,6 +47,8 @@ class Port:
         L.orc_castray2.argtypes = [vp, vp, vp, ci, vp, ctypes.c_size_t, ci]
         L.orc_castray2.restype = None
         L.orc_build_rle.argtypes = [vp, ci, ci, vp]
+        L.orc_render.argtypes = [vp, vp, vp, ci, ci, vp, ctypes.c_float, ci, ci, ci, vp, vp]
+        L.orc_last_lines.argtypes = [ctypes.POINTER(ci), ctypes.POINTER(vp), ctypes.POINTER(vp)]
 
     def vxl_load(self, data: bytes):
         solid = np.zeros((512, 512), np.uint64)
@@ -64,6 +66,25 @@ class Port:
         self.L.orc_castray2(solid.ctypes.data, v0.ctypes.data, dirs.ctypes.data, max_steps, out.ctypes.data,
                             len(v0), threads)
         return out
+
+    def render(self, solid, color, scene, w, h, fog_color, fog_dist, numerics, threads=4, under=1, depth=None):
+        fb = np.zeros((h, w), np.uint32)
+        dp = np.zeros((h, w), np.float32) if depth is None else depth
+        sc = np.ascontiguousarray(scene)
+        fc = np.asarray(fog_color, np.float32)
+        rc = self.L.orc_render(solid.ctypes.data, color.ctypes.data, sc.ctypes.data, w, h, fc.ctypes.data,
+                               fog_dist, numerics, threads, under, fb.ctypes.data, dp.ctypes.data)
+        if rc:
+            raise ValueError("orc_render failed")
+        return fb, dp
+
+    def last_lines(self):
+        lr = ci()
+        pc, pd = vp(), vp()
+        n = self.L.orc_last_lines(ctypes.byref(lr), ctypes.byref(pc), ctypes.byref(pd))
+        comb = np.ctypeslib.as_array(ctypes.cast(pc, ctypes.POINTER(ctypes.c_uint32)), shape=(n, lr.value)).copy()
+        dep = np.ctypeslib.as_array(ctypes.cast(pd, ctypes.POINTER(ctypes.c_float)), shape=(n, lr.value)).copy()
+        return comb, dep
 
     def build_rle(self, solid, x, y):
         out = np.zeros(400, np.int8)
