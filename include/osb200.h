@@ -110,6 +110,20 @@ OSB200_API int osb200_castray2(osb200_ctx *ctx, const float *v0, const float *di
 OSB200_API int osb200_castray2_device(osb200_ctx *ctx, const float *d_v0, const float *d_dir,
                                       int maxSteps, osb200_rayhit *d_out, size_t n);
 
+/* ---- terrain pass + fog: SWRenderer::StartScene + EndScene for the map (SWRenderer.cpp:549-563,709-745;
+ *      SWMapRenderer::Render SWMapRenderer.cpp:1176-1194; SWRenderer::ApplyFog SWRenderer.cpp:341-516) ----
+ * Renders nViews independent scenes of w x h pixels (both multiples of 8, SWRenderer.cpp:105-107).
+ * bgrx: nViews*w*h uint32, memory order B,G,R,X, top-down rows (== Bitmap pixels of SWPort::GetFramebuffer);
+ * depth: nViews*w*h float view-space Z (== SWRenderer::depthBuffer).  The depth buffer is read-modify:
+ * like the reference it is not cleared, and a view whose eye is inside a solid voxel keeps its previous
+ * depth and gets the clear colour 0x7f7f7f before fog (SWMapRenderer.cpp:1181-1184).
+ * osb200_render keeps context-owned device buffers (persistent depth) and copies to the nullable host
+ * pointers, then synchronises; osb200_render_device writes caller-owned device buffers and only enqueues. */
+OSB200_API int osb200_render(osb200_ctx *ctx, const osb200_scene *scenes, int nViews, int w, int h,
+                             const float fogColor[3], float fogDist, uint32_t *host_bgrx, float *host_depth);
+OSB200_API int osb200_render_device(osb200_ctx *ctx, const osb200_scene *scenes, int nViews, int w, int h,
+                                    const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth);
+
 #ifdef __cplusplus
 }
 #endif

@@ -68,6 +68,9 @@ def load_library():
     lib.osb200_map_read_solid.argtypes = [vp, vp]
     lib.osb200_castray2.argtypes = [vp, vp, vp, ci, vp, sz]
     lib.osb200_castray2_device.argtypes = [vp, vp, vp, ci, vp, sz]
+    fp = ctypes.c_float
+    lib.osb200_render.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
+    lib.osb200_render_device.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
     _lib = lib
     return lib
 
@@ -179,3 +182,24 @@ class Context:
         """Device pointers (ints or torch CUDA tensors); enqueue only."""
         self._check(self._lib.osb200_castray2_device(self._h, _ptr(d_v0), _ptr(d_dir), int(max_steps),
                                                      _ptr(d_out), int(n)))
+
+    # ---- terrain pass + fog ----
+    def render(self, scenes, w, h, fog_color, fog_dist, want_depth=True, out_bgrx=None, out_depth=None):
+        """Host entry point: scenes = SCENE_DTYPE array (n,), returns (bgrx[n,h,w] uint32, depth[n,h,w] f32)."""
+        scenes = np.ascontiguousarray(np.atleast_1d(scenes))
+        assert scenes.dtype == SCENE_DTYPE
+        n = len(scenes)
+        fb = np.empty((n, h, w), np.uint32) if out_bgrx is None else out_bgrx
+        dp = (np.empty((n, h, w), np.float32) if out_depth is None else out_depth) if want_depth else None
+        fc = np.asarray(fog_color, np.float32)
+        self._check(self._lib.osb200_render(self._h, scenes.ctypes.data, n, w, h, fc.ctypes.data, float(fog_dist),
+                                            _ptr(fb), _ptr(dp)))
+        return fb, dp
+
+    def render_device(self, scenes, w, h, fog_color, fog_dist, d_bgrx, d_depth):
+        """Device outputs (torch CUDA tensors or raw pointers); enqueue only."""
+        scenes = np.ascontiguousarray(np.atleast_1d(scenes))
+        assert scenes.dtype == SCENE_DTYPE
+        fc = np.asarray(fog_color, np.float32)
+        self._check(self._lib.osb200_render_device(self._h, scenes.ctypes.data, len(scenes), w, h, fc.ctypes.data,
+                                                   float(fog_dist), _ptr(d_bgrx), _ptr(d_depth)))

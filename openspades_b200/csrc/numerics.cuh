@@ -1,0 +1,89 @@
+// Device-side equivalents of the reference's numeric helpers in the three variants it has
+// (Sources/Draw/SWFeatureLevel.h:89-121):
+//   IEEE : fastRcp = 1/x, fastRSqrt = 1/sqrtf(x), fastDiv = a/b            (build without SSE)
+//   SSE* : RCPSS / RSQRTSS approximations, reproduced from tables calibrated on the host CPU
+//          (sse_calibrate.cpp documents and verifies the table model).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace osbn {
+
+	struct SseTables {
+		const uint32_t *rcp;   // 1 << rcpBits entries
+		const uint32_t *rsqrt; // 2 << rsqrtBits entries
+		int rcpBits, rsqrtBits;
+	};
+
+	// x86 cvttss2si: out-of-range and NaN give the "integer indefinite" value
+	__device__ __forceinline__ int x86_f2i(float f) {
+		return (f >= -2147483648.f && f < 2147483648.f) ? __float2int_rz(f) : (int)0x80000000;
+	}
+	// x86 cvtps2dq under the default MXCSR (round to nearest even)
+	__device__ __forceinline__ int x86_f2i_rn(float f) {
+		return (f >= -2147483648.f && f < 2147483648.f) ? __float2int_rn(f) : (int)0x80000000;
+	}
+
+	__device__ __forceinline__ float rcpss(float x, const SseTables &t) {
+		const uint32_t u = __float_as_uint(x);
+		const uint32_t sign = u & 0x80000000u, e = (u >> 23) & 0xff, m = u & 0x7fffff;
+		if (e == 0)
+			return __uint_as_float(sign | 0x7f800000u); // zero / denormal -> +-inf
+		if (e == 255)
+			return __uint_as_float(m ? (u | 0x00400000u) : sign);
+		const uint32_t r = __ldg(t.rcp + (m >> (23 - t.rcpBits)));
+		const int re = (int)((r >> 23) & 0xff) - ((int)e - 127);
+		if (re <= 0)
+			return __uint_as_float(sign); // underflow flushes to zero
+		return __uint_as_float(sign | ((uint32_t)re << 23) | (r & 0x7fffff));
+	}
+
+	__device__ __forceinline__ float rsqrtss(float x, const SseTables &t) {
+		const uint32_t u = __float_as_uint(x);
+		const uint32_t sign = u & 0x80000000u, e = (u >> 23) & 0xff, m = u & 0x7fffff;
+		if (e == 255 && m)
+			return __uint_as_float(u | 0x00400000u);
+		if (e == 0)
+			return __uint_as_float(sign | 0x7f800000u);
+		if (sign)
+			return __uint_as_float(0xffc00000u);
+		if (e == 255)
+			return 0.f;
+		const int E = (int)e - 127, p = E & 1;
+		const uint32_t r = __ldg(t.rsqrt + (((uint32_t)p << t.rsqrtBits) | (m >> (23 - t.rsqrtBits))));
+		const int re = (int)((r >> 23) & 0xff) - ((E - p) >> 1);
+		return __uint_as_float(((uint32_t)re << 23) | (r & 0x7fffff));
+	}
+
+	template <bool kSse> struct Num {
+		SseTables t;
+		__device__ __forceinline__ float rcp(float b) const {
+			if (kSse)
+				return rcpss(b, t);
+			return __fdiv_rn(1.f, b);
+		}
+		__device__ __forceinline__ float div(float a, float b) const {
+			if (kSse)
+				return __fmul_rn(a, rcpss(b, t));
+			return __fdiv_rn(a, b);
+		}
+		__device__ __forceinline__ float rsqrt(float b) const {
+			if (kSse)
+				return rsqrtss(b, t);
+			return __fdiv_rn(1.f, __fsqrt_rn(b));
+		}
+		__device__ __forceinline__ float sqrt(float s) const { // fastSqrt, SWFeatureLevel.h:117-121
+			if (s == 0.f)
+				return 0.f;
+			return __fmul_rn(s, rsqrt(s));
+		}
+		// ToSpecialTan, SWMapRenderer.cpp:59-66
+		__device__ __forceinline__ float toSpecialTan(float v) const {
+			if (v < -1.f)
+				return __fsub_rn(-2.f, rcp(v));
+			else if (v > 1.f)
+				return __fsub_rn(2.f, rcp(v));
+			return v;
+		}
+	};
+} // namespace osbn

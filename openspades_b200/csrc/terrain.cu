@@ -1,5 +1,1029 @@
-// placeholder until the terrain pass lands
+// Software-renderer terrain pass + fog on the GPU, reproducing the reference's results:
+//   SWRenderer::EndScene / BuildFrustrum   Sources/Draw/SWRenderer.cpp:207-227,709-745
+//   SWMapRenderer::RenderInner             Sources/Draw/SWMapRenderer.cpp:1045-1174  (per-view set-up)
+//   SWMapRenderer::BuildLine               Sources/Draw/SWMapRenderer.cpp:219-671    (k_build_lines)
+//   SWMapRenderer::RenderFinal             Sources/Draw/SWMapRenderer.cpp:744-1043   (k_gather_fog)
+//   SWRenderer::ApplyFog                   Sources/Draw/SWRenderer.cpp:341-516       (fused into k_gather_fog)
+//
+// Design: the reference renders a view as ~2.5-5k vertical "yaw lines", each a 1-D strip
+// of (colour, depth) built by a 2-D DDA through map columns, then gathers every screen pixel from
+// (line, pitch index).  Here
+//   * one thread builds one line; the six per-column RLE z-lists of the reference are never stored --
+//     tops/bottoms/walls are bit expressions of the 64-bit column mask and of the mask of the cell the
+//     DDA just left, so a step costs one 8-byte load from the 2 MiB tiled bitmap;
+//   * "first writer wins" along a strip is kept in a per-thread bitmask in shared memory, so strip
+//     pixels are written once, write-only, and colours are fetched only for spans that land;
+//   * gather and fog are one kernel: each warp owns an 8-pixel-wide column of 8x8 blocks, replays the
+//     reference's per-thread float recurrences for its start vectors and writes BGRX + depth once.
+// All float arithmetic is separate IEEE mul/add (--fmad=false) in the reference's evaluation order.
 #include "ctx.h"
+#include "libm_f32.cuh"
+#include "numerics.cuh"
+
+#include <cmath>
+#include <cstring>
+
 namespace osb {
-	void terrain_destroy(osb200_ctx *) {}
+
+	// Per-view constants.  Everything that the reference computes once per frame with libm
+	// (tanf/atanf/asinf/atan2l/cosf/sinf, SWMapRenderer.cpp:1057-1133, SWRenderer.cpp:207-227,345-357)
+	// is evaluated on the host with the same libm and shipped here.
+	struct ViewParams {
+		float origin[3];
+		float right[3], up[3], front[3];
+		float frN[4][3]; // frustum side-plane normals, SWRenderer::frustrum[2..5].n
+		float fovXt, fovYt;
+		float yawMin, yawMax;
+		float cosYawMin, sinYawMin, cosScl, sinScl;
+		int numLines, lineRes;
+		int yawScale2, yawMin2;
+		uint32_t lineBase;  // first line slot of this view inside the chunk
+		uint32_t tabBase;   // first float of this view's recurrence tables
+		float fogScale;     // 255 / fogDistance
+		float dvx, dvy;     // ApplyFog steps
+		uint32_t pad;
+	};
+
+	// Recurrence tables of one view, laid out at tabs + tabBase:
+	//   vx[fw/4]            ApplyFog per-4-pixel-column vx          (SWRenderer.cpp:372,409)
+	//   vy[fh/4]            ApplyFog per-4-row vy, per emulated thread band (:365-369,412)
+	//   v1[fw/8][3]         RenderFinal per-8-pixel-column start vector, per emulated thread (:757,789,1040)
+	__host__ __device__ inline uint32_t tab_floats(int fw, int fh) { return fw / 4 + fh / 4 + (fw / 8) * 3; }
+
+	struct FrameGeom {
+		int fw, fh, under, swThreads, sse2Fog, sse2Shade;
+		uint32_t fogB, fogG, fogR;
+	};
+
+	// One sequential float recurrence per role; the same code runs on the host (few views) or on one
+	// lane per role on the device (many views).
+	__host__ __device__ inline void prep_line_dirs(const ViewParams &v, float2 *dirs) {
+		// SWMapRenderer.cpp:1129-1143
+		float hx = v.cosYawMin, hy = v.sinYawMin;
+		const float c = v.cosScl, s = v.sinScl;
+		for (int i = 0; i < v.numLines; i++) {
+			dirs[i] = make_float2(hx, hy);
+			const float x = osbm::subf(osbm::mulf(hx, c), osbm::mulf(hy, s));
+			const float y = osbm::addf(osbm::mulf(hx, s), osbm::mulf(hy, c));
+			hx = x;
+			hy = y;
+		}
+	}
+	__host__ __device__ inline void prep_fog_vx(const ViewParams &v, const FrameGeom &g, float *vx) {
+		float x = v.fovXt;
+		for (int i = 0; i < g.fw / 4; i++) {
+			vx[i] = x;
+			x = osbm::addf(x, v.dvx);
+		}
+	}
+	__host__ __device__ inline void prep_fog_vy(const ViewParams &v, const FrameGeom &g, int t, float *vy) {
+		// band of emulated thread t, SWRenderer.cpp:359-369
+		int startY = (int)((unsigned)g.fh * (unsigned)t / (unsigned)g.swThreads) & ~3;
+		int endY = (int)((unsigned)g.fh * (unsigned)(t + 1) / (unsigned)g.swThreads) & ~3;
+		float y = osbm::addf(v.fovYt, osbm::mulf(v.dvy, (float)(startY >> 2)));
+		for (int r = startY; r < endY; r += 4) {
+			vy[r >> 2] = y;
+			y = osbm::addf(y, v.dvy);
+		}
+	}
+	__host__ __device__ inline void prep_v1(const ViewParams &v, const FrameGeom &g, int t, float *v1tab) {
+		// SWMapRenderer.cpp:757-759,774-781,789,1040
+		const float fx = v.fovXt, fy = v.fovYt;
+		float v1[3], dR[3], dRL[3];
+		const float sR = osbm::mulf(osbm::divf(osbm::mulf(fx, 2.f), (float)g.fw), (float)g.under);
+		unsigned startX = (unsigned)t * (unsigned)g.fw / (unsigned)g.swThreads;
+		unsigned endX = (unsigned)(t + 1) * (unsigned)g.fw / (unsigned)g.swThreads;
+		startX = (startX / 8) * 8;
+		endX = (endX / 8) * 8;
+		for (int k = 0; k < 3; k++) {
+			v1[k] = osbm::addf(osbm::subf(v.front[k], osbm::mulf(v.right[k], fx)), osbm::mulf(v.up[k], fy));
+			dR[k] = osbm::mulf(v.right[k], sR);
+			dRL[k] = osbm::mulf(dR[k], (float)(8 / g.under));
+			v1[k] = osbm::addf(v1[k], osbm::mulf(dR[k], (float)(startX / (unsigned)g.under)));
+		}
+		for (unsigned x = startX; x < endX; x += 8) {
+			for (int k = 0; k < 3; k++) {
+				v1tab[(x >> 3) * 3 + k] = v1[k];
+				v1[k] = osbm::addf(v1[k], dRL[k]);
+			}
+		}
+	}
+
+	struct TerrainState {
+		// chunk-sized device buffers
+		ViewParams *d_views = nullptr;
+		ViewParams *h_views = nullptr; // pinned
+		size_t viewCap = 0, dViewCap = 0, lineParamCap = 0, hTabCap = 0;
+		float2 *d_lineDirs = nullptr;
+		int4 *d_lineParams = nullptr;
+		uint2 *d_strips = nullptr;
+		size_t lineCap = 0, stripCap = 0;
+		float *d_tabs = nullptr;
+		float *h_tabs = nullptr; // pinned (host-prep path)
+		float2 *h_lineDirs = nullptr;
+		size_t tabCap = 0, hLineCap = 0;
+		uint16_t *d_atan = nullptr; // 4 x 5000: sm, lg, smN, lgN
+		// persistent output buffers of the host-pointer entry point
+		uint32_t *d_fb = nullptr;
+		float *d_depth = nullptr;
+		size_t outCap = 0;
+		cudaEvent_t stageFree = nullptr;
+	};
 } // namespace osb
+
+namespace osb {
+
+	constexpr int kLineThreads = 64; // lines per CTA of k_build_lines
+	enum { F_POSX = 0, F_NEGX = 1, F_POSY = 2, F_NEGY = 3, F_POSZ = 4, F_NEGZ = 5 }; // SWMapRenderer.cpp:68
+
+	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map.
+	template <bool kSse2Shade> __device__ __forceinline__ uint32_t shade(uint32_t col, int face) {
+		if (kSse2Shade) {
+			// 16-bit lanes B,G,R,H: PosZ >>1; PosX/PosY/NegX (>>1)+(>>2); health<100 >>1; pack; filled bit
+			uint32_t b = (col >> 16) & 0xff, g = (col >> 8) & 0xff, r = col & 0xff, h = col >> 24;
+			const bool weak = h < 100;
+			if (face == F_POSZ) {
+				b >>= 1; g >>= 1; r >>= 1; h >>= 1;
+			} else if (face == F_POSX || face == F_POSY || face == F_NEGX) {
+				b = (b >> 1) + (b >> 2); g = (g >> 1) + (g >> 2); r = (r >> 1) + (r >> 2); h = (h >> 1) + (h >> 2);
+			}
+			if (weak) {
+				b >>= 1; g >>= 1; r >>= 1; h >>= 1;
+			}
+			return (b | (g << 8) | (r << 16) | (h << 24)) | (1u << 24);
+		} else {
+			uint32_t c = (col & 0xff00) | ((col & 0xff) << 16) | ((col & 0xff0000) >> 16);
+			if (face == F_POSZ)
+				c = (c & 0xfcfcfc) >> 2;
+			else if (face == F_POSX || face == F_POSY || face == F_NEGX)
+				c = (c & 0xfefefe) >> 1;
+			return c | (1u << 24);
+		}
+	}
+
+	template <bool kSse> struct LineCtx {
+		osbn::Num<kSse> num;
+		float cz, transScale, transOffset, vmax;
+		// transform lambda, SWMapRenderer.cpp:395-401
+		__device__ __forceinline__ int transform(float invDist, int z) const {
+			const float zv = __fsub_rn((float)z, cz);
+			float p = __fadd_rn(__fmul_rn(num.toSpecialTan(__fmul_rn(invDist, zv)), transScale), transOffset);
+			p = p < 0.f ? 0.f : p;
+			p = vmax < p ? vmax : p;
+			return __float2int_rz(p);
+		}
+	};
+
+	// Writes [from,to) of the strip where still empty.  `filled` is this thread's bitmask in shared
+	// memory, word-major across the CTA (filled[word * kLineThreads]) so lanes never share a bank.
+	__device__ __forceinline__ void fill_span(uint2 *__restrict__ strip, uint32_t *filled, int from, int to,
+	                                          uint32_t combined, float depth) {
+		const uint2 px = make_uint2(combined, __float_as_uint(depth));
+		int w0 = from >> 5, w1 = (to - 1) >> 5;
+		for (int w = w0; w <= w1; w++) {
+			uint32_t m = 0xffffffffu;
+			if (w == w0)
+				m &= 0xffffffffu << (from & 31);
+			if (w == w1)
+				m &= 0xffffffffu >> (31 - ((to - 1) & 31));
+			const uint32_t cur = filled[w * kLineThreads];
+			uint32_t todo = m & ~cur;
+			if (!todo)
+				continue;
+			filled[w * kLineThreads] = cur | todo;
+			while (todo) {
+				const int b = __ffs(todo) - 1;
+				todo &= todo - 1;
+				strip[(w << 5) + b] = px;
+			}
+		}
+	}
+	__device__ __forceinline__ bool span_has_empty(const uint32_t *filled, int from, int to) {
+		int w0 = from >> 5, w1 = (to - 1) >> 5;
+		for (int w = w0; w <= w1; w++) {
+			uint32_t m = 0xffffffffu;
+			if (w == w0)
+				m &= 0xffffffffu << (from & 31);
+			if (w == w1)
+				m &= 0xffffffffu >> (31 - ((to - 1) & 31));
+			if (m & ~filled[w * kLineThreads])
+				return true;
+		}
+		return false;
+	}
+
+	// One thread = one yaw line (SWMapRenderer::BuildLine, SWMapRenderer.cpp:219-671).
+	template <bool kSse, bool kSse2Shade>
+	__global__ void __launch_bounds__(kLineThreads)
+	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
+	                const uint64_t *__restrict__ solid, const uint32_t *__restrict__ color,
+	                osbn::SseTables tabs, uint2 *__restrict__ strips, int4 *__restrict__ lineParams,
+	                uint32_t totalLines, int lineRes) {
+		extern __shared__ uint32_t s_filled[]; // (lineRes/32) words x kLineThreads
+		const uint32_t lineBase = blockIdx.x * kLineThreads;
+		const uint32_t gl = lineBase + threadIdx.x;
+		const int words = lineRes >> 5;
+
+		// cooperative clear of this CTA's strips: LinePixel::Clear = {0, 10000.f} (:89-92)
+		{
+			const uint32_t nl = min((uint32_t)kLineThreads, totalLines - lineBase);
+			uint4 *dst = reinterpret_cast<uint4 *>(strips + (size_t)lineBase * lineRes);
+			const uint32_t n4 = nl * (uint32_t)lineRes / 2;
+			const uint4 clr = make_uint4(0u, __float_as_uint(10000.f), 0u, __float_as_uint(10000.f));
+			for (uint32_t i = threadIdx.x; i < n4; i += kLineThreads)
+				dst[i] = clr;
+			for (int w = 0; w < words; w++)
+				s_filled[w * kLineThreads + threadIdx.x] = 0;
+		}
+		__syncthreads();
+		if (gl >= totalLines)
+			return;
+
+		// which view does this line belong to (views are few per chunk: binary search on lineBase)
+		int lo = 0, hi = nViews - 1;
+		while (lo < hi) {
+			const int mid = (lo + hi + 1) >> 1;
+			if (views[mid].lineBase <= gl)
+				lo = mid;
+			else
+				hi = mid - 1;
+		}
+		const ViewParams &V = views[lo];
+		uint32_t *filled = s_filled + threadIdx.x;
+		uint2 *strip = strips + (size_t)gl * lineRes;
+		const float2 hd = lineDirs[gl];
+		const float pi = 3.14159274101257324f; // static const float pi = M_PI
+
+		// ---- pitch culling against the four side planes (:232-289) ----
+		osbn::Num<kSse> num{tabs};
+		float minPitch = -pi * 0.4999f, maxPitch = pi * 0.4999f;
+#pragma unroll 1
+		for (int k = 0; k < 4; k++) {
+			const float px = V.frN[k][0], py = V.frN[k][1], pz = V.frN[k][2];
+			if (px == 0.f && py == 0.f) {
+				if (pz > 0.f)
+					minPitch = minPitch < 0.f ? 0.f : minPitch;
+				else
+					maxPitch = 0.f < maxPitch ? 0.f : maxPitch;
+			} else if (pz == 0.f) {
+				// Vector3::Dot(plane, horz) with horz.z = 0: x*x' + y*y' + z*0
+				const float d = __fadd_rn(__fadd_rn(__fmul_rn(px, hd.x), __fmul_rn(py, hd.y)), __fmul_rn(pz, 0.f));
+				if (d < 0.f) {
+					minPitch = 2.f;
+					maxPitch = -2.f;
+				}
+			} else {
+				// prj = (px,py,0).Normalize()
+				float sc = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), 0.f));
+				if (sc != 0.f)
+					sc = __fdiv_rn(1.f, sc);
+				const float qx = __fmul_rn(px, sc), qy = __fmul_rn(py, sc), qz = __fmul_rn(0.f, sc);
+				const float zv = fabsf(pz);
+				const float cs = __fadd_rn(__fadd_rn(__fmul_rn(qx, hd.x), __fmul_rn(qy, hd.y)), __fmul_rn(qz, 0.f));
+				const float cs2 = __fmul_rn(cs, cs);
+				float ang = __fdiv_rn(__fmul_rn(__fmul_rn(zv, zv), __fsub_rn(1.f, cs2)), cs2);
+				ang = __fmul_rn(-cs, num.sqrt(__fadd_rn(1.f, ang)));
+				ang = __fdiv_rn(zv, ang);
+				if (isnan(ang) || isinf(ang) || ang == 0.f)
+					continue;
+				ang = __fdiv_rn(num.sqrt(__fsub_rn(1.f, __fmul_rn(ang, ang))), ang);
+				ang = osbm::atanf_glibc(ang);
+				if (isnan(ang) || isinf(ang))
+					continue;
+				if (pz > 0.f) {
+					const float c = __fsub_rn(ang, 0.01f);
+					minPitch = minPitch < c ? c : minPitch;
+				} else {
+					const float c = __fadd_rn(-ang, 0.01f);
+					maxPitch = c < maxPitch ? c : maxPitch;
+				}
+			}
+		}
+		// SpecialTan (:43-57)
+		auto specialTan = [&](float v) -> float {
+			if (v <= -pi * 0.5f)
+				return -2.f;
+			else if (v < -pi * 0.25f)
+				return __fsub_rn(-2.f, __fdiv_rn(1.f, osbm::tanf_glibc(v)));
+			else if (v < pi * 0.25f)
+				return osbm::tanf_glibc(v);
+			else if (v < pi * 0.5f)
+				return __fsub_rn(2.f, __fdiv_rn(1.f, osbm::tanf_glibc(v)));
+			return 2.f;
+		};
+		const float minTan = specialTan(minPitch);
+		float maxTan = specialTan(maxPitch);
+		{
+			const float minDiff = __fdiv_rn((float)lineRes, 10000.f);
+			if (maxTan < __fadd_rn(minTan, minDiff))
+				maxTan = __fadd_rn(minTan, minDiff);
+		}
+		const float pitchScale = __fdiv_rn((float)lineRes, __fsub_rn(maxTan, minTan));
+		lineParams[gl] = make_int4(__float_as_int(minTan), __float_as_int(pitchScale),
+		                           osbn::x86_f2i(__fmul_rn(minTan, 65536.f)), osbn::x86_f2i(__fmul_rn(pitchScale, 65536.f)));
+		if (minPitch >= maxPitch)
+			return; // culled: strip stays cleared (:387-389)
+
+		// ---- DDA set-up (:309-351) ----
+		float dirX = hd.x, dirY = hd.y;
+		if (fabsf(dirY) < 1.e-4f)
+			dirY = 1.e-4f;
+		if (fabsf(dirX) < 1.e-4f)
+			dirX = 1.e-4f;
+		const float invDirX = __fdiv_rn(1.f, dirX), invDirY = __fdiv_rn(1.f, dirY);
+		const bool posX = dirX > 0.f, posY = dirY > 0.f;
+		const int invDirXI = abs(osbn::x86_f2i(__fmul_rn(invDirX, 256.f)));
+		const int invDirYI = abs(osbn::x86_f2i(__fmul_rn(invDirY, 256.f)));
+		const uint32_t dirXI = (uint32_t)abs(osbn::x86_f2i(__fmul_rn(dirX, 512.f)));
+		const uint32_t dirYI = (uint32_t)abs(osbn::x86_f2i(__fmul_rn(dirY, 512.f)));
+
+		const float cx = V.origin[0], cy = V.origin[1], cz = V.origin[2];
+		const int icz = osbn::x86_f2i(floorf(cz));
+		int rx = osbn::x86_f2i(__fmul_rn(cx, 512.f)), ry = osbn::x86_f2i(__fmul_rn(cy, 512.f));
+		int irx = rx >> 9, iry = ry >> 9;
+
+		const float fogDist = 128.f;
+		float distance = 1.e-20f;
+		float invDist = __fdiv_rn(1.f, distance);
+
+		LineCtx<kSse> L;
+		L.num = num;
+		L.cz = cz;
+		L.transScale = pitchScale; // same expression as line.pitchScale (:303,358)
+		L.transOffset = __fmul_rn(-minTan, L.transScale);
+		L.vmax = __fadd_rn((float)lineRes, 0.5f);
+
+		// zscale = Dot(horizonDir, viewAxis[2]) (horizonDir.z = 0), heightScale, depthBias (:403-414)
+		const float zscale = __fadd_rn(__fadd_rn(__fmul_rn(hd.x, V.front[0]), __fmul_rn(hd.y, V.front[1])),
+		                               __fmul_rn(0.f, V.front[2]));
+		const float heightScale = V.front[2];
+		const float depthBias = __fmul_rn(-cz, heightScale);
+
+		// z > icz / z < icz as bit masks
+		const uint64_t belowEye = icz >= 63 ? 0ull : (icz < 0 ? ~0ull : (~0ull << (icz + 1)));
+		const uint64_t aboveEye = icz <= 0 ? 0ull : (icz >= 64 ? ~0ull : ((1ull << icz) - 1ull));
+
+		uint64_t sOld = solid[tiled_index(irx & 511, iry & 511)];
+		uint32_t tOld = tiled_index(irx & 511, iry & 511);
+		int count = 1;
+		uint32_t cnt2 = 1024; // static_cast<int>(fogDist * 8.f)
+
+		while (distance < fogDist && (--cnt2) > 0) {
+			// ---- one DDA step (:426-522) ----
+			int wallFace;
+			const uint32_t tx = (uint32_t)((posX ? 512 - (rx & 511) : (rx & 511)) * invDirXI);
+			const uint32_t ty = (uint32_t)((posY ? 512 - (ry & 511) : (ry & 511)) * invDirYI);
+			if (tx < ty) {
+				irx += posX ? 1 : -1;
+				rx = posX ? (irx << 9) : (irx << 9) - 1;
+				const int d = (int)((dirYI * tx) >> 17);
+				ry = posY ? ry + d : ry - d;
+				distance = __fadd_rn(distance, __fmul_rn((float)tx, 1.f / 512.f / 256.f));
+				wallFace = posX ? F_NEGX : F_POSX;
+			} else {
+				iry += posY ? 1 : -1;
+				const int d = (int)((dirXI * ty) >> 17);
+				rx = posX ? rx + d : rx - d;
+				ry = posY ? (iry << 9) : (iry << 9) - 1;
+				distance = __fadd_rn(distance, __fmul_rn((float)ty, 1.f / 512.f / 256.f));
+				wallFace = posY ? F_NEGY : F_POSY;
+			}
+			const float oldInvDist = invDist;
+			invDist = num.rcp(distance);
+			const float medDist = __fadd_rn(__fmul_rn(distance, zscale), depthBias);
+
+			const uint32_t tNew = tiled_index(irx & 511, iry & 511);
+			const uint64_t sNew = solid[tNew];
+
+			// ---- floor / ceiling of the cell being left (:579-624) ----
+			{
+				uint64_t tops = sOld & ~(sOld << 1) & belowEye; // solid with air above, below the eye, ascending
+				while (tops) {
+					const int z = __ffsll((long long)tops) - 1;
+					tops &= tops - 1;
+					const int p1 = L.transform(invDist, z), p2 = L.transform(oldInvDist, z);
+					if (p1 < p2 && span_has_empty(filled, p1, p2)) {
+						const uint32_t c = shade<kSse2Shade>(color[(size_t)tOld * 64 + z], F_NEGZ);
+						fill_span(strip, filled, p1, p2, c, __fadd_rn(medDist, __fmul_rn((float)z, heightScale)));
+					}
+				}
+				uint64_t bots = sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye; // solid with air below, descending
+				while (bots) {
+					const int z = 63 - __clzll((long long)bots);
+					bots &= ~(1ull << z);
+					const int p1 = L.transform(invDist, z + 1), p2 = L.transform(oldInvDist, z + 1);
+					if (p2 < p1 && span_has_empty(filled, p2, p1)) {
+						const uint32_t c = shade<kSse2Shade>(color[(size_t)tOld * 64 + z], F_POSZ);
+						fill_span(strip, filled, p2, p1, c, __fadd_rn(medDist, __fmul_rn((float)(z + 1), heightScale)));
+					}
+				}
+			}
+			// ---- walls of the cell being entered: solid there, air in the cell just left (:627-659) ----
+			{
+				uint64_t walls = sNew & ~sOld;
+				int savedZ = 127, savedP = 0;
+				while (walls) {
+					const int z = __ffsll((long long)walls) - 1;
+					walls &= walls - 1;
+					const int p1 = savedZ == z ? savedP : L.transform(invDist, z);
+					const int p2 = L.transform(invDist, z + 1);
+					savedZ = z + 1;
+					savedP = p2;
+					if (p1 < p2 && span_has_empty(filled, p1, p2)) {
+						const uint32_t c = shade<kSse2Shade>(color[(size_t)tNew * 64 + z], wallFace);
+						fill_span(strip, filled, p1, p2, c, __fadd_rn(medDist, __fmul_rn((float)z, heightScale)));
+					}
+				}
+			}
+			sOld = sNew;
+			tOld = tNew;
+			// ---- pitch cull every 4th step (:661-667) ----
+			if ((--count) == 0) {
+				if ((L.transform(invDist, 0) >= lineRes - 1 && icz >= 0) || L.transform(invDist, 63) <= 0)
+					break;
+				count = 4;
+			}
+		}
+	}
+
+	// ---- fastATan / fastATan2 (SWMapRenderer.cpp:697-742); tab = sm | lg | smN | lgN, 5000 each ----
+	template <bool kSse>
+	__device__ __forceinline__ uint32_t fast_atan(const osbn::Num<kSse> &num, const uint16_t *__restrict__ tab, float v) {
+		int idx, base;
+		if (v < 0.f) {
+			if (v > -1.f) {
+				idx = osbn::x86_f2i(__fmul_rn(v, -4096.f));
+				base = 10000;
+			} else {
+				idx = osbn::x86_f2i(num.div(-4096.f, v));
+				base = 15000;
+			}
+		} else {
+			if (v < 1.f) {
+				idx = osbn::x86_f2i(__fmul_rn(v, 4096.f));
+				base = 0;
+			} else {
+				idx = osbn::x86_f2i(num.div(4096.f, v));
+				base = 5000;
+			}
+		}
+		idx = min(max(idx, 0), 4999); // memory safety only; in range for every finite input
+		return __ldg(tab + base + idx);
+	}
+	template <bool kSse>
+	__device__ __forceinline__ uint32_t fast_atan2(const osbn::Num<kSse> &num, const uint16_t *__restrict__ tab, float y,
+	                                               float x) {
+		if (x == 0.f)
+			return y > 0.f ? 16384u : 49152u; // (uint16_t)-16384
+		else if (x > 0.f)
+			return fast_atan(num, tab, num.div(y, x));
+		return (fast_atan(num, tab, num.div(y, x)) + 32768u) & 0xffffu;
+	}
+
+	constexpr int kGatherWarps = 4;
+	constexpr int kSegRows = 8; // 8x8 blocks per warp task (vertical)
+
+	// RenderFinal + ApplyFog, one warp per (view, 8-pixel column, segment of kSegRows block rows).
+	template <bool kSse, bool kSse2Fog>
+	__global__ void __launch_bounds__(kGatherWarps * 32)
+	  k_gather_fog(const ViewParams *__restrict__ views, int nViews, FrameGeom g, const float *__restrict__ tabs,
+	               const uint64_t *__restrict__ solid, const uint16_t *__restrict__ atanTab, osbn::SseTables sse,
+	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams, int lineRes,
+	               uint32_t *__restrict__ fb, float *__restrict__ depthBuf) {
+		const int lane = threadIdx.x & 31;
+		const int colBlocks = g.fw >> 3, rowBlocks = g.fh >> 3;
+		const int segs = (rowBlocks + kSegRows - 1) / kSegRows;
+		const uint32_t task = blockIdx.x * kGatherWarps + (threadIdx.x >> 5);
+		const uint32_t perView = (uint32_t)colBlocks * segs;
+		if (task >= perView * (uint32_t)nViews)
+			return;
+		const int vi = task / perView;
+		const uint32_t rem = task - (uint32_t)vi * perView;
+		const int seg = rem / colBlocks, bx = rem - seg * colBlocks;
+		const ViewParams &V = views[vi];
+		osbn::Num<kSse> num{sse};
+		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2), *v1Tab = vyTab + (g.fh >> 2);
+		uint32_t *fbV = fb + (size_t)vi * g.fw * g.fh;
+		float *dbV = depthBuf + (size_t)vi * g.fw * g.fh;
+
+		// SWMapRenderer::Render :1181-1184: eye inside a solid voxel -> terrain skipped, fb keeps the clear
+		// colour and the depth buffer keeps its previous contents
+		bool skip;
+		{
+			const int ex = osbn::x86_f2i(floorf(V.origin[0])), ey = osbn::x86_f2i(floorf(V.origin[1])),
+			          ez = osbn::x86_f2i(floorf(V.origin[2]));
+			skip = ez >= 64 || (ez >= 0 && ((solid[tiled_index(ex & 511, ey & 511)] >> ez) & 1ull));
+		}
+
+		// per-view deltas (:757-775)
+		const int under = g.under, hBlock = 8 / under;
+		const float sD = __fdiv_rn(__fmul_rn(V.fovYt, 2.f), (float)g.fh);
+		const float sR = __fmul_rn(__fdiv_rn(__fmul_rn(V.fovXt, 2.f), (float)g.fw), (float)under);
+		float dD[3], dR[3], dDL[3], dRL[3], v2[3];
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			dD[k] = __fmul_rn(-V.up[k], sD);
+			dR[k] = __fmul_rn(V.right[k], sR);
+			dDL[k] = __fmul_rn(dD[k], 8.f);
+			dRL[k] = __fmul_rn(dR[k], (float)hBlock);
+			v2[k] = v1Tab[bx * 3 + k];
+		}
+		const int by0 = seg * kSegRows, by1 = min(by0 + kSegRows, rowBlocks);
+		for (int i = 0; i < by0; i++) { // replay v2 += deltaDownLarge (:1037)
+#pragma unroll
+			for (int k = 0; k < 3; k++)
+				v2[k] = __fadd_rn(v2[k], dDL[k]);
+		}
+		const uint32_t numLines = (uint32_t)V.numLines;
+		const uint32_t yawScale2 = (uint32_t)V.yawScale2;
+		const int yawMin2 = V.yawMin2;
+		const uint2 *stripsV = strips + (size_t)V.lineBase * lineRes;
+		const int4 *lpV = lineParams + V.lineBase;
+		const int px = lane & 7;             // pixel column inside the block
+		const int pxq = px - (px % under);   // undersampling: pixels share their group leader's sample
+		const int xs = pxq / under;
+		const float fogVx = vxTab[(bx << 1) + (px >> 2)];
+
+		for (int by = by0; by < by1; by++) {
+			const bool slow = v2[2] > 0.99f || v2[2] < -0.99f;
+			int yaw1 = 0, yaw2 = 0, yaw3 = 0, yaw4 = 0, pit1 = 0, pit2 = 0, pit3 = 0, pit4 = 0;
+			if (!slow && !skip) {
+				// four block corners, one per lane 0..3 (:810-835)
+				const int cr = lane & 1, cd = (lane >> 1) & 1;
+				float c[3];
+#pragma unroll
+				for (int k = 0; k < 3; k++) {
+					c[k] = v2[k];
+					if (cr)
+						c[k] = __fadd_rn(c[k], dRL[k]);
+					if (cd)
+						c[k] = __fadd_rn(c[k], dDL[k]);
+				}
+				const int yaw = (int)((((int)fast_atan2(num, atanTab, c[1], c[0]) - yawMin2) & 0xffff) << 8);
+				float pitch = __fmul_rn(c[2], num.rsqrt(__fadd_rn(__fmul_rn(c[0], c[0]), __fmul_rn(c[1], c[1]))));
+				pitch = num.toSpecialTan(pitch);
+				const int pit = osbn::x86_f2i(__fmul_rn(pitch, 65536.f * 8192.f));
+				yaw1 = __shfl_sync(0xffffffffu, yaw, 0);
+				yaw2 = __shfl_sync(0xffffffffu, yaw, 1);
+				yaw3 = __shfl_sync(0xffffffffu, yaw, 2);
+				yaw4 = __shfl_sync(0xffffffffu, yaw, 3);
+				pit1 = __shfl_sync(0xffffffffu, pit, 0);
+				pit2 = __shfl_sync(0xffffffffu, pit, 1);
+				pit3 = __shfl_sync(0xffffffffu, pit, 2);
+				pit4 = __shfl_sync(0xffffffffu, pit, 3);
+			}
+#pragma unroll
+			for (int pass = 0; pass < 2; pass++) {
+				const int py = (lane >> 3) + pass * 4;
+				const size_t o = (size_t)(by * 8 + py) * g.fw + (size_t)bx * 8 + px;
+				uint32_t col;
+				float dep;
+				if (skip) {
+					col = 0x7f7f7f;
+					dep = dbV[o];
+				} else {
+					uint32_t yawIndex;
+					int pitchIndex;
+					if (!slow) {
+						// bilinear interpolation in integers; `<<8>>8` is the reference's phase unwrap (:837-881)
+						const int yawDiff1 = (((yaw2 - yaw1) << 8) >> 8) / hBlock, yawDiff2 = (((yaw4 - yaw3) << 8) >> 8) / hBlock;
+						const int pitDiff1 = (pit2 - pit1) / hBlock, pitDiff2 = (pit4 - pit3) / hBlock;
+						const int yawA = yaw1 + xs * yawDiff1, yawB = yaw3 + xs * yawDiff2;
+						const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
+						const int yawC = yawA + py * ((((yawB - yawA) << 8) >> 8) / 8);
+						const int pitC = pitA + py * ((pitB - pitA) / 8);
+						yawIndex = (uint32_t)((yawC << 8) >> 16);
+						yawIndex = (yawIndex * yawScale2) >> 16;
+						yawIndex = (yawIndex * numLines) >> 16;
+						yawIndex = min(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
+						const int4 lp = __ldg(lpV + yawIndex);
+						pitchIndex = (pitC >> 13) - lp.z;
+						pitchIndex = (int)(((long long)pitchIndex * (long long)lp.w) >> 32);
+					} else {
+						// exact per-pixel path near the poles (:940-1033)
+						float v4[3];
+#pragma unroll
+						for (int k = 0; k < 3; k++)
+							v4[k] = v2[k];
+						for (int i = 0; i < xs; i++) {
+#pragma unroll
+							for (int k = 0; k < 3; k++)
+								v4[k] = __fadd_rn(v4[k], dR[k]);
+						}
+						for (int i = 0; i < py; i++) {
+#pragma unroll
+							for (int k = 0; k < 3; k++)
+								v4[k] = __fadd_rn(v4[k], dD[k]);
+						}
+						yawIndex = (uint32_t)(((int)fast_atan2(num, atanTab, v4[1], v4[0]) - yawMin2) & 0xffff);
+						yawIndex = (yawIndex * yawScale2) >> 16;
+						yawIndex = (yawIndex * numLines) >> 16;
+						yawIndex = min(yawIndex, numLines - 1);
+						const int4 lp = __ldg(lpV + yawIndex);
+						float pitch = __fmul_rn(v4[2], num.rsqrt(__fadd_rn(__fmul_rn(v4[0], v4[0]), __fmul_rn(v4[1], v4[1]))));
+						pitch = num.toSpecialTan(pitch);
+						pitch = __fmul_rn(__fsub_rn(pitch, __int_as_float(lp.x)), __int_as_float(lp.y));
+						pitchIndex = osbn::x86_f2i(pitch);
+					}
+					pitchIndex &= lineRes - 1;
+					const uint2 pix = __ldg(stripsV + (size_t)yawIndex * lineRes + pitchIndex);
+					col = pix.x;
+					dep = __uint_as_float(pix.y);
+				}
+				// ---- ApplyFog for this pixel (SWRenderer.cpp:341-516) ----
+				{
+					const float vy = vyTab[(by << 1) + (py >> 2)];
+					float depthScale = __fadd_rn(__fadd_rn(1.f, __fmul_rn(fogVx, fogVx)), __fmul_rn(vy, vy));
+					depthScale = __fmul_rn(depthScale, __fmul_rn(num.rsqrt(depthScale), V.fogScale));
+					const float dist = __fmul_rn(dep, depthScale);
+					int factor;
+					if (kSse2Fog) {
+						float d = dist > 0.f ? dist : 0.f; // maxps / minps return the 2nd operand on NaN
+						d = d < 256.f ? d : 256.f;
+						factor = osbn::x86_f2i_rn(d);
+					} else {
+						factor = min(osbn::x86_f2i(dist), 256);
+						factor = max(0, factor);
+					}
+					const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
+					const uint32_t b = (((col & 0xff) * f2 + g.fogB * f1) >> 8) & 0xff;
+					const uint32_t gg = ((((col >> 8) & 0xff) * f2 + g.fogG * f1) >> 8) & 0xff;
+					const uint32_t r = ((((col >> 16) & 0xff) * f2 + g.fogR * f1) >> 8) & 0xff;
+					const uint32_t a = kSse2Fog ? (((col >> 24) * f2) >> 8) & 0xff : 0u; // lane 3 of the SSE2 path
+					col = b | (gg << 8) | (r << 16) | (a << 24);
+				}
+				fbV[o] = col;
+				dbV[o] = dep;
+			}
+#pragma unroll
+			for (int k = 0; k < 3; k++)
+				v2[k] = __fadd_rn(v2[k], dDL[k]);
+		}
+	}
+
+	// Device-side recurrences for large batches: one warp per view, one lane per role.
+	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs,
+	                            float *tabs) {
+		const int vi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+		const int lane = threadIdx.x & 31;
+		if (vi >= nViews)
+			return;
+		const ViewParams &V = views[vi];
+		float *vx = tabs + V.tabBase, *vy = vx + (g.fw >> 2), *v1 = vy + (g.fh >> 2);
+		if (lane == 0)
+			prep_line_dirs(V, lineDirs + V.lineBase);
+		else if (lane == 1)
+			prep_fog_vx(V, g, vx);
+		// the emulated SW threads (<= 32) are spread over the lanes for the vy bands and v1 columns
+		for (int t = lane; t < g.swThreads; t += 32)
+			prep_fog_vy(V, g, t, vy);
+		for (int t = 31 - lane; t < g.swThreads; t += 32)
+			prep_v1(V, g, t, v1);
+	}
+
+	static int terrain_init(osb200_ctx *c) {
+		if (c->terrain)
+			return 0;
+		auto *T = new TerrainState();
+		c->terrain = T;
+		// AtanTable (SWMapRenderer.cpp:673-696), built with the host libm exactly like the reference
+		std::vector<uint16_t> tab(20000);
+		auto toFixed = [](float v) -> uint16_t {
+			v /= (M_PI * 2.f);
+			v *= 65536.f;
+			int i = static_cast<int>(v);
+			return static_cast<uint16_t>(i & 65535);
+		};
+		for (int i = 0; i < 5000; i++) {
+			tab[i] = toFixed(atanf(i / 4096.f));
+			tab[5000 + i] = toFixed(atanf(1.f / ((i + .5f) / 4096.f)));
+			tab[10000 + i] = toFixed(-atanf(i / 4096.f));
+			tab[15000 + i] = toFixed(-atanf(1.f / ((i + .5f) / 4096.f)));
+		}
+		OSB_CUDA(cudaMalloc(&T->d_atan, tab.size() * 2));
+		OSB_CUDA(cudaMemcpy(T->d_atan, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
+		OSB_CUDA(cudaEventCreateWithFlags(&T->stageFree, cudaEventDisableTiming));
+		return 0;
+	}
+
+	void terrain_destroy(osb200_ctx *c) {
+		TerrainState *T = c->terrain;
+		if (!T)
+			return;
+		cudaFree(T->d_views);
+		cudaFreeHost(T->h_views);
+		cudaFree(T->d_lineDirs);
+		cudaFree(T->d_lineParams);
+		cudaFree(T->d_strips);
+		cudaFree(T->d_tabs);
+		cudaFreeHost(T->h_tabs);
+		cudaFreeHost(T->h_lineDirs);
+		cudaFree(T->d_atan);
+		cudaFree(T->d_fb);
+		cudaFree(T->d_depth);
+		if (T->stageFree)
+			cudaEventDestroy(T->stageFree);
+		delete T;
+		c->terrain = nullptr;
+	}
+
+	// Host half of RenderInner (SWMapRenderer.cpp:1057-1133) + BuildFrustrum (SWRenderer.cpp:207-227) +
+	// ApplyFog's scalars (SWRenderer.cpp:345-357) for one view, with the host libm.
+	static void fill_view(const osb200_scene &s, int fw, int fh, int under, float fogDist, ViewParams &v) {
+		static const float pi = M_PI;
+		std::memset(&v, 0, sizeof(v));
+		for (int k = 0; k < 3; k++) {
+			v.origin[k] = s.origin[k];
+			v.right[k] = s.axis[0][k];
+			v.up[k] = s.axis[1][k];
+			v.front[k] = s.axis[2][k];
+		}
+		const float xCos = cosf(s.fovX * .5f), xSin = sinf(s.fovX * .5f);
+		const float yCos = cosf(s.fovY * .5f), ySin = sinf(s.fovY * .5f);
+		for (int k = 0; k < 3; k++) {
+			v.frN[0][k] = v.front[k] * xSin - v.right[k] * xCos;
+			v.frN[1][k] = v.front[k] * xSin + v.right[k] * xCos;
+			v.frN[2][k] = v.front[k] * ySin - v.up[k] * yCos;
+			v.frN[3][k] = v.front[k] * ySin + v.up[k] * yCos;
+		}
+		const float fovX = tanf(s.fovX * 0.5f), fovY = tanf(s.fovY * 0.5f);
+		v.fovXt = fovX;
+		v.fovYt = fovY;
+		const float fovDiag = sqrtf(fovX * fovX + fovY * fovY);
+		const float fovDiagAng = atanf(fovDiag);
+		const float pitch = asinf(v.front[2]);
+		float yawMin, yawMax;
+		if (fabsf(pitch) >= pi * 0.49f - fovDiagAng) { // pole is visible
+			yawMin = 0.f;
+			yawMax = pi * 2.f;
+		} else {
+			const float yaw = atan2l(v.front[1], v.front[0]);
+			yawMin = yaw - pi * .5f;
+			yawMax = yaw + pi * .5f;
+		}
+		float interval = static_cast<float>(fh);
+		interval = fovY * 2.f / interval;
+		int lineRes = fh;
+		for (int i = lineRes, j = 1; j <= i; j <<= 1)
+			lineRes = j;
+		size_t numLines = static_cast<size_t>((yawMax - yawMin) / interval);
+		numLines /= under;
+		if (numLines < 8)
+			numLines = 8;
+		if (numLines > 65536)
+			numLines = 65536;
+		v.yawMin = yawMin;
+		v.yawMax = yawMax;
+		v.numLines = (int)numLines;
+		v.lineRes = lineRes;
+		const float scl = (yawMax - yawMin) / numLines;
+		v.cosYawMin = cosf(yawMin);
+		v.sinYawMin = sinf(yawMin);
+		v.cosScl = cosf(scl);
+		v.sinScl = sinf(scl);
+		const float yawScale = 65536.f / (pi * 2.f);
+		v.yawScale2 = static_cast<int32_t>(pi * 2.f / (yawMax - yawMin) * 65536.f);
+		v.yawMin2 = static_cast<int32_t>(yawMin * yawScale);
+		v.fogScale = 255.f / fogDist;
+		v.dvx = -fovX * 2.f / static_cast<float>(fw / 4);
+		v.dvy = -fovY * 2.f / static_cast<float>(fh / 4);
+	}
+} // namespace osb
+
+namespace osb {
+	template <class T> static int grow(T *&p, size_t &cap, size_t want, bool pinned = false) {
+		if (want <= cap)
+			return 0;
+		if (p) {
+			if (pinned)
+				cudaFreeHost(p);
+			else
+				cudaFree(p);
+		}
+		p = nullptr;
+		cap = 0;
+		size_t n = want + (want >> 2);
+		if (pinned)
+			OSB_CUDA(cudaMallocHost((void **)&p, n * sizeof(T)));
+		else
+			OSB_CUDA(cudaMalloc((void **)&p, n * sizeof(T)));
+		cap = n;
+		return 0;
+	}
+
+	static size_t strip_budget_bytes() {
+		static size_t v = 0;
+		if (!v) {
+			const char *e = getenv("OSB200_STRIP_MB");
+			long mb = e ? atol(e) : 0;
+			if (mb <= 0)
+				mb = 1024;
+			v = (size_t)mb << 20;
+		}
+		return v;
+	}
+
+	static int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
+	                       const float fogColor[3], float fogDist, uint32_t *d_fb, float *d_depth) {
+		if (!c || !c->mapLoaded) {
+			set_error("osb200_render: no context or no map uploaded");
+			return -1;
+		}
+		if (nViews == 0)
+			return 0;
+		if (!scenes || !fogColor || !d_fb || !d_depth || nViews < 0) {
+			set_error("osb200_render: null argument");
+			return -1;
+		}
+		if (w <= 0 || h <= 0 || (w & 7) || (h & 7)) {
+			set_error("Framebuffer size is not multiple of 8."); // SWRenderer.cpp:105-107
+			return -1;
+		}
+		if (h >= 8192 || w > 32768) {
+			set_error("osb200_render: framebuffer too large (h < 8192, w <= 32768)");
+			return -1;
+		}
+		OSB_CUDA(cudaSetDevice(c->device));
+		if (terrain_init(c))
+			return -2;
+		TerrainState *T = c->terrain;
+		const int under = c->opts.undersampling;
+		FrameGeom g;
+		g.fw = w;
+		g.fh = h;
+		g.under = under;
+		g.swThreads = c->opts.sw_threads;
+		g.sse2Fog = g.sse2Shade = c->opts.numerics == OSB200_NUM_SSE2;
+		auto toFixed8 = [](float v) { // SWUtils.h:68-71
+			int i = static_cast<int>(v * 255.f + .5f);
+			return (uint32_t)std::max(std::min(i, 255), 0);
+		};
+		g.fogR = toFixed8(fogColor[0]);
+		g.fogG = toFixed8(fogColor[1]);
+		g.fogB = toFixed8(fogColor[2]);
+
+		// the pinned staging buffers may still be in flight from the previous call
+		OSB_CUDA(cudaEventSynchronize(T->stageFree));
+		if (grow(T->h_views, T->viewCap, (size_t)nViews, true))
+			return -2;
+		if (grow(T->d_views, T->dViewCap, (size_t)nViews))
+			return -2;
+		const uint32_t tabF = tab_floats(w, h);
+		int lineRes = 0;
+		for (int i = 0; i < nViews; i++) {
+			fill_view(scenes[i], w, h, under, fogDist, T->h_views[i]);
+			lineRes = T->h_views[i].lineRes;
+		}
+		// ---- chunking: strips of one chunk must fit the budget ----
+		const size_t budgetLines = std::max<size_t>(strip_budget_bytes() / ((size_t)lineRes * 8), 65536);
+		std::vector<int> chunkStart;
+		size_t maxLines = 0, maxViews = 0;
+		{
+			size_t lines = 0;
+			int start = 0;
+			chunkStart.push_back(0);
+			for (int i = 0; i < nViews; i++) {
+				ViewParams &v = T->h_views[i];
+				if (lines + (size_t)v.numLines > budgetLines && i > start) {
+					chunkStart.push_back(i);
+					start = i;
+					lines = 0;
+				}
+				v.lineBase = (uint32_t)lines;
+				v.tabBase = (uint32_t)(i - start) * tabF;
+				lines += (size_t)v.numLines;
+				maxLines = std::max(maxLines, lines);
+				maxViews = std::max(maxViews, (size_t)(i - start + 1));
+			}
+			chunkStart.push_back(nViews);
+		}
+		const bool hostPrep = nViews <= 8;
+		if (grow(T->d_lineDirs, T->lineCap, maxLines))
+			return -2;
+		if (grow(T->d_lineParams, T->lineParamCap, maxLines))
+			return -2;
+		if (grow(T->d_strips, T->stripCap, maxLines * (size_t)lineRes))
+			return -2;
+		if (grow(T->d_tabs, T->tabCap, maxViews * tabF))
+			return -2;
+		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
+		                         c->stream));
+		if (hostPrep) {
+			if (grow(T->h_lineDirs, T->hLineCap, maxLines, true))
+				return -2;
+			if (grow(T->h_tabs, T->hTabCap, maxViews * tabF, true))
+				return -2;
+		}
+		osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
+		const int num = c->opts.numerics;
+		for (size_t ci = 0; ci + 1 < chunkStart.size(); ci++) {
+			const int v0 = chunkStart[ci], nv = chunkStart[ci + 1] - v0;
+			const ViewParams &last = T->h_views[v0 + nv - 1];
+			const uint32_t totalLines = last.lineBase + (uint32_t)last.numLines;
+			const ViewParams *dV = T->d_views + v0;
+			if (hostPrep) {
+				for (int i = 0; i < nv; i++) {
+					const ViewParams &V = T->h_views[v0 + i];
+					float *vx = T->h_tabs + V.tabBase, *vy = vx + (w >> 2), *v1 = vy + (h >> 2);
+					prep_line_dirs(V, T->h_lineDirs + V.lineBase);
+					prep_fog_vx(V, g, vx);
+					for (int t = 0; t < g.swThreads; t++) {
+						prep_fog_vy(V, g, t, vy);
+						prep_v1(V, g, t, v1);
+					}
+				}
+				OSB_CUDA(cudaMemcpyAsync(T->d_lineDirs, T->h_lineDirs, sizeof(float2) * totalLines,
+				                         cudaMemcpyHostToDevice, c->stream));
+				OSB_CUDA(cudaMemcpyAsync(T->d_tabs, T->h_tabs, sizeof(float) * tabF * nv, cudaMemcpyHostToDevice,
+				                         c->stream));
+			} else {
+				k_view_prep<<<(nv + 3) / 4, 128, 0, c->stream>>>(dV, nv, g, T->d_lineDirs, T->d_tabs);
+				c->launches++;
+			}
+			const unsigned lineBlocks = (totalLines + kLineThreads - 1) / kLineThreads;
+			const size_t smem = (size_t)lineRes * 8;
+#define LAUNCH_LINES(SSE, SH)                                                                      \
+	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, c->stream>>>(                          \
+	  dV, nv, T->d_lineDirs, c->d_solid, c->d_color, sse, T->d_strips, T->d_lineParams, totalLines, lineRes)
+			if (num == OSB200_NUM_IEEE)
+				LAUNCH_LINES(false, false);
+			else if (num == OSB200_NUM_SSE)
+				LAUNCH_LINES(true, false);
+			else
+				LAUNCH_LINES(true, true);
+#undef LAUNCH_LINES
+			c->launches++;
+			const int segs = ((h >> 3) + kSegRows - 1) / kSegRows;
+			const size_t tasks = (size_t)nv * (w >> 3) * segs;
+			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
+			uint32_t *fbC = d_fb + (size_t)v0 * w * h;
+			float *dbC = d_depth + (size_t)v0 * w * h;
+#define LAUNCH_GATHER(SSE, FOG)                                                                    \
+	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, c->stream>>>(                           \
+	  dV, nv, g, T->d_tabs, c->d_solid, T->d_atan, sse, T->d_strips, T->d_lineParams, lineRes, fbC, dbC)
+			if (num == OSB200_NUM_IEEE)
+				LAUNCH_GATHER(false, false);
+			else if (num == OSB200_NUM_SSE)
+				LAUNCH_GATHER(true, false);
+			else
+				LAUNCH_GATHER(true, true);
+#undef LAUNCH_GATHER
+			c->launches++;
+			if (hostPrep && ci + 2 < chunkStart.size()) // staging reused by the next chunk
+				OSB_CUDA(cudaStreamSynchronize(c->stream));
+		}
+		OSB_CUDA(cudaGetLastError());
+		OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
+		return 0;
+	}
+} // namespace osb
+
+extern "C" {
+
+int osb200_render_device(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
+                         const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth) {
+	return osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, d_bgrx, d_depth);
+}
+
+int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
+                  float fogDist, uint32_t *host_bgrx, float *host_depth) {
+	if (!c || !c->mapLoaded) {
+		osb::set_error("osb200_render: no context or no map uploaded");
+		return -1;
+	}
+	if (nViews <= 0)
+		return nViews == 0 ? 0 : -1;
+	if (w <= 0 || h <= 0 || (w & 7) || (h & 7)) {
+		osb::set_error("Framebuffer size is not multiple of 8.");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	if (osb::terrain_init(c))
+		return -2;
+	osb::TerrainState *T = c->terrain;
+	const size_t n = (size_t)nViews * w * h;
+	if (n > T->outCap) {
+		// the depth buffer persists between frames like SWRenderer::depthBuffer (never cleared, SWRenderer.cpp:83);
+		// a fresh one starts at zero like std::vector<float>::resize
+		cudaFree(T->d_fb);
+		cudaFree(T->d_depth);
+		T->d_fb = nullptr;
+		T->d_depth = nullptr;
+		T->outCap = 0;
+		OSB_CUDA(cudaMalloc(&T->d_fb, n * 4));
+		OSB_CUDA(cudaMalloc(&T->d_depth, n * 4));
+		OSB_CUDA(cudaMemsetAsync(T->d_depth, 0, n * 4, c->stream));
+		T->outCap = n;
+	}
+	int rc = osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, T->d_fb, T->d_depth);
+	if (rc)
+		return rc;
+	if (host_bgrx)
+		OSB_CUDA(cudaMemcpyAsync(host_bgrx, T->d_fb, n * 4, cudaMemcpyDeviceToHost, c->stream));
+	if (host_depth)
+		OSB_CUDA(cudaMemcpyAsync(host_depth, T->d_depth, n * 4, cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+} // extern "C"
