@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the OpenSpades voxel hot path on B200 (contract: see the task brief).
+
+Headline workload (BASELINE.json configs[3], the one the north_star's roofline target is quoted on and the
+only render workload that shards): a batch of independent 256x256 camera views of the bundled
+Title.vxl map, fovY 68 deg, fog (0.8,1,1)/128, V-SSE2 numerics with r_swNumThreads = 4 -- 4096 views PER
+GPU (weak scaling: views are sharded by view, map replicated, no data-path collective).
+A "step" renders the whole batch once: terrain pass (k_build_lines) + fused gather/fog (k_gather_fog).
+
+  value   Mpixel/s, device-timed, inputs resident in HBM (scene constants upload is part of the call).
+  e2e     same metric through the host-pointer C-ABI call osb200_render: host scenes in, frames + depth
+          copied back to pinned host memory inside the timed region.
+  extra   configs[1] (1920x1080 single view) and configs[2] (16 Mi CastRay2 rays) measured the same way.
+
+`--impl reference` times the reference's own CPU code (oracle/_ref, else the oracle port) on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mpixel/s voxel terrain render (batched 256x256 views, terrain + fog)"
+UNIT = "Mpixel/s"
+FOG = (0.8, 1.0, 1.0)  # Client.cpp:112-113
+FOG_DIST = 128.0
+BYTES_PER_PIXEL = 8  # 4 B BGRX + 4 B f32 depth written once per pixel
+BYTES_PER_RAY = 64   # 24 B in + 40 B RayCastResult out
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--views", type=int, default=4096, help="views per GPU")
+    ap.add_argument("--size", type=int, default=256)
+    ap.add_argument("--rays", type=int, default=1 << 24, help="rays per GPU for the CastRay2 extra")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 1080p / CastRay2 extras")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU work per cpu_baseline sample")
+    return ap.parse_args()
+
+
+def load_map():
+    """Title.vxl decoded by the product's host VoxelMap (GameMap::Load equivalent)."""
+    from openspades_b200 import workloads
+    from openspades_b200.hostlib import VoxelMap
+    m = VoxelMap.load_file(workloads.TITLE_VXL)
+    return m.solid.copy(), m.color.copy()
+
+
+def load_map_cpu_only():
+    """Same arrays without touching the product libraries (reference arm): oracle VXL decoder."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracles
+    return oracles.Port().vxl_load(open(oracles.TITLE_VXL, "rb").read())
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        rows = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.15 and len(r) >= 9]
+        if not rows:
+            rows = [r for (_, r) in self.rows if len(r) >= 9]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = sorted(float(r[1]) for r in rows)
+        reasons = set()
+        for r in rows:
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
+                              ("sw_power_cap", 8)):
+                if r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": sorted(reasons),
+                "samples": len(rows), "power_w_max": max(float(r[3]) for r in rows)}
+
+
+def read_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except (KeyError, ValueError):
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def read_traffic(kernel, workload):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload, {}).get(kernel)
+        except ValueError:
+            pass
+    return None
+
+
+def cpu_views_sample(args, solid, color, S, per_worker):
+    """Reference SWRenderer on the host cores over a bounded sample of the same view distribution."""
+    from oracle import cpu_bench
+    from openspades_b200 import workloads
+    workers = cpu_bench.usable_cores()
+    n = workers * per_worker
+    scenes = workloads.random_scenes(n, solid, S, S, 68.0, seed=4321)
+    return cpu_bench.Pool("views", solid, color, scenes, workers=workers, w=S, h=S, fog=list(FOG),
+                          fog_dist=FOG_DIST, sw_threads=1), n
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU code, all host cores, same metric / config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import cpu_bench
+    S = args.size
+    solid, color = load_map_cpu_only()
+    # bounded sample: 32 views per worker process per step (~0.2 s of work per core per step)
+    pool, n = cpu_views_sample(args, solid, color, S, 32)
+    with pool:
+        for _ in range(args.warmup):
+            pool.step()
+        secs = 0.0
+        for _ in range(args.steps):
+            secs += pool.step()["seconds"]
+    ms = secs * 1e3 / args.steps
+    value = n * S * S / (ms * 1e-3) / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32+u8", "data": "synthetic poses on the bundled Title.vxl map",
+        "config": {"workload": f"C4 batched {S}x{S} views, fovY 68, fog (0.8,1,1)/128, Title.vxl",
+                   "views_per_step": n, "width": S, "height": S},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": pool.workers, "kind": pool.kind,
+                         "sample": f"{n} views per step = 32 per worker process x {pool.workers} processes, each a private "
+                                   "SWRenderer (V-SSE2, r_swNumThreads=1), StartScene+EndScene+FrameDone"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import openspades_b200 as osb
+    from openspades_b200 import workloads
+
+    S, nv, K, W = args.size, args.views, args.steps, args.warmup
+    solid, color = load_map()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- cpu_baseline leg (rank 0, N = 1 only), before the GPU is busy ----
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        try:
+            pool, n_cpu = cpu_views_sample(args, solid, color, S, 256)
+            with pool:
+                pool.step()  # warm
+                r = pool.step()
+            cpu_baseline = {
+                "value": n_cpu * S * S / r["seconds"] / 1e6, "unit": UNIT, "cores": pool.workers, "kind": pool.kind,
+                "sample": f"{n_cpu} of the same {S}x{S} views (256 per worker process x {pool.workers} processes, each a "
+                          f"private SWRenderer V-SSE2 r_swNumThreads=1), {r['seconds']:.2f} s wall"}
+        except Exception as e:  # the baseline is a reported extra; never let it sink the GPU numbers
+            cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(e)}
+
+    ctx = osb.Context(device=local, numerics=osb.NUM_SSE2, sw_threads=4)
+    ctx.map_upload(solid, color)
+    ext = torch.cuda.ExternalStream(ctx.stream, device=dev)
+    scenes = workloads.random_scenes(nv, solid, S, S, 68.0, seed=4321 + rank)
+    d_fb = torch.empty((nv, S, S), dtype=torch.int32, device=dev)
+    d_dp = torch.zeros((nv, S, S), dtype=torch.float32, device=dev)
+    pixels_per_step = nv * S * S
+
+    def step_device():
+        ctx.render_device(scenes, S, S, FOG, FOG_DIST, d_fb, d_dp)
+
+    # ---- device-timed value ----
+    for _ in range(W):
+        step_device()
+    ctx.sync()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ctx.timing_enable(True)
+    ctx.timing_read()
+    launches0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_wall0 = time.time()
+    e0.record(ext)
+    for _ in range(K):
+        step_device()
+    e1.record(ext)
+    e1.synchronize()
+    barrier()
+    t_wall1 = time.time()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    gpu_launches = ctx.launch_count - launches0
+    ktimes = ctx.timing_read()
+    ctx.timing_enable(False)
+    ms_per_step = ms_total / K
+    value = world * pixels_per_step / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e through the host-pointer C-ABI call (H2D scenes, D2H frames + depth every step) ----
+    h_fb = torch.empty((nv, S, S), dtype=torch.int32, pin_memory=True)
+    h_dp = torch.empty((nv, S, S), dtype=torch.float32, pin_memory=True)
+
+    def step_e2e():
+        ctx.render(scenes, S, S, FOG, FOG_DIST, out_bgrx=h_fb, out_depth=h_dp)
+
+    for _ in range(max(1, min(W, 2))):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        step_e2e()
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / K
+    t_wall2 = time.time()
+    e2e = {"value": world * pixels_per_step / (e2e_ms * 1e-3) / 1e6, "unit": UNIT,
+           "h2d_bytes_per_step": int(scenes.nbytes), "d2h_bytes_per_step": int(pixels_per_step * BYTES_PER_PIXEL),
+           "ms_per_step": e2e_ms}
+    clocks = sampler.summary(t_wall0, t_wall2)
+    checksum = int(h_fb.view(-1)[:: 4099].to(torch.int64).sum().item())  # the step's result was read on the host
+
+    # ---- roofline of the dominant kernel (CUDA events around every launch, on the launching stream) ----
+    peak, peak_src = read_peaks()
+    dom = max(ktimes, key=lambda k: ktimes[k][1])
+    dl, dms = ktimes[dom]
+    bytes_per_launch = BYTES_PER_PIXEL * pixels_per_step * K / max(dl, 1)
+    achieved = bytes_per_launch / (dms / max(dl, 1) * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": read_traffic(dom, "views256"), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": dms / max(dl, 1),
+                "kernel_ms_per_step": {k: v[1] / K for k, v in ktimes.items() if v[0]},
+                "kernel_launches_per_step": {k: v[0] / K for k, v in ktimes.items() if v[0]}}
+
+    extra = {}
+    if not args.no_extra:
+        extra = run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
+    sampler.stop()
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32+u8", "data": "synthetic poses (seeded) on the bundled Title.vxl map",
+            "config": {"workload": f"C4 batched {S}x{S} views, fovY 68, fog (0.8,1,1)/128, Title.vxl, V-SSE2 numerics "
+                                   "(r_swNumThreads=4)", "views_per_gpu": nv, "views_total": nv * world, "width": S,
+                       "height": S, "parallelism": f"views sharded over {world} GPU(s), map replicated",
+                       "l2": "no flush: each step writes 8 B/pixel x %.2f Gpixel = %.2f GB per GPU plus its strip "
+                             "buffers, far beyond the 126 MB L2; the 2 MiB map bitmap is L2-resident by design"
+                             % (pixels_per_step / 1e9, pixels_per_step * 8 / 1e9)},
+            "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "extra": extra, "result_checksum": checksum,
+        }
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak):
+    """configs[1] (1920x1080 single view; replicas only, rank-local) and configs[2] (CastRay2 batch,
+    rays sharded by ray, aggregate over ranks).  Same timing rules: warm-up, events on the context stream."""
+    import torch
+    from openspades_b200 import workloads
+    import openspades_b200 as osb
+    out = {}
+    # ---- 1920x1080 single view, title pose + fog (0.1,0.1,0.1)/128 ----
+    w, h = 1920, 1080
+    sc = workloads.title_scene(w, h, 68.0)
+    fb = torch.empty((1, h, w), dtype=torch.int32, device=dev)
+    dp = torch.zeros((1, h, w), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    n_it = 20
+    for _ in range(3):
+        ctx.render_device(sc, w, h, (0.1, 0.1, 0.1), 128.0, fb, dp)
+    ctx.sync()
+    tot = 0.0
+    for _ in range(n_it):
+        flush.fill_(1)  # L2 flush between timed iterations (torch current stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        ctx.render_device(sc, w, h, (0.1, 0.1, 0.1), 128.0, fb, dp)
+        e1.record(ext)
+        e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    ms = tot / n_it
+    hfb = torch.empty((1, h, w), dtype=torch.int32, pin_memory=True)
+    hdp = torch.empty((1, h, w), dtype=torch.float32, pin_memory=True)
+    ctx.render(sc, w, h, (0.1, 0.1, 0.1), 128.0, out_bgrx=hfb, out_depth=hdp)
+    t0 = time.perf_counter()
+    for _ in range(n_it):
+        ctx.render(sc, w, h, (0.1, 0.1, 0.1), 128.0, out_bgrx=hfb, out_depth=hdp)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / n_it
+    out["frame_1080p"] = {"workload": "C2 1920x1080 single view, title pose fovY 68, fog, Title.vxl (per GPU replica; L2 "
+                                      "flushed between iterations)", "ms_per_frame": ms,
+                          "mpixel_s": w * h / ms / 1e3, "e2e_ms_per_frame": e2e_ms, "e2e_mpixel_s": w * h / e2e_ms / 1e3,
+                          "hbm_frac_algorithmic": (BYTES_PER_PIXEL * w * h / (ms * 1e-3) / 1e9) / peak}
+    del fb, dp, hfb, hdp, flush
+
+    # ---- CastRay2, args.rays rays per GPU, maxSteps 256 ----
+    n = args.rays
+    rank = int(os.environ.get("RANK", "0"))
+    v0, d = workloads.random_rays(n, seed=1234 + rank)
+    d_v0 = torch.from_numpy(v0).to(dev)
+    d_d = torch.from_numpy(d).to(dev)
+    d_out = torch.empty((n, 10), dtype=torch.int32, device=dev)
+    for _ in range(2):
+        ctx.castray2_device(d_v0, d_d, 256, d_out, n)
+    ctx.sync()
+    K = 5
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(ext)
+    for _ in range(K):
+        ctx.castray2_device(d_v0, d_d, 256, d_out, n)
+    e1.record(ext)
+    e1.synchronize()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1)) / K
+    hits = int((d_out[:, 0] & 1).sum().item())
+    # e2e: pageable numpy in / out through osb200_castray2 on a 4 Mi ray slice
+    ne = min(n, 1 << 22)
+    ctx.castray2(v0[:ne], d[:ne], 256)
+    t0 = time.perf_counter()
+    ctx.castray2(v0[:ne], d[:ne], 256)
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    out["castray2"] = {"workload": f"C3 {n} random rays per GPU, maxSteps 256, Title.vxl (in+out {n * 64 / 1e9:.2f} GB > L2)",
+                       "ms_per_batch": ms, "mrays_s": world * n / ms / 1e3, "hit_fraction": hits / n,
+                       "hbm_frac_algorithmic": (BYTES_PER_RAY * n / (ms * 1e-3) / 1e9) / peak,
+                       "e2e_mrays_s": world * ne / e2e_ms / 1e3, "e2e_rays": ne}
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -87,6 +87,18 @@ OSB200_API void *osb200_stream(osb200_ctx *ctx);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 OSB200_API uint64_t osb200_launch_count(osb200_ctx *ctx);
 
+/* Per-kernel device time, measured with CUDA events recorded on the context stream around every launch
+ * while timing is enabled (bench.py's roofline numbers).  osb200_timing_read synchronises the stream,
+ * fills up to `cap` records (one per kernel class, fixed order), resets the accumulators and returns
+ * the number of records written. */
+typedef struct osb200_kernel_time {
+	const char *name; /* static string, e.g. "k_build_lines" */
+	uint64_t launches;
+	double total_ms;
+} osb200_kernel_time;
+OSB200_API int osb200_timing_enable(osb200_ctx *ctx, int on);
+OSB200_API int osb200_timing_read(osb200_ctx *ctx, osb200_kernel_time *out, int cap);
+
 /* ---- map residency (replaces SWRenderer::SetGameMap + SWMapRenderer ctor's RLE build,
  *      SWRenderer.cpp:172-191, SWMapRenderer.cpp:107-203) ----
  * solid: uint64[512][512] indexed [x][y], bit z set = solid (GameMap.h:160)

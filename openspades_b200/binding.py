@@ -33,6 +33,10 @@ class Opts(ctypes.Structure):
     ]
 
 
+class KernelTime(ctypes.Structure):
+    _fields_ = [("name", ctypes.c_char_p), ("launches", ctypes.c_uint64), ("total_ms", ctypes.c_double)]
+
+
 # numpy dtypes matching the C structs
 SCENE_DTYPE = np.dtype([("origin", "<f4", 3), ("axis", "<f4", (3, 3)), ("fovX", "<f4"), ("fovY", "<f4"),
                         ("zNear", "<f4"), ("zFar", "<f4")])
@@ -62,6 +66,8 @@ def load_library():
     lib.osb200_stream.restype = vp
     lib.osb200_launch_count.argtypes = [vp]
     lib.osb200_launch_count.restype = ctypes.c_uint64
+    lib.osb200_timing_enable.argtypes = [vp, ci]
+    lib.osb200_timing_read.argtypes = [vp, ctypes.POINTER(KernelTime), ci]
     lib.osb200_map_upload.argtypes = [vp, vp, vp]
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
     lib.osb200_map_flush.argtypes = [vp, vp, vp]
@@ -145,6 +151,15 @@ class Context:
 
     def sync(self):
         self._check(self._lib.osb200_sync(self._h))
+
+    def timing_enable(self, on=True):
+        self._check(self._lib.osb200_timing_enable(self._h, int(bool(on))))
+
+    def timing_read(self):
+        """{kernel name: (launches, total_ms)} since the last read (CUDA events on the context stream)."""
+        arr = (KernelTime * 16)()
+        n = self._check(self._lib.osb200_timing_read(self._h, arr, 16))
+        return {arr[i].name.decode(): (int(arr[i].launches), float(arr[i].total_ms)) for i in range(n)}
 
     # ---- map ----
     def map_upload(self, solid, color):

@@ -21,11 +21,43 @@ namespace osb {
 		va_end(ap);
 		g_err = buf;
 	}
+	const char *kernel_name(int id) {
+		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_build_lines",
+		                                     "k_gather_fog", "k_castray2", "k_shadow_bitmap", "k_radiosity"};
+		return id >= 0 && id < K_COUNT ? names[id] : "?";
+	}
+	KLaunch::KLaunch(osb200_ctx *ctx, int kid) : c(ctx), slot(-1) {
+		c->launches++;
+		if (!c->timing)
+			return;
+		osb200_ctx::TimedLaunch t{kid, c->take_event(), c->take_event()};
+		if (!t.a || !t.b)
+			return;
+		cudaEventRecord(t.a, c->stream);
+		c->timed.push_back(t);
+		slot = (int)c->timed.size() - 1;
+	}
+	KLaunch::~KLaunch() {
+		if (slot >= 0)
+			cudaEventRecord(c->timed[slot].b, c->stream);
+	}
 	void terrain_destroy(osb200_ctx *ctx);   // terrain.cu
 	void radiosity_destroy(osb200_ctx *ctx); // radiosity.cu
 	void radiosity_map_replaced(osb200_ctx *ctx);
 	void radiosity_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
 } // namespace osb
+
+cudaEvent_t osb200_ctx::take_event() {
+	if (!eventPool.empty()) {
+		cudaEvent_t e = eventPool.back();
+		eventPool.pop_back();
+		return e;
+	}
+	cudaEvent_t e = nullptr;
+	if (cudaEventCreate(&e) != cudaSuccess)
+		return nullptr;
+	return e;
+}
 
 int osb200_ctx::ensure_scratch(size_t bytes) {
 	if (bytes <= d_scratch_bytes)
@@ -211,6 +243,12 @@ void osb200_destroy(osb200_ctx *c) {
 	cudaFree(c->d_stage);
 	if (c->h_stage)
 		cudaFreeHost(c->h_stage);
+	for (auto &t : c->timed) {
+		cudaEventDestroy(t.a);
+		cudaEventDestroy(t.b);
+	}
+	for (auto e : c->eventPool)
+		cudaEventDestroy(e);
 	if (c->stream)
 		cudaStreamDestroy(c->stream);
 	delete c;
@@ -221,6 +259,42 @@ int osb200_sync(osb200_ctx *c) {
 		return -1;
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	return 0;
+}
+
+int osb200_timing_enable(osb200_ctx *c, int on) {
+	if (!c)
+		return -1;
+	c->timing = on != 0;
+	return 0;
+}
+
+int osb200_timing_read(osb200_ctx *c, osb200_kernel_time *out, int cap) {
+	if (!c || (!out && cap > 0)) {
+		osb::set_error("osb200_timing_read: null argument");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	osb200_kernel_time acc[osb::K_COUNT];
+	for (int k = 0; k < osb::K_COUNT; k++) {
+		acc[k].name = osb::kernel_name(k);
+		acc[k].launches = 0;
+		acc[k].total_ms = 0.0;
+	}
+	for (auto &t : c->timed) {
+		float ms = 0.f;
+		if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) {
+			acc[t.kid].launches++;
+			acc[t.kid].total_ms += ms;
+		}
+		c->eventPool.push_back(t.a);
+		c->eventPool.push_back(t.b);
+	}
+	c->timed.clear();
+	int n = 0;
+	for (int k = 0; k < osb::K_COUNT && n < cap; k++)
+		out[n++] = acc[k];
+	return n;
 }
 
 void *osb200_stream(osb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
@@ -240,8 +314,10 @@ int osb200_map_upload(osb200_ctx *c, const uint64_t *solid, const uint32_t *colo
 	auto *dC = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(c->d_scratch) + sb);
 	OSB_CUDA(cudaMemcpyAsync(dS, solid, sb, cudaMemcpyHostToDevice, c->stream));
 	OSB_CUDA(cudaMemcpyAsync(dC, color, cb, cudaMemcpyHostToDevice, c->stream));
-	k_map_repack<<<(unsigned)(ncol / 16), 256, 0, c->stream>>>(dS, dC, c->d_solid, c->d_color);
-	c->launches++;
+	{
+		osb::KLaunch kl(c, osb::K_MAP_REPACK);
+		k_map_repack<<<(unsigned)(ncol / 16), 256, 0, c->stream>>>(dS, dC, c->d_solid, c->d_color);
+	}
 	OSB_CUDA(cudaGetLastError());
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
@@ -301,9 +377,11 @@ int osb200_map_flush(osb200_ctx *c, const uint64_t *solid, const uint32_t *color
 	c->anyDirty = false;
 	OSB_CUDA(cudaMemcpyAsync(c->d_stage, recs, (size_t)n * sizeof(DirtyColumn), cudaMemcpyHostToDevice,
 	                         c->stream));
-	k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n,
-	                                                    c->d_solid, c->d_color);
-	c->launches++;
+	{
+		osb::KLaunch kl(c, osb::K_MAP_SCATTER);
+		k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n,
+		                                                    c->d_solid, c->d_color);
+	}
 	OSB_CUDA(cudaGetLastError());
 	return n;
 }

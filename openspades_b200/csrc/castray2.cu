@@ -159,9 +159,11 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	static_assert(sizeof(osb200_rayhit) == 40, "RayCastResult layout");
 	OSB_CUDA(cudaSetDevice(c->device));
 	size_t blocks = (n + kThreads - 1) / kThreads;
-	k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(c->d_solid, d_v0, d_dir, maxSteps,
-	                                                       reinterpret_cast<uint32_t *>(d_out), n);
-	c->launches++;
+	{
+		osb::KLaunch kl(c, osb::K_CASTRAY2);
+		k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(c->d_solid, d_v0, d_dir, maxSteps,
+		                                                       reinterpret_cast<uint32_t *>(d_out), n);
+	}
 	OSB_CUDA(cudaGetLastError());
 	return 0;
 }

@@ -30,9 +30,34 @@ namespace osb {
 		       (uint32_t)(y & 3);
 	}
 
-	struct Ctx;
+	// kernel classes reported by osb200_timing_read (index = osb200_kernel_time slot)
+	enum KernelId {
+		K_MAP_REPACK = 0,
+		K_MAP_SCATTER,
+		K_VIEW_PREP,
+		K_BUILD_LINES,
+		K_GATHER_FOG,
+		K_CASTRAY2,
+		K_SHADOW_BITMAP,
+		K_RADIOSITY,
+		K_COUNT
+	};
+	const char *kernel_name(int id);
+
 	struct TerrainState;   // terrain.cu
 	struct RadiosityState; // radiosity.cu
+} // namespace osb
+
+struct osb200_ctx;
+namespace osb {
+	// RAII bracket around one kernel launch: counts it and, when timing is on, records CUDA events
+	// on the context stream before and after it.
+	struct KLaunch {
+		osb200_ctx *c;
+		int slot;
+		KLaunch(osb200_ctx *c, int kid);
+		~KLaunch();
+	};
 } // namespace osb
 
 struct osb200_ctx {
@@ -41,6 +66,16 @@ struct osb200_ctx {
 	cudaStream_t stream = nullptr;
 	uint64_t launches = 0;
 	int smCount = 148;
+
+	// ---- per-kernel CUDA-event timing (osb200_timing_enable / osb200_timing_read) ----
+	struct TimedLaunch {
+		int kid;
+		cudaEvent_t a, b;
+	};
+	bool timing = false;
+	std::vector<TimedLaunch> timed;      // recorded, not yet read
+	std::vector<cudaEvent_t> eventPool;  // recycled events
+	cudaEvent_t take_event();
 
 	// ---- resident map ----
 	bool mapLoaded = false;

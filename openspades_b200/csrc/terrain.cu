@@ -937,22 +937,24 @@ namespace osb {
 				OSB_CUDA(cudaMemcpyAsync(T->d_tabs, T->h_tabs, sizeof(float) * tabF * nv, cudaMemcpyHostToDevice,
 				                         c->stream));
 			} else {
+				KLaunch kl(c, K_VIEW_PREP);
 				k_view_prep<<<(nv + 3) / 4, 128, 0, c->stream>>>(dV, nv, g, T->d_lineDirs, T->d_tabs);
-				c->launches++;
 			}
 			const unsigned lineBlocks = (totalLines + kLineThreads - 1) / kLineThreads;
 			const size_t smem = (size_t)lineRes * 8;
 #define LAUNCH_LINES(SSE, SH)                                                                      \
 	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, c->stream>>>(                          \
 	  dV, nv, T->d_lineDirs, c->d_solid, c->d_color, sse, T->d_strips, T->d_lineParams, totalLines, lineRes)
-			if (num == OSB200_NUM_IEEE)
-				LAUNCH_LINES(false, false);
-			else if (num == OSB200_NUM_SSE)
-				LAUNCH_LINES(true, false);
-			else
-				LAUNCH_LINES(true, true);
+			{
+				KLaunch kl(c, K_BUILD_LINES);
+				if (num == OSB200_NUM_IEEE)
+					LAUNCH_LINES(false, false);
+				else if (num == OSB200_NUM_SSE)
+					LAUNCH_LINES(true, false);
+				else
+					LAUNCH_LINES(true, true);
+			}
 #undef LAUNCH_LINES
-			c->launches++;
 			const int segs = ((h >> 3) + kSegRows - 1) / kSegRows;
 			const size_t tasks = (size_t)nv * (w >> 3) * segs;
 			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
@@ -961,14 +963,16 @@ namespace osb {
 #define LAUNCH_GATHER(SSE, FOG)                                                                    \
 	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, c->stream>>>(                           \
 	  dV, nv, g, T->d_tabs, c->d_solid, T->d_atan, sse, T->d_strips, T->d_lineParams, lineRes, fbC, dbC)
-			if (num == OSB200_NUM_IEEE)
-				LAUNCH_GATHER(false, false);
-			else if (num == OSB200_NUM_SSE)
-				LAUNCH_GATHER(true, false);
-			else
-				LAUNCH_GATHER(true, true);
+			{
+				KLaunch kl(c, K_GATHER_FOG);
+				if (num == OSB200_NUM_IEEE)
+					LAUNCH_GATHER(false, false);
+				else if (num == OSB200_NUM_SSE)
+					LAUNCH_GATHER(true, false);
+				else
+					LAUNCH_GATHER(true, true);
+			}
 #undef LAUNCH_GATHER
-			c->launches++;
 			if (hostPrep && ci + 2 < chunkStart.size()) // staging reused by the next chunk
 				OSB_CUDA(cudaStreamSynchronize(c->stream));
 		}
