@@ -61,6 +61,16 @@ int orc_last_lines(int *lineRes, const uint32_t **combined, const float **depth)
 
 /* Draw/GLMapShadowRenderer.cpp:177-218 GeneratePixel over the whole map: out uint32[y*512+x] */
 void orc_shadow_bitmap(const uint64_t *solid, const uint32_t *color, uint32_t *out);
+uint32_t orc_shadow_pixel(const uint64_t *solid, const uint32_t *color, int x, int y);
+/* Draw/GLMapShadowRenderer.cpp:220-229 GameMapChanged/MarkUpdate on a 512*16-word dirty bitset */
+void orc_shadow_mark(uint32_t *words, int x, int y, int z);
+/* Draw/GLMapShadowRenderer.cpp:78-108 Update: regenerate marked words, invalidate radiosity chunk boxes
+ * (radState: 4096 x {dirty,minX,minY,minZ,maxX,maxY,maxZ}, index (cx + cy*32)*4 + cz; may be NULL).
+ * Returns the number of pixels that changed. */
+int orc_shadow_update(const uint64_t *solid, const uint32_t *color, uint32_t *bitmap, uint32_t *words,
+                      int32_t *radState);
+/* Draw/GLRadiosityRenderer.cpp:277-336 GameMapChanged + Invalidate */
+void orc_radiosity_invalidate(int32_t *radState, int x, int y, int z);
 /* Draw/GLRadiosityRenderer.cpp:162-275 Evaluate: 12 floats (base,x,y,z as rgb each) */
 void orc_radiosity_evaluate(const uint32_t *bitmap, int x, int y, int z, float out[12]);
 /* Draw/GLRadiosityRenderer.cpp:456-515 EncodeValue (mode = r_radiosity) */

@@ -62,6 +62,22 @@ OREF_API int oref_renderer_rle(void *r, int x, int y, int8_t *out, int cap);
 OREF_API int oref_renderer_lines(void *r, int *lineRes);
 OREF_API int oref_renderer_line(void *r, int i, uint32_t *combined, float *depth, float *misc /*horizX,horizY,pitchTanMin,pitchScale*/, int32_t *misci);
 
+/* ---- CPU halves of GLMapShadowRenderer / GLRadiosityRenderer (oref_gl.cpp) ---- */
+OREF_API void *oref_rad_create(void *map, int mode /* r_radiosity: 1 sqrt-compressed, 2 linear */);
+OREF_API void oref_rad_free(void *h);
+OREF_API void oref_rad_map_changed(void *h, int x, int y, int z);  /* GLMapShadowRenderer::GameMapChanged */
+OREF_API void oref_rad_shadow_update(void *h);                     /* GLMapShadowRenderer::Update */
+OREF_API void oref_rad_shadow_bitmap(void *h, uint32_t *out /*[y*512+x]*/);
+OREF_API uint32_t oref_rad_generate_pixel(void *h, int x, int y);   /* GLMapShadowRenderer::GeneratePixel */
+OREF_API void oref_rad_evaluate(void *h, int x, int y, int z, float out[12]); /* GLRadiosityRenderer::Evaluate */
+OREF_API void oref_rad_evaluate_box(void *h, int x0, int y0, int z0, int x1, int y1, int z1, float *out, int threads);
+OREF_API uint32_t oref_rad_encode(void *h, const float v[3]);      /* GLRadiosityRenderer::EncodeValue */
+OREF_API void oref_rad_chunk_info(void *h, int cx, int cy, int cz, int out[7]);
+OREF_API int oref_rad_num_dirty(void *h);
+OREF_API void oref_rad_update_chunk(void *h, int cx, int cy, int cz); /* GLRadiosityRenderer::UpdateChunk */
+OREF_API int oref_rad_update_all(void *h, int threads);
+OREF_API void oref_rad_read_chunk(void *h, int cx, int cy, int cz, uint32_t *flat, uint32_t *x, uint32_t *y, uint32_t *z);
+
 #ifdef __cplusplus
 }
 #endif

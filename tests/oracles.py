@@ -49,6 +49,19 @@ class Port:
         L.orc_build_rle.argtypes = [vp, ci, ci, vp]
         L.orc_render.argtypes = [vp, vp, vp, ci, ci, vp, ctypes.c_float, ci, ci, ci, vp, vp]
         L.orc_last_lines.argtypes = [ctypes.POINTER(ci), ctypes.POINTER(vp), ctypes.POINTER(vp)]
+        L.orc_shadow_bitmap.argtypes = [vp, vp, vp]
+        L.orc_shadow_bitmap.restype = None
+        L.orc_shadow_mark.argtypes = [vp, ci, ci, ci]
+        L.orc_shadow_mark.restype = None
+        L.orc_shadow_update.argtypes = [vp, vp, vp, vp, vp]
+        L.orc_radiosity_invalidate.argtypes = [vp, ci, ci, ci]
+        L.orc_radiosity_invalidate.restype = None
+        L.orc_radiosity_evaluate.argtypes = [vp, ci, ci, ci, vp]
+        L.orc_radiosity_evaluate.restype = None
+        L.orc_radiosity_encode.argtypes = [vp, ci]
+        L.orc_radiosity_encode.restype = ctypes.c_uint32
+        L.orc_radiosity_box.argtypes = [vp] + [ci] * 7 + [vp, vp, ci]
+        L.orc_radiosity_box.restype = None
 
     def vxl_load(self, data: bytes):
         solid = np.zeros((512, 512), np.uint64)
@@ -90,6 +103,38 @@ class Port:
         out = np.zeros(400, np.int8)
         n = self.L.orc_build_rle(solid.ctypes.data, x, y, out.ctypes.data)
         return out[:n].copy()
+
+    # ---- shadow bitmap + radiosity ----
+    def shadow_bitmap(self, solid, color):
+        out = np.zeros((512, 512), np.uint32)  # [y][x]
+        self.L.orc_shadow_bitmap(solid.ctypes.data, color.ctypes.data, out.ctypes.data)
+        return out
+
+    def shadow_mark(self, words, x, y, z):
+        self.L.orc_shadow_mark(words.ctypes.data, x, y, z)
+
+    def shadow_update(self, solid, color, bitmap, words, rad_state=None):
+        return self.L.orc_shadow_update(solid.ctypes.data, color.ctypes.data, bitmap.ctypes.data, words.ctypes.data,
+                                        None if rad_state is None else rad_state.ctypes.data)
+
+    def radiosity_evaluate(self, bitmap, x, y, z):
+        out = np.zeros(12, np.float32)
+        self.L.orc_radiosity_evaluate(bitmap.ctypes.data, x, y, z, out.ctypes.data)
+        return out
+
+    def radiosity_encode(self, v, mode):
+        v = np.ascontiguousarray(v, np.float32)
+        return int(self.L.orc_radiosity_encode(v.ctypes.data, mode))
+
+    def radiosity_box(self, bitmap, lo, hi, mode, threads=8, want_f32=True, want_enc=True):
+        """Box [lo, hi] inclusive; returns (f32[nz,ny,nx,12], enc[nz,ny,nx,4])."""
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        f32 = np.zeros((nz, ny, nx, 12), np.float32) if want_f32 else None
+        enc = np.zeros((nz, ny, nx, 4), np.uint32) if want_enc else None
+        self.L.orc_radiosity_box(bitmap.ctypes.data, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], mode,
+                                 None if f32 is None else f32.ctypes.data, None if enc is None else enc.ctypes.data,
+                                 threads)
+        return f32, enc
 
 
 class Ref:
@@ -152,6 +197,91 @@ class Ref:
         out = np.zeros(len(v0), RAYHIT_DTYPE)
         self.L.oref_castray2(m, v0.ctypes.data, dirs.ctypes.data, max_steps, out.ctypes.data, len(v0), threads)
         return out
+
+
+class RefRadiosity:
+    """GLMapShadowRenderer + GLRadiosityRenderer CPU halves of the reference (oracle/ref_harness/oref_gl.cpp)."""
+
+    def __init__(self, ref: Ref, m, mode=1):
+        L = self.L = ref.L
+        L.oref_rad_create.restype = vp
+        L.oref_rad_create.argtypes = [vp, ci]
+        L.oref_rad_free.argtypes = [vp]
+        L.oref_rad_map_changed.argtypes = [vp, ci, ci, ci]
+        L.oref_rad_shadow_update.argtypes = [vp]
+        L.oref_rad_shadow_bitmap.argtypes = [vp, vp]
+        L.oref_rad_generate_pixel.argtypes = [vp, ci, ci]
+        L.oref_rad_generate_pixel.restype = ctypes.c_uint32
+        L.oref_rad_evaluate.argtypes = [vp, ci, ci, ci, vp]
+        L.oref_rad_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp, ci]
+        L.oref_rad_encode.argtypes = [vp, vp]
+        L.oref_rad_encode.restype = ctypes.c_uint32
+        L.oref_rad_chunk_info.argtypes = [vp, ci, ci, ci, vp]
+        L.oref_rad_num_dirty.argtypes = [vp]
+        L.oref_rad_update_chunk.argtypes = [vp, ci, ci, ci]
+        L.oref_rad_update_all.argtypes = [vp, ci]
+        L.oref_rad_read_chunk.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp]
+        self.h = L.oref_rad_create(m, mode)
+
+    def close(self):
+        if self.h:
+            self.L.oref_rad_free(self.h)
+            self.h = None
+
+    def map_changed(self, x, y, z):
+        self.L.oref_rad_map_changed(self.h, x, y, z)
+
+    def shadow_update(self):
+        self.L.oref_rad_shadow_update(self.h)
+
+    def shadow_bitmap(self):
+        out = np.zeros((512, 512), np.uint32)
+        self.L.oref_rad_shadow_bitmap(self.h, out.ctypes.data)
+        return out
+
+    def evaluate(self, x, y, z):
+        out = np.zeros(12, np.float32)
+        self.L.oref_rad_evaluate(self.h, x, y, z, out.ctypes.data)
+        return out
+
+    def evaluate_box(self, lo, hi, threads=8):
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        out = np.zeros((nz, ny, nx, 12), np.float32)
+        self.L.oref_rad_evaluate_box(self.h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], out.ctypes.data, threads)
+        return out
+
+    def encode(self, v):
+        v = np.ascontiguousarray(v, np.float32)
+        return int(self.L.oref_rad_encode(self.h, v.ctypes.data))
+
+    def chunk_info(self, cx, cy, cz):
+        out = np.zeros(7, np.int32)
+        self.L.oref_rad_chunk_info(self.h, cx, cy, cz, out.ctypes.data)
+        return out
+
+    def chunk_state(self):
+        """All 4096 chunks x 7 ints in the oracle port's order (cx + cy*32)*4 + cz."""
+        out = np.zeros((4096, 7), np.int32)
+        for cx in range(32):
+            for cy in range(32):
+                for cz in range(4):
+                    out[(cx + cy * 32) * 4 + cz] = self.chunk_info(cx, cy, cz)
+        return out
+
+    def num_dirty(self):
+        return self.L.oref_rad_num_dirty(self.h)
+
+    def update_chunk(self, cx, cy, cz):
+        self.L.oref_rad_update_chunk(self.h, cx, cy, cz)
+
+    def update_all(self, threads=8):
+        return self.L.oref_rad_update_all(self.h, threads)
+
+    def read_chunk(self, cx, cy, cz):
+        """(16,16,16,4) uint32 [z][y][x][flat,x,y,z]"""
+        a = [np.zeros((16, 16, 16), np.uint32) for _ in range(4)]
+        self.L.oref_rad_read_chunk(self.h, cx, cy, cz, *[v.ctypes.data for v in a])
+        return np.stack(a, axis=-1)
 
 
 class RefRenderer:
