@@ -136,6 +136,41 @@ OSB200_API int osb200_render(osb200_ctx *ctx, const osb200_scene *scenes, int nV
 OSB200_API int osb200_render_device(osb200_ctx *ctx, const osb200_scene *scenes, int nViews, int w, int h,
                                     const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth);
 
+/* ---- sun-shadow bitmap + radiosity: the CPU halves of GLMapShadowRenderer / GLRadiosityRenderer ----
+ * State is created lazily by the first call below and starts like freshly constructed reference objects:
+ * every shadow pixel and every 16^3 chunk dirty, volumes filled with 0x20080200 (GLRadiosityRenderer.cpp:79-88).
+ * Edits reach it through osb200_map_mark_dirty (= GLMapShadowRenderer::GameMapChanged, GLMapShadowRenderer.cpp:220-229)
+ * followed by osb200_map_flush; each call here first runs GLMapShadowRenderer::Update (:78-108) for the pending marks,
+ * which regenerates the marked 32-pixel words and invalidates the radiosity chunks around every changed pixel
+ * (GLRadiosityRenderer::GameMapChanged/Invalidate, GLRadiosityRenderer.cpp:277-336).  Calling with unflushed
+ * edits is an error (-1). */
+
+/* replaces GLMapShadowRenderer::Update + read of its `bitmap` (GLMapShadowRenderer.cpp:78-218):
+ * out = uint32[512*512] indexed [y*512 + x]: depth<<24 | B6<<16 | G6<<8 | side<<7 | R6.  out may be NULL. */
+OSB200_API int osb200_shadow_bitmap(osb200_ctx *ctx, uint32_t *out);
+/* replaces GLRadiosityRenderer::Update/UpdateDirtyChunks/UpdateChunk (GLRadiosityRenderer.cpp:348-450,517-543):
+ * evaluates up to maxChunks dirty chunks (< 0: all of them) and stores Evaluate + EncodeValue x4 for every voxel
+ * of their dirty boxes.  eye (nullable, 3 floats = SceneDefinition::viewOrigin) gives the reference's priority:
+ * dirty chunks within 6 chunks of the eye first, any dirty chunk only when there is none (:398-430); among the
+ * candidates the reference picks 8 at random, this picks the first maxChunks in chunk-index order.
+ * Returns the number of chunks updated (>= 0) or < 0. */
+OSB200_API int osb200_radiosity_update(osb200_ctx *ctx, int maxChunks, const float *eye);
+/* chunk (cx 0..31, cy 0..31, cz 0..3): out = {dirty, minX, minY, minZ, maxX, maxY, maxZ} (GLRadiosityRenderer.h:52-59;
+ * the box is meaningful only when dirty) */
+OSB200_API int osb200_radiosity_chunk_info(osb200_ctx *ctx, int cx, int cy, int cz, int out[7]);
+/* Chunk::dataFlat/dataX/dataY/dataZ (GLRadiosityRenderer.h:46-51): 4096 RGB10A2 words each, [z][y][x]; any may be NULL */
+OSB200_API int osb200_radiosity_read_chunk(osb200_ctx *ctx, int cx, int cy, int cz, uint32_t *flat, uint32_t *x,
+                                           uint32_t *y, uint32_t *z);
+/* GLRadiosityRenderer::Evaluate (GLRadiosityRenderer.cpp:162-275) un-encoded over the inclusive voxel box:
+ * 12 floats per voxel (base.rgb, x.rgb, y.rgb, z.rgb), box-ordered [z][y][x].  Coordinates may run past the
+ * map edge in x / y (the bitmap wraps).  Independent of the chunk state -- parity hook. */
+OSB200_API int osb200_radiosity_evaluate_box(osb200_ctx *ctx, int x0, int y0, int z0, int x1, int y1, int z1,
+                                             float *out);
+/* device pointers of the four resident 512x512x64 RGB10A2 volumes ([z][y][x], the layout of the reference's
+ * 3-D textures, GLRadiosityRenderer.cpp:120-129) and of the 512x512 shadow bitmap; any may be NULL */
+OSB200_API int osb200_radiosity_volumes(osb200_ctx *ctx, const uint32_t **flat, const uint32_t **x,
+                                        const uint32_t **y, const uint32_t **z, const uint32_t **shadow);
+
 #ifdef __cplusplus
 }
 #endif

@@ -77,6 +77,12 @@ def load_library():
     fp = ctypes.c_float
     lib.osb200_render.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
     lib.osb200_render_device.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
+    lib.osb200_shadow_bitmap.argtypes = [vp, vp]
+    lib.osb200_radiosity_update.argtypes = [vp, ci, vp]
+    lib.osb200_radiosity_chunk_info.argtypes = [vp, ci, ci, ci, vp]
+    lib.osb200_radiosity_read_chunk.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp]
+    lib.osb200_radiosity_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
+    lib.osb200_radiosity_volumes.argtypes = [vp] + [ctypes.POINTER(vp)] * 5
     _lib = lib
     return lib
 
@@ -218,3 +224,37 @@ class Context:
         fc = np.asarray(fog_color, np.float32)
         self._check(self._lib.osb200_render_device(self._h, scenes.ctypes.data, len(scenes), w, h, fc.ctypes.data,
                                                    float(fog_dist), _ptr(d_bgrx), _ptr(d_depth)))
+
+    # ---- shadow bitmap + radiosity ----
+    def shadow_bitmap(self):
+        out = np.zeros((512, 512), np.uint32)  # [y][x]
+        self._check(self._lib.osb200_shadow_bitmap(self._h, out.ctypes.data))
+        return out
+
+    def radiosity_update(self, max_chunks=-1, eye=None):
+        e = None if eye is None else np.ascontiguousarray(eye, np.float32)
+        return self._check(self._lib.osb200_radiosity_update(self._h, int(max_chunks), None if e is None else e.ctypes.data))
+
+    def radiosity_chunk_info(self, cx, cy, cz):
+        out = np.zeros(7, np.int32)
+        self._check(self._lib.osb200_radiosity_chunk_info(self._h, cx, cy, cz, out.ctypes.data))
+        return out
+
+    def radiosity_read_chunk(self, cx, cy, cz):
+        """(16,16,16,4) uint32, [z][y][x][flat,x,y,z]"""
+        a = [np.zeros((16, 16, 16), np.uint32) for _ in range(4)]
+        self._check(self._lib.osb200_radiosity_read_chunk(self._h, cx, cy, cz, *[v.ctypes.data for v in a]))
+        return np.stack(a, axis=-1)
+
+    def radiosity_evaluate_box(self, lo, hi):
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        out = np.zeros((nz, ny, nx, 12), np.float32)
+        self._check(self._lib.osb200_radiosity_evaluate_box(self._h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                                                            out.ctypes.data))
+        return out
+
+    def radiosity_volumes(self):
+        """Device pointers (ints): flat, x, y, z volumes ([z][y][x] uint32) and the shadow bitmap."""
+        p = [ctypes.c_void_p() for _ in range(5)]
+        self._check(self._lib.osb200_radiosity_volumes(self._h, *[ctypes.byref(v) for v in p]))
+        return [v.value for v in p]

@@ -23,7 +23,8 @@ namespace osb {
 	}
 	const char *kernel_name(int id) {
 		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_build_lines",
-		                                     "k_gather_fog", "k_castray2", "k_shadow_bitmap", "k_radiosity"};
+		                                     "k_gather_fog", "k_castray2", "k_shadow_update", "k_radiosity",
+		                                     "k_rad_select"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
 	KLaunch::KLaunch(osb200_ctx *ctx, int kid) : c(ctx), slot(-1) {

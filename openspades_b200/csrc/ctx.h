@@ -40,6 +40,7 @@ namespace osb {
 		K_CASTRAY2,
 		K_SHADOW_BITMAP,
 		K_RADIOSITY,
+		K_RAD_SELECT,
 		K_COUNT
 	};
 	const char *kernel_name(int id);
