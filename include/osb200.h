@@ -104,6 +104,8 @@ OSB200_API int osb200_timing_read(osb200_ctx *ctx, osb200_kernel_time *out, int 
  * solid: uint64[512][512] indexed [x][y], bit z set = solid (GameMap.h:160)
  * color: uint32[512][512][64] indexed [x][y][z], 0xHHBBGGRR (GameMap.h:161)            */
 OSB200_API int osb200_map_upload(osb200_ctx *ctx, const uint64_t *solid, const uint32_t *color);
+/* SWRenderer::SetGameMap(null) (SWRenderer.cpp:172-181): no map resident any more; buffers are kept */
+OSB200_API int osb200_map_clear(osb200_ctx *ctx);
 /* replaces SWRenderer::GameMapChanged -> SWFlatMapRenderer::SetNeedsUpdate (SWRenderer.cpp:1148-1154,
  * SWFlatMapRenderer.cpp:107-111): O(1), host-only. */
 OSB200_API int osb200_map_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
@@ -129,12 +131,17 @@ OSB200_API int osb200_castray2_device(osb200_ctx *ctx, const float *d_v0, const 
  * depth: nViews*w*h float view-space Z (== SWRenderer::depthBuffer).  The depth buffer is read-modify:
  * like the reference it is not cleared, and a view whose eye is inside a solid voxel keeps its previous
  * depth and gets the clear colour 0x7f7f7f before fog (SWMapRenderer.cpp:1181-1184).
+ * Without a map (SetGameMap(null)) every view takes that same path: clear colour fogged over the stale depth,
+ * exactly what SWRenderer::EndScene does when mapRenderer is null (SWRenderer.cpp:713-744).
  * osb200_render keeps context-owned device buffers (persistent depth) and copies to the nullable host
  * pointers, then synchronises; osb200_render_device writes caller-owned device buffers and only enqueues. */
 OSB200_API int osb200_render(osb200_ctx *ctx, const osb200_scene *scenes, int nViews, int w, int h,
                              const float fogColor[3], float fogDist, uint32_t *host_bgrx, float *host_depth);
 OSB200_API int osb200_render_device(osb200_ctx *ctx, const osb200_scene *scenes, int nViews, int w, int h,
                                     const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth);
+
+/* SWRenderer::depthBuffer of the frames last rendered by osb200_render (context-owned, persistent): the first n floats */
+OSB200_API int osb200_read_depth(osb200_ctx *ctx, float *out, size_t n);
 
 /* ---- sun-shadow bitmap + radiosity: the CPU halves of GLMapShadowRenderer / GLRadiosityRenderer ----
  * State is created lazily by the first call below and starts like freshly constructed reference objects:

@@ -69,6 +69,7 @@ def load_library():
     lib.osb200_timing_enable.argtypes = [vp, ci]
     lib.osb200_timing_read.argtypes = [vp, ctypes.POINTER(KernelTime), ci]
     lib.osb200_map_upload.argtypes = [vp, vp, vp]
+    lib.osb200_map_clear.argtypes = [vp]
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
     lib.osb200_map_flush.argtypes = [vp, vp, vp]
     lib.osb200_map_read_solid.argtypes = [vp, vp]
@@ -77,6 +78,7 @@ def load_library():
     fp = ctypes.c_float
     lib.osb200_render.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
     lib.osb200_render_device.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
+    lib.osb200_read_depth.argtypes = [vp, vp, sz]
     lib.osb200_shadow_bitmap.argtypes = [vp, vp]
     lib.osb200_radiosity_update.argtypes = [vp, ci, vp]
     lib.osb200_radiosity_chunk_info.argtypes = [vp, ci, ci, ci, vp]
@@ -173,6 +175,9 @@ class Context:
         color = np.ascontiguousarray(color, np.uint32)
         assert solid.shape == (512, 512) and color.shape == (512, 512, 64)
         self._check(self._lib.osb200_map_upload(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def map_clear(self):
+        self._check(self._lib.osb200_map_clear(self._h))
 
     def map_mark_dirty(self, x, y, z):
         self._check(self._lib.osb200_map_mark_dirty(self._h, int(x), int(y), int(z)))

@@ -328,6 +328,15 @@ int osb200_map_upload(osb200_ctx *c, const uint64_t *solid, const uint32_t *colo
 	return 0;
 }
 
+int osb200_map_clear(osb200_ctx *c) {
+	if (!c)
+		return -1;
+	c->mapLoaded = false;
+	std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
+	c->anyDirty = false;
+	return 0;
+}
+
 int osb200_map_mark_dirty(osb200_ctx *c, int x, int y, int z) {
 	if (!c || x < 0 || x >= OSB200_MAP_W || y < 0 || y >= OSB200_MAP_H) {
 		osb::set_error("osb200_map_mark_dirty: bad argument");

@@ -52,6 +52,7 @@ namespace osb {
 
 	struct FrameGeom {
 		int fw, fh, under, swThreads, sse2Fog, sse2Shade;
+		int noMap; // no map set: SWRenderer::EndScene still clears and fogs over the stale depth (SWRenderer.cpp:713-744)
 		uint32_t fogB, fogG, fogR;
 	};
 
@@ -512,7 +513,7 @@ namespace osb {
 		{
 			const int ex = osbn::x86_f2i(floorf(V.origin[0])), ey = osbn::x86_f2i(floorf(V.origin[1])),
 			          ez = osbn::x86_f2i(floorf(V.origin[2]));
-			skip = ez >= 64 || (ez >= 0 && ((solid[tiled_index(ex & 511, ey & 511)] >> ez) & 1ull));
+			skip = g.noMap || ez >= 64 || (ez >= 0 && ((solid[tiled_index(ex & 511, ey & 511)] >> ez) & 1ull));
 		}
 
 		// per-view deltas (:757-775)
@@ -825,8 +826,8 @@ namespace osb {
 
 	static int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
 	                       const float fogColor[3], float fogDist, uint32_t *d_fb, float *d_depth) {
-		if (!c || !c->mapLoaded) {
-			set_error("osb200_render: no context or no map uploaded");
+		if (!c) {
+			set_error("osb200_render: no context");
 			return -1;
 		}
 		if (nViews == 0)
@@ -854,6 +855,7 @@ namespace osb {
 		g.under = under;
 		g.swThreads = c->opts.sw_threads;
 		g.sse2Fog = g.sse2Shade = c->opts.numerics == OSB200_NUM_SSE2;
+		g.noMap = c->mapLoaded ? 0 : 1;
 		auto toFixed8 = [](float v) { // SWUtils.h:68-71
 			int i = static_cast<int>(v * 255.f + .5f);
 			return (uint32_t)std::max(std::min(i, 255), 0);
@@ -945,7 +947,7 @@ namespace osb {
 #define LAUNCH_LINES(SSE, SH)                                                                      \
 	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, c->stream>>>(                          \
 	  dV, nv, T->d_lineDirs, c->d_solid, c->d_color, sse, T->d_strips, T->d_lineParams, totalLines, lineRes)
-			{
+			if (!g.noMap) {
 				KLaunch kl(c, K_BUILD_LINES);
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_LINES(false, false);
@@ -991,8 +993,8 @@ int osb200_render_device(osb200_ctx *c, const osb200_scene *scenes, int nViews, 
 
 int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
                   float fogDist, uint32_t *host_bgrx, float *host_depth) {
-	if (!c || !c->mapLoaded) {
-		osb::set_error("osb200_render: no context or no map uploaded");
+	if (!c) {
+		osb::set_error("osb200_render: no context");
 		return -1;
 	}
 	if (nViews <= 0)
@@ -1006,7 +1008,7 @@ int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, 
 		return -2;
 	osb::TerrainState *T = c->terrain;
 	const size_t n = (size_t)nViews * w * h;
-	if (n > T->outCap) {
+	if (n != T->outCap) {
 		// the depth buffer persists between frames like SWRenderer::depthBuffer (never cleared, SWRenderer.cpp:83);
 		// a fresh one starts at zero like std::vector<float>::resize
 		cudaFree(T->d_fb);
@@ -1026,6 +1028,21 @@ int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, 
 		OSB_CUDA(cudaMemcpyAsync(host_bgrx, T->d_fb, n * 4, cudaMemcpyDeviceToHost, c->stream));
 	if (host_depth)
 		OSB_CUDA(cudaMemcpyAsync(host_depth, T->d_depth, n * 4, cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+int osb200_read_depth(osb200_ctx *c, float *out, size_t n) {
+	if (!c || !out) {
+		osb::set_error("osb200_read_depth: null argument");
+		return -1;
+	}
+	if (!c->terrain || n > c->terrain->outCap) {
+		osb::set_error("osb200_read_depth: no frame of that size has been rendered by osb200_render");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	OSB_CUDA(cudaMemcpyAsync(out, c->terrain->d_depth, n * 4, cudaMemcpyDeviceToHost, c->stream));
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	return 0;
 }

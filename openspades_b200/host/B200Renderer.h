@@ -1,0 +1,162 @@
+// Host-side renderer with draw::SWRenderer's public surface for the voxel hot path
+// (Sources/Draw/SWRenderer.h:48-219 implementing client::IRenderer, Sources/Client/IRenderer.h:98-174, and
+// client::IGameMapListener, Sources/Client/IGameMapListener.h:26-29).  Same method names, argument meaning,
+// call-order rules and error messages; every piece of per-pixel / per-voxel work goes through the osb200 C ABI
+// (include/osb200.h) to the CUDA kernels.  There is no CPU rendering path in this class.
+//
+// What is mirrored:  Init / Shutdown, SetGameMap (+ listener registration), SetFogDistance / SetFogColor,
+//   StartScene / EndScene (terrain pass + fog of EndScene, SWRenderer.cpp:709-745), FrameDone, Flip, ReadBitmap,
+//   ScreenWidth / ScreenHeight, GameMapChanged -> dirty-column bitset -> re-upload at the next EndScene
+//   (SWFlatMapRenderer::SetNeedsUpdate / Update, SWFlatMapRenderer.cpp:52-111).
+// What is accepted and NOT drawn (out of scope): RenderModel, AddLight, AddSprite,
+//   AddLongSprite, AddDebugLine and the 2-D DrawImage family; they only enforce the same call-order rules.
+// Extension beyond SWRenderer (the CPU halves of GLRenderer's map shadow + radiosity):
+//   UpdateRadiosity().
+//
+// The reference's own types (Vector3, Handle<T>, Bitmap, SWPort) are not linkable here, so this header names
+// small layout-compatible stand-ins; INTEGRATION.md shows the 1:1 adapter a maintainer adds inside Sources/Draw.
+#pragma once
+#include <cstdint>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <vector>
+
+#include "../../include/osb200.h"
+#include "VoxelMap.h"
+
+namespace osb200 {
+
+	struct Vector3 {
+		float x, y, z;
+	};
+
+	// client::SceneDefinition (Sources/Client/SceneDefinition.h:26-46); only the geometric fields reach the kernels
+	struct SceneDefinition {
+		int viewportLeft = 0, viewportTop = 0, viewportWidth = 0, viewportHeight = 0;
+		float fovX = 0.f, fovY = 0.f;
+		Vector3 viewOrigin{0, 0, 0};
+		Vector3 viewAxis[3]{{1, 0, 0}, {0, 1, 0}, {0, 0, 1}}; // right, up, front
+		float zNear = 0.1f, zFar = 200.f;
+		bool skipWorld = false;
+		float depthOfFieldFocalLength = 0.f, depthOfFieldNearBlurStrength = 0.f, depthOfFieldFarBlurStrength = 0.f;
+		unsigned int time = 0;
+		bool denyCameraBlur = false;
+		float blurVignette = 0.f, globalBlur = 0.f, saturation = 1.f, radialBlur = 0.f;
+	};
+
+	// spades::Bitmap as the SW port hands it out: BGRX words, top-down rows
+	class Framebuffer {
+	public:
+		Framebuffer(int w, int h) : w_(w), h_(h), px_((size_t)w * h, 0u) {}
+		int GetWidth() const { return w_; }
+		int GetHeight() const { return h_; }
+		uint32_t *GetPixels() { return px_.data(); }
+		const uint32_t *GetPixels() const { return px_.data(); }
+
+	private:
+		int w_, h_;
+		std::vector<uint32_t> px_;
+	};
+
+	// draw::SWPort (Sources/Draw/SWPort.h:28-43): the head-less framebuffer provider
+	class FramebufferPort {
+	public:
+		virtual ~FramebufferPort() {}
+		virtual Framebuffer &GetFramebuffer() = 0;
+		virtual void Swap() = 0;
+	};
+
+	// in-memory port (the pattern of Client/HitTestDebugger.cpp:38-50)
+	class MemoryPort : public FramebufferPort {
+	public:
+		MemoryPort(int w, int h) : fb_(w, h) {}
+		Framebuffer &GetFramebuffer() override { return fb_; }
+		void Swap() override { swaps_++; }
+		int SwapCount() const { return swaps_; }
+
+	private:
+		Framebuffer fb_;
+		int swaps_ = 0;
+	};
+
+	// what SPRaise throws in the reference (Core/Exception.h:29-46)
+	class RendererError : public std::runtime_error {
+	public:
+		explicit RendererError(const std::string &m) : std::runtime_error(m) {}
+	};
+
+	struct B200RendererOptions {
+		int device = 0;
+		int numerics = OSB200_NUM_SSE2; // the reference's default feature level (SWFeatureLevel.cpp:29-37)
+		int swThreads = 4;              // r_swNumThreads (SWRenderer.cpp:41)
+		int undersampling = 1;          // r_swUndersampling (SWMapRenderer.cpp:37)
+		int radiosityMode = 1;          // r_radiosity
+	};
+
+	class B200Renderer : public IVoxelMapListener {
+	public:
+		explicit B200Renderer(std::shared_ptr<FramebufferPort> port, const B200RendererOptions &opts = B200RendererOptions());
+		~B200Renderer() override;
+
+		void Init();
+		void Shutdown();
+
+		void SetGameMap(VoxelMap *map); // nullptr detaches (stmp::optional<GameMap&> in the reference)
+		void SetFogDistance(float v) { fogDistance_ = v; }
+		void SetFogColor(Vector3 v) { fogColor_ = v; }
+
+		void StartScene(const SceneDefinition &def);
+		// accepted, order-checked, not drawn (see header comment)
+		void AddLight(const void *dynamicLightParam);
+		void RenderModel(const void *model, const void *modelRenderParam);
+		void AddDebugLine(Vector3 a, Vector3 b, const float color[4]);
+		void AddSprite(const void *image, Vector3 center, float radius, float rotation);
+		void AddLongSprite(const void *image, Vector3 p1, Vector3 p2, float radius);
+		void EndScene();
+
+		void FrameDone();
+		void Flip();
+		// RGBA, bottom-up copy of the framebuffer with alpha forced to 0xff (SWRenderer.cpp:1078-1098)
+		std::unique_ptr<Framebuffer> ReadBitmap();
+
+		float ScreenWidth() const;
+		float ScreenHeight() const;
+
+		// client::IGameMapListener
+		void GameMapChanged(int x, int y, int z, VoxelMap *map) override;
+
+		// view-space Z of the last frame (SWRenderer::depthBuffer), copied from the device on demand
+		std::vector<float> ReadDepthBuffer();
+
+		// GLRenderer::EndScene's "Upload Dynamic Data" leg for the map (GLRenderer.cpp:745-759):
+		// GLMapShadowRenderer::Update + GLRadiosityRenderer::Update with a chunk budget (8 in the reference,
+		// < 0 = drain); prioritises chunks near the last scene's eye.  Returns the number of chunks updated.
+		int UpdateRadiosity(int maxChunks = 8);
+
+		osb200_ctx *Context() { return ctx_; }
+		int LastFlushedColumns() const { return lastFlushed_; }
+
+	private:
+		void EnsureInitialized() const;
+		void EnsureValid() const;
+		void EnsureSceneStarted() const;
+		void EnsureSceneNotStarted() const;
+		void SetFramebuffer(Framebuffer *fb);
+		[[noreturn]] void RaiseAbi(const char *what) const;
+
+		std::shared_ptr<FramebufferPort> port_;
+		B200RendererOptions opts_;
+		osb200_ctx *ctx_ = nullptr;
+		VoxelMap *map_ = nullptr;
+		Framebuffer *fb_ = nullptr;
+		bool inited_ = false;
+		bool duringSceneRendering_ = false;
+		bool haveScene_ = false;
+		SceneDefinition sceneDef_;
+		float fogDistance_ = 128.f;
+		Vector3 fogColor_{0.f, 0.f, 0.f};
+		int lastFlushed_ = 0;
+		std::mutex dirtyMutex_; // GameMapChanged may arrive from another thread (SWFlatMapRenderer.cpp:107-111)
+	};
+} // namespace osb200

@@ -47,3 +47,101 @@ OSBH_API int osbh_map_set_arrays(void *m, const uint64_t *solid, const uint32_t 
 	std::memcpy(map->MutableColorData(), color, sizeof(uint32_t) * 512 * 512 * 64);
 	return 0;
 }
+
+// ---- B200Renderer ----
+#include "B200Renderer.h"
+
+namespace {
+	struct RendererBox {
+		std::shared_ptr<osb200::MemoryPort> port;
+		std::unique_ptr<osb200::B200Renderer> r;
+	};
+} // namespace
+
+OSBH_API void *osbh_renderer_new(int w, int h, int device, int numerics, int swThreads, int undersampling,
+                                 int radiosityMode) {
+	RendererBox *b = nullptr;
+	guarded([&] {
+		auto box = std::unique_ptr<RendererBox>(new RendererBox());
+		box->port = std::make_shared<osb200::MemoryPort>(w, h);
+		osb200::B200RendererOptions o;
+		o.device = device;
+		o.numerics = numerics;
+		o.swThreads = swThreads;
+		o.undersampling = undersampling;
+		o.radiosityMode = radiosityMode;
+		box->r.reset(new osb200::B200Renderer(box->port, o));
+		b = box.release();
+	});
+	return b;
+}
+OSBH_API void osbh_renderer_free(void *p) { delete static_cast<RendererBox *>(p); }
+#define R(p) (static_cast<RendererBox *>(p)->r)
+OSBH_API int osbh_renderer_init(void *p) { return guarded([&] { R(p)->Init(); }); }
+OSBH_API int osbh_renderer_shutdown(void *p) { return guarded([&] { R(p)->Shutdown(); }); }
+OSBH_API int osbh_renderer_set_map(void *p, void *map) {
+	return guarded([&] { R(p)->SetGameMap(static_cast<osb200::VoxelMap *>(map)); });
+}
+OSBH_API int osbh_renderer_set_fog(void *p, float r, float g, float b, float dist) {
+	return guarded([&] {
+		R(p)->SetFogColor(osb200::Vector3{r, g, b});
+		R(p)->SetFogDistance(dist);
+	});
+}
+// scene = osb200_scene layout (origin, axis[3], fovX, fovY, zNear, zFar)
+OSBH_API int osbh_renderer_start_scene(void *p, const osb200_scene *s) {
+	return guarded([&] {
+		osb200::SceneDefinition d;
+		d.viewOrigin = osb200::Vector3{s->origin[0], s->origin[1], s->origin[2]};
+		for (int i = 0; i < 3; i++)
+			d.viewAxis[i] = osb200::Vector3{s->axis[i][0], s->axis[i][1], s->axis[i][2]};
+		d.fovX = s->fovX;
+		d.fovY = s->fovY;
+		d.zNear = s->zNear;
+		d.zFar = s->zFar;
+		R(p)->StartScene(d);
+	});
+}
+OSBH_API int osbh_renderer_add_sprite(void *p) {
+	return guarded([&] { R(p)->AddSprite(nullptr, osb200::Vector3{0, 0, 0}, 1.f, 0.f); });
+}
+OSBH_API int osbh_renderer_end_scene(void *p) { return guarded([&] { R(p)->EndScene(); }); }
+OSBH_API int osbh_renderer_frame_done(void *p) { return guarded([&] { R(p)->FrameDone(); }); }
+OSBH_API int osbh_renderer_flip(void *p) { return guarded([&] { R(p)->Flip(); }); }
+OSBH_API int osbh_renderer_swap_count(void *p) { return static_cast<RendererBox *>(p)->port->SwapCount(); }
+OSBH_API int osbh_renderer_read_bitmap(void *p, uint32_t *out) {
+	return guarded([&] {
+		auto bm = R(p)->ReadBitmap();
+		std::memcpy(out, bm->GetPixels(), (size_t)bm->GetWidth() * bm->GetHeight() * 4);
+	});
+}
+OSBH_API int osbh_renderer_framebuffer(void *p, uint32_t *out) {
+	return guarded([&] {
+		auto &fb = static_cast<RendererBox *>(p)->port->GetFramebuffer();
+		std::memcpy(out, fb.GetPixels(), (size_t)fb.GetWidth() * fb.GetHeight() * 4);
+	});
+}
+OSBH_API int osbh_renderer_read_depth(void *p, float *out) {
+	return guarded([&] {
+		auto d = R(p)->ReadDepthBuffer();
+		std::memcpy(out, d.data(), d.size() * 4);
+	});
+}
+OSBH_API int osbh_renderer_screen(void *p, float *w, float *h) {
+	return guarded([&] {
+		*w = R(p)->ScreenWidth();
+		*h = R(p)->ScreenHeight();
+	});
+}
+OSBH_API int osbh_renderer_update_radiosity(void *p, int maxChunks, int *updated) {
+	return guarded([&] { *updated = R(p)->UpdateRadiosity(maxChunks); });
+}
+OSBH_API int osbh_renderer_last_flushed(void *p) { return R(p)->LastFlushedColumns(); }
+OSBH_API void *osbh_renderer_context(void *p) { return R(p)->Context(); }
+OSBH_API int osbh_map_castray2(void *m, void *ctx, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
+                               size_t n) {
+	return guarded([&] {
+		static_cast<osb200::VoxelMap *>(m)->CastRay2Batch(static_cast<osb200_ctx *>(ctx), v0, dir, maxSteps, out, n);
+	});
+}
+#undef R

@@ -96,3 +96,118 @@ class VoxelMap:
             self.close()
         except Exception:
             pass
+
+
+class B200Renderer:
+    """osb200::B200Renderer (host/B200Renderer.h): SWRenderer's surface over the C ABI, on an in-memory port."""
+
+    def __init__(self, w, h, device=0, numerics=2, sw_threads=4, undersampling=1, radiosity_mode=1):
+        L = self._L = load_host_library()
+        ci, fp = ctypes.c_int, ctypes.c_float
+        L.osbh_renderer_new.restype = vp
+        L.osbh_renderer_new.argtypes = [ci] * 7
+        L.osbh_renderer_context.restype = vp
+        for f in ("free", "init", "shutdown", "end_scene", "frame_done", "flip", "swap_count", "add_sprite",
+                  "last_flushed", "context"):
+            getattr(L, "osbh_renderer_" + f).argtypes = [vp]
+        L.osbh_renderer_free.restype = None
+        L.osbh_renderer_set_map.argtypes = [vp, vp]
+        L.osbh_renderer_set_fog.argtypes = [vp, fp, fp, fp, fp]
+        L.osbh_renderer_start_scene.argtypes = [vp, vp]
+        L.osbh_renderer_read_bitmap.argtypes = [vp, vp]
+        L.osbh_renderer_framebuffer.argtypes = [vp, vp]
+        L.osbh_renderer_read_depth.argtypes = [vp, vp]
+        L.osbh_renderer_screen.argtypes = [vp, ctypes.POINTER(fp), ctypes.POINTER(fp)]
+        L.osbh_renderer_update_radiosity.argtypes = [vp, ci, ctypes.POINTER(ci)]
+        L.osbh_map_castray2.argtypes = [vp, vp, vp, vp, ci, vp, ctypes.c_size_t]
+        self.w, self.h = w, h
+        self._h = L.osbh_renderer_new(w, h, device, numerics, sw_threads, undersampling, radiosity_mode)
+        if not self._h:
+            raise OsbError(L.osbh_last_error().decode())
+
+    def _chk(self, rc):
+        if rc:
+            raise OsbError(self._L.osbh_last_error().decode())
+
+    def init(self):
+        self._chk(self._L.osbh_renderer_init(self._h))
+
+    def shutdown(self):
+        self._chk(self._L.osbh_renderer_shutdown(self._h))
+
+    def set_game_map(self, m):
+        self._map = m  # keep the host map alive while it is attached
+        self._chk(self._L.osbh_renderer_set_map(self._h, None if m is None else m.handle))
+
+    def set_fog(self, color, dist):
+        self._chk(self._L.osbh_renderer_set_fog(self._h, color[0], color[1], color[2], dist))
+
+    def start_scene(self, scene):
+        sc = np.ascontiguousarray(scene)
+        self._chk(self._L.osbh_renderer_start_scene(self._h, sc.ctypes.data))
+
+    def add_sprite(self):
+        self._chk(self._L.osbh_renderer_add_sprite(self._h))
+
+    def end_scene(self):
+        self._chk(self._L.osbh_renderer_end_scene(self._h))
+
+    def frame_done(self):
+        self._chk(self._L.osbh_renderer_frame_done(self._h))
+
+    def flip(self):
+        self._chk(self._L.osbh_renderer_flip(self._h))
+
+    @property
+    def swap_count(self):
+        return self._L.osbh_renderer_swap_count(self._h)
+
+    @property
+    def last_flushed(self):
+        return self._L.osbh_renderer_last_flushed(self._h)
+
+    def framebuffer(self):
+        out = np.zeros((self.h, self.w), np.uint32)
+        self._chk(self._L.osbh_renderer_framebuffer(self._h, out.ctypes.data))
+        return out
+
+    def read_bitmap(self):
+        out = np.zeros((self.h, self.w), np.uint32)
+        self._chk(self._L.osbh_renderer_read_bitmap(self._h, out.ctypes.data))
+        return out
+
+    def read_depth(self):
+        out = np.zeros((self.h, self.w), np.float32)
+        self._chk(self._L.osbh_renderer_read_depth(self._h, out.ctypes.data))
+        return out
+
+    def screen(self):
+        w, h = ctypes.c_float(), ctypes.c_float()
+        self._chk(self._L.osbh_renderer_screen(self._h, ctypes.byref(w), ctypes.byref(h)))
+        return w.value, h.value
+
+    def update_radiosity(self, max_chunks=8):
+        n = ctypes.c_int()
+        self._chk(self._L.osbh_renderer_update_radiosity(self._h, max_chunks, ctypes.byref(n)))
+        return n.value
+
+    def castray2(self, vmap, v0, dirs, max_steps):
+        """VoxelMap::CastRay2Batch on this renderer's context."""
+        from .binding import RAYHIT_DTYPE
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        out = np.zeros(len(v0), RAYHIT_DTYPE)
+        self._chk(self._L.osbh_map_castray2(vmap.handle, self._L.osbh_renderer_context(self._h), v0.ctypes.data,
+                                            dirs.ctypes.data, max_steps, out.ctypes.data, len(v0)))
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.osbh_renderer_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,69 @@
+"""CPU: the C-ABI library loads, exports every symbol include/osb200.h declares, and refuses to compute
+without a CUDA device (there is no CPU fallback in the product).  No kernel is launched here."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import openspades_b200 as osb
+from openspades_b200 import binding, hostlib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "osb200.h")).read()
+    return sorted(set(re.findall(r"OSB200_API[^;(]*?\b(osb200_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = binding.load_library()
+    names = _declared_symbols()
+    assert len(names) >= 25 and "osb200_render" in names and "osb200_radiosity_update" in names
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def test_struct_layouts_match_the_reference_types():
+    # GameMap::RayCastResult (GameMap.h:150-156) is 40 bytes; osb200_scene is 64
+    assert binding.RAYHIT_DTYPE.itemsize == 40 and binding.SCENE_DTYPE.itemsize == 64
+    assert binding.RAYHIT_DTYPE.fields["hitPos"][1] == 4 and binding.RAYHIT_DTYPE.fields["hitBlock"][1] == 16
+    assert binding.RAYHIT_DTYPE.fields["normal"][1] == 28
+
+
+def _have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.mark.skipif(_have_gpu(), reason="a CUDA device is present")
+def test_no_gpu_fails_loudly():
+    with pytest.raises(osb.OsbError, match="no CUDA device|no CPU fallback"):
+        osb.Context(device=0)
+    with pytest.raises(osb.OsbError, match="no CUDA device|no CPU fallback"):
+        hostlib.B200Renderer(64, 64)
+
+
+def test_sse_calibration_is_host_only_and_consistent():
+    rcp, rb, rsq, sb = osb.calibrate_sse()
+    assert 8 <= rb <= 16 and 8 <= sb <= 16 and len(rcp) == 1 << rb and len(rsq) == 2 << sb
+    # table entry 0 = rcpss(1.0): within 1.5 * 2^-12 of 1 (Intel SDM bound for RCPSS)
+    one = rcp[:1].view(np.float32)[0]
+    assert abs(one - 1.0) <= 1.5 * 2.0 ** -12
+
+
+def test_host_voxelmap_set_and_listener_contract():
+    m = hostlib.VoxelMap()
+    assert m.solid.shape == (512, 512) and m.color.shape == (512, 512, 64)
+    before = int(m.solid[5, 6])
+    m.set(5, 6, 10, True, 0x64112233)
+    assert int(m.solid[5, 6]) == before | (1 << 10) and int(m.color[5, 6, 10]) == 0x64112233
+    m.set(5, 6, 10, False, 0)
+    assert int(m.solid[5, 6]) == before
+    with pytest.raises(osb.OsbError):
+        m.set(512, 0, 0, True, 0)

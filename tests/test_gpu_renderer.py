@@ -1,0 +1,123 @@
+"""GPU: the host-side B200Renderer (openspades_b200/host/B200Renderer.*, SWRenderer's surface) driven the way
+Client::DrawScene / HitTestDebugger drive SWRenderer (SetGameMap, StartScene, EndScene, FrameDone, ReadBitmap,
+Flip; edits through the map's Set() -> GameMapChanged), frame for frame against the unmodified reference
+SWRenderer where oracle/_ref travelled, else against the oracle restatement."""
+import numpy as np
+import pytest
+
+import oracles
+import openspades_b200 as osb
+from openspades_b200 import workloads
+from openspades_b200.hostlib import B200Renderer, VoxelMap
+
+pytestmark = pytest.mark.gpu
+FOG = (0.1, 0.1, 0.1)
+
+
+def test_state_machine_errors_match_swrenderer():
+    """Same misuse errors as SWRenderer's Ensure* guards (SWRenderer.cpp:520-547) and SetFramebuffer (:94-108)."""
+    with pytest.raises(osb.OsbError, match="multiple of 8"):
+        B200Renderer(100, 60)
+    r = B200Renderer(64, 64, numerics=osb.NUM_IEEE)
+    m = VoxelMap.load_file(oracles.TITLE_VXL)
+    sc = workloads.title_scene(64, 64, 68.0)
+    with pytest.raises(osb.OsbError, match="not initialized"):
+        r.set_game_map(m)
+    with pytest.raises(osb.OsbError, match="not initialized"):
+        r.start_scene(sc)
+    r.init()
+    assert r.screen() == (64.0, 64.0)
+    with pytest.raises(osb.OsbError, match="outside of StartScene"):
+        r.end_scene()
+    with pytest.raises(osb.OsbError, match="outside of StartScene"):
+        r.add_sprite()
+    r.set_game_map(m)
+    r.start_scene(sc)
+    r.add_sprite()  # accepted, not drawn
+    with pytest.raises(osb.OsbError, match="between StartScene"):
+        r.start_scene(sc)
+    with pytest.raises(osb.OsbError, match="between StartScene"):
+        r.frame_done()
+    with pytest.raises(osb.OsbError, match="between StartScene"):
+        r.read_bitmap()
+    r.end_scene()
+    r.frame_done()
+    r.flip()
+    assert r.swap_count == 1
+    r.shutdown()
+    with pytest.raises(osb.OsbError, match="not valid"):
+        r.frame_done()
+    r.close()
+
+
+def test_frames_with_edits_match_reference():
+    w, h = 320, 240
+    m = VoxelMap.load_file(oracles.TITLE_VXL)
+    have_ref = oracles.ref_available("sse2")
+    port = oracles.Port()
+    if have_ref:
+        ref = oracles.Ref("sse2")
+        rm = ref.map_from_arrays(m.solid.copy(), m.color.copy())
+        rr = oracles.RefRenderer(ref, w, h, -1, 4)
+        rr.set_map(rm)
+        rr.set_fog(FOG, 128.0)
+    r = B200Renderer(w, h, numerics=osb.NUM_SSE2, sw_threads=4)
+    r.init()
+    r.set_fog(FOG, 128.0)
+    # before a map is set: clear colour, fog over the zero depth buffer leaves it untouched
+    r.start_scene(workloads.title_scene(w, h, 68.0))
+    r.end_scene()
+    assert np.all((r.framebuffer() & 0xFFFFFF) == 0x7F7F7F)
+    r.set_game_map(m)
+    rng = np.random.default_rng(17)
+    scenes = [workloads.title_scene(w, h, 68.0)] + list(workloads.random_scenes(5, m.solid, w, h, 68.0, seed=5))
+    for fi, sc in enumerate(scenes):
+        # edits in view of the camera between frames, through the map's Set() (listeners fire)
+        ex, ey = int(sc["origin"][0]), int(sc["origin"][1])
+        n_edit = 0 if fi == 0 else 60
+        for _ in range(n_edit):
+            x, y = (ex + int(rng.integers(-20, 21))) & 511, (ey + int(rng.integers(-20, 21))) & 511
+            col = int(m.solid[x, y])
+            top = (col & -col).bit_length() - 1
+            eye_z = int(np.floor(sc["origin"][2]))
+            if rng.random() < 0.5 and top < 62:
+                z, s, c = top, False, 0
+            else:
+                z, s, c = max(top - 1, 0), True, 0x64000000 | int(rng.integers(0, 1 << 24))
+                if x == ex and y == ey and z <= eye_z:
+                    continue  # do not bury the camera
+            m.set(x, y, z, s, c)
+            if have_ref:
+                ref.map_set(rm, x, y, z, s, c)
+        r.start_scene(sc)
+        r.end_scene()
+        r.frame_done()
+        assert (r.last_flushed > 0) == (n_edit > 0)
+        fb, dp = r.framebuffer(), r.read_depth()
+        if have_ref:
+            wfb, wdp = rr.render(sc)
+        else:
+            wfb, wdp = port.render(m.solid.copy(), m.color.copy(), sc, w, h, FOG, 128.0, 2, 4, 1)
+        same = ((fb & 0xFFFFFF) == (wfb & 0xFFFFFF)).mean()
+        dsame = (dp.view(np.uint32) == wdp.view(np.uint32)).mean()
+        assert same == 1.0 and dsame == 1.0, (fi, same, dsame)
+        # ReadBitmap: RGBA, bottom-up, alpha 0xff (SWRenderer.cpp:1078-1098)
+        bm = r.read_bitmap()
+        exp = 0xFF000000 | (fb & 0xFF00) | ((fb & 0xFF) << 16) | ((fb & 0xFF0000) >> 16)
+        assert np.array_equal(bm, exp[::-1])
+        r.flip()
+    # CastRay2Batch through the host map on the renderer's context sees the edited map
+    v0, d = workloads.random_rays(50000, seed=3)
+    got = r.castray2(m, v0, d, 256)
+    want = port.castray2(m.solid.copy(), v0, d, 256, threads=8)
+    assert got.tobytes() == want.tobytes()
+    # radiosity leg with the reference's 8-chunk budget, then drain
+    assert r.update_radiosity(8) == 8
+    assert r.update_radiosity(-1) == 4096 - 8
+    assert r.update_radiosity(8) == 0
+    r.set_game_map(None)
+    r.close()
+    if have_ref:
+        rr.set_map(None)
+        rr.close()
+        ref.map_free(rm)
