@@ -484,31 +484,68 @@ namespace osb {
 	constexpr int kGatherWarps = 4;
 	constexpr int kSegRows = 8; // 8x8 blocks per warp task (vertical)
 
-	// RenderFinal + ApplyFog, one warp per (view, 8-pixel column, segment of kSegRows block rows).
+	// truncating (C) division by 2^sh without the 40-instruction generic idiv
+	__device__ __forceinline__ int tdiv_pow2(int x, int sh) { return (x + ((x >> 31) & ((1 << sh) - 1))) >> sh; }
+
+	// ApplyFog blend of one pixel (SWRenderer.cpp:381-407 scalar, :462-510 SSE2).  col = B | G<<8 | R<<16 | X<<24.
+	// B and R share one multiply: each 8-bit channel times a factor <= 256 stays below 2^16.
+	template <bool kSse2Fog>
+	__device__ __forceinline__ uint32_t fog_blend(uint32_t col, float dist, uint32_t fogBR, uint32_t fogG8) {
+		int factor;
+		if (kSse2Fog) {
+			float d = dist > 0.f ? dist : 0.f; // maxps / minps return the 2nd operand on NaN
+			d = d < 256.f ? d : 256.f;
+			factor = osbn::x86_f2i_rn(d);
+		} else {
+			factor = min(osbn::x86_f2i(dist), 256);
+			factor = max(0, factor);
+		}
+		const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
+		const uint32_t br = (((col & 0x00ff00ffu) * f2 + fogBR * f1) >> 8) & 0x00ff00ffu;
+		const uint32_t gg = (((col & 0x0000ff00u) * f2 + fogG8 * f1) >> 8) & 0x0000ff00u;
+		uint32_t out = br | gg;
+		if (kSse2Fog) // lane 3 of the SSE2 path keeps (X * f2) >> 8
+			out |= (((col >> 24) * f2) << 16) & 0xff000000u;
+		return out;
+	}
+
+	// RenderFinal + ApplyFog.  One warp per (view, 32-pixel column group = four 8x8 block columns, segment of
+	// kSegRows block rows); one lane per pixel column, so every row is written as one 128-byte run per buffer.
+	// Per block row the 16 block corners (4 blocks x 4) are evaluated by 16 lanes in one instruction stream
+	// and shared by shuffle; per pixel only the reference's integer interpolation, the gather and the blend remain.
 	template <bool kSse, bool kSse2Fog>
 	__global__ void __launch_bounds__(kGatherWarps * 32)
 	  k_gather_fog(const ViewParams *__restrict__ views, int nViews, FrameGeom g, const float *__restrict__ tabs,
 	               const uint64_t *__restrict__ solid, const uint16_t *__restrict__ atanTab, osbn::SseTables sse,
 	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams, int lineRes,
 	               uint32_t *__restrict__ fb, float *__restrict__ depthBuf) {
-		const int lane = threadIdx.x & 31;
+		__shared__ float s_fog[kGatherWarps][kSegRows * 2][8];
+		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 		const int colBlocks = g.fw >> 3, rowBlocks = g.fh >> 3;
+		const int colGroups = (colBlocks + 3) >> 2;
 		const int segs = (rowBlocks + kSegRows - 1) / kSegRows;
-		const uint32_t task = blockIdx.x * kGatherWarps + (threadIdx.x >> 5);
-		const uint32_t perView = (uint32_t)colBlocks * segs;
+		const uint32_t task = blockIdx.x * kGatherWarps + wid;
+		const uint32_t perView = (uint32_t)colGroups * segs;
 		if (task >= perView * (uint32_t)nViews)
 			return;
 		const int vi = task / perView;
 		const uint32_t rem = task - (uint32_t)vi * perView;
-		const int seg = rem / colBlocks, bx = rem - seg * colBlocks;
+		const int seg = rem / colGroups, cg = rem - seg * colGroups;
 		const ViewParams &V = views[vi];
 		osbn::Num<kSse> num{sse};
 		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2), *v1Tab = vyTab + (g.fh >> 2);
 		uint32_t *fbV = fb + (size_t)vi * g.fw * g.fh;
 		float *dbV = depthBuf + (size_t)vi * g.fw * g.fh;
+		const int by0 = seg * kSegRows, by1 = min(by0 + kSegRows, rowBlocks);
 
-		// SWMapRenderer::Render :1181-1184: eye inside a solid voxel -> terrain skipped, fb keeps the clear
-		// colour and the depth buffer keeps its previous contents
+		const int bx = (cg << 2) + (lane >> 3);  // this lane's block column
+		const bool colValid = bx < colBlocks;    // a partial last group when fw is not a multiple of 32
+		const int bxc = colValid ? bx : colBlocks - 1;
+		const int px = lane & 7;                 // pixel column inside the block
+		const int x = (bxc << 3) + px;
+
+		// SWMapRenderer::Render :1181-1184: eye inside a solid voxel (or no map at all) -> terrain skipped, fb keeps
+		// the clear colour and the depth buffer keeps its previous contents
 		bool skip;
 		{
 			const int ex = osbn::x86_f2i(floorf(V.origin[0])), ey = osbn::x86_f2i(floorf(V.origin[1])),
@@ -516,8 +553,24 @@ namespace osb {
 			skip = g.noMap || ez >= 64 || (ez >= 0 && ((solid[tiled_index(ex & 511, ey & 511)] >> ez) & 1ull));
 		}
 
+		// ---- fog scale of every 4x4 pixel block this task covers (SWRenderer.cpp:372-380) ----
+		{
+			const int nRows4 = (by1 - by0) * 2;
+			for (int i = lane; i < nRows4 * 8; i += 32) {
+				const int r4 = i >> 3, c4 = i & 7;
+				const int cx4 = min((cg << 3) + c4, (g.fw >> 2) - 1);
+				const float vx = vxTab[cx4], vy = vyTab[(by0 << 1) + r4];
+				float ds = __fadd_rn(__fadd_rn(1.f, __fmul_rn(vx, vx)), __fmul_rn(vy, vy));
+				ds = __fmul_rn(ds, __fmul_rn(num.rsqrt(ds), V.fogScale));
+				s_fog[wid][r4][c4] = ds;
+			}
+			__syncwarp();
+		}
+		const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
+
 		// per-view deltas (:757-775)
-		const int under = g.under, hBlock = 8 / under;
+		const int under = g.under, hSh = under == 1 ? 3 : (under == 2 ? 2 : 1); // log2(8 / under)
+		const int pxq = px - (px % under), xs = pxq / under; // undersampling: pixels share their group leader's sample
 		const float sD = __fdiv_rn(__fmul_rn(V.fovYt, 2.f), (float)g.fh);
 		const float sR = __fmul_rn(__fdiv_rn(__fmul_rn(V.fovXt, 2.f), (float)g.fw), (float)under);
 		float dD[3], dR[3], dDL[3], dRL[3], v2[3];
@@ -526,10 +579,9 @@ namespace osb {
 			dD[k] = __fmul_rn(-V.up[k], sD);
 			dR[k] = __fmul_rn(V.right[k], sR);
 			dDL[k] = __fmul_rn(dD[k], 8.f);
-			dRL[k] = __fmul_rn(dR[k], (float)hBlock);
-			v2[k] = v1Tab[bx * 3 + k];
+			dRL[k] = __fmul_rn(dR[k], (float)(8 / under));
+			v2[k] = v1Tab[bxc * 3 + k];
 		}
-		const int by0 = seg * kSegRows, by1 = min(by0 + kSegRows, rowBlocks);
 		for (int i = 0; i < by0; i++) { // replay v2 += deltaDownLarge (:1037)
 #pragma unroll
 			for (int k = 0; k < 3; k++)
@@ -538,19 +590,29 @@ namespace osb {
 		const uint32_t numLines = (uint32_t)V.numLines;
 		const uint32_t yawScale2 = (uint32_t)V.yawScale2;
 		const int yawMin2 = V.yawMin2;
+		const int lineShift = 31 - __clz(lineRes);
 		const uint2 *stripsV = strips + (size_t)V.lineBase * lineRes;
 		const int4 *lpV = lineParams + V.lineBase;
-		const int px = lane & 7;             // pixel column inside the block
-		const int pxq = px - (px % under);   // undersampling: pixels share their group leader's sample
-		const int xs = pxq / under;
-		const float fogVx = vxTab[(bx << 1) + (px >> 2)];
+		const int blkLane = lane & ~7;
 
 		for (int by = by0; by < by1; by++) {
-			const bool slow = v2[2] > 0.99f || v2[2] < -0.99f;
-			int yaw1 = 0, yaw2 = 0, yaw3 = 0, yaw4 = 0, pit1 = 0, pit2 = 0, pit3 = 0, pit4 = 0;
-			if (!slow && !skip) {
-				// four block corners, one per lane 0..3 (:810-835)
-				const int cr = lane & 1, cd = (lane >> 1) & 1;
+			size_t o = (size_t)(by * 8) * g.fw + x;
+			const float *fogRow = &s_fog[wid][(by - by0) * 2][lane >> 2];
+			if (skip) {
+				if (colValid) {
+#pragma unroll
+					for (int py = 0; py < 8; py++, o += g.fw) {
+						const float dep = dbV[o];
+						fbV[o] = fog_blend<kSse2Fog>(0x7f7f7fu, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8);
+					}
+				}
+				continue;
+			}
+			const bool slow = v2[2] > 0.99f || v2[2] < -0.99f; // uniform within a block (8 lanes)
+			// ---- block corners: lanes 0..3 of every block (:810-835) ----
+			int yaw = 0, pit = 0;
+			if (px < 4 && !slow) {
+				const int cr = px & 1, cd = (px >> 1) & 1;
 				float c[3];
 #pragma unroll
 				for (int k = 0; k < 3; k++) {
@@ -560,63 +622,53 @@ namespace osb {
 					if (cd)
 						c[k] = __fadd_rn(c[k], dDL[k]);
 				}
-				const int yaw = (int)((((int)fast_atan2(num, atanTab, c[1], c[0]) - yawMin2) & 0xffff) << 8);
+				yaw = (int)((((int)fast_atan2(num, atanTab, c[1], c[0]) - yawMin2) & 0xffff) << 8);
 				float pitch = __fmul_rn(c[2], num.rsqrt(__fadd_rn(__fmul_rn(c[0], c[0]), __fmul_rn(c[1], c[1]))));
 				pitch = num.toSpecialTan(pitch);
-				const int pit = osbn::x86_f2i(__fmul_rn(pitch, 65536.f * 8192.f));
-				yaw1 = __shfl_sync(0xffffffffu, yaw, 0);
-				yaw2 = __shfl_sync(0xffffffffu, yaw, 1);
-				yaw3 = __shfl_sync(0xffffffffu, yaw, 2);
-				yaw4 = __shfl_sync(0xffffffffu, yaw, 3);
-				pit1 = __shfl_sync(0xffffffffu, pit, 0);
-				pit2 = __shfl_sync(0xffffffffu, pit, 1);
-				pit3 = __shfl_sync(0xffffffffu, pit, 2);
-				pit4 = __shfl_sync(0xffffffffu, pit, 3);
+				pit = osbn::x86_f2i(__fmul_rn(pitch, 65536.f * 8192.f));
 			}
+			const int yaw1 = __shfl_sync(0xffffffffu, yaw, blkLane), yaw2 = __shfl_sync(0xffffffffu, yaw, blkLane + 1);
+			const int yaw3 = __shfl_sync(0xffffffffu, yaw, blkLane + 2), yaw4 = __shfl_sync(0xffffffffu, yaw, blkLane + 3);
+			const int pit1 = __shfl_sync(0xffffffffu, pit, blkLane), pit2 = __shfl_sync(0xffffffffu, pit, blkLane + 1);
+			const int pit3 = __shfl_sync(0xffffffffu, pit, blkLane + 2), pit4 = __shfl_sync(0xffffffffu, pit, blkLane + 3);
+			if (colValid) {
+				if (!slow) {
+					// bilinear interpolation in integers; `<<8>>8` is the reference's phase unwrap (:837-881)
+					const int yawDiff1 = tdiv_pow2(((yaw2 - yaw1) << 8) >> 8, hSh), yawDiff2 = tdiv_pow2(((yaw4 - yaw3) << 8) >> 8, hSh);
+					const int pitDiff1 = tdiv_pow2(pit2 - pit1, hSh), pitDiff2 = tdiv_pow2(pit4 - pit3, hSh);
+					const int yawA = yaw1 + xs * yawDiff1, yawB = yaw3 + xs * yawDiff2;
+					const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
+					const int dYaw = tdiv_pow2(((yawB - yawA) << 8) >> 8, 3), dPit = tdiv_pow2(pitB - pitA, 3);
+					int yawC = yawA, pitC = pitA;
 #pragma unroll
-			for (int pass = 0; pass < 2; pass++) {
-				const int py = (lane >> 3) + pass * 4;
-				const size_t o = (size_t)(by * 8 + py) * g.fw + (size_t)bx * 8 + px;
-				uint32_t col;
-				float dep;
-				if (skip) {
-					col = 0x7f7f7f;
-					dep = dbV[o];
-				} else {
-					uint32_t yawIndex;
-					int pitchIndex;
-					if (!slow) {
-						// bilinear interpolation in integers; `<<8>>8` is the reference's phase unwrap (:837-881)
-						const int yawDiff1 = (((yaw2 - yaw1) << 8) >> 8) / hBlock, yawDiff2 = (((yaw4 - yaw3) << 8) >> 8) / hBlock;
-						const int pitDiff1 = (pit2 - pit1) / hBlock, pitDiff2 = (pit4 - pit3) / hBlock;
-						const int yawA = yaw1 + xs * yawDiff1, yawB = yaw3 + xs * yawDiff2;
-						const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
-						const int yawC = yawA + py * ((((yawB - yawA) << 8) >> 8) / 8);
-						const int pitC = pitA + py * ((pitB - pitA) / 8);
-						yawIndex = (uint32_t)((yawC << 8) >> 16);
+					for (int py = 0; py < 8; py++, o += g.fw, yawC += dYaw, pitC += dPit) {
+						uint32_t yawIndex = (uint32_t)((yawC << 8) >> 16);
 						yawIndex = (yawIndex * yawScale2) >> 16;
 						yawIndex = (yawIndex * numLines) >> 16;
 						yawIndex = min(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
 						const int4 lp = __ldg(lpV + yawIndex);
-						pitchIndex = (pitC >> 13) - lp.z;
-						pitchIndex = (int)(((long long)pitchIndex * (long long)lp.w) >> 32);
-					} else {
-						// exact per-pixel path near the poles (:940-1033)
-						float v4[3];
+						int pitchIndex = (pitC >> 13) - lp.z;
+						pitchIndex = __mulhi(pitchIndex, lp.w);
+						pitchIndex &= lineRes - 1;
+						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+						const float dep = __uint_as_float(pix.y);
+						__stcs(fbV + o, fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
+						__stcs(dbV + o, dep);
+					}
+				} else {
+					// exact per-pixel path near the poles (:940-1033)
+					float v4[3];
+#pragma unroll
+					for (int k = 0; k < 3; k++)
+						v4[k] = v2[k];
+					for (int i = 0; i < xs; i++) {
 #pragma unroll
 						for (int k = 0; k < 3; k++)
-							v4[k] = v2[k];
-						for (int i = 0; i < xs; i++) {
-#pragma unroll
-							for (int k = 0; k < 3; k++)
-								v4[k] = __fadd_rn(v4[k], dR[k]);
-						}
-						for (int i = 0; i < py; i++) {
-#pragma unroll
-							for (int k = 0; k < 3; k++)
-								v4[k] = __fadd_rn(v4[k], dD[k]);
-						}
-						yawIndex = (uint32_t)(((int)fast_atan2(num, atanTab, v4[1], v4[0]) - yawMin2) & 0xffff);
+							v4[k] = __fadd_rn(v4[k], dR[k]);
+					}
+#pragma unroll 1
+					for (int py = 0; py < 8; py++, o += g.fw) {
+						uint32_t yawIndex = (uint32_t)(((int)fast_atan2(num, atanTab, v4[1], v4[0]) - yawMin2) & 0xffff);
 						yawIndex = (yawIndex * yawScale2) >> 16;
 						yawIndex = (yawIndex * numLines) >> 16;
 						yawIndex = min(yawIndex, numLines - 1);
@@ -624,37 +676,16 @@ namespace osb {
 						float pitch = __fmul_rn(v4[2], num.rsqrt(__fadd_rn(__fmul_rn(v4[0], v4[0]), __fmul_rn(v4[1], v4[1]))));
 						pitch = num.toSpecialTan(pitch);
 						pitch = __fmul_rn(__fsub_rn(pitch, __int_as_float(lp.x)), __int_as_float(lp.y));
-						pitchIndex = osbn::x86_f2i(pitch);
+						const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
+						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+						const float dep = __uint_as_float(pix.y);
+						__stcs(fbV + o, fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
+						__stcs(dbV + o, dep);
+#pragma unroll
+						for (int k = 0; k < 3; k++)
+							v4[k] = __fadd_rn(v4[k], dD[k]);
 					}
-					pitchIndex &= lineRes - 1;
-					const uint2 pix = __ldg(stripsV + (size_t)yawIndex * lineRes + pitchIndex);
-					col = pix.x;
-					dep = __uint_as_float(pix.y);
 				}
-				// ---- ApplyFog for this pixel (SWRenderer.cpp:341-516) ----
-				{
-					const float vy = vyTab[(by << 1) + (py >> 2)];
-					float depthScale = __fadd_rn(__fadd_rn(1.f, __fmul_rn(fogVx, fogVx)), __fmul_rn(vy, vy));
-					depthScale = __fmul_rn(depthScale, __fmul_rn(num.rsqrt(depthScale), V.fogScale));
-					const float dist = __fmul_rn(dep, depthScale);
-					int factor;
-					if (kSse2Fog) {
-						float d = dist > 0.f ? dist : 0.f; // maxps / minps return the 2nd operand on NaN
-						d = d < 256.f ? d : 256.f;
-						factor = osbn::x86_f2i_rn(d);
-					} else {
-						factor = min(osbn::x86_f2i(dist), 256);
-						factor = max(0, factor);
-					}
-					const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
-					const uint32_t b = (((col & 0xff) * f2 + g.fogB * f1) >> 8) & 0xff;
-					const uint32_t gg = ((((col >> 8) & 0xff) * f2 + g.fogG * f1) >> 8) & 0xff;
-					const uint32_t r = ((((col >> 16) & 0xff) * f2 + g.fogR * f1) >> 8) & 0xff;
-					const uint32_t a = kSse2Fog ? (((col >> 24) * f2) >> 8) & 0xff : 0u; // lane 3 of the SSE2 path
-					col = b | (gg << 8) | (r << 16) | (a << 24);
-				}
-				fbV[o] = col;
-				dbV[o] = dep;
 			}
 #pragma unroll
 			for (int k = 0; k < 3; k++)
@@ -958,7 +989,7 @@ namespace osb {
 			}
 #undef LAUNCH_LINES
 			const int segs = ((h >> 3) + kSegRows - 1) / kSegRows;
-			const size_t tasks = (size_t)nv * (w >> 3) * segs;
+			const size_t tasks = (size_t)nv * (((w >> 3) + 3) >> 2) * segs;
 			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
 			uint32_t *fbC = d_fb + (size_t)v0 * w * h;
 			float *dbC = d_depth + (size_t)v0 * w * h;
