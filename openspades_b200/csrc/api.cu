@@ -8,7 +8,9 @@
 //   SWFlatMapRenderer dirty bitset  Sources/Draw/SWFlatMapRenderer.cpp:52-111
 #include "ctx.h"
 
+#include <algorithm>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 
 namespace osb {
@@ -211,8 +213,35 @@ int osb200_create(const osb200_opts *opts, osb200_ctx **out) {
 	TRY(cudaGetDeviceProperties(&prop, c->device));
 	c->smCount = prop.multiProcessorCount;
 	TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-	TRY(cudaMalloc(&c->d_solid, sizeof(uint64_t) * OSB200_MAP_W * OSB200_MAP_H));
-	TRY(cudaMalloc(&c->d_color, sizeof(uint32_t) * OSB200_MAP_W * OSB200_MAP_H * OSB200_MAP_D));
+	{
+		// one allocation for bitmap (2 MiB) + colours (64 MiB) so that a single L2 access-policy window covers
+		// the whole resident map: the DDA / ray loops do dependent random reads into it while GBs of strips,
+		// rays and frames stream past, so it is pinned in L2 (persisting hits, streaming misses elsewhere)
+		const size_t sb = sizeof(uint64_t) * OSB200_MAP_W * OSB200_MAP_H;
+		const size_t cb = sizeof(uint32_t) * OSB200_MAP_W * OSB200_MAP_H * OSB200_MAP_D;
+		void *base = nullptr;
+		TRY(cudaMalloc(&base, sb + cb));
+		c->d_solid = reinterpret_cast<uint64_t *>(base);
+		c->d_color = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(base) + sb);
+		const char *env = getenv("OSB200_L2_PERSIST");
+		const bool want = env && atoi(env) != 0; // measured on B200: the carve-out costs more (strip write-combining capacity) than it saves -> opt-in only
+		if (want && prop.persistingL2CacheMaxSize > 0 && prop.accessPolicyMaxWindowSize > 0) {
+			const size_t win = std::min<size_t>(sb + cb, (size_t)prop.accessPolicyMaxWindowSize);
+			const size_t carve = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, win);
+			if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess) {
+				cudaStreamAttrValue attr;
+				memset(&attr, 0, sizeof(attr));
+				attr.accessPolicyWindow.base_ptr = base;
+				attr.accessPolicyWindow.num_bytes = win;
+				attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)win);
+				attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+				attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+				if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr) == cudaSuccess)
+					c->l2PersistBytes = carve;
+			}
+			cudaGetLastError(); // the window is an optimisation: never fatal
+		}
+	}
 	if (opts->numerics != OSB200_NUM_IEEE) {
 		c->rcpBits = rcpBits;
 		c->rsqrtBits = rsqrtBits;
@@ -236,8 +265,7 @@ void osb200_destroy(osb200_ctx *c) {
 		cudaStreamSynchronize(c->stream);
 	osb::terrain_destroy(c);
 	osb::radiosity_destroy(c);
-	cudaFree(c->d_solid);
-	cudaFree(c->d_color);
+	cudaFree(c->d_solid); // bitmap + colours are one allocation
 	cudaFree(c->d_rcp);
 	cudaFree(c->d_rsqrt);
 	cudaFree(c->d_scratch);

@@ -81,7 +81,8 @@ struct osb200_ctx {
 	// ---- resident map ----
 	bool mapLoaded = false;
 	uint64_t *d_solid = nullptr; // [tiled_index(x,y)] 2 MiB
-	uint32_t *d_color = nullptr; // [(tiled_index(x,y)) * 64 + z] 64 MiB, 0xHHBBGGRR as in GameMap
+	uint32_t *d_color = nullptr; // [(tiled_index(x,y)) * 64 + z] 64 MiB, 0xHHBBGGRR as in GameMap (same allocation)
+	size_t l2PersistBytes = 0;   // L2 carve-out pinned to the map window (0 = not available)
 	// dirty tracking (same 32-column words as SWFlatMapRenderer::updateMap, SWFlatMapRenderer.cpp:107-111)
 	std::vector<uint32_t> dirtyWords; // 512*512/32
 	bool anyDirty = false;

@@ -27,6 +27,12 @@ namespace osbn {
 	__device__ __forceinline__ float rcpss(float x, const SseTables &t) {
 		const uint32_t u = __float_as_uint(x);
 		const uint32_t sign = u & 0x80000000u, e = (u >> 23) & 0xff, m = u & 0x7fffff;
+		if (e - 1u < 252u) {
+			// normal input, normal result (table entries lie in [0.5, 1]: biased exponent 126 or 127, so the
+			// result exponent 127 - e + {126,127} stays in 1..253): add the exponent difference in place
+			const uint32_t r = __ldg(t.rcp + (m >> (23 - t.rcpBits)));
+			return __uint_as_float(sign | (r + ((127u - e) << 23)));
+		}
 		if (e == 0)
 			return __uint_as_float(sign | 0x7f800000u); // zero / denormal -> +-inf
 		if (e == 255)

@@ -129,12 +129,14 @@ namespace osb {
 		float *d_depth = nullptr;
 		size_t outCap = 0;
 		cudaEvent_t stageFree = nullptr;
+		cudaStream_t copyStream = nullptr; // D2H of finished chunks, overlapped with the next chunk's kernels
+		cudaEvent_t chunkDone = nullptr, copyDone = nullptr;
 	};
 } // namespace osb
 
 namespace osb {
 
-	constexpr int kLineThreads = 64; // lines per CTA of k_build_lines
+	constexpr int kLineThreads = 32; // lines per CTA of k_build_lines
 	enum { F_POSX = 0, F_NEGX = 1, F_POSY = 2, F_NEGY = 3, F_POSZ = 4, F_NEGZ = 5 }; // SWMapRenderer.cpp:68
 
 	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map.
@@ -195,7 +197,7 @@ namespace osb {
 			while (todo) {
 				const int b = __ffs(todo) - 1;
 				todo &= todo - 1;
-				strip[(w << 5) + b] = px;
+				__stcs(strip + ((w << 5) + b), px);
 			}
 		}
 	}
@@ -232,7 +234,7 @@ namespace osb {
 			const uint32_t n4 = nl * (uint32_t)lineRes / 2;
 			const uint4 clr = make_uint4(0u, __float_as_uint(10000.f), 0u, __float_as_uint(10000.f));
 			for (uint32_t i = threadIdx.x; i < n4; i += kLineThreads)
-				dst[i] = clr;
+				__stcs(dst + i, clr);
 			for (int w = 0; w < words; w++)
 				s_filled[w * kLineThreads + threadIdx.x] = 0;
 		}
@@ -364,76 +366,98 @@ namespace osb {
 		const uint64_t belowEye = icz >= 63 ? 0ull : (icz < 0 ? ~0ull : (~0ull << (icz + 1)));
 		const uint64_t aboveEye = icz <= 0 ? 0ull : (icz >= 64 ? ~0ull : ((1ull << icz) - 1ull));
 
-		uint64_t sOld = solid[tiled_index(irx & 511, iry & 511)];
 		uint32_t tOld = tiled_index(irx & 511, iry & 511);
+		uint64_t sOld = solid[tOld];
 		int count = 1;
 		uint32_t cnt2 = 1024; // static_cast<int>(fogDist * 8.f)
 
-		while (distance < fogDist && (--cnt2) > 0) {
-			// ---- one DDA step (:426-522) ----
-			int wallFace;
-			const uint32_t tx = (uint32_t)((posX ? 512 - (rx & 511) : (rx & 511)) * invDirXI);
-			const uint32_t ty = (uint32_t)((posY ? 512 - (ry & 511) : (ry & 511)) * invDirYI);
+		// One DDA step (:426-522) depends only on (rx, ry), never on map data, so the step after the current
+		// one is computed ahead and its column mask is requested before the current step's spans are
+		// processed: the dependent 8-byte load is off the critical path.
+		struct Step {
+			int rx, ry, irx, iry, wallFace;
+			float distance;
+			uint32_t t;
+		};
+		auto advance = [&](int rx0, int ry0, int irx0, int iry0, float dist0) -> Step {
+			Step n;
+			const uint32_t tx = (uint32_t)((posX ? 512 - (rx0 & 511) : (rx0 & 511)) * invDirXI);
+			const uint32_t ty = (uint32_t)((posY ? 512 - (ry0 & 511) : (ry0 & 511)) * invDirYI);
 			if (tx < ty) {
-				irx += posX ? 1 : -1;
-				rx = posX ? (irx << 9) : (irx << 9) - 1;
+				n.irx = irx0 + (posX ? 1 : -1);
+				n.iry = iry0;
+				n.rx = posX ? (n.irx << 9) : (n.irx << 9) - 1;
 				const int d = (int)((dirYI * tx) >> 17);
-				ry = posY ? ry + d : ry - d;
-				distance = __fadd_rn(distance, __fmul_rn((float)tx, 1.f / 512.f / 256.f));
-				wallFace = posX ? F_NEGX : F_POSX;
+				n.ry = posY ? ry0 + d : ry0 - d;
+				n.distance = __fadd_rn(dist0, __fmul_rn((float)tx, 1.f / 512.f / 256.f));
+				n.wallFace = posX ? F_NEGX : F_POSX;
 			} else {
-				iry += posY ? 1 : -1;
+				n.iry = iry0 + (posY ? 1 : -1);
+				n.irx = irx0;
 				const int d = (int)((dirXI * ty) >> 17);
-				rx = posX ? rx + d : rx - d;
-				ry = posY ? (iry << 9) : (iry << 9) - 1;
-				distance = __fadd_rn(distance, __fmul_rn((float)ty, 1.f / 512.f / 256.f));
-				wallFace = posY ? F_NEGY : F_POSY;
+				n.rx = posX ? rx0 + d : rx0 - d;
+				n.ry = posY ? (n.iry << 9) : (n.iry << 9) - 1;
+				n.distance = __fadd_rn(dist0, __fmul_rn((float)ty, 1.f / 512.f / 256.f));
+				n.wallFace = posY ? F_NEGY : F_POSY;
 			}
+			n.t = tiled_index(n.irx & 511, n.iry & 511);
+			return n;
+		};
+		Step nx = advance(rx, ry, irx, iry, distance);
+		uint64_t sNext = solid[nx.t];
+
+		while (distance < fogDist && (--cnt2) > 0) {
+			// ---- take the precomputed step, start the one after it ----
+			const Step cur = nx;
+			const uint64_t sNew = sNext;
+			distance = cur.distance;
+			nx = advance(cur.rx, cur.ry, cur.irx, cur.iry, cur.distance);
+			sNext = solid[nx.t];
+			const int wallFace = cur.wallFace;
+			const uint32_t tNew = cur.t;
+
 			const float oldInvDist = invDist;
 			invDist = num.rcp(distance);
 			const float medDist = __fadd_rn(__fmul_rn(distance, zscale), depthBias);
 
-			const uint32_t tNew = tiled_index(irx & 511, iry & 511);
-			const uint64_t sNew = solid[tNew];
-
-			// ---- floor / ceiling of the cell being left (:579-624) ----
-			{
-				uint64_t tops = sOld & ~(sOld << 1) & belowEye; // solid with air above, below the eye, ascending
-				while (tops) {
-					const int z = __ffsll((long long)tops) - 1;
+			// ---- spans of this step, one merged work list per lane, in the reference's order:
+			//   floor tops of the cell being left (ascending z, :584-603), its ceilings (descending z, :604-622),
+			//   then the walls of the cell being entered for the crossed face (ascending z, :627-657).
+			// Merging the three loops keeps lanes with different mixes of work in one instruction stream.
+			uint64_t tops = sOld & ~(sOld << 1) & belowEye;                   // solid, air above, below the eye
+			uint64_t bots = sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye;   // solid, air below, above the eye
+			uint64_t walls = sNew & ~sOld;                                    // solid there, air in the cell left
+			int savedZ = 127, savedP = 0;
+			while (tops | bots | walls) {
+				int z, kind;
+				if (tops) {
+					z = __ffsll((long long)tops) - 1;
 					tops &= tops - 1;
-					const int p1 = L.transform(invDist, z), p2 = L.transform(oldInvDist, z);
-					if (p1 < p2 && span_has_empty(filled, p1, p2)) {
-						const uint32_t c = shade<kSse2Shade>(color[(size_t)tOld * 64 + z], F_NEGZ);
-						fill_span(strip, filled, p1, p2, c, __fadd_rn(medDist, __fmul_rn((float)z, heightScale)));
-					}
-				}
-				uint64_t bots = sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye; // solid with air below, descending
-				while (bots) {
-					const int z = 63 - __clzll((long long)bots);
+					kind = 0;
+				} else if (bots) {
+					z = 63 - __clzll((long long)bots);
 					bots &= ~(1ull << z);
-					const int p1 = L.transform(invDist, z + 1), p2 = L.transform(oldInvDist, z + 1);
-					if (p2 < p1 && span_has_empty(filled, p2, p1)) {
-						const uint32_t c = shade<kSse2Shade>(color[(size_t)tOld * 64 + z], F_POSZ);
-						fill_span(strip, filled, p2, p1, c, __fadd_rn(medDist, __fmul_rn((float)(z + 1), heightScale)));
-					}
-				}
-			}
-			// ---- walls of the cell being entered: solid there, air in the cell just left (:627-659) ----
-			{
-				uint64_t walls = sNew & ~sOld;
-				int savedZ = 127, savedP = 0;
-				while (walls) {
-					const int z = __ffsll((long long)walls) - 1;
+					kind = 1;
+				} else {
+					z = __ffsll((long long)walls) - 1;
 					walls &= walls - 1;
-					const int p1 = savedZ == z ? savedP : L.transform(invDist, z);
-					const int p2 = L.transform(invDist, z + 1);
+					kind = 2;
+				}
+				// colour is requested before the projection math; it is only used when the span lands
+				const uint32_t rawCol = color[(size_t)(kind == 2 ? tNew : tOld) * 64 + z];
+				const int zA = kind == 1 ? z + 1 : z;       // first transform: (invDist, zA)
+				const int zB = kind == 0 ? z : z + 1;       // second: (oldInvDist or invDist, zB)
+				const int pA = (kind == 2 && savedZ == z) ? savedP : L.transform(invDist, zA);
+				const int pB = L.transform(kind == 2 ? invDist : oldInvDist, zB);
+				if (kind == 2) {
 					savedZ = z + 1;
-					savedP = p2;
-					if (p1 < p2 && span_has_empty(filled, p1, p2)) {
-						const uint32_t c = shade<kSse2Shade>(color[(size_t)tNew * 64 + z], wallFace);
-						fill_span(strip, filled, p1, p2, c, __fadd_rn(medDist, __fmul_rn((float)z, heightScale)));
-					}
+					savedP = pB;
+				}
+				const int from = kind == 1 ? pB : pA, to = kind == 1 ? pA : pB;
+				if (from < to && span_has_empty(filled, from, to)) {
+					const int face = kind == 0 ? F_NEGZ : (kind == 1 ? F_POSZ : wallFace);
+					const uint32_t c = shade<kSse2Shade>(rawCol, face);
+					fill_span(strip, filled, from, to, c, __fadd_rn(medDist, __fmul_rn((float)zA, heightScale)));
 				}
 			}
 			sOld = sNew;
@@ -735,6 +759,9 @@ namespace osb {
 		OSB_CUDA(cudaMalloc(&T->d_atan, tab.size() * 2));
 		OSB_CUDA(cudaMemcpy(T->d_atan, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
 		OSB_CUDA(cudaEventCreateWithFlags(&T->stageFree, cudaEventDisableTiming));
+		OSB_CUDA(cudaStreamCreateWithFlags(&T->copyStream, cudaStreamNonBlocking));
+		OSB_CUDA(cudaEventCreateWithFlags(&T->chunkDone, cudaEventDisableTiming));
+		OSB_CUDA(cudaEventCreateWithFlags(&T->copyDone, cudaEventDisableTiming));
 		return 0;
 	}
 
@@ -755,6 +782,12 @@ namespace osb {
 		cudaFree(T->d_depth);
 		if (T->stageFree)
 			cudaEventDestroy(T->stageFree);
+		if (T->chunkDone)
+			cudaEventDestroy(T->chunkDone);
+		if (T->copyDone)
+			cudaEventDestroy(T->copyDone);
+		if (T->copyStream)
+			cudaStreamDestroy(T->copyStream);
 		delete T;
 		c->terrain = nullptr;
 	}
@@ -849,14 +882,17 @@ namespace osb {
 			const char *e = getenv("OSB200_STRIP_MB");
 			long mb = e ? atol(e) : 0;
 			if (mb <= 0)
-				mb = 1024;
+				mb = 4096; // measured on B200: each launch ends in a latency-bound tail, so few large chunks win
 			v = (size_t)mb << 20;
 		}
 		return v;
 	}
 
+	// host_fb / host_depth (nullable): when given, each chunk's finished frames are copied to the host on a second
+	// stream while the next chunk renders (PCIe overlaps the kernels); the caller synchronises copyDone.
 	static int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
-	                       const float fogColor[3], float fogDist, uint32_t *d_fb, float *d_depth) {
+	                       const float fogColor[3], float fogDist, uint32_t *d_fb, float *d_depth,
+	                       uint32_t *host_fb = nullptr, float *host_depth = nullptr) {
 		if (!c) {
 			set_error("osb200_render: no context");
 			return -1;
@@ -1006,6 +1042,15 @@ namespace osb {
 					LAUNCH_GATHER(true, true);
 			}
 #undef LAUNCH_GATHER
+			if (host_fb || host_depth) {
+				const size_t off = (size_t)v0 * w * h, cnt = (size_t)nv * w * h;
+				OSB_CUDA(cudaEventRecord(T->chunkDone, c->stream));
+				OSB_CUDA(cudaStreamWaitEvent(T->copyStream, T->chunkDone, 0));
+				if (host_fb)
+					OSB_CUDA(cudaMemcpyAsync(host_fb + off, d_fb + off, cnt * 4, cudaMemcpyDeviceToHost, T->copyStream));
+				if (host_depth)
+					OSB_CUDA(cudaMemcpyAsync(host_depth + off, d_depth + off, cnt * 4, cudaMemcpyDeviceToHost, T->copyStream));
+			}
 			if (hostPrep && ci + 2 < chunkStart.size()) // staging reused by the next chunk
 				OSB_CUDA(cudaStreamSynchronize(c->stream));
 		}
@@ -1052,14 +1097,13 @@ int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, 
 		OSB_CUDA(cudaMemsetAsync(T->d_depth, 0, n * 4, c->stream));
 		T->outCap = n;
 	}
-	int rc = osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, T->d_fb, T->d_depth);
+	// the previous call's copies must not race with this call's kernels overwriting the same device buffers
+	OSB_CUDA(cudaStreamSynchronize(T->copyStream));
+	int rc = osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, T->d_fb, T->d_depth, host_bgrx, host_depth);
 	if (rc)
 		return rc;
-	if (host_bgrx)
-		OSB_CUDA(cudaMemcpyAsync(host_bgrx, T->d_fb, n * 4, cudaMemcpyDeviceToHost, c->stream));
-	if (host_depth)
-		OSB_CUDA(cudaMemcpyAsync(host_depth, T->d_depth, n * 4, cudaMemcpyDeviceToHost, c->stream));
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	OSB_CUDA(cudaStreamSynchronize(T->copyStream));
 	return 0;
 }
 

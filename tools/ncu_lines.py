@@ -17,5 +17,6 @@ for r in rows:
         except ValueError: pass
 tot = sum(a[0] for a in agg); tots = sum(a[2] for a in agg)
 print(f"total warp-inst {tot}, samples {tots}")
-for a in sorted(agg, reverse=True)[:top]:
+key = (lambda a: a[2]) if "--by-samples" in sys.argv else (lambda a: a[0])
+for a in sorted(agg, key=key, reverse=True)[:top]:
     print(f"{a[0]:>12} {100*a[0]/tot:5.1f}%  smp {100*a[2]/max(tots,1):5.1f}%  {a[3]}:{a[4]:<5} {a[5]}")
