@@ -400,6 +400,50 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                        "ms_per_batch": ms, "mrays_s": world * n / ms / 1e3, "hit_fraction": hits / n,
                        "hbm_frac_algorithmic": (BYTES_PER_RAY * n / (ms * 1e-3) / 1e9) / peak,
                        "e2e_mrays_s": world * ne / e2e_ms / 1e3, "e2e_rays": ne}
+    del d_v0, d_d, d_out
+
+    # ---- C5: full-map radiosity + incremental edits (GLRadiosityRenderer CPU half) ----
+    from openspades_b200 import sharding
+    solid2, color2 = load_map()
+    with osb.Context(device=dev.index, numerics=osb.NUM_IEEE, radiosity_mode=1) as rc:
+        rc.map_upload(solid2, color2)
+        rc.shadow_bitmap()
+        rc.timing_enable(True)
+        rc.timing_read()
+        t0 = time.perf_counter()
+        n_chunks = rc.radiosity_update(-1)
+        full_wall_ms = (time.perf_counter() - t0) * 1e3
+        kt = rc.timing_read()
+        full_ms = kt["k_radiosity"][1]
+        # 100 frames x 100 random dig/build edits: mark_dirty -> flush -> shadow update -> radiosity(all dirty)
+        rng = np.random.default_rng(99)
+        frames, per_frame = 100, 100
+        t0 = time.perf_counter()
+        upd = 0
+        for _ in range(frames):
+            xs, ys = rng.integers(0, 512, per_frame), rng.integers(0, 512, per_frame)
+            ed = []
+            for x, y in zip(xs, ys):
+                col = int(solid2[x, y])
+                top = (col & -col).bit_length() - 1
+                if rng.random() < 0.5 and top < 62:
+                    ed.append((x, y, top, 0, 0))
+                else:
+                    ed.append((x, y, max(top - 1, 0), 1, 0x64000000 | int(rng.integers(0, 1 << 24))))
+            e = sharding.make_edits(*zip(*ed))
+            sharding.apply_edits_arrays(solid2, color2, e, rc)
+            rc.map_flush(solid2, color2)
+            upd += rc.radiosity_update(-1)
+        inc_s = time.perf_counter() - t0
+        kt2 = rc.timing_read()
+    out["radiosity"] = {"workload": "C5 Title.vxl: all 4096 chunks dirty -> osb200_radiosity_update(all) (16.8 M voxels, <=169 "
+                                    "taps each), then 100 frames x 100 random block edits, each frame flush + shadow update + "
+                                    "radiosity update of every dirty chunk (host edit generation inside the wall time)",
+                        "full_map_chunks": n_chunks, "full_map_kernel_ms": full_ms, "full_map_wall_ms": full_wall_ms,
+                        "full_map_mvoxels_s": 512 * 512 * 64 / full_ms / 1e3,
+                        "hbm_frac_algorithmic": (16 * 512 * 512 * 64 / (full_ms * 1e-3) / 1e9) / peak,
+                        "edits_per_s": frames * per_frame / inc_s, "chunk_updates": upd,
+                        "incremental_kernel_ms_per_frame": {k: v[1] / frames for k, v in kt2.items() if v[0]}}
     return out
 
 

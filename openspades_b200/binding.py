@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libosb200.so")
+LIB_PATH = os.environ.get("OSB200_LIB") or os.path.join(_HERE, "lib", "libosb200.so")  # override: kernel A/B experiments
 
 NUM_IEEE, NUM_SSE, NUM_SSE2 = 0, 1, 2
 

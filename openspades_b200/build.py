@@ -19,6 +19,10 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 # --fmad=false: the reference is x86-64 code without FMA contraction; parity needs separate mul/add.
 CUFLAGS = ["-O3", "-std=c++17", "-lineinfo", "--fmad=false", "-Xcompiler", "-fPIC,-fvisibility=hidden",
            "-ccbin", "/usr/bin/g++"]
+CUFLAGS += os.environ.get("OSB200_NVCC_EXTRA", "").split()
+if os.environ.get("OSB200_LIB_OUT"):  # experiment builds: a differently named library next to the default one
+    LIB = os.environ["OSB200_LIB_OUT"]
+    OBJ_DIR = LIB + ".obj"
 CU_SOURCES = ["api.cu", "castray2.cu", "terrain.cu", "radiosity.cu", "sse_calibrate.cpp"]
 
 

@@ -136,7 +136,10 @@ namespace osb {
 
 namespace osb {
 
-	constexpr int kLineThreads = 32; // lines per CTA of k_build_lines
+	#ifndef OSB_LINE_THREADS
+#define OSB_LINE_THREADS 32
+#endif
+	constexpr int kLineThreads = OSB_LINE_THREADS; // lines per CTA of k_build_lines
 	enum { F_POSX = 0, F_NEGX = 1, F_POSY = 2, F_NEGY = 3, F_POSZ = 4, F_NEGZ = 5 }; // SWMapRenderer.cpp:68
 
 	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map.
@@ -217,7 +220,10 @@ namespace osb {
 
 	// One thread = one yaw line (SWMapRenderer::BuildLine, SWMapRenderer.cpp:219-671).
 	template <bool kSse, bool kSse2Shade>
-	__global__ void __launch_bounds__(kLineThreads)
+#ifndef OSB_LINE_MINB
+#define OSB_LINE_MINB 1
+#endif
+	__global__ void __launch_bounds__(kLineThreads, OSB_LINE_MINB)
 	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
 	                const uint64_t *__restrict__ solid, const uint32_t *__restrict__ color,
 	                osbn::SseTables tabs, uint2 *__restrict__ strips, int4 *__restrict__ lineParams,
