@@ -16,128 +16,163 @@ namespace {
 		return (f >= -2147483648.f && f < 2147483648.f) ? __float2int_rz(f) : (int)0x80000000;
 	}
 
-	constexpr int kThreads = 256;
-	constexpr int kWordsPerHit = 10; // sizeof(osb200_rayhit) / 4
+	constexpr int kThreads = 128;
+	constexpr int kWordsPerHit = 10;   // sizeof(osb200_rayhit) / 4
+	constexpr int kRaysPerWarp = 1024; // contiguous share of the batch one warp works through
+	constexpr int kRefillAt = 8;       // idle lanes that trigger a refill (ray set-up is the divergent part)
 
+	struct RayState {
+		float fx, fy, fz;       // distance to the next boundary per axis (fv in the reference)
+		float ax, ay, az;       // |dir|
+		float invX, invY, invZ; // 1 / |dir|, 0 when the component is 0
+		int ix, iy, iz;         // current cell
+		uint32_t sign;          // bit0..2: dir.x/y/z > 0
+		uint64_t col;           // solid mask of column (ix, iy)
+		int axis, steps;
+		size_t ray;
+	};
+
+	__device__ __forceinline__ void write_hit(uint32_t *__restrict__ out, size_t ray, uint32_t flags, float hx, float hy,
+	                                          float hz, int bx, int by, int bz, int nx, int ny, int nz) {
+		uint2 *o = reinterpret_cast<uint2 *>(out + ray * kWordsPerHit); // 40-byte records are 8-byte aligned
+		o[0] = make_uint2(flags, __float_as_uint(hx));
+		o[1] = make_uint2(__float_as_uint(hy), __float_as_uint(hz));
+		o[2] = make_uint2((uint32_t)bx, (uint32_t)by);
+		o[3] = make_uint2((uint32_t)bz, (uint32_t)nx);
+		o[4] = make_uint2((uint32_t)ny, (uint32_t)nz);
+	}
+
+	// IsSolidWrapped on an already fetched column (GameMap.h:91-98): z < 0 air, z >= 64 solid
+	__device__ __forceinline__ bool solid_at(uint64_t col, int z) {
+		if ((unsigned)z < 64u) {
+			const uint32_t w = (z & 32) ? (uint32_t)(col >> 32) : (uint32_t)col;
+			return (w >> (z & 31)) & 1u;
+		}
+		return z >= 64;
+	}
+
+	// Each warp owns kRaysPerWarp consecutive rays and keeps its 32 lanes busy: a lane whose ray has ended
+	// (hit, start-solid or step limit) writes its record and waits; once kRefillAt lanes wait, they are handed
+	// the next rays of the warp's share.  Ray lengths differ by two orders of magnitude (start-solid: 0 steps,
+	// sky rays: maxSteps), so one-ray-per-thread leaves two thirds of the lanes idle.
 	__global__ void __launch_bounds__(kThreads)
 	  k_castray2(const uint64_t *__restrict__ solid, const float *__restrict__ v0s,
 	             const float *__restrict__ dirs, int maxSteps, uint32_t *__restrict__ out, size_t n) {
-		__shared__ uint32_t s_out[kThreads * kWordsPerHit];
-		const size_t base = (size_t)blockIdx.x * kThreads;
-		const size_t i = base + threadIdx.x;
-		const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-		uint32_t *my = s_out + (size_t)threadIdx.x * kWordsPerHit;
+		const int lane = threadIdx.x & 31;
+		const size_t warpId = ((size_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+		size_t next = warpId * kRaysPerWarp;
+		const size_t end = min(next + (size_t)kRaysPerWarp, n);
+		if (next >= n)
+			return;
+		RayState r;
+		bool active = false;
+		r.fx = r.fy = r.fz = r.ax = r.ay = r.az = r.invX = r.invY = r.invZ = 0.f;
+		r.ix = r.iy = r.iz = r.axis = r.steps = 0;
+		r.sign = 0;
+		r.col = 0;
+		r.ray = 0;
 
-		if (i < n) {
-			const float v0x = v0s[i * 3], v0y = v0s[i * 3 + 1], v0z = v0s[i * 3 + 2];
-			float dx = dirs[i * 3], dy = dirs[i * 3 + 1], dz = dirs[i * 3 + 2];
-
-			// dir = dir.Normalize()  (Core/Math.h:369-374; GetLength = sqrtf(x*x + y*y + z*z))
-			float scale = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
-			if (scale != 0.f)
-				scale = __fdiv_rn(1.f, scale);
-			dx = __fmul_rn(dx, scale);
-			dy = __fmul_rn(dy, scale);
-			dz = __fmul_rn(dz, scale);
-
-			int ix = x86_f2i(floorf(v0x)), iy = x86_f2i(floorf(v0y)), iz = x86_f2i(floorf(v0z));
-
-			uint32_t flags = 0; // hit | startSolid << 8
-			float hx = v0x, hy = v0y, hz = v0z;
-			int bx = 0, by = 0, bz = 0, nx = 0, ny = 0, nz = 0;
-
-			// IsSolidWrapped (GameMap.h:91-98): z < 0 air, z >= 64 solid, x/y wrap & 511
-			uint64_t col = solid[osb::tiled_index(ix & 511, iy & 511)];
-			bool startSolid = iz >= 64 || (iz >= 0 && ((col >> iz) & 1ull));
-			if (startSolid) {
-				flags = 1u | (1u << 8);
-				bx = ix;
-				by = iy;
-				bz = iz;
-			} else {
-				const bool px = dx > 0.f, py = dy > 0.f, pz = dz > 0.f;
-				float fx = px ? __fsub_rn((float)(ix + 1), v0x) : __fsub_rn(v0x, (float)ix);
-				float fy = py ? __fsub_rn((float)(iy + 1), v0y) : __fsub_rn(v0y, (float)iy);
-				float fz = pz ? __fsub_rn((float)(iz + 1), v0z) : __fsub_rn(v0z, (float)iz);
-				const float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
-				const float invX = dx != 0.f ? __fdiv_rn(1.f, ax) : dx;
-				const float invY = dy != 0.f ? __fdiv_rn(1.f, ay) : dy;
-				const float invZ = dz != 0.f ? __fdiv_rn(1.f, az) : dz;
-				const bool hasX = invX != 0.f, hasY = invY != 0.f, hasZ = invZ != 0.f;
-				const int sx = px ? 1 : -1, sy = py ? 1 : -1, sz = pz ? 1 : -1;
-
-				for (int s = 0; s < maxSteps; s++) {
-					int axis = 0;
-					float t = 0.f;
-					if (hasX) {
-						t = __fmul_rn(fx, invX);
-						axis = 1;
+		for (;;) {
+			const unsigned idle = __ballot_sync(0xffffffffu, !active);
+			if (idle == 0xffffffffu && next >= end)
+				break;
+			if (next < end && (idle == 0xffffffffu || __popc(idle) >= kRefillAt)) {
+				// ---- hand the idle lanes the next rays; set-up = GameMap.cpp:361-411 ----
+				const size_t mine = next + __popc(idle & ((1u << lane) - 1u));
+				next += __popc(idle);
+				if (!active && mine < end) {
+					const float v0x = v0s[mine * 3], v0y = v0s[mine * 3 + 1], v0z = v0s[mine * 3 + 2];
+					float dx = dirs[mine * 3], dy = dirs[mine * 3 + 1], dz = dirs[mine * 3 + 2];
+					// dir = dir.Normalize()  (Core/Math.h:369-374; GetLength = sqrtf(x*x + y*y + z*z))
+					float scale = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+					if (scale != 0.f)
+						scale = __fdiv_rn(1.f, scale);
+					dx = __fmul_rn(dx, scale);
+					dy = __fmul_rn(dy, scale);
+					dz = __fmul_rn(dz, scale);
+					const int ix = x86_f2i(floorf(v0x)), iy = x86_f2i(floorf(v0y)), iz = x86_f2i(floorf(v0z));
+					const uint64_t col = solid[osb::tiled_index(ix & 511, iy & 511)];
+					if (solid_at(col, iz)) { // startSolid (:375-384)
+						write_hit(out, mine, 1u | (1u << 8), v0x, v0y, v0z, ix, iy, iz, 0, 0, 0);
+					} else if (maxSteps <= 0) { // the loop never runs: hit = false, hitPos = v0, rest untouched (:503-506)
+						write_hit(out, mine, 0u, v0x, v0y, v0z, 0, 0, 0, 0, 0, 0);
+					} else {
+						const bool px = dx > 0.f, py = dy > 0.f, pz = dz > 0.f;
+						r.fx = px ? __fsub_rn((float)(ix + 1), v0x) : __fsub_rn(v0x, (float)ix);
+						r.fy = py ? __fsub_rn((float)(iy + 1), v0y) : __fsub_rn(v0y, (float)iy);
+						r.fz = pz ? __fsub_rn((float)(iz + 1), v0z) : __fsub_rn(v0z, (float)iz);
+						r.ax = fabsf(dx);
+						r.ay = fabsf(dy);
+						r.az = fabsf(dz);
+						r.invX = dx != 0.f ? __fdiv_rn(1.f, r.ax) : dx;
+						r.invY = dy != 0.f ? __fdiv_rn(1.f, r.ay) : dy;
+						r.invZ = dz != 0.f ? __fdiv_rn(1.f, r.az) : dz;
+						r.sign = (px ? 1u : 0u) | (py ? 2u : 0u) | (pz ? 4u : 0u);
+						r.ix = ix;
+						r.iy = iy;
+						r.iz = iz;
+						r.col = col;
+						r.steps = 0;
+						r.axis = 0;
+						r.ray = mine;
+						active = true;
 					}
-					if (hasY) {
-						float ty = __fmul_rn(fy, invY);
-						if (!axis || ty < t) {
-							t = ty;
-							axis = 2;
-						}
-					}
-					if (hasZ) {
-						float tz = __fmul_rn(fz, invZ);
-						if (!axis || tz < t) {
-							t = tz;
-							axis = 3;
-						}
-					}
-					fx = axis == 1 ? 1.f : __fsub_rn(fx, __fmul_rn(ax, t));
-					fy = axis == 2 ? 1.f : __fsub_rn(fy, __fmul_rn(ay, t));
-					fz = axis == 3 ? 1.f : __fsub_rn(fz, __fmul_rn(az, t));
-
-					int qx = ix + (axis == 1 ? sx : 0);
-					int qy = iy + (axis == 2 ? sy : 0);
-					int qz = iz + (axis == 3 ? sz : 0);
-					bx = qx;
-					by = qy;
-					bz = qz;
-					nx = ix - qx;
-					ny = iy - qy;
-					nz = iz - qz;
-					if (axis == 1 || axis == 2)
-						col = solid[osb::tiled_index(qx & 511, qy & 511)];
-					bool isSolid = qz >= 64 || (qz >= 0 && ((col >> qz) & 1ull));
-					if (isSolid) {
-						hx = px ? __fsub_rn((float)(qx + 1), fx) : __fadd_rn((float)qx, fx);
-						hy = py ? __fsub_rn((float)(qy + 1), fy) : __fadd_rn((float)qy, fy);
-						hz = pz ? __fsub_rn((float)(qz + 1), fz) : __fadd_rn((float)qz, fz);
-						flags = 1u;
-						break;
-					}
-					ix = qx;
-					iy = qy;
-					iz = qz;
 				}
 			}
-			my[0] = flags;
-			my[1] = __float_as_uint(hx);
-			my[2] = __float_as_uint(hy);
-			my[3] = __float_as_uint(hz);
-			my[4] = (uint32_t)bx;
-			my[5] = (uint32_t)by;
-			my[6] = (uint32_t)bz;
-			my[7] = (uint32_t)nx;
-			my[8] = (uint32_t)ny;
-			my[9] = (uint32_t)nz;
-		}
-		__syncwarp();
-		// coalesced write-out of this warp's 32 records (320 words)
-		const size_t wbase = base + (size_t)warp * 32;
-		if (wbase < n) {
-			size_t cnt = n - wbase;
-			if (cnt > 32)
-				cnt = 32;
-			const uint32_t *src = s_out + (size_t)warp * 32 * kWordsPerHit;
-			uint32_t *dst = out + wbase * kWordsPerHit;
-			const int words = (int)cnt * kWordsPerHit;
-			for (int w = lane; w < words; w += 32)
-				dst[w] = src[w];
+			// ---- a few DDA steps between idle checks (:413-497) ----
+#pragma unroll 1
+			for (int k = 0; k < 4; k++) {
+				if (active) {
+					const bool hasX = r.invX != 0.f, hasY = r.invY != 0.f, hasZ = r.invZ != 0.f;
+					int axis = 0;
+					float t = 0.f;
+					const float tx = __fmul_rn(r.fx, r.invX), ty = __fmul_rn(r.fy, r.invY), tz = __fmul_rn(r.fz, r.invZ);
+					if (hasX) {
+						t = tx;
+						axis = 1;
+					}
+					if (hasY && (!axis || ty < t)) {
+						t = ty;
+						axis = 2;
+					}
+					if (hasZ && (!axis || tz < t)) {
+						t = tz;
+						axis = 3;
+					}
+					const float nfx = __fsub_rn(r.fx, __fmul_rn(r.ax, t));
+					const float nfy = __fsub_rn(r.fy, __fmul_rn(r.ay, t));
+					const float nfz = __fsub_rn(r.fz, __fmul_rn(r.az, t));
+					r.fx = axis == 1 ? 1.f : nfx;
+					r.fy = axis == 2 ? 1.f : nfy;
+					r.fz = axis == 3 ? 1.f : nfz;
+					r.ix += axis == 1 ? ((r.sign & 1u) ? 1 : -1) : 0;
+					r.iy += axis == 2 ? ((r.sign & 2u) ? 1 : -1) : 0;
+					r.iz += axis == 3 ? ((r.sign & 4u) ? 1 : -1) : 0;
+					r.axis = axis;
+					r.steps++;
+					if (axis == 1 || axis == 2)
+						r.col = solid[osb::tiled_index(r.ix & 511, r.iy & 511)];
+					const bool hit = solid_at(r.col, r.iz);
+					if (hit || r.steps >= maxSteps) {
+						// normal = iv - next = minus the step just taken; a zero-axis step (all components 0) moves nowhere
+						const int nx = axis == 1 ? ((r.sign & 1u) ? -1 : 1) : 0;
+						const int ny = axis == 2 ? ((r.sign & 2u) ? -1 : 1) : 0;
+						const int nz = axis == 3 ? ((r.sign & 4u) ? -1 : 1) : 0;
+						float hx, hy, hz;
+						if (hit) {
+							hx = (r.sign & 1u) ? __fsub_rn((float)(r.ix + 1), r.fx) : __fadd_rn((float)r.ix, r.fx);
+							hy = (r.sign & 2u) ? __fsub_rn((float)(r.iy + 1), r.fy) : __fadd_rn((float)r.iy, r.fy);
+							hz = (r.sign & 4u) ? __fsub_rn((float)(r.iz + 1), r.fz) : __fadd_rn((float)r.iz, r.fz);
+						} else { // hit = false, hitPos = v0 (:503-506); hitBlock / normal = last visited
+							hx = v0s[r.ray * 3];
+							hy = v0s[r.ray * 3 + 1];
+							hz = v0s[r.ray * 3 + 2];
+						}
+						write_hit(out, r.ray, hit ? 1u : 0u, hx, hy, hz, r.ix, r.iy, r.iz, nx, ny, nz);
+						active = false;
+					}
+				}
+			}
 		}
 	}
 } // namespace
@@ -158,7 +193,8 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	}
 	static_assert(sizeof(osb200_rayhit) == 40, "RayCastResult layout");
 	OSB_CUDA(cudaSetDevice(c->device));
-	size_t blocks = (n + kThreads - 1) / kThreads;
+	const size_t warps = (n + kRaysPerWarp - 1) / kRaysPerWarp;
+	size_t blocks = (warps * 32 + kThreads - 1) / kThreads;
 	{
 		osb::KLaunch kl(c, osb::K_CASTRAY2);
 		k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(c->d_solid, d_v0, d_dir, maxSteps,
