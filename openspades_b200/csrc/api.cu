@@ -269,6 +269,7 @@ void osb200_destroy(osb200_ctx *c) {
 	cudaFree(c->d_rcp);
 	cudaFree(c->d_rsqrt);
 	cudaFree(c->d_scratch);
+	cudaFree(c->d_rayCursor);
 	cudaFree(c->d_stage);
 	if (c->h_stage)
 		cudaFreeHost(c->h_stage);

@@ -9,6 +9,8 @@
 // are transposed through shared memory so that each warp writes its 1280 B contiguously.
 #include "ctx.h"
 
+#include <algorithm>
+
 namespace {
 
 	// x86 cvttss2si semantics ("integer indefinite" on overflow/NaN) for (int)floorf(x), Core/Math.h:376-378
@@ -18,7 +20,7 @@ namespace {
 
 	constexpr int kThreads = 128;
 	constexpr int kWordsPerHit = 10;   // sizeof(osb200_rayhit) / 4
-	constexpr int kRaysPerWarp = 1024; // contiguous share of the batch one warp works through
+	constexpr int kCtasPerSm = 10;     // persistent grid: 48 registers x 128 threads -> 10 CTAs per SM
 	constexpr int kRefillAt = 8;       // idle lanes that trigger a refill (ray set-up is the divergent part)
 
 	struct RayState {
@@ -51,19 +53,17 @@ namespace {
 		return z >= 64;
 	}
 
-	// Each warp owns kRaysPerWarp consecutive rays and keeps its 32 lanes busy: a lane whose ray has ended
-	// (hit, start-solid or step limit) writes its record and waits; once kRefillAt lanes wait, they are handed
-	// the next rays of the warp's share.  Ray lengths differ by two orders of magnitude (start-solid: 0 steps,
-	// sky rays: maxSteps), so one-ray-per-thread leaves two thirds of the lanes idle.
+	// Persistent grid (one CTA slot per resident CTA).  Every warp keeps its 32 lanes busy: a lane whose ray has
+	// ended (hit, start-solid or step limit) writes its record and waits; once kRefillAt lanes wait, the warp takes
+	// that many rays from the batch-wide cursor (one atomicAdd per refill) and re-arms them.  Ray lengths differ by
+	// two orders of magnitude (start-solid: 0 steps, sky rays: maxSteps), so one-ray-per-thread left two thirds
+	// of the lanes idle, and a static split left whole SMs idle in the tail.
 	__global__ void __launch_bounds__(kThreads)
 	  k_castray2(const uint64_t *__restrict__ solid, const float *__restrict__ v0s,
-	             const float *__restrict__ dirs, int maxSteps, uint32_t *__restrict__ out, size_t n) {
+	             const float *__restrict__ dirs, int maxSteps, uint32_t *__restrict__ out, size_t n,
+	             unsigned long long *__restrict__ cursor) {
 		const int lane = threadIdx.x & 31;
-		const size_t warpId = ((size_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
-		size_t next = warpId * kRaysPerWarp;
-		const size_t end = min(next + (size_t)kRaysPerWarp, n);
-		if (next >= n)
-			return;
+		bool drained = false; // the cursor ran past n: no more refills for this warp
 		RayState r;
 		bool active = false;
 		r.fx = r.fy = r.fz = r.ax = r.ay = r.az = r.invX = r.invY = r.invZ = 0.f;
@@ -74,12 +74,17 @@ namespace {
 
 		for (;;) {
 			const unsigned idle = __ballot_sync(0xffffffffu, !active);
-			if (idle == 0xffffffffu && next >= end)
+			if (idle == 0xffffffffu && drained)
 				break;
-			if (next < end && (idle == 0xffffffffu || __popc(idle) >= kRefillAt)) {
+			if (!drained && (idle == 0xffffffffu || __popc(idle) >= kRefillAt)) {
 				// ---- hand the idle lanes the next rays; set-up = GameMap.cpp:361-411 ----
-				const size_t mine = next + __popc(idle & ((1u << lane) - 1u));
-				next += __popc(idle);
+				unsigned long long base = 0;
+				if (lane == 0)
+					base = atomicAdd(cursor, (unsigned long long)__popc(idle));
+				base = __shfl_sync(0xffffffffu, base, 0);
+				const size_t end = n;
+				const size_t mine = (size_t)base + __popc(idle & ((1u << lane) - 1u));
+				drained = base + __popc(idle) >= n;
 				if (!active && mine < end) {
 					const float v0x = v0s[mine * 3], v0y = v0s[mine * 3 + 1], v0z = v0s[mine * 3 + 2];
 					float dx = dirs[mine * 3], dy = dirs[mine * 3 + 1], dz = dirs[mine * 3 + 2];
@@ -193,12 +198,14 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	}
 	static_assert(sizeof(osb200_rayhit) == 40, "RayCastResult layout");
 	OSB_CUDA(cudaSetDevice(c->device));
-	const size_t warps = (n + kRaysPerWarp - 1) / kRaysPerWarp;
-	size_t blocks = (warps * 32 + kThreads - 1) / kThreads;
+	if (!c->d_rayCursor)
+		OSB_CUDA(cudaMalloc(&c->d_rayCursor, sizeof(unsigned long long)));
+	OSB_CUDA(cudaMemsetAsync(c->d_rayCursor, 0, sizeof(unsigned long long), c->stream));
+	size_t blocks = std::min<size_t>((size_t)c->smCount * kCtasPerSm, (n + kThreads - 1) / kThreads);
 	{
 		osb::KLaunch kl(c, osb::K_CASTRAY2);
 		k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(c->d_solid, d_v0, d_dir, maxSteps,
-		                                                       reinterpret_cast<uint32_t *>(d_out), n);
+		                                                       reinterpret_cast<uint32_t *>(d_out), n, c->d_rayCursor);
 	}
 	OSB_CUDA(cudaGetLastError());
 	return 0;

@@ -98,6 +98,8 @@ struct osb200_ctx {
 	uint32_t *d_rsqrt = nullptr;
 	int rsqrtBits = 0;
 
+	unsigned long long *d_rayCursor = nullptr; // batch-wide work cursor of k_castray2
+
 	// ---- scratch for host-pointer convenience entry points ----
 	void *d_scratch = nullptr;
 	size_t d_scratch_bytes = 0;

@@ -21,6 +21,6 @@ ctx.sync()
 print('chunks', ctx.radiosity_update(-1))
 PY
 python /tmp/drv.py > gpurun_out/plain_misc.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'k_castray2|k_radiosity' -s 2 -c 2 \
-  -o gpurun_out/prof_r01_misc python /tmp/drv.py > gpurun_out/ncu_misc.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'k_castray2' -s 2 -c 2 \
+  -o gpurun_out/prof_r01b_misc python /tmp/drv.py > gpurun_out/ncu_misc.log 2>&1
 echo "ncu rc=$?"; tail -2 gpurun_out/ncu_misc.log
