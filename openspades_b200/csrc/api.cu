@@ -29,20 +29,20 @@ namespace osb {
 		                                     "k_rad_select"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
-	KLaunch::KLaunch(osb200_ctx *ctx, int kid) : c(ctx), slot(-1) {
+	KLaunch::KLaunch(osb200_ctx *ctx, int kid, cudaStream_t stream) : c(ctx), slot(-1), st(stream ? stream : ctx->stream) {
 		c->launches++;
 		if (!c->timing)
 			return;
 		osb200_ctx::TimedLaunch t{kid, c->take_event(), c->take_event()};
 		if (!t.a || !t.b)
 			return;
-		cudaEventRecord(t.a, c->stream);
+		cudaEventRecord(t.a, st);
 		c->timed.push_back(t);
 		slot = (int)c->timed.size() - 1;
 	}
 	KLaunch::~KLaunch() {
 		if (slot >= 0)
-			cudaEventRecord(c->timed[slot].b, c->stream);
+			cudaEventRecord(c->timed[slot].b, st);
 	}
 	void terrain_destroy(osb200_ctx *ctx);   // terrain.cu
 	void radiosity_destroy(osb200_ctx *ctx); // radiosity.cu

@@ -56,7 +56,8 @@ namespace osb {
 	struct KLaunch {
 		osb200_ctx *c;
 		int slot;
-		KLaunch(osb200_ctx *c, int kid);
+		cudaStream_t st;
+		KLaunch(osb200_ctx *c, int kid, cudaStream_t stream = nullptr); // default: the context stream
 		~KLaunch();
 	};
 } // namespace osb

@@ -61,8 +61,27 @@ namespace osbn {
 		return __uint_as_float(((uint32_t)re << 23) | (r & 0x7fffff));
 	}
 
+	// rcpss for callers that only use the value when x is a normal number of magnitude >= 2^-126 (ToSpecialTan uses
+	// it for |x| > 1, the DDA for distances >= 1e-20): normal input, normal result, no branch.  Huge / inf / NaN
+	// inputs still go through the general routine; for zero and denormals the value is unspecified.
+	__device__ __forceinline__ float rcpss_normal(float x, const SseTables &t) {
+		const uint32_t u = __float_as_uint(x);
+		const uint32_t e = (u >> 23) & 0xff;
+		const uint32_t r = __ldg(t.rcp + ((u & 0x7fffff) >> (23 - t.rcpBits)));
+		if (e >= 253u)
+			return rcpss(x, t);
+		return __uint_as_float((u & 0x80000000u) | (r + ((127u - e) << 23)));
+	}
+
 	template <bool kSse> struct Num {
 		SseTables t;
+		// reciprocal whose value is only used when |b| > 1 (or b a DDA distance >= 1e-20): skips nothing in IEEE
+		// mode, takes the branch-free table path in SSE mode
+		__device__ __forceinline__ float rcpBig(float b) const {
+			if (kSse)
+				return rcpss_normal(b, t);
+			return __fdiv_rn(1.f, b);
+		}
 		__device__ __forceinline__ float rcp(float b) const {
 			if (kSse)
 				return rcpss(b, t);

@@ -110,19 +110,27 @@ namespace osb {
 		}
 	}
 
-	struct TerrainState {
-		// chunk-sized device buffers
-		ViewParams *d_views = nullptr;
-		ViewParams *h_views = nullptr; // pinned
-		size_t viewCap = 0, dViewCap = 0, lineParamCap = 0, hTabCap = 0;
+	// Per-chunk working set.  Two of them, each with its own stream: chunk k+1's line build runs beside chunk k's
+	// gather and fills the SMs that chunk k's launch tail leaves idle (a single yaw line is ~150 dependent DDA steps,
+	// so every k_build_lines launch ends in a long low-occupancy tail).
+	struct ChunkBufs {
 		float2 *d_lineDirs = nullptr;
 		int4 *d_lineParams = nullptr;
 		uint2 *d_strips = nullptr;
-		size_t lineCap = 0, stripCap = 0;
 		float *d_tabs = nullptr;
+		size_t lineCap = 0, lineParamCap = 0, stripCap = 0, tabCap = 0;
+		cudaStream_t stream = nullptr;
+		cudaEvent_t done = nullptr; // last kernel of the newest chunk that used this set
+	};
+
+	struct TerrainState {
+		ViewParams *d_views = nullptr;
+		ViewParams *h_views = nullptr; // pinned
+		size_t viewCap = 0, dViewCap = 0, hTabCap = 0;
+		ChunkBufs set[2];
 		float *h_tabs = nullptr; // pinned (host-prep path)
 		float2 *h_lineDirs = nullptr;
-		size_t tabCap = 0, hLineCap = 0;
+		size_t hLineCap = 0;
 		uint16_t *d_atan = nullptr; // 4 x 5000: sm, lg, smN, lgN
 		// persistent output buffers of the host-pointer entry point
 		uint32_t *d_fb = nullptr;
@@ -130,39 +138,47 @@ namespace osb {
 		size_t outCap = 0;
 		cudaEvent_t stageFree = nullptr;
 		cudaStream_t copyStream = nullptr; // D2H of finished chunks, overlapped with the next chunk's kernels
-		cudaEvent_t chunkDone = nullptr, copyDone = nullptr;
+		cudaEvent_t fork = nullptr, copyDone = nullptr;
 	};
 } // namespace osb
 
 namespace osb {
 
 	#ifndef OSB_LINE_THREADS
-#define OSB_LINE_THREADS 32
+#define OSB_LINE_THREADS 64
 #endif
 	constexpr int kLineThreads = OSB_LINE_THREADS; // lines per CTA of k_build_lines
+#ifndef OSB_COLOR_EARLY
+#define OSB_COLOR_EARLY 0
+#endif
+#ifndef OSB_EXP
+#define OSB_EXP 0
+#endif
+#ifndef OSB_TRANSFORM_BRANCHY
+#define OSB_TRANSFORM_BRANCHY 1
+#endif
+#ifdef OSB_STATS
+	__device__ unsigned long long g_stats[16];
+#define STAT(i, n) atomicAdd(&g_stats[i], (unsigned long long)(n))
+#else
+#define STAT(i, n)
+#endif
 	enum { F_POSX = 0, F_NEGX = 1, F_POSY = 2, F_NEGY = 3, F_POSZ = 4, F_NEGZ = 5 }; // SWMapRenderer.cpp:68
 
-	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map.
-	template <bool kSse2Shade> __device__ __forceinline__ uint32_t shade(uint32_t col, int face) {
+	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map; mode 0 = NegY walls and
+	// tops (NegZ), 1 = PosX/PosY/NegX walls, 2 = undersides (PosZ).  All four 8-bit lanes are shaded in one
+	// register: (x>>1)+(x>>2) <= 190 never carries into the neighbouring lane.
+	template <bool kSse2Shade> __device__ __forceinline__ uint32_t shade(uint32_t col, int mode) {
 		if (kSse2Shade) {
 			// 16-bit lanes B,G,R,H: PosZ >>1; PosX/PosY/NegX (>>1)+(>>2); health<100 >>1; pack; filled bit
-			uint32_t b = (col >> 16) & 0xff, g = (col >> 8) & 0xff, r = col & 0xff, h = col >> 24;
-			const bool weak = h < 100;
-			if (face == F_POSZ) {
-				b >>= 1; g >>= 1; r >>= 1; h >>= 1;
-			} else if (face == F_POSX || face == F_POSY || face == F_NEGX) {
-				b = (b >> 1) + (b >> 2); g = (g >> 1) + (g >> 2); r = (r >> 1) + (r >> 2); h = (h >> 1) + (h >> 2);
-			}
-			if (weak) {
-				b >>= 1; g >>= 1; r >>= 1; h >>= 1;
-			}
-			return (b | (g << 8) | (r << 16) | (h << 24)) | (1u << 24);
+			const bool weak = (col >> 24) < 100u;
+			const uint32_t half = (col >> 1) & 0x7f7f7f7fu, quarter = (col >> 2) & 0x3f3f3f3fu;
+			uint32_t v = mode == 2 ? half : (mode == 1 ? half + quarter : col);
+			v = weak ? (v >> 1) & 0x7f7f7f7fu : v;
+			return __byte_perm(v, 0u, 0x3012) | (1u << 24); // H B G R -> H R G B
 		} else {
-			uint32_t c = (col & 0xff00) | ((col & 0xff) << 16) | ((col & 0xff0000) >> 16);
-			if (face == F_POSZ)
-				c = (c & 0xfcfcfc) >> 2;
-			else if (face == F_POSX || face == F_POSY || face == F_NEGX)
-				c = (c & 0xfefefe) >> 1;
+			uint32_t c = __byte_perm(col, 0u, 0x4012); // 0 R G B
+			c = mode == 2 ? (c & 0xfcfcfcu) >> 2 : (mode == 1 ? (c & 0xfefefeu) >> 1 : c);
 			return c | (1u << 24);
 		}
 	}
@@ -170,58 +186,33 @@ namespace osb {
 	template <bool kSse> struct LineCtx {
 		osbn::Num<kSse> num;
 		float cz, transScale, transOffset, vmax;
-		// transform lambda, SWMapRenderer.cpp:395-401
+		// transform lambda, SWMapRenderer.cpp:395-401 (ToSpecialTan :59-66 inlined).  Branch-free: the reciprocal is
+		// always formed and selected by |v| > 1, so lanes on different sides of the seam share one instruction stream.
 		__device__ __forceinline__ int transform(float invDist, int z) const {
 			const float zv = __fsub_rn((float)z, cz);
-			float p = __fadd_rn(__fmul_rn(num.toSpecialTan(__fmul_rn(invDist, zv)), transScale), transOffset);
-			p = p < 0.f ? 0.f : p;
-			p = vmax < p ? vmax : p;
+			const float v = __fmul_rn(invDist, zv);
+#if OSB_TRANSFORM_BRANCHY
+			float t = v;
+			if (fabsf(v) > 1.f)
+				t = __fsub_rn(v < 0.f ? -2.f : 2.f, num.rcpBig(v));
+#else
+			const float r = num.rcpBig(v);
+			float t = v;
+			t = v < -1.f ? __fsub_rn(-2.f, r) : t;
+			t = v > 1.f ? __fsub_rn(2.f, r) : t;
+#endif
+			float p = __fadd_rn(__fmul_rn(t, transScale), transOffset);
+			// p < 0 ? 0 : p;  vmax < p ? vmax : p;  truncation.  p is never NaN here (finite * finite), and a NaN
+			// would end as 0 either way (cvttss2si of the clamp result vs fmaxf dropping the NaN).
+			p = fminf(fmaxf(p, 0.f), vmax);
 			return __float2int_rz(p);
 		}
 	};
 
-	// Writes [from,to) of the strip where still empty.  `filled` is this thread's bitmask in shared
-	// memory, word-major across the CTA (filled[word * kLineThreads]) so lanes never share a bank.
-	__device__ __forceinline__ void fill_span(uint2 *__restrict__ strip, uint32_t *filled, int from, int to,
-	                                          uint32_t combined, float depth) {
-		const uint2 px = make_uint2(combined, __float_as_uint(depth));
-		int w0 = from >> 5, w1 = (to - 1) >> 5;
-		for (int w = w0; w <= w1; w++) {
-			uint32_t m = 0xffffffffu;
-			if (w == w0)
-				m &= 0xffffffffu << (from & 31);
-			if (w == w1)
-				m &= 0xffffffffu >> (31 - ((to - 1) & 31));
-			const uint32_t cur = filled[w * kLineThreads];
-			uint32_t todo = m & ~cur;
-			if (!todo)
-				continue;
-			filled[w * kLineThreads] = cur | todo;
-			while (todo) {
-				const int b = __ffs(todo) - 1;
-				todo &= todo - 1;
-				__stcs(strip + ((w << 5) + b), px);
-			}
-		}
-	}
-	__device__ __forceinline__ bool span_has_empty(const uint32_t *filled, int from, int to) {
-		int w0 = from >> 5, w1 = (to - 1) >> 5;
-		for (int w = w0; w <= w1; w++) {
-			uint32_t m = 0xffffffffu;
-			if (w == w0)
-				m &= 0xffffffffu << (from & 31);
-			if (w == w1)
-				m &= 0xffffffffu >> (31 - ((to - 1) & 31));
-			if (m & ~filled[w * kLineThreads])
-				return true;
-		}
-		return false;
-	}
-
 	// One thread = one yaw line (SWMapRenderer::BuildLine, SWMapRenderer.cpp:219-671).
 	template <bool kSse, bool kSse2Shade>
 #ifndef OSB_LINE_MINB
-#define OSB_LINE_MINB 1
+#define OSB_LINE_MINB 14
 #endif
 	__global__ void __launch_bounds__(kLineThreads, OSB_LINE_MINB)
 	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
@@ -379,33 +370,30 @@ namespace osb {
 
 		// One DDA step (:426-522) depends only on (rx, ry), never on map data, so the step after the current
 		// one is computed ahead and its column mask is requested before the current step's spans are
-		// processed: the dependent 8-byte load is off the critical path.
+		// processed: the dependent 8-byte load is off the critical path.  Both crossing cases are formed with
+		// selects so that lanes crossing x and lanes crossing y stay in one instruction stream.
 		struct Step {
-			int rx, ry, irx, iry, wallFace;
+			int rx, ry, irx, iry, wallMode;
 			float distance;
 			uint32_t t;
 		};
+		const int sx = posX ? 1 : -1, sy = posY ? 1 : -1;
+		const int edgeX = posX ? 0 : 1, edgeY = posY ? 0 : 1;
+		// wall face of an x crossing is NegX / PosX (both 3/4-shaded, mode 1); of a y crossing NegY (mode 0) / PosY (1)
+		const int wallModeY = posY ? 0 : 1;
 		auto advance = [&](int rx0, int ry0, int irx0, int iry0, float dist0) -> Step {
 			Step n;
 			const uint32_t tx = (uint32_t)((posX ? 512 - (rx0 & 511) : (rx0 & 511)) * invDirXI);
 			const uint32_t ty = (uint32_t)((posY ? 512 - (ry0 & 511) : (ry0 & 511)) * invDirYI);
-			if (tx < ty) {
-				n.irx = irx0 + (posX ? 1 : -1);
-				n.iry = iry0;
-				n.rx = posX ? (n.irx << 9) : (n.irx << 9) - 1;
-				const int d = (int)((dirYI * tx) >> 17);
-				n.ry = posY ? ry0 + d : ry0 - d;
-				n.distance = __fadd_rn(dist0, __fmul_rn((float)tx, 1.f / 512.f / 256.f));
-				n.wallFace = posX ? F_NEGX : F_POSX;
-			} else {
-				n.iry = iry0 + (posY ? 1 : -1);
-				n.irx = irx0;
-				const int d = (int)((dirXI * ty) >> 17);
-				n.rx = posX ? rx0 + d : rx0 - d;
-				n.ry = posY ? (n.iry << 9) : (n.iry << 9) - 1;
-				n.distance = __fadd_rn(dist0, __fmul_rn((float)ty, 1.f / 512.f / 256.f));
-				n.wallFace = posY ? F_NEGY : F_POSY;
-			}
+			const bool xs = tx < ty;
+			const uint32_t tt = xs ? tx : ty;
+			const int d = (int)(((xs ? dirYI : dirXI) * tt) >> 17);
+			n.irx = irx0 + (xs ? sx : 0);
+			n.iry = iry0 + (xs ? 0 : sy);
+			n.rx = xs ? (n.irx << 9) - edgeX : rx0 + sx * d;
+			n.ry = xs ? ry0 + sy * d : (n.iry << 9) - edgeY;
+			n.distance = __fadd_rn(dist0, __fmul_rn((float)tt, 1.f / 512.f / 256.f));
+			n.wallMode = xs ? 1 : wallModeY;
 			n.t = tiled_index(n.irx & 511, n.iry & 511);
 			return n;
 		};
@@ -416,54 +404,78 @@ namespace osb {
 			// ---- take the precomputed step, start the one after it ----
 			const Step cur = nx;
 			const uint64_t sNew = sNext;
+			STAT(0, 1);
 			distance = cur.distance;
 			nx = advance(cur.rx, cur.ry, cur.irx, cur.iry, cur.distance);
 			sNext = solid[nx.t];
-			const int wallFace = cur.wallFace;
 			const uint32_t tNew = cur.t;
 
 			const float oldInvDist = invDist;
-			invDist = num.rcp(distance);
+			invDist = num.rcpBig(distance); // distance is in [1e-20, ~200]
 			const float medDist = __fadd_rn(__fmul_rn(distance, zscale), depthBias);
 
 			// ---- spans of this step, one merged work list per lane, in the reference's order:
 			//   floor tops of the cell being left (ascending z, :584-603), its ceilings (descending z, :604-622),
 			//   then the walls of the cell being entered for the crossed face (ascending z, :627-657).
-			// Merging the three loops keeps lanes with different mixes of work in one instruction stream.
-			uint64_t tops = sOld & ~(sOld << 1) & belowEye;                   // solid, air above, below the eye
-			uint64_t bots = sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye;   // solid, air below, above the eye
-			uint64_t walls = sNew & ~sOld;                                    // solid there, air in the cell left
-			int savedZ = 127, savedP = 0;
-			while (tops | bots | walls) {
-				int z, kind;
-				if (tops) {
-					z = __ffsll((long long)tops) - 1;
-					tops &= tops - 1;
-					kind = 0;
-				} else if (bots) {
-					z = 63 - __clzll((long long)bots);
-					bots &= ~(1ull << z);
-					kind = 1;
-				} else {
-					z = __ffsll((long long)walls) - 1;
-					walls &= walls - 1;
-					kind = 2;
-				}
+			// One loop body serves all three kinds (ceilings are kept bit-reversed so that "next" is always the
+			// lowest set bit), and everything up to the landing test is straight-line code.
+			uint64_t tops = sOld & ~(sOld << 1) & belowEye;                                // solid, air above, below the eye
+			uint64_t botsR = __brevll(sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye);      // solid, air below, above the eye
+			uint64_t walls = sNew & ~sOld;                                                  // solid there, air in the cell left
+			while (tops | botsR | walls) {
+				const bool isTop = tops != 0, isBot = !isTop && botsR != 0;
+				const uint64_t src = isTop ? tops : (isBot ? botsR : walls);
+				const int bit = __ffsll((long long)src) - 1;
+				const uint64_t rest = src & (src - 1);
+				tops = isTop ? rest : tops;
+				botsR = isBot ? rest : botsR;
+				walls = (isTop || isBot) ? walls : rest;
+				const int z = isBot ? 63 - bit : bit;
+				const bool isWall = !(isTop || isBot);
+#if OSB_COLOR_EARLY
 				// colour is requested before the projection math; it is only used when the span lands
-				const uint32_t rawCol = color[(size_t)(kind == 2 ? tNew : tOld) * 64 + z];
-				const int zA = kind == 1 ? z + 1 : z;       // first transform: (invDist, zA)
-				const int zB = kind == 0 ? z : z + 1;       // second: (oldInvDist or invDist, zB)
-				const int pA = (kind == 2 && savedZ == z) ? savedP : L.transform(invDist, zA);
-				const int pB = L.transform(kind == 2 ? invDist : oldInvDist, zB);
-				if (kind == 2) {
-					savedZ = z + 1;
-					savedP = pB;
-				}
-				const int from = kind == 1 ? pB : pA, to = kind == 1 ? pA : pB;
-				if (from < to && span_has_empty(filled, from, to)) {
-					const int face = kind == 0 ? F_NEGZ : (kind == 1 ? F_POSZ : wallFace);
-					const uint32_t c = shade<kSse2Shade>(rawCol, face);
-					fill_span(strip, filled, from, to, c, __fadd_rn(medDist, __fmul_rn((float)zA, heightScale)));
+				const uint32_t rawCol = color[(size_t)(isWall ? tNew : tOld) * 64 + z];
+#endif
+				const int zA = isBot ? z + 1 : z;      // first transform: (invDist, zA)
+				const int zB = isTop ? z : z + 1;      // second: (oldInvDist or invDist, zB)
+				const int pA = L.transform(invDist, zA);
+				const int pB = L.transform(isWall ? invDist : oldInvDist, zB);
+				const int from = isBot ? pB : pA, to = isBot ? pA : pB;
+				if (from < to) {
+					const int w0 = from >> 5, w1 = (to - 1) >> 5;
+					const uint32_t mFirst = 0xffffffffu << (from & 31), mLast = 0xffffffffu >> (31 - ((to - 1) & 31));
+					uint2 px;
+					bool havePx = false;
+					for (int w = w0; w <= w1; w++) {
+						uint32_t m = 0xffffffffu;
+						m = w == w0 ? m & mFirst : m;
+						m = w == w1 ? m & mLast : m;
+						const uint32_t curMask = filled[w * kLineThreads];
+						uint32_t todo = m & ~curMask;
+						if (!todo)
+							continue;
+						filled[w * kLineThreads] = curMask | todo;
+						if (!havePx) {
+#if OSB_EXP == 1
+							const uint32_t rawCol = 0x64000000u | (uint32_t)z * 0x030201u;
+#elif !OSB_COLOR_EARLY
+							const uint32_t rawCol = color[(size_t)(isWall ? tNew : tOld) * 64 + z];
+#endif
+							const int mode = isTop ? 0 : (isBot ? 2 : cur.wallMode);
+							px = make_uint2(shade<kSse2Shade>(rawCol, mode),
+							                __float_as_uint(__fadd_rn(medDist, __fmul_rn((float)zA, heightScale))));
+							havePx = true;
+						}
+						uint2 *dst = strip + (w << 5);
+						do {
+							const int b = __ffs(todo) - 1;
+							todo &= todo - 1;
+#if OSB_EXP == 2
+							if (px.x == 0xdeadbeefu)
+#endif
+							__stcs(dst + b, px);
+						} while (todo);
+					}
 				}
 			}
 			sOld = sNew;
@@ -766,8 +778,12 @@ namespace osb {
 		OSB_CUDA(cudaMemcpy(T->d_atan, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
 		OSB_CUDA(cudaEventCreateWithFlags(&T->stageFree, cudaEventDisableTiming));
 		OSB_CUDA(cudaStreamCreateWithFlags(&T->copyStream, cudaStreamNonBlocking));
-		OSB_CUDA(cudaEventCreateWithFlags(&T->chunkDone, cudaEventDisableTiming));
+		OSB_CUDA(cudaEventCreateWithFlags(&T->fork, cudaEventDisableTiming));
 		OSB_CUDA(cudaEventCreateWithFlags(&T->copyDone, cudaEventDisableTiming));
+		for (ChunkBufs &b : T->set) {
+			OSB_CUDA(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+			OSB_CUDA(cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming));
+		}
 		return 0;
 	}
 
@@ -777,10 +793,16 @@ namespace osb {
 			return;
 		cudaFree(T->d_views);
 		cudaFreeHost(T->h_views);
-		cudaFree(T->d_lineDirs);
-		cudaFree(T->d_lineParams);
-		cudaFree(T->d_strips);
-		cudaFree(T->d_tabs);
+		for (ChunkBufs &b : T->set) {
+			cudaFree(b.d_lineDirs);
+			cudaFree(b.d_lineParams);
+			cudaFree(b.d_strips);
+			cudaFree(b.d_tabs);
+			if (b.done)
+				cudaEventDestroy(b.done);
+			if (b.stream)
+				cudaStreamDestroy(b.stream);
+		}
 		cudaFreeHost(T->h_tabs);
 		cudaFreeHost(T->h_lineDirs);
 		cudaFree(T->d_atan);
@@ -788,8 +810,8 @@ namespace osb {
 		cudaFree(T->d_depth);
 		if (T->stageFree)
 			cudaEventDestroy(T->stageFree);
-		if (T->chunkDone)
-			cudaEventDestroy(T->chunkDone);
+		if (T->fork)
+			cudaEventDestroy(T->fork);
 		if (T->copyDone)
 			cudaEventDestroy(T->copyDone);
 		if (T->copyStream)
@@ -882,16 +904,25 @@ namespace osb {
 		return 0;
 	}
 
+	static size_t env_mb(const char *name, long dflt) {
+		const char *e = getenv(name);
+		long mb = e ? atol(e) : 0;
+		return (size_t)(mb > 0 ? mb : dflt) << 20;
+	}
+	// Strip bytes per chunk.  Measured on B200: every launch ends in a latency-bound tail, so chunks must be large
+	// for the tail to be small against the launch, and there must be several of them for the two streams to overlap
+	// one chunk's tail with the other chunk's kernels.
 	static size_t strip_budget_bytes() {
-		static size_t v = 0;
-		if (!v) {
-			const char *e = getenv("OSB200_STRIP_MB");
-			long mb = e ? atol(e) : 0;
-			if (mb <= 0)
-				mb = 4096; // measured on B200: each launch ends in a latency-bound tail, so few large chunks win
-			v = (size_t)mb << 20;
-		}
+		static size_t v = env_mb("OSB200_STRIP_MB", 3072);
 		return v;
+	}
+	static bool dual_stream() {
+		static int v = -1;
+		if (v < 0) {
+			const char *e = getenv("OSB200_DUAL_STREAM");
+			v = e ? atoi(e) != 0 : 1;
+		}
+		return v != 0;
 	}
 
 	// host_fb / host_depth (nullable): when given, each chunk's finished frames are copied to the host on a second
@@ -949,8 +980,18 @@ namespace osb {
 			fill_view(scenes[i], w, h, under, fogDist, T->h_views[i]);
 			lineRes = T->h_views[i].lineRes;
 		}
-		// ---- chunking: strips of one chunk must fit the budget ----
-		const size_t budgetLines = std::max<size_t>(strip_budget_bytes() / ((size_t)lineRes * 8), 65536);
+		// ---- chunking: strips of one chunk must fit the budget; chunks are made equal (the two streams overlap
+		// best with equal partners), and a large batch is split in two even when it would fit one chunk ----
+		size_t budgetLines = std::max<size_t>(strip_budget_bytes() / ((size_t)lineRes * 8), 65536);
+		{
+			size_t total = 0;
+			for (int i = 0; i < nViews; i++)
+				total += (size_t)T->h_views[i].numLines;
+			size_t want = (total + budgetLines - 1) / budgetLines;
+			if (want < 2 && nViews >= 512 && dual_stream())
+				want = 2;
+			budgetLines = std::max<size_t>((total + want - 1) / want + 65536 / 32, 65536);
+		}
 		std::vector<int> chunkStart;
 		size_t maxLines = 0, maxViews = 0;
 		{
@@ -973,14 +1014,16 @@ namespace osb {
 			chunkStart.push_back(nViews);
 		}
 		const bool hostPrep = nViews <= 8;
-		if (grow(T->d_lineDirs, T->lineCap, maxLines))
-			return -2;
-		if (grow(T->d_lineParams, T->lineParamCap, maxLines))
-			return -2;
-		if (grow(T->d_strips, T->stripCap, maxLines * (size_t)lineRes))
-			return -2;
-		if (grow(T->d_tabs, T->tabCap, maxViews * tabF))
-			return -2;
+		const size_t nChunks = chunkStart.size() - 1;
+		// one chunk (or the host-prep path with its shared pinned staging): everything on the context stream
+		// (per-kernel event timing wants each kernel alone on the GPU: with timing on, chunks run back to back)
+		const bool dual = dual_stream() && nChunks > 1 && !hostPrep && !c->timing;
+		for (int k = 0; k < (dual ? 2 : 1); k++) {
+			ChunkBufs &B = T->set[k];
+			if (grow(B.d_lineDirs, B.lineCap, maxLines) || grow(B.d_lineParams, B.lineParamCap, maxLines) ||
+			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
+				return -2;
+		}
 		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
 		                         c->stream));
 		if (hostPrep) {
@@ -989,9 +1032,16 @@ namespace osb {
 			if (grow(T->h_tabs, T->hTabCap, maxViews * tabF, true))
 				return -2;
 		}
+		if (dual) {
+			OSB_CUDA(cudaEventRecord(T->fork, c->stream));
+			for (ChunkBufs &B : T->set)
+				OSB_CUDA(cudaStreamWaitEvent(B.stream, T->fork, 0));
+		}
 		osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
 		const int num = c->opts.numerics;
-		for (size_t ci = 0; ci + 1 < chunkStart.size(); ci++) {
+		for (size_t ci = 0; ci < nChunks; ci++) {
+			ChunkBufs &B = T->set[dual ? (ci & 1) : 0];
+			const cudaStream_t st = dual ? B.stream : c->stream;
 			const int v0 = chunkStart[ci], nv = chunkStart[ci + 1] - v0;
 			const ViewParams &last = T->h_views[v0 + nv - 1];
 			const uint32_t totalLines = last.lineBase + (uint32_t)last.numLines;
@@ -1007,21 +1057,20 @@ namespace osb {
 						prep_v1(V, g, t, v1);
 					}
 				}
-				OSB_CUDA(cudaMemcpyAsync(T->d_lineDirs, T->h_lineDirs, sizeof(float2) * totalLines,
-				                         cudaMemcpyHostToDevice, c->stream));
-				OSB_CUDA(cudaMemcpyAsync(T->d_tabs, T->h_tabs, sizeof(float) * tabF * nv, cudaMemcpyHostToDevice,
-				                         c->stream));
+				OSB_CUDA(cudaMemcpyAsync(B.d_lineDirs, T->h_lineDirs, sizeof(float2) * totalLines,
+				                         cudaMemcpyHostToDevice, st));
+				OSB_CUDA(cudaMemcpyAsync(B.d_tabs, T->h_tabs, sizeof(float) * tabF * nv, cudaMemcpyHostToDevice, st));
 			} else {
-				KLaunch kl(c, K_VIEW_PREP);
-				k_view_prep<<<(nv + 3) / 4, 128, 0, c->stream>>>(dV, nv, g, T->d_lineDirs, T->d_tabs);
+				KLaunch kl(c, K_VIEW_PREP, st);
+				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
 			const unsigned lineBlocks = (totalLines + kLineThreads - 1) / kLineThreads;
-			const size_t smem = (size_t)lineRes * 8;
+			const size_t smem = (size_t)(lineRes >> 5) * kLineThreads * sizeof(uint32_t);
 #define LAUNCH_LINES(SSE, SH)                                                                      \
-	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, c->stream>>>(                          \
-	  dV, nv, T->d_lineDirs, c->d_solid, c->d_color, sse, T->d_strips, T->d_lineParams, totalLines, lineRes)
+	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, st>>>(                                 \
+	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, totalLines, lineRes)
 			if (!g.noMap) {
-				KLaunch kl(c, K_BUILD_LINES);
+				KLaunch kl(c, K_BUILD_LINES, st);
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_LINES(false, false);
 				else if (num == OSB200_NUM_SSE)
@@ -1036,10 +1085,10 @@ namespace osb {
 			uint32_t *fbC = d_fb + (size_t)v0 * w * h;
 			float *dbC = d_depth + (size_t)v0 * w * h;
 #define LAUNCH_GATHER(SSE, FOG)                                                                    \
-	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, c->stream>>>(                           \
-	  dV, nv, g, T->d_tabs, c->d_solid, T->d_atan, sse, T->d_strips, T->d_lineParams, lineRes, fbC, dbC)
+	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, st>>>(                                  \
+	  dV, nv, g, B.d_tabs, c->d_solid, T->d_atan, sse, B.d_strips, B.d_lineParams, lineRes, fbC, dbC)
 			{
-				KLaunch kl(c, K_GATHER_FOG);
+				KLaunch kl(c, K_GATHER_FOG, st);
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_GATHER(false, false);
 				else if (num == OSB200_NUM_SSE)
@@ -1048,17 +1097,21 @@ namespace osb {
 					LAUNCH_GATHER(true, true);
 			}
 #undef LAUNCH_GATHER
+			OSB_CUDA(cudaEventRecord(B.done, st));
 			if (host_fb || host_depth) {
 				const size_t off = (size_t)v0 * w * h, cnt = (size_t)nv * w * h;
-				OSB_CUDA(cudaEventRecord(T->chunkDone, c->stream));
-				OSB_CUDA(cudaStreamWaitEvent(T->copyStream, T->chunkDone, 0));
+				OSB_CUDA(cudaStreamWaitEvent(T->copyStream, B.done, 0));
 				if (host_fb)
 					OSB_CUDA(cudaMemcpyAsync(host_fb + off, d_fb + off, cnt * 4, cudaMemcpyDeviceToHost, T->copyStream));
 				if (host_depth)
 					OSB_CUDA(cudaMemcpyAsync(host_depth + off, d_depth + off, cnt * 4, cudaMemcpyDeviceToHost, T->copyStream));
 			}
-			if (hostPrep && ci + 2 < chunkStart.size()) // staging reused by the next chunk
-				OSB_CUDA(cudaStreamSynchronize(c->stream));
+			if (hostPrep && ci + 1 < nChunks) // staging reused by the next chunk
+				OSB_CUDA(cudaStreamSynchronize(st));
+		}
+		if (dual) { // join: the context stream continues after both working streams
+			for (ChunkBufs &B : T->set)
+				OSB_CUDA(cudaStreamWaitEvent(c->stream, B.done, 0));
 		}
 		OSB_CUDA(cudaGetLastError());
 		OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
@@ -1067,6 +1120,17 @@ namespace osb {
 } // namespace osb
 
 extern "C" {
+#ifdef OSB_STATS
+__attribute__((visibility("default"))) int osb200_debug_stats(unsigned long long *out, int reset) {
+	cudaDeviceSynchronize();
+	cudaMemcpyFromSymbol(out, osb::g_stats, sizeof(unsigned long long) * 16);
+	if (reset) {
+		unsigned long long z[16] = {0};
+		cudaMemcpyToSymbol(osb::g_stats, z, sizeof(z));
+	}
+	return 0;
+}
+#endif
 
 int osb200_render_device(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
                          const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth) {
