@@ -80,6 +80,22 @@ uint32_t orc_radiosity_encode(const float v[3], int mode);
 void orc_radiosity_box(const uint32_t *bitmap, int x0, int y0, int z0, int x1, int y1, int z1, int mode,
                        float *f32, uint32_t *enc, int threads);
 
+/* Client/GameMap.cpp:208-359 GameMap::CastRay.  out[i] = {hit, hitBlock.x, .y, .z} (zeros on a miss) */
+int orc_castray_one(const uint64_t *solid, const float v0[3], const float dir[3], float length, int32_t hit[3]);
+void orc_castray(const uint64_t *solid, const float *v0, const float *dir, float length, int32_t *out, size_t n,
+                 int threads);
+/* Draw/GLAmbientShadowRenderer.cpp:130-169 Evaluate (rays = the instance's 16 directions, 48 floats) */
+float orc_ao_evaluate(const uint64_t *solid, const float rays[48], int x, int y, int z);
+void orc_ao_evaluate_box(const uint64_t *solid, const float rays[48], int x0, int y0, int z0, int x1, int y1, int z1,
+                         float *out, int threads);
+/* chunk state 4096 x {dirty,minX,minY,minZ,maxX,maxY,maxZ}, index (cx + cy*32)*4 + cz */
+void orc_ao_state_init(int32_t *state);
+/* Draw/GLAmbientShadowRenderer.cpp:171-237 GameMapChanged + Invalidate */
+void orc_ao_invalidate(int32_t *state, int x, int y, int z);
+/* Draw/GLAmbientShadowRenderer.cpp:334-507 UpdateChunk; data = the chunk's float[16][16][16][2] */
+void orc_ao_update_chunk(const uint64_t *solid, const float rays[48], int32_t *state, int cx, int cy, int cz,
+                         float *data);
+
 #ifdef __cplusplus
 }
 #endif

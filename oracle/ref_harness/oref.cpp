@@ -122,6 +122,22 @@ void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps, o
 	}
 }
 
+/* GameMap::CastRay (GameMap.cpp:208-359) */
+void oref_castray(void *map, const float *v0, const float *dir, float length, int32_t *out, size_t n, int threads) {
+	auto *m = reinterpret_cast<const client::GameMap *>(map);
+	if (threads < 1) threads = 1;
+#pragma omp parallel for num_threads(threads) schedule(static)
+	for (long long i = 0; i < (long long)n; i++) {
+		IntVector3 hb = IntVector3::Make(0, 0, 0);
+		const bool hit = m->CastRay(MakeVector3(v0[i * 3], v0[i * 3 + 1], v0[i * 3 + 2]),
+		                            MakeVector3(dir[i * 3], dir[i * 3 + 1], dir[i * 3 + 2]), length, hb);
+		out[i * 4] = hit ? 1 : 0;
+		out[i * 4 + 1] = hit ? hb.x : 0;
+		out[i * 4 + 2] = hit ? hb.y : 0;
+		out[i * 4 + 3] = hit ? hb.z : 0;
+	}
+}
+
 void oref_renderer_set_threads(int threads) {
 	Settings::ItemHandle h("r_swNumThreads", nullptr);
 	h = threads;

@@ -78,6 +78,22 @@ OREF_API void oref_rad_update_chunk(void *h, int cx, int cy, int cz); /* GLRadio
 OREF_API int oref_rad_update_all(void *h, int threads);
 OREF_API void oref_rad_read_chunk(void *h, int cx, int cy, int cz, uint32_t *flat, uint32_t *x, uint32_t *y, uint32_t *z);
 
+/* ---- GameMap::CastRay (GameMap.cpp:208-359) and the CPU half of GLAmbientShadowRenderer (oref_gl.cpp) ---- */
+/* out[i] = {hit, hitBlock.x, hitBlock.y, hitBlock.z}; hitBlock is left 0 on a miss */
+OREF_API void oref_castray(void *map, const float *v0, const float *dir, float length, int32_t *out, size_t n, int threads);
+OREF_API void *oref_ao_create(void *map);
+OREF_API void oref_ao_free(void *h);
+OREF_API void oref_ao_get_rays(void *h, float out[48]);  /* the 16 random directions of this instance */
+OREF_API void oref_ao_set_rays(void *h, const float in[48]);
+OREF_API float oref_ao_evaluate(void *h, int x, int y, int z); /* GLAmbientShadowRenderer::Evaluate */
+OREF_API void oref_ao_evaluate_box(void *h, int x0, int y0, int z0, int x1, int y1, int z1, float *out, int threads);
+OREF_API void oref_ao_map_changed(void *h, int x, int y, int z); /* GLAmbientShadowRenderer::GameMapChanged */
+OREF_API void oref_ao_chunk_info(void *h, int cx, int cy, int cz, int out[7]);
+OREF_API int oref_ao_num_dirty(void *h);
+OREF_API void oref_ao_update_chunk(void *h, int cx, int cy, int cz); /* GLAmbientShadowRenderer::UpdateChunk */
+OREF_API int oref_ao_update_all(void *h, int threads);
+OREF_API void oref_ao_read_chunk(void *h, int cx, int cy, int cz, float *out /*[16][16][16][2]*/);
+
 #ifdef __cplusplus
 }
 #endif

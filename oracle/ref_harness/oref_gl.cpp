@@ -19,6 +19,7 @@
 
 #include <Client/GameMap.h>
 #include <Core/Settings.h>
+#include <Draw/GLAmbientShadowRenderer.h>
 #include <Draw/GLMapShadowRenderer.h>
 #include <Draw/GLProfiler.h>
 #include <Draw/GLRadiosityRenderer.h>
@@ -38,6 +39,12 @@ namespace spades {
 } // namespace spades
 
 namespace {
+	struct Ao {
+		alignas(64) unsigned char storage[sizeof(GLRenderer)];
+		GLRenderer *renderer;
+		client::GameMap *map;
+		GLAmbientShadowRenderer *ao;
+	};
 	struct Rad {
 		alignas(64) unsigned char storage[sizeof(GLRenderer)];
 		GLRenderer *renderer;
@@ -163,6 +170,97 @@ void oref_rad_read_chunk(void *p, int cx, int cy, int cz, uint32_t *flat, uint32
 	std::memcpy(x, c.dataX, sizeof(c.dataX));
 	std::memcpy(y, c.dataY, sizeof(c.dataY));
 	std::memcpy(z, c.dataZ, sizeof(c.dataZ));
+}
+
+/* ---- GLAmbientShadowRenderer (Draw/GLAmbientShadowRenderer.cpp), CPU half: Evaluate :130-169, GameMapChanged /
+   Invalidate :171-237, UpdateChunk :334-507.  Constructed over the same zeroed GLRenderer storage + NullGLDevice. */
+void *oref_ao_create(void *map) {
+	Ao *h = new Ao();
+	std::memset(h->storage, 0, sizeof(h->storage));
+	h->renderer = reinterpret_cast<GLRenderer *>(h->storage);
+	h->map = static_cast<client::GameMap *>(map);
+	new (&h->renderer->device) Handle<IGLDevice>(Handle<oref::NullGLDevice>::New().Cast<IGLDevice>());
+	new (&h->renderer->settings) GLSettings();
+	h->renderer->map = h->map;
+	h->ao = new GLAmbientShadowRenderer(*h->renderer, *h->map);
+	return h;
+}
+
+void oref_ao_free(void *p) {
+	Ao *h = static_cast<Ao *>(p);
+	delete h->ao;
+	h->renderer->settings.~GLSettings();
+	h->renderer->device.~Handle<IGLDevice>();
+	delete h;
+}
+
+void oref_ao_get_rays(void *p, float out[48]) {
+	auto &r = static_cast<Ao *>(p)->ao->rays;
+	for (int i = 0; i < 16; i++) {
+		out[i * 3] = r[i].x;
+		out[i * 3 + 1] = r[i].y;
+		out[i * 3 + 2] = r[i].z;
+	}
+}
+void oref_ao_set_rays(void *p, const float in[48]) {
+	auto &r = static_cast<Ao *>(p)->ao->rays;
+	for (int i = 0; i < 16; i++)
+		r[i] = MakeVector3(in[i * 3], in[i * 3 + 1], in[i * 3 + 2]);
+}
+
+float oref_ao_evaluate(void *p, int x, int y, int z) {
+	return static_cast<Ao *>(p)->ao->Evaluate(IntVector3::Make(x, y, z));
+}
+
+void oref_ao_evaluate_box(void *p, int x0, int y0, int z0, int x1, int y1, int z1, float *out, int threads) {
+	Ao *h = static_cast<Ao *>(p);
+	const int nx = x1 - x0 + 1, ny = y1 - y0 + 1, nz = z1 - z0 + 1;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic, 4)
+	for (int row = 0; row < nz * ny; row++) {
+		const int z = z0 + row / ny, y = y0 + row % ny;
+		for (int x = x0; x <= x1; x++)
+			out[(size_t)row * nx + (x - x0)] = h->ao->Evaluate(IntVector3::Make(x, y, z));
+	}
+}
+
+void oref_ao_map_changed(void *p, int x, int y, int z) {
+	Ao *h = static_cast<Ao *>(p);
+	h->ao->GameMapChanged(x, y, z, h->map);
+}
+
+void oref_ao_chunk_info(void *p, int cx, int cy, int cz, int out[7]) {
+	auto &c = static_cast<Ao *>(p)->ao->GetChunk(cx, cy, cz);
+	out[0] = c.dirty ? 1 : 0;
+	out[1] = c.dirtyMinX;
+	out[2] = c.dirtyMinY;
+	out[3] = c.dirtyMinZ;
+	out[4] = c.dirtyMaxX;
+	out[5] = c.dirtyMaxY;
+	out[6] = c.dirtyMaxZ;
+}
+
+int oref_ao_num_dirty(void *p) { return static_cast<Ao *>(p)->ao->GetNumDirtyChunks(); }
+
+void oref_ao_update_chunk(void *p, int cx, int cy, int cz) { static_cast<Ao *>(p)->ao->UpdateChunk(cx, cy, cz); }
+
+int oref_ao_update_all(void *p, int threads) {
+	GLAmbientShadowRenderer *r = static_cast<Ao *>(p)->ao;
+	const int n = (int)r->chunks.size();
+	int cnt = 0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic, 1) reduction(+ : cnt)
+	for (int i = 0; i < n; i++) {
+		auto &c = r->chunks[i];
+		if (c.dirty) {
+			r->UpdateChunk(c.cx, c.cy, c.cz);
+			cnt++;
+		}
+	}
+	return cnt;
+}
+
+void oref_ao_read_chunk(void *p, int cx, int cy, int cz, float *out) {
+	auto &c = static_cast<Ao *>(p)->ao->GetChunk(cx, cy, cz);
+	std::memcpy(out, c.data, sizeof(c.data));
 }
 
 } // extern "C"

@@ -62,6 +62,18 @@ class Port:
         L.orc_radiosity_encode.restype = ctypes.c_uint32
         L.orc_radiosity_box.argtypes = [vp] + [ci] * 7 + [vp, vp, ci]
         L.orc_radiosity_box.restype = None
+        L.orc_castray.argtypes = [vp, vp, vp, ctypes.c_float, vp, ctypes.c_size_t, ci]
+        L.orc_castray.restype = None
+        L.orc_ao_evaluate.argtypes = [vp, vp, ci, ci, ci]
+        L.orc_ao_evaluate.restype = ctypes.c_float
+        L.orc_ao_evaluate_box.argtypes = [vp, vp] + [ci] * 6 + [vp, ci]
+        L.orc_ao_evaluate_box.restype = None
+        L.orc_ao_state_init.argtypes = [vp]
+        L.orc_ao_state_init.restype = None
+        L.orc_ao_invalidate.argtypes = [vp, ci, ci, ci]
+        L.orc_ao_invalidate.restype = None
+        L.orc_ao_update_chunk.argtypes = [vp, vp, vp, ci, ci, ci, vp]
+        L.orc_ao_update_chunk.restype = None
 
     def vxl_load(self, data: bytes):
         solid = np.zeros((512, 512), np.uint64)
@@ -137,6 +149,45 @@ class Port:
         return f32, enc
 
 
+    # ---- GameMap::CastRay + ambient occlusion ----
+    def castray(self, solid, v0, dirs, length, threads=1):
+        """(n,4) int32: hit, hitBlock.xyz"""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        out = np.zeros((len(v0), 4), np.int32)
+        self.L.orc_castray(solid.ctypes.data, v0.ctypes.data, dirs.ctypes.data, float(length), out.ctypes.data,
+                           len(v0), threads)
+        return out
+
+    def ao_evaluate(self, solid, rays, x, y, z):
+        rays = np.ascontiguousarray(rays, np.float32)
+        return float(self.L.orc_ao_evaluate(solid.ctypes.data, rays.ctypes.data, x, y, z))
+
+    def ao_evaluate_box(self, solid, rays, lo, hi, threads=8):
+        rays = np.ascontiguousarray(rays, np.float32)
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        out = np.zeros((nz, ny, nx), np.float32)
+        self.L.orc_ao_evaluate_box(solid.ctypes.data, rays.ctypes.data, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                                   out.ctypes.data, threads)
+        return out
+
+    def ao_state_init(self):
+        st = np.zeros((4096, 7), np.int32)
+        self.L.orc_ao_state_init(st.ctypes.data)
+        return st
+
+    def ao_invalidate(self, state, x, y, z):
+        self.L.orc_ao_invalidate(state.ctypes.data, x, y, z)
+
+    def ao_update_chunk(self, solid, rays, state, cx, cy, cz, data=None):
+        """data: (16,16,16,2) float32 [z][y][x][ao, air]; a fresh chunk is all ones"""
+        rays = np.ascontiguousarray(rays, np.float32)
+        if data is None:
+            data = np.ones((16, 16, 16, 2), np.float32)
+        self.L.orc_ao_update_chunk(solid.ctypes.data, rays.ctypes.data, state.ctypes.data, cx, cy, cz, data.ctypes.data)
+        return data
+
+
 class Ref:
     """oracle/_ref/liboref_{variant}.so -- the reference's own code."""
 
@@ -159,6 +210,8 @@ class Ref:
         L.oref_map_get_arrays.argtypes = [vp, vp, vp]
         L.oref_map_set.argtypes = [vp, ci, ci, ci, ci, ctypes.c_uint32]
         L.oref_castray2.argtypes = [vp, vp, vp, ci, vp, ctypes.c_size_t, ci]
+        L.oref_castray.argtypes = [vp, vp, vp, ctypes.c_float, vp, ctypes.c_size_t, ci]
+        L.oref_castray.restype = None
         L.oref_renderer_create.argtypes = [ci] * 4
         L.oref_renderer_free.argtypes = [vp]
         L.oref_renderer_level.argtypes = [vp]
@@ -196,6 +249,90 @@ class Ref:
         dirs = np.ascontiguousarray(dirs, np.float32)
         out = np.zeros(len(v0), RAYHIT_DTYPE)
         self.L.oref_castray2(m, v0.ctypes.data, dirs.ctypes.data, max_steps, out.ctypes.data, len(v0), threads)
+        return out
+
+    def castray(self, m, v0, dirs, length, threads=1):
+        """GameMap::CastRay: (n,4) int32 hit, hitBlock.xyz"""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        out = np.zeros((len(v0), 4), np.int32)
+        self.L.oref_castray(m, v0.ctypes.data, dirs.ctypes.data, float(length), out.ctypes.data, len(v0), threads)
+        return out
+
+
+class RefAmbient:
+    """GLAmbientShadowRenderer CPU half of the reference (oracle/ref_harness/oref_gl.cpp)."""
+
+    def __init__(self, ref: Ref, m):
+        L = self.L = ref.L
+        L.oref_ao_create.restype = vp
+        L.oref_ao_create.argtypes = [vp]
+        L.oref_ao_free.argtypes = [vp]
+        L.oref_ao_get_rays.argtypes = [vp, vp]
+        L.oref_ao_set_rays.argtypes = [vp, vp]
+        L.oref_ao_evaluate.argtypes = [vp, ci, ci, ci]
+        L.oref_ao_evaluate.restype = ctypes.c_float
+        L.oref_ao_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp, ci]
+        L.oref_ao_map_changed.argtypes = [vp, ci, ci, ci]
+        L.oref_ao_chunk_info.argtypes = [vp, ci, ci, ci, vp]
+        L.oref_ao_num_dirty.argtypes = [vp]
+        L.oref_ao_update_chunk.argtypes = [vp, ci, ci, ci]
+        L.oref_ao_update_all.argtypes = [vp, ci]
+        L.oref_ao_read_chunk.argtypes = [vp, ci, ci, ci, vp]
+        self.h = L.oref_ao_create(m)
+
+    def close(self):
+        if self.h:
+            self.L.oref_ao_free(self.h)
+            self.h = None
+
+    def rays(self):
+        out = np.zeros((16, 3), np.float32)
+        self.L.oref_ao_get_rays(self.h, out.ctypes.data)
+        return out
+
+    def set_rays(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32)
+        self.L.oref_ao_set_rays(self.h, rays.ctypes.data)
+
+    def evaluate(self, x, y, z):
+        return float(self.L.oref_ao_evaluate(self.h, x, y, z))
+
+    def evaluate_box(self, lo, hi, threads=8):
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        out = np.zeros((nz, ny, nx), np.float32)
+        self.L.oref_ao_evaluate_box(self.h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], out.ctypes.data, threads)
+        return out
+
+    def map_changed(self, x, y, z):
+        self.L.oref_ao_map_changed(self.h, x, y, z)
+
+    def chunk_info(self, cx, cy, cz):
+        out = np.zeros(7, np.int32)
+        self.L.oref_ao_chunk_info(self.h, cx, cy, cz, out.ctypes.data)
+        return out
+
+    def chunk_state(self):
+        out = np.zeros((4096, 7), np.int32)
+        for cx in range(32):
+            for cy in range(32):
+                for cz in range(4):
+                    out[(cx + cy * 32) * 4 + cz] = self.chunk_info(cx, cy, cz)
+        return out
+
+    def num_dirty(self):
+        return self.L.oref_ao_num_dirty(self.h)
+
+    def update_chunk(self, cx, cy, cz):
+        self.L.oref_ao_update_chunk(self.h, cx, cy, cz)
+
+    def update_all(self, threads=8):
+        return self.L.oref_ao_update_all(self.h, threads)
+
+    def read_chunk(self, cx, cy, cz):
+        """(16,16,16,2) float32 [z][y][x][ao, air]"""
+        out = np.zeros((16, 16, 16, 2), np.float32)
+        self.L.oref_ao_read_chunk(self.h, cx, cy, cz, out.ctypes.data)
         return out
 
 
