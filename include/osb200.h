@@ -178,6 +178,39 @@ OSB200_API int osb200_radiosity_evaluate_box(osb200_ctx *ctx, int x0, int y0, in
 OSB200_API int osb200_radiosity_volumes(osb200_ctx *ctx, const uint32_t **flat, const uint32_t **x,
                                         const uint32_t **y, const uint32_t **z, const uint32_t **shadow);
 
+/* ---- GameMap::CastRay (GameMap.cpp:208-359), batched: the integer cell-wall walk used by the ambient-occlusion
+ *      evaluation and by the game's hit tests.  v0, dir: n x 3 floats; one length for the batch (the walk takes at most
+ *      (long)length cell walls); out: n x {hit, hitBlock.x, hitBlock.y, hitBlock.z} int32 (zeros on a miss). ---- */
+OSB200_API int osb200_castray(osb200_ctx *ctx, const float *v0, const float *dir, float length, int32_t *out, size_t n);
+OSB200_API int osb200_castray_device(osb200_ctx *ctx, const float *d_v0, const float *d_dir, float length,
+                                     int32_t *d_out, size_t n);
+
+/* ---- ray-traced ambient occlusion: the CPU half of GLAmbientShadowRenderer (Draw/GLAmbientShadowRenderer.cpp) ----
+ * State is created lazily and starts like a freshly constructed reference object: every 16^3 chunk dirty over its whole
+ * box, the volume filled with (1, 1).  Edits reach it through osb200_map_mark_dirty (= GameMapChanged -> Invalidate of
+ * the +-16 box, :171-237) followed by osb200_map_flush; updating with unflushed edits is an error (-1).
+ * The 16 ray directions are an input: the reference draws them per instance from its global RNG (:53-60), so a caller
+ * that wants the reference's values passes the reference's rays; the defaults follow the same recipe from a fixed seed. */
+OSB200_API int osb200_ambient_set_rays(osb200_ctx *ctx, const float rays[48]);
+OSB200_API int osb200_ambient_get_rays(osb200_ctx *ctx, float rays[48]);
+/* replaces GLAmbientShadowRenderer::Update/UpdateDirtyChunks/UpdateChunk (:239-507): re-evaluates up to maxChunks dirty
+ * chunks (< 0: all): Evaluate (16 rays x GameMap::CastRay, :130-169) over the dirty box grown by 2, the under-shadowing
+ * compensation, two rounds of in-place 3-tap blurs along x, y, z, copy-out.  eye (nullable) gives the reference's
+ * priority: dirty chunks within 6 chunks of the eye first (:276-292); among the candidates the reference draws 8 at
+ * random, this takes the first maxChunks in chunk-index order.  Returns the number of chunks updated or < 0. */
+OSB200_API int osb200_ambient_update(osb200_ctx *ctx, int maxChunks, const float *eye);
+/* out = {dirty, minX, minY, minZ, maxX, maxY, maxZ} (GLAmbientShadowRenderer.h:55-62) */
+OSB200_API int osb200_ambient_chunk_info(osb200_ctx *ctx, int cx, int cy, int cz, int out[7]);
+/* Chunk::data (GLAmbientShadowRenderer.h:54): float[16][16][16][2] = [z][y][x]{AO term, 1 for air / 0 for solid} */
+OSB200_API int osb200_ambient_read_chunk(osb200_ctx *ctx, int cx, int cy, int cz, float *out);
+/* GLAmbientShadowRenderer::Evaluate over the inclusive voxel box, [z][y][x]; coordinates may leave the map (x / y wrap,
+ * z < 0 is air, z >= 64 solid).  Independent of the chunk state -- parity hook. */
+OSB200_API int osb200_ambient_evaluate_box(osb200_ctx *ctx, int x0, int y0, int z0, int x1, int y1, int z1, float *out);
+/* device pointer of the resident volume in the layout of the reference's RG-float 3-D texture (:93-105,255-262):
+ * float2[65][512][512], slice z + 1 holds map depth z, slice 0 stays (1, 1) */
+OSB200_API int osb200_ambient_volume(osb200_ctx *ctx, const float **d_volume);
+
+
 #ifdef __cplusplus
 }
 #endif

@@ -85,6 +85,15 @@ def load_library():
     lib.osb200_radiosity_read_chunk.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp]
     lib.osb200_radiosity_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
     lib.osb200_radiosity_volumes.argtypes = [vp] + [ctypes.POINTER(vp)] * 5
+    lib.osb200_castray.argtypes = [vp, vp, vp, fp, vp, sz]
+    lib.osb200_castray_device.argtypes = [vp, vp, vp, fp, vp, sz]
+    lib.osb200_ambient_set_rays.argtypes = [vp, vp]
+    lib.osb200_ambient_get_rays.argtypes = [vp, vp]
+    lib.osb200_ambient_update.argtypes = [vp, ci, vp]
+    lib.osb200_ambient_chunk_info.argtypes = [vp, ci, ci, ci, vp]
+    lib.osb200_ambient_read_chunk.argtypes = [vp, ci, ci, ci, vp]
+    lib.osb200_ambient_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
+    lib.osb200_ambient_volume.argtypes = [vp, ctypes.POINTER(vp)]
     _lib = lib
     return lib
 
@@ -257,6 +266,58 @@ class Context:
         self._check(self._lib.osb200_radiosity_evaluate_box(self._h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
                                                             out.ctypes.data))
         return out
+
+    # ---- GameMap::CastRay + ambient occlusion ----
+    def castray(self, v0, dirs, length):
+        """GameMap::CastRay batch: host arrays in, (n,4) int32 out: hit, hitBlock.xyz."""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n = v0.shape[0]
+        assert v0.shape == (n, 3) and dirs.shape == (n, 3)
+        out = np.zeros((n, 4), np.int32)
+        self._check(self._lib.osb200_castray(self._h, v0.ctypes.data, dirs.ctypes.data, float(length), out.ctypes.data, n))
+        return out
+
+    def castray_device(self, d_v0, d_dir, length, d_out, n):
+        self._check(self._lib.osb200_castray_device(self._h, _ptr(d_v0), _ptr(d_dir), float(length), _ptr(d_out), int(n)))
+
+    def ambient_set_rays(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32)
+        assert rays.size == 48
+        self._check(self._lib.osb200_ambient_set_rays(self._h, rays.ctypes.data))
+
+    def ambient_rays(self):
+        out = np.zeros((16, 3), np.float32)
+        self._check(self._lib.osb200_ambient_get_rays(self._h, out.ctypes.data))
+        return out
+
+    def ambient_update(self, max_chunks=-1, eye=None):
+        e = None if eye is None else np.ascontiguousarray(eye, np.float32)
+        return self._check(self._lib.osb200_ambient_update(self._h, int(max_chunks), None if e is None else e.ctypes.data))
+
+    def ambient_chunk_info(self, cx, cy, cz):
+        out = np.zeros(7, np.int32)
+        self._check(self._lib.osb200_ambient_chunk_info(self._h, cx, cy, cz, out.ctypes.data))
+        return out
+
+    def ambient_read_chunk(self, cx, cy, cz):
+        """(16,16,16,2) float32, [z][y][x][ao, air]"""
+        out = np.zeros((16, 16, 16, 2), np.float32)
+        self._check(self._lib.osb200_ambient_read_chunk(self._h, cx, cy, cz, out.ctypes.data))
+        return out
+
+    def ambient_evaluate_box(self, lo, hi):
+        nx, ny, nz = hi[0] - lo[0] + 1, hi[1] - lo[1] + 1, hi[2] - lo[2] + 1
+        out = np.zeros((nz, ny, nx), np.float32)
+        self._check(self._lib.osb200_ambient_evaluate_box(self._h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                                                          out.ctypes.data))
+        return out
+
+    def ambient_volume(self):
+        """Device pointer (int) of the float2[65][512][512] volume."""
+        p = ctypes.c_void_p()
+        self._check(self._lib.osb200_ambient_volume(self._h, ctypes.byref(p)))
+        return p.value
 
     def radiosity_volumes(self):
         """Device pointers (ints): flat, x, y, z volumes ([z][y][x] uint32) and the shadow bitmap."""

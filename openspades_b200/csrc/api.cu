@@ -26,7 +26,7 @@ namespace osb {
 	const char *kernel_name(int id) {
 		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_build_lines",
 		                                     "k_gather_fog", "k_castray2", "k_shadow_update", "k_radiosity",
-		                                     "k_rad_select"};
+		                                     "k_rad_select", "k_castray", "k_ao_chunk"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
 	KLaunch::KLaunch(osb200_ctx *ctx, int kid, cudaStream_t stream) : c(ctx), slot(-1), st(stream ? stream : ctx->stream) {
@@ -48,6 +48,9 @@ namespace osb {
 	void radiosity_destroy(osb200_ctx *ctx); // radiosity.cu
 	void radiosity_map_replaced(osb200_ctx *ctx);
 	void radiosity_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
+	void ambient_destroy(osb200_ctx *ctx);   // ambient.cu
+	void ambient_map_replaced(osb200_ctx *ctx);
+	void ambient_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
 } // namespace osb
 
 cudaEvent_t osb200_ctx::take_event() {
@@ -265,6 +268,7 @@ void osb200_destroy(osb200_ctx *c) {
 		cudaStreamSynchronize(c->stream);
 	osb::terrain_destroy(c);
 	osb::radiosity_destroy(c);
+	osb::ambient_destroy(c);
 	cudaFree(c->d_solid); // bitmap + colours are one allocation
 	cudaFree(c->d_rcp);
 	cudaFree(c->d_rsqrt);
@@ -354,6 +358,7 @@ int osb200_map_upload(osb200_ctx *c, const uint64_t *solid, const uint32_t *colo
 	c->anyDirty = false;
 	c->mapLoaded = true;
 	osb::radiosity_map_replaced(c);
+	osb::ambient_map_replaced(c);
 	return 0;
 }
 
@@ -374,6 +379,7 @@ int osb200_map_mark_dirty(osb200_ctx *c, int x, int y, int z) {
 	c->dirtyWords[(x + y * OSB200_MAP_W) >> 5] |= 1u << (x & 31);
 	c->anyDirty = true;
 	osb::radiosity_mark_dirty(c, x, y, z);
+	osb::ambient_mark_dirty(c, x, y, z);
 	return 0;
 }
 

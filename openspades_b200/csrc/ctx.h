@@ -41,12 +41,15 @@ namespace osb {
 		K_SHADOW_BITMAP,
 		K_RADIOSITY,
 		K_RAD_SELECT,
+		K_CASTRAY,
+		K_AMBIENT,
 		K_COUNT
 	};
 	const char *kernel_name(int id);
 
 	struct TerrainState;   // terrain.cu
 	struct RadiosityState; // radiosity.cu
+	struct AmbientState;   // ambient.cu
 } // namespace osb
 
 struct osb200_ctx;
@@ -107,6 +110,7 @@ struct osb200_ctx {
 
 	osb::TerrainState *terrain = nullptr;
 	osb::RadiosityState *radiosity = nullptr;
+	osb::AmbientState *ambient = nullptr;
 
 	int ensure_scratch(size_t bytes);
 	int ensure_stage(size_t bytes);
