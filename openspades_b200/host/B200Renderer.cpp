@@ -237,4 +237,27 @@ namespace osb200 {
 			RaiseAbi("osb200_radiosity_update");
 		return n;
 	}
+	int B200Renderer::UpdateAmbient(int maxChunks) {
+		EnsureInitialized();
+		EnsureSceneNotStarted();
+		if (!map_)
+			return 0;
+		{
+			std::lock_guard<std::mutex> guard(dirtyMutex_);
+			lastFlushed_ = osb200_map_flush(ctx_, map_->SolidData(), map_->ColorData());
+		}
+		if (lastFlushed_ < 0)
+			RaiseAbi("osb200_map_flush");
+		const float eye[3] = {sceneDef_.viewOrigin.x, sceneDef_.viewOrigin.y, sceneDef_.viewOrigin.z};
+		const int n = osb200_ambient_update(ctx_, maxChunks, haveScene_ ? eye : nullptr);
+		if (n < 0)
+			RaiseAbi("osb200_ambient_update");
+		return n;
+	}
+
+	void B200Renderer::SetAmbientRays(const float rays[48]) {
+		EnsureInitialized();
+		if (osb200_ambient_set_rays(ctx_, rays) != 0)
+			RaiseAbi("osb200_ambient_set_rays");
+	}
 } // namespace osb200

@@ -11,7 +11,7 @@
 // What is accepted and NOT drawn (out of scope): RenderModel, AddLight, AddSprite,
 //   AddLongSprite, AddDebugLine and the 2-D DrawImage family; they only enforce the same call-order rules.
 // Extension beyond SWRenderer (the CPU halves of GLRenderer's map shadow + radiosity):
-//   UpdateRadiosity().
+//   UpdateRadiosity(), and of the ray-traced ambient occlusion volume (GLAmbientShadowRenderer): UpdateAmbient().
 //
 // The reference's own types (Vector3, Handle<T>, Bitmap, SWPort) are not linkable here, so this header names
 // small layout-compatible stand-ins; INTEGRATION.md shows the 1:1 adapter a maintainer adds inside Sources/Draw.
@@ -133,6 +133,12 @@ namespace osb200 {
 		// GLMapShadowRenderer::Update + GLRadiosityRenderer::Update with a chunk budget (8 in the reference,
 		// < 0 = drain); prioritises chunks near the last scene's eye.  Returns the number of chunks updated.
 		int UpdateRadiosity(int maxChunks = 8);
+		// Same leg for the ray-traced ambient-occlusion volume (GLAmbientShadowRenderer::Update ->
+		// UpdateDirtyChunks -> UpdateChunk, GLAmbientShadowRenderer.cpp:239-507; r_radiosity's sibling cvar
+		// r_ambientOcclusion... the reference runs it on a worker thread, 8 chunks per dispatch).
+		int UpdateAmbient(int maxChunks = 8);
+		// the 16 ray directions of the ambient evaluation (GLAmbientShadowRenderer ctor :53-60 draws them at random)
+		void SetAmbientRays(const float rays[48]);
 
 		osb200_ctx *Context() { return ctx_; }
 		int LastFlushedColumns() const { return lastFlushed_; }

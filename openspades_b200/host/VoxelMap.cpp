@@ -140,4 +140,10 @@ namespace osb200 {
 		if (osb200_castray2(ctx, v0, dir, maxSteps, out, n) != 0)
 			throw std::runtime_error(osb200_last_error());
 	}
+
+	void VoxelMap::CastRayBatch(osb200_ctx *ctx, const float *v0, const float *dir, float length, int32_t *out,
+	                            size_t n) const {
+		if (osb200_castray(ctx, v0, dir, length, out, n) != 0)
+			throw std::runtime_error(osb200_last_error());
+	}
 } // namespace osb200

@@ -65,6 +65,9 @@ namespace osb200 {
 		// Throws std::runtime_error on C-ABI failure.
 		void CastRay2Batch(osb200_ctx *ctx, const float *v0, const float *dir, int maxSteps,
 		                   osb200_rayhit *out, size_t n) const;
+		// Batched GameMap::CastRay (GameMap.cpp:208-359): out[i] = {hit, hitBlock.x, .y, .z}
+		void CastRayBatch(osb200_ctx *ctx, const float *v0, const float *dir, float length, int32_t *out,
+		                  size_t n) const;
 
 	private:
 		static size_t Idx(int x, int y) { return (size_t)x * DefaultHeight + (size_t)y; }

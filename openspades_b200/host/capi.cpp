@@ -136,12 +136,23 @@ OSBH_API int osbh_renderer_screen(void *p, float *w, float *h) {
 OSBH_API int osbh_renderer_update_radiosity(void *p, int maxChunks, int *updated) {
 	return guarded([&] { *updated = R(p)->UpdateRadiosity(maxChunks); });
 }
+OSBH_API int osbh_renderer_update_ambient(void *p, int maxChunks, int *updated) {
+	return guarded([&] { *updated = R(p)->UpdateAmbient(maxChunks); });
+}
+OSBH_API int osbh_renderer_set_ambient_rays(void *p, const float *rays) {
+	return guarded([&] { R(p)->SetAmbientRays(rays); });
+}
 OSBH_API int osbh_renderer_last_flushed(void *p) { return R(p)->LastFlushedColumns(); }
 OSBH_API void *osbh_renderer_context(void *p) { return R(p)->Context(); }
 OSBH_API int osbh_map_castray2(void *m, void *ctx, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
                                size_t n) {
 	return guarded([&] {
 		static_cast<osb200::VoxelMap *>(m)->CastRay2Batch(static_cast<osb200_ctx *>(ctx), v0, dir, maxSteps, out, n);
+	});
+}
+OSBH_API int osbh_map_castray(void *m, void *ctx, const float *v0, const float *dir, float length, int32_t *out, size_t n) {
+	return guarded([&] {
+		static_cast<osb200::VoxelMap *>(m)->CastRayBatch(static_cast<osb200_ctx *>(ctx), v0, dir, length, out, n);
 	});
 }
 #undef R

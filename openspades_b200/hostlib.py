@@ -119,6 +119,9 @@ class B200Renderer:
         L.osbh_renderer_read_depth.argtypes = [vp, vp]
         L.osbh_renderer_screen.argtypes = [vp, ctypes.POINTER(fp), ctypes.POINTER(fp)]
         L.osbh_renderer_update_radiosity.argtypes = [vp, ci, ctypes.POINTER(ci)]
+        L.osbh_renderer_update_ambient.argtypes = [vp, ci, ctypes.POINTER(ci)]
+        L.osbh_renderer_set_ambient_rays.argtypes = [vp, vp]
+        L.osbh_map_castray.argtypes = [vp, vp, vp, vp, ctypes.c_float, vp, ctypes.c_size_t]
         L.osbh_map_castray2.argtypes = [vp, vp, vp, vp, ci, vp, ctypes.c_size_t]
         self.w, self.h = w, h
         self._h = L.osbh_renderer_new(w, h, device, numerics, sw_threads, undersampling, radiosity_mode)
@@ -190,6 +193,25 @@ class B200Renderer:
         n = ctypes.c_int()
         self._chk(self._L.osbh_renderer_update_radiosity(self._h, max_chunks, ctypes.byref(n)))
         return n.value
+
+    def update_ambient(self, max_chunks=8):
+        n = ctypes.c_int()
+        self._chk(self._L.osbh_renderer_update_ambient(self._h, max_chunks, ctypes.byref(n)))
+        return n.value
+
+    def set_ambient_rays(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32)
+        assert rays.size == 48
+        self._chk(self._L.osbh_renderer_set_ambient_rays(self._h, rays.ctypes.data))
+
+    def castray(self, vmap, v0, dirs, length):
+        """VoxelMap::CastRayBatch on this renderer's context: (n,4) int32 hit, hitBlock.xyz."""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        out = np.zeros((len(v0), 4), np.int32)
+        self._chk(self._L.osbh_map_castray(vmap.handle, self._L.osbh_renderer_context(self._h), v0.ctypes.data,
+                                           dirs.ctypes.data, float(length), out.ctypes.data, len(v0)))
+        return out
 
     def castray2(self, vmap, v0, dirs, max_steps):
         """VoxelMap::CastRay2Batch on this renderer's context."""

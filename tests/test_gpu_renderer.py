@@ -115,6 +115,12 @@ def test_frames_with_edits_match_reference():
     assert r.update_radiosity(8) == 8
     assert r.update_radiosity(-1) == 4096 - 8
     assert r.update_radiosity(8) == 0
+    # GameMap::CastRay batch + the ambient-occlusion leg (GLAmbientShadowRenderer) on the same context
+    d1 = d / np.linalg.norm(d, axis=1, keepdims=True)
+    assert np.array_equal(r.castray(m, v0, d1, 64.0), port.castray(m.solid.copy(), v0, d1, 64.0, threads=8))
+    assert r.update_ambient(8) == 8
+    assert r.update_ambient(-1) == 4096 - 8
+    assert r.update_ambient(8) == 0
     r.set_game_map(None)
     r.close()
     if have_ref:
