@@ -444,6 +444,59 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
             upd += rc.radiosity_update(-1)
         inc_s = time.perf_counter() - t0
         kt2 = rc.timing_read()
+        # ---- ambient half of C5 (GLAmbientShadowRenderer): full map, then 20 frames x 100 edits, drain every frame ----
+        rc.timing_read()
+        t0 = time.perf_counter()
+        ao_chunks = rc.ambient_update(-1)
+        rc.sync()
+        ao_wall_ms = (time.perf_counter() - t0) * 1e3
+        ao_ms = rc.timing_read()["k_ao_chunk"][1]
+        ao_frames = 20
+        t0 = time.perf_counter()
+        ao_upd = 0
+        for _ in range(ao_frames):
+            xs, ys = rng.integers(0, 512, per_frame), rng.integers(0, 512, per_frame)
+            ed = []
+            for x, y in zip(xs, ys):
+                col = int(solid2[x, y])
+                top = (col & -col).bit_length() - 1
+                if rng.random() < 0.5 and top < 62:
+                    ed.append((x, y, top, 0, 0))
+                else:
+                    ed.append((x, y, max(top - 1, 0), 1, 0x64000000 | int(rng.integers(0, 1 << 24))))
+            e = sharding.make_edits(*zip(*ed))
+            sharding.apply_edits_arrays(solid2, color2, e, rc)
+            rc.map_flush(solid2, color2)
+            ao_upd += rc.ambient_update(-1)
+        rc.sync()
+        ao_inc_s = time.perf_counter() - t0
+        ao_kt = rc.timing_read()
+        # ---- GameMap::CastRay batch: 16 Mi unit rays of length 128 (the hit-test form), device resident ----
+        import torch
+        nr = min(args.rays, 1 << 24)
+        rv0, rd = workloads.random_rays(nr, seed=4321)
+        rd /= np.linalg.norm(rd, axis=1, keepdims=True)
+        t_v0, t_d = torch.from_numpy(rv0).to(dev), torch.from_numpy(rd.astype(np.float32)).to(dev)
+        t_out = torch.empty((nr, 4), dtype=torch.int32, device=dev)
+        rc.castray_device(t_v0, t_d, 128.0, t_out, nr)
+        rc.sync()
+        rc.timing_read()
+        for _ in range(5):
+            rc.castray_device(t_v0, t_d, 128.0, t_out, nr)
+        rc.sync()
+        cr_ms = rc.timing_read()["k_castray"][1] / 5
+        cr_hits = float((t_out[:, 0] != 0).float().mean().item())
+    out["ambient"] = {"workload": "C5 ambient half, Title.vxl: all 4096 chunks dirty -> osb200_ambient_update(all) (16 rays x <=16 "
+                                  "cell walls per air voxel of each 20^3 window, 2 x 3 in-place blurs), then 20 frames x 100 random "
+                                  "block edits, each frame flush + update of every dirty chunk",
+                      "full_map_chunks": ao_chunks, "full_map_kernel_ms": ao_ms, "full_map_wall_ms": ao_wall_ms,
+                      "full_map_mvoxels_s": 512 * 512 * 64 / ao_ms / 1e3,
+                      "window_mrays_s": 4096 * 8000 * 16 / ao_ms / 1e3,
+                      "edits_per_s": ao_frames * per_frame / ao_inc_s, "chunk_updates": ao_upd,
+                      "incremental_kernel_ms_per_frame": {k: v[1] / ao_frames for k, v in ao_kt.items() if v[0]}}
+    out["castray"] = {"workload": f"GameMap::CastRay batch, {nr} unit rays of length 128 per GPU, Title.vxl (in 24 B + out 16 B per ray)",
+                      "ms_per_batch": cr_ms, "mrays_s": nr / cr_ms / 1e3, "hit_fraction": cr_hits,
+                      "hbm_frac_algorithmic": (40 * nr / (cr_ms * 1e-3) / 1e9) / peak}
     out["radiosity"] = {"workload": "C5 Title.vxl: all 4096 chunks dirty -> osb200_radiosity_update(all) (16.8 M voxels, <=169 "
                                     "taps each), then 100 frames x 100 random block edits, each frame flush + shadow update + "
                                     "radiosity update of every dirty chunk (host edit generation inside the wall time)",
