@@ -49,6 +49,42 @@ def test_port_matches_golden(port, title_arrays):
         assert np.array_equal(fb & 0xFFFFFF, t["bgr"][i]) and np.array_equal(dp.view(np.uint32), t["depth"][i].view(np.uint32))
 
 
+def _ambient_case():
+    return np.load(os.path.join(GOLD, "ambient_title.npz"))
+
+
+def test_port_matches_golden_ambient(port, title_arrays):
+    """GameMap::CastRay + GLAmbientShadowRenderer fixtures (make_golden_ambient.py)."""
+    solid, _ = title_arrays
+    a = _ambient_case()
+    for L in (16.0, 128.0, 3.5):
+        assert np.array_equal(port.castray(solid, a["v0"], a["dir"], L), a[f"hits_{int(L * 10)}"]), L
+    got = port.ao_evaluate_box(solid, a["rays"], tuple(int(v) for v in a["box_lo"]), tuple(int(v) for v in a["box_hi"]))
+    assert np.array_equal(got.view(np.uint32), a["box"].view(np.uint32))
+    st = port.ao_state_init()
+    for key in ("chunk_16_16_2", "chunk_0_31_0", "chunk_31_0_3"):
+        c = [int(v) for v in key.split("_")[1:]]
+        assert np.array_equal(port.ao_update_chunk(solid, a["rays"], st, *c).view(np.uint32), a[key].view(np.uint32)), key
+
+
+@pytest.mark.gpu
+def test_cuda_matches_golden_ambient(title_arrays):
+    import openspades_b200 as osb
+    solid, color = title_arrays
+    a = _ambient_case()
+    with osb.Context(0, osb.NUM_IEEE) as ctx:
+        ctx.map_upload(solid, color)
+        for L in (16.0, 128.0, 3.5):
+            assert np.array_equal(ctx.castray(a["v0"], a["dir"], L), a[f"hits_{int(L * 10)}"]), L
+        ctx.ambient_set_rays(a["rays"])
+        got = ctx.ambient_evaluate_box(tuple(int(v) for v in a["box_lo"]), tuple(int(v) for v in a["box_hi"]))
+        assert np.array_equal(got.view(np.uint32), a["box"].view(np.uint32))
+        ctx.ambient_update(-1)
+        for key in ("chunk_16_16_2", "chunk_0_31_0", "chunk_31_0_3"):
+            c = [int(v) for v in key.split("_")[1:]]
+            assert np.array_equal(ctx.ambient_read_chunk(*c).view(np.uint32), a[key].view(np.uint32)), key
+
+
 @pytest.mark.gpu
 def test_cuda_matches_golden(title_arrays):
     import openspades_b200 as osb
