@@ -207,6 +207,12 @@ namespace osb {
 		float w[kAoWin][kAoWin][kAoWin];
 		uint8_t flags[kAoWin][kAoWin][kAoWin];
 		float rays[kAoRays * 3];
+		uint64_t reach[kAoWin][kAoWin]; // OR of the column masks within ray reach (+-16 columns) of a window column
+		union {
+			uint64_t reachY[kAoPatch][kAoWin];            // first half of the separable OR (along y)
+			uint16_t list[kAoWin * kAoWin * kAoWin];      // window voxels that need rays, compacted
+		} u;
+		int listCount;
 	};
 
 	// UpdateChunk for one task per CTA.
@@ -252,19 +258,60 @@ namespace osb {
 		}
 		__syncthreads();
 
-		// ---- Evaluate per air voxel (16 lanes each) + the under-shadowing compensation d *= d*d + 1 - d (:417-423)
+		// ---- which voxels need rays at all.  A ray crosses at most 16 cell walls, so it stays within +-16 cells of its
+		// voxel on every axis; when no solid voxel (and not the solid half-space z >= 64) lies in that box all 16 rays
+		// miss and Evaluate is exactly min(16 * 2/16, 1) = 1, which the compensation maps to 1.  The per-column OR over
+		// the 33 x 33 neighbourhood is separable: along y into reachY, then along x into reach.
+		for (int i = threadIdx.x; i < kAoPatch * kAoWin; i += kAoThreads) {
+			const int px = i / kAoWin, wy = i % kAoWin;
+			uint64_t m = 0;
+			for (int dy = 0; dy <= 2 * kAoRayLen; dy++)
+				m |= S.patch[px * kAoPatch + wy + dy];
+			S.u.reachY[px][wy] = m;
+		}
+		if (threadIdx.x == 0)
+			S.listCount = 0;
+		__syncthreads();
+		for (int i = threadIdx.x; i < kAoWin * kAoWin; i += kAoThreads) {
+			const int wx = i / kAoWin, wy = i % kAoWin;
+			uint64_t m = 0;
+			for (int dx = 0; dx <= 2 * kAoRayLen; dx++)
+				m |= S.u.reachY[wx + dx][wy];
+			S.reach[wx][wy] = m;
+		}
+		__syncthreads();
+		for (int i = threadIdx.x; i < nvox; i += kAoThreads) {
+			const int x = x0 + i % nx, y = y0 + (i / nx) % ny, z = z0 + i / (nx * ny);
+			const int wz = z + oz;
+			if (S.flags[z][y][x] & 1) {
+				S.w[z][y][x] = 0.f; // solid: 0 before and after the compensation
+				continue;
+			}
+			const int lo = max(wz - kAoRayLen, 0), hi = min(wz + kAoRayLen, 63);
+			bool clear = wz + kAoRayLen <= 63;
+			if (clear && hi >= lo) {
+				const uint64_t zmask = (hi == 63 ? ~0ull : ((1ull << (hi + 1)) - 1ull)) & ~((1ull << lo) - 1ull);
+				clear = (S.reach[x][y] & zmask) == 0;
+			}
+			if (clear)
+				S.w[z][y][x] = 1.f;
+			else
+				S.u.list[atomicAdd(&S.listCount, 1)] = (uint16_t)((z * kAoWin + y) * kAoWin + x);
+		}
+		__syncthreads();
+
+		// ---- Evaluate for the listed voxels (16 lanes each) + the under-shadowing compensation d *= d*d + 1 - d (:417-423)
 		{
 			const int group = threadIdx.x >> 4, groups = kAoThreads >> 4;
-			const int rounds = (nvox + groups - 1) / groups;
+			const int n = S.listCount;
+			const int rounds = (n + groups - 1) / groups;
 			for (int k = 0; k < rounds; k++) {
 				const int i = k * groups + group;
-				const bool inside = i < nvox;
-				const int ii = inside ? i : 0;
-				const int x = x0 + ii % nx, y = y0 + (ii / nx) % ny, z = z0 + ii / (nx * ny);
-				const bool air = inside && !(S.flags[z][y][x] & 1);
-				float d = ao_evaluate16(col, S.rays, x + ox, y + oy, z + oz, air);
+				const bool inside = i < n;
+				const int v = inside ? S.u.list[i] : 0;
+				const int x = v % kAoWin, y = (v / kAoWin) % kAoWin, z = v / (kAoWin * kAoWin);
+				float d = ao_evaluate16(col, S.rays, x + ox, y + oy, z + oz, inside);
 				if (inside && (threadIdx.x & 15) == 0) {
-					d = air ? d : 0.f;
 					d = __fmul_rn(d, __fsub_rn(__fadd_rn(__fmul_rn(d, d), 1.0f), d));
 					S.w[z][y][x] = d;
 				}

@@ -154,6 +154,9 @@ namespace osb {
 #ifndef OSB_EXP
 #define OSB_EXP 0
 #endif
+#ifndef OSB_RCP_SMEM
+#define OSB_RCP_SMEM 0 // measured on B200: no gain over the L1-cached global table (3.79 vs 3.76 ms), left as a knob
+#endif
 #ifndef OSB_TRANSFORM_BRANCHY
 #define OSB_TRANSFORM_BRANCHY 1
 #endif
@@ -183,9 +186,27 @@ namespace osb {
 		}
 	}
 
+	constexpr int kRcpSmemBits = 12; // rcpss tables up to 4096 entries (16 KB) are copied into shared memory per CTA
+
 	template <bool kSse> struct LineCtx {
 		osbn::Num<kSse> num;
 		float cz, transScale, transOffset, vmax;
+		uint32_t srcp; // shared-window address of the CTA's copy of the rcpss table, 0 = use the global one
+		// reciprocal for the two hot uses (DDA distance, ToSpecialTan beyond the seam): same value as Num::rcpBig,
+		// table entry fetched with ld.shared when the CTA holds a copy (keeps it out of the thrashed L1)
+		__device__ __forceinline__ float rcpBig(float b) const {
+#if OSB_RCP_SMEM
+			if (kSse && srcp) {
+				const uint32_t u = __float_as_uint(b), e = (u >> 23) & 0xff;
+				uint32_t r;
+				asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(srcp + (((u & 0x7fffff) >> (23 - num.t.rcpBits)) << 2)));
+				if (e >= 253u)
+					return osbn::rcpss(b, num.t);
+				return __uint_as_float((u & 0x80000000u) | (r + ((127u - e) << 23)));
+			}
+#endif
+			return num.rcpBig(b);
+		}
 		// transform lambda, SWMapRenderer.cpp:395-401 (ToSpecialTan :59-66 inlined).  Branch-free: the reciprocal is
 		// always formed and selected by |v| > 1, so lanes on different sides of the seam share one instruction stream.
 		__device__ __forceinline__ int transform(float invDist, int z) const {
@@ -194,9 +215,9 @@ namespace osb {
 #if OSB_TRANSFORM_BRANCHY
 			float t = v;
 			if (fabsf(v) > 1.f)
-				t = __fsub_rn(v < 0.f ? -2.f : 2.f, num.rcpBig(v));
+				t = __fsub_rn(v < 0.f ? -2.f : 2.f, rcpBig(v));
 #else
-			const float r = num.rcpBig(v);
+			const float r = rcpBig(v);
 			float t = v;
 			t = v < -1.f ? __fsub_rn(-2.f, r) : t;
 			t = v > 1.f ? __fsub_rn(2.f, r) : t;
@@ -235,6 +256,16 @@ namespace osb {
 			for (int w = 0; w < words; w++)
 				s_filled[w * kLineThreads + threadIdx.x] = 0;
 		}
+		// CTA copy of the rcpss table (SSE numerics, table small enough), behind the fill masks
+		uint32_t srcp = 0;
+#if OSB_RCP_SMEM
+		if (kSse && tabs.rcpBits <= kRcpSmemBits) {
+			uint32_t *s_rcp = s_filled + words * kLineThreads;
+			for (int i = threadIdx.x; i < (1 << tabs.rcpBits); i += kLineThreads)
+				s_rcp[i] = __ldg(tabs.rcp + i);
+			srcp = (uint32_t)__cvta_generic_to_shared(s_rcp);
+		}
+#endif
 		__syncthreads();
 		if (gl >= totalLines)
 			return;
@@ -352,6 +383,7 @@ namespace osb {
 		L.transScale = pitchScale; // same expression as line.pitchScale (:303,358)
 		L.transOffset = __fmul_rn(-minTan, L.transScale);
 		L.vmax = __fadd_rn((float)lineRes, 0.5f);
+		L.srcp = srcp;
 
 		// zscale = Dot(horizonDir, viewAxis[2]) (horizonDir.z = 0), heightScale, depthBias (:403-414)
 		const float zscale = __fadd_rn(__fadd_rn(__fmul_rn(hd.x, V.front[0]), __fmul_rn(hd.y, V.front[1])),
@@ -411,7 +443,7 @@ namespace osb {
 			const uint32_t tNew = cur.t;
 
 			const float oldInvDist = invDist;
-			invDist = num.rcpBig(distance); // distance is in [1e-20, ~200]
+			invDist = L.rcpBig(distance); // distance is in [1e-20, ~200]
 			const float medDist = __fadd_rn(__fmul_rn(distance, zscale), depthBias);
 
 			// ---- spans of this step, one merged work list per lane, in the reference's order:
@@ -1065,7 +1097,9 @@ namespace osb {
 				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
 			const unsigned lineBlocks = (totalLines + kLineThreads - 1) / kLineThreads;
-			const size_t smem = (size_t)(lineRes >> 5) * kLineThreads * sizeof(uint32_t);
+			size_t smem = (size_t)(lineRes >> 5) * kLineThreads * sizeof(uint32_t);
+			if (OSB_RCP_SMEM && num != OSB200_NUM_IEEE && c->rcpBits <= kRcpSmemBits)
+				smem += sizeof(uint32_t) << c->rcpBits;
 #define LAUNCH_LINES(SSE, SH)                                                                      \
 	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, st>>>(                                 \
 	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, totalLines, lineRes)
