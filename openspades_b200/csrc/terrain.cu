@@ -1022,6 +1022,10 @@ namespace osb {
 			size_t want = (total + budgetLines - 1) / budgetLines;
 			if (want < 2 && nViews >= 512 && dual_stream())
 				want = 2;
+			// frames going back to the host: the PCIe copy (4-8 B/pixel) is the long pole, so start it early --
+			// more, smaller chunks cost kernel time that hides under the copy of the previous chunk
+			if ((host_fb || host_depth) && nViews >= 1024 && want < 8)
+				want = 8;
 			budgetLines = std::max<size_t>((total + want - 1) / want + 65536 / 32, 65536);
 		}
 		std::vector<int> chunkStart;
