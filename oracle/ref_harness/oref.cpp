@@ -6,6 +6,7 @@
 
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <Client/GameMap.h>
@@ -16,7 +17,9 @@
 #include <Core/Settings.h>
 #include <Core/StdStream.h>
 #include <Draw/SWFeatureLevel.h>
+#include <Core/VoxelModel.h>
 #include <Draw/SWMapRenderer.h>
+#include <Draw/SWModel.h>
 #include <Draw/SWPort.h>
 #include <Draw/SWRenderer.h>
 
@@ -236,6 +239,106 @@ int oref_renderer_line(void *r, int i, uint32_t *combined, float *depth, float *
 	if (misc) { misc[0] = l.horizonDir.x; misc[1] = l.horizonDir.y; misc[2] = l.pitchTanMin; misc[3] = l.pitchScale; }
 	if (misci) { misci[0] = l.pitchTanMinI; misci[1] = l.pitchScaleI; }
 	return n;
+}
+
+/* ---- voxel models + dynamic lights ---- */
+void *oref_vmodel_load_kv6(const void *data, size_t len) {
+	try {
+		MemoryStream ms(reinterpret_cast<char *>(const_cast<void *>(data)), len);
+		Handle<VoxelModel> vm = VoxelModel::LoadKV6(ms);
+		return std::move(vm).Unmanage();
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+void *oref_vmodel_from_arrays(int w, int h, int d, const float origin[3], const uint64_t *solid, const uint32_t *colors) {
+	try {
+		Handle<VoxelModel> vm = Handle<VoxelModel>::New(w, h, d);
+		vm->SetOrigin(MakeVector3(origin[0], origin[1], origin[2]));
+		for (int y = 0; y < h; y++)
+			for (int x = 0; x < w; x++) {
+				vm->GetSolidBitsAt(x, y) = solid[x + y * w];
+				for (int z = 0; z < d; z++)
+					vm->GetColor(x, y, z) = colors[(size_t)(x + y * w) * d + z];
+			}
+		return std::move(vm).Unmanage();
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+void oref_vmodel_free(void *vm) { reinterpret_cast<VoxelModel *>(vm)->Release(); }
+
+void oref_vmodel_info(void *p, int dims[3], float origin[3]) {
+	auto *vm = reinterpret_cast<VoxelModel *>(p);
+	dims[0] = vm->GetWidth(); dims[1] = vm->GetHeight(); dims[2] = vm->GetDepth();
+	Vector3 o = vm->GetOrigin();
+	origin[0] = o.x; origin[1] = o.y; origin[2] = o.z;
+}
+
+void oref_vmodel_arrays(void *p, uint64_t *solid, uint32_t *colors) {
+	auto *vm = reinterpret_cast<VoxelModel *>(p);
+	const int w = vm->GetWidth(), h = vm->GetHeight(), d = vm->GetDepth();
+	for (int y = 0; y < h; y++)
+		for (int x = 0; x < w; x++) {
+			solid[x + y * w] = vm->GetSolidBitsAt(x, y);
+			for (int z = 0; z < d; z++)
+				colors[(size_t)(x + y * w) * d + z] = vm->GetColor(x, y, z);
+		}
+}
+
+void *oref_model_create(void *r, void *vm) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	try {
+		Handle<client::IModel> m = R->r->CreateModel(*reinterpret_cast<VoxelModel *>(vm));
+		return std::move(m).Unmanage();
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+void oref_model_free(void *m) { reinterpret_cast<client::IModel *>(m)->Release(); }
+
+int oref_model_render_data(void *m, uint32_t *data, int dataCap, uint32_t *addr, int addrCap) {
+	auto *sm = dynamic_cast<draw::SWModel *>(reinterpret_cast<client::IModel *>(m));
+	if (!sm) return -1;
+	if (data && dataCap >= (int)sm->renderData.size())
+		std::memcpy(data, sm->renderData.data(), sm->renderData.size() * 4);
+	if (addr && addrCap >= (int)sm->renderDataAddr.size())
+		std::memcpy(addr, sm->renderDataAddr.data(), sm->renderDataAddr.size() * 4);
+	return (int)sm->renderData.size();
+}
+
+int oref_renderer_render_scene(void *r, const oref_scene *s, void *const *models, const oref_model_param *params,
+                               int nModels, const oref_light *lights, int nLights, uint32_t *bgrx, float *depth) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	try {
+		client::SceneDefinition def;
+		def.viewportLeft = def.viewportTop = 0;
+		def.viewportWidth = R->w; def.viewportHeight = R->h;
+		def.fovX = s->fovX; def.fovY = s->fovY;
+		def.viewOrigin = MakeVector3(s->origin[0], s->origin[1], s->origin[2]);
+		for (int i = 0; i < 3; i++)
+			def.viewAxis[i] = MakeVector3(s->axis[i][0], s->axis[i][1], s->axis[i][2]);
+		def.zNear = s->zNear; def.zFar = s->zFar;
+		def.skipWorld = false;
+		R->r->StartScene(def);
+		for (int i = 0; i < nModels; i++) {
+			client::ModelRenderParam p;
+			for (int k = 0; k < 16; k++) p.matrix.m[k] = params[i].matrix[k];
+			p.customColor = MakeVector3(params[i].customColor[0], params[i].customColor[1], params[i].customColor[2]);
+			R->r->RenderModel(*reinterpret_cast<client::IModel *>(models[i]), p);
+		}
+		for (int i = 0; i < nLights; i++) {
+			client::DynamicLightParam p;
+			p.type = client::DynamicLightTypePoint;
+			p.origin = MakeVector3(lights[i].origin[0], lights[i].origin[1], lights[i].origin[2]);
+			p.radius = lights[i].radius;
+			p.color = MakeVector3(lights[i].color[0], lights[i].color[1], lights[i].color[2]);
+			R->r->AddLight(p);
+		}
+		R->r->EndScene();
+		R->r->FrameDone();
+		size_t n = (size_t)R->w * R->h;
+		if (bgrx) std::memcpy(bgrx, R->port->GetFramebuffer().GetPixels(), n * 4);
+		if (depth) std::memcpy(depth, R->r->depthBuffer.data(), n * 4);
+		return 0;
+	} catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
 } // extern "C"

@@ -62,6 +62,30 @@ OREF_API int oref_renderer_rle(void *r, int x, int y, int8_t *out, int cap);
 OREF_API int oref_renderer_lines(void *r, int *lineRes);
 OREF_API int oref_renderer_line(void *r, int i, uint32_t *combined, float *depth, float *misc /*horizX,horizY,pitchTanMin,pitchScale*/, int32_t *misci);
 
+/* ---- voxel models + dynamic lights inside EndScene (SWModel, SWModelRenderer, SWRenderer::AddLight / ApplyDynamicLight) ---- */
+typedef struct oref_model_param { /* client::ModelRenderParam fields the SW path reads (IRenderer.h:39-63) */
+	float matrix[16];
+	float customColor[3];
+} oref_model_param;
+typedef struct oref_light { /* client::DynamicLightParam, point lights only (SWRenderer.cpp:581-585) */
+	float origin[3];
+	float radius;
+	float color[3];
+} oref_light;
+OREF_API void *oref_vmodel_load_kv6(const void *data, size_t len);   /* VoxelModel::LoadKV6 */
+OREF_API void *oref_vmodel_from_arrays(int w, int h, int d, const float origin[3], const uint64_t *solid /*[x + y*w]*/,
+                                       const uint32_t *colors /*[(x + y*w)*d + z]*/);
+OREF_API void oref_vmodel_free(void *vm);
+OREF_API void oref_vmodel_info(void *vm, int dims[3], float origin[3]);
+OREF_API void oref_vmodel_arrays(void *vm, uint64_t *solid, uint32_t *colors);
+OREF_API void *oref_model_create(void *renderer, void *vm);           /* SWRenderer::CreateModel -> SWModel ctor */
+OREF_API void oref_model_free(void *model);
+/* SWModel::renderData / renderDataAddr (SWModel.cpp:25-100): returns renderData.size(); copies when the caps suffice */
+OREF_API int oref_model_render_data(void *model, uint32_t *data, int dataCap, uint32_t *addr, int addrCap);
+/* StartScene + RenderModel x nModels + AddLight x nLights + EndScene + FrameDone */
+OREF_API int oref_renderer_render_scene(void *r, const oref_scene *s, void *const *models, const oref_model_param *params,
+                                        int nModels, const oref_light *lights, int nLights, uint32_t *bgrx, float *depth);
+
 /* ---- CPU halves of GLMapShadowRenderer / GLRadiosityRenderer (oref_gl.cpp) ---- */
 OREF_API void *oref_rad_create(void *map, int mode /* r_radiosity: 1 sqrt-compressed, 2 linear */);
 OREF_API void oref_rad_free(void *h);

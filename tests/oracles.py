@@ -12,6 +12,8 @@ TITLE_VXL = os.path.join(ROOT, "tests", "golden", "maps", "Title.vxl")
 
 SCENE_DTYPE = np.dtype([("origin", "<f4", 3), ("axis", "<f4", (3, 3)), ("fovX", "<f4"), ("fovY", "<f4"),
                         ("zNear", "<f4"), ("zFar", "<f4")])
+MODEL_PARAM_DTYPE = np.dtype([("matrix", "<f4", 16), ("customColor", "<f4", 3)])
+LIGHT_DTYPE = np.dtype([("origin", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 3)])
 RAYHIT_DTYPE = np.dtype([("hit", "u1"), ("startSolid", "u1"), ("pad", "u1", 2), ("hitPos", "<f4", 3),
                          ("hitBlock", "<i4", 3), ("normal", "<i4", 3)])
 
@@ -421,9 +423,56 @@ class RefRadiosity:
         return np.stack(a, axis=-1)
 
 
+class RefVoxelModel:
+    """spades::VoxelModel of the reference (Core/VoxelModel.cpp) -- KV6 loader or raw arrays."""
+
+    def __init__(self, ref: Ref, kv6: bytes = None, arrays=None):
+        L = self.L = ref.L
+        L.oref_vmodel_load_kv6.restype = vp
+        L.oref_vmodel_load_kv6.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+        L.oref_vmodel_from_arrays.restype = vp
+        L.oref_vmodel_from_arrays.argtypes = [ci, ci, ci, vp, vp, vp]
+        L.oref_vmodel_free.argtypes = [vp]
+        L.oref_vmodel_info.argtypes = [vp, vp, vp]
+        L.oref_vmodel_arrays.argtypes = [vp, vp, vp]
+        if kv6 is not None:
+            self.h = L.oref_vmodel_load_kv6(kv6, len(kv6))
+        else:
+            w, h, d, origin, solid, colors = arrays
+            o = np.asarray(origin, np.float32)
+            solid = np.ascontiguousarray(solid, np.uint64)
+            colors = np.ascontiguousarray(colors, np.uint32)
+            self.h = L.oref_vmodel_from_arrays(w, h, d, o.ctypes.data, solid.ctypes.data, colors.ctypes.data)
+        if not self.h:
+            raise ValueError(L.oref_last_error().decode())
+        dims = np.zeros(3, np.int32)
+        org = np.zeros(3, np.float32)
+        L.oref_vmodel_info(self.h, dims.ctypes.data, org.ctypes.data)
+        self.w, self.hgt, self.d = (int(v) for v in dims)
+        self.origin = org
+
+    def arrays(self):
+        """solid uint64[h][w] (index x + y*w), colors uint32[h][w][d]"""
+        solid = np.zeros((self.hgt, self.w), np.uint64)
+        colors = np.zeros((self.hgt, self.w, self.d), np.uint32)
+        self.L.oref_vmodel_arrays(self.h, solid.ctypes.data, colors.ctypes.data)
+        return solid, colors
+
+    def close(self):
+        if self.h:
+            self.L.oref_vmodel_free(self.h)
+            self.h = None
+
+
 class RefRenderer:
     def __init__(self, ref: Ref, w, h, level=-1, threads=4):
         self.ref, self.w, self.h = ref, w, h
+        L = ref.L
+        L.oref_model_create.restype = vp
+        L.oref_model_create.argtypes = [vp, vp]
+        L.oref_model_free.argtypes = [vp]
+        L.oref_model_render_data.argtypes = [vp, vp, ci, vp, ci]
+        L.oref_renderer_render_scene.argtypes = [vp, vp, vp, vp, ci, vp, ci, vp, vp]
         self.r = ref.L.oref_renderer_create(w, h, level, threads)
         if not self.r:
             raise RuntimeError(ref.L.oref_last_error().decode())
@@ -439,6 +488,36 @@ class RefRenderer:
         dp = np.zeros((self.h, self.w), np.float32)
         sc = np.ascontiguousarray(scene)
         rc = self.ref.L.oref_renderer_render(self.r, sc.ctypes.data, fb.ctypes.data, dp.ctypes.data)
+        if rc:
+            raise RuntimeError(self.ref.L.oref_last_error().decode())
+        return fb, dp
+
+    def create_model(self, vmodel: "RefVoxelModel"):
+        m = self.ref.L.oref_model_create(self.r, vmodel.h)
+        if not m:
+            raise RuntimeError(self.ref.L.oref_last_error().decode())
+        return m
+
+    def free_model(self, m):
+        self.ref.L.oref_model_free(m)
+
+    def model_render_data(self, m, ncols):
+        n = self.ref.L.oref_model_render_data(m, None, 0, None, 0)
+        data = np.zeros(n, np.uint32)
+        addr = np.zeros(ncols, np.uint32)
+        self.ref.L.oref_model_render_data(m, data.ctypes.data, n, addr.ctypes.data, ncols)
+        return data, addr
+
+    def render_scene(self, scene, models=(), params=None, lights=None):
+        """StartScene + RenderModel* + AddLight* + EndScene; params: MODEL_PARAM_DTYPE[n], lights: LIGHT_DTYPE[m]"""
+        fb = np.zeros((self.h, self.w), np.uint32)
+        dp = np.zeros((self.h, self.w), np.float32)
+        sc = np.ascontiguousarray(scene)
+        arr = (vp * max(1, len(models)))(*models)
+        params = np.zeros(0, MODEL_PARAM_DTYPE) if params is None else np.ascontiguousarray(params)
+        lights = np.zeros(0, LIGHT_DTYPE) if lights is None else np.ascontiguousarray(lights)
+        rc = self.ref.L.oref_renderer_render_scene(self.r, sc.ctypes.data, arr, params.ctypes.data, len(models),
+                                                   lights.ctypes.data, len(lights), fb.ctypes.data, dp.ctypes.data)
         if rc:
             raise RuntimeError(self.ref.L.oref_last_error().decode())
         return fb, dp
