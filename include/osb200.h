@@ -178,6 +178,39 @@ OSB200_API int osb200_radiosity_evaluate_box(osb200_ctx *ctx, int x0, int y0, in
 OSB200_API int osb200_radiosity_volumes(osb200_ctx *ctx, const uint32_t **flat, const uint32_t **x,
                                         const uint32_t **y, const uint32_t **z, const uint32_t **shadow);
 
+/* ---- the full EndScene of the software renderer: terrain, voxel models, dynamic lights, fog (SWRenderer.cpp:709-745) ----
+ * A model is created once from a VoxelModel's arrays (= SWRenderer::CreateModel -> SWModel::SWModel, SWModel.cpp:25-100):
+ * solid[x + y*w] has bit z set for a solid voxel, colors[(x + y*w)*d + z] = material << 24 | 0xBBGGRR as VoxelModel
+ * stores them (VoxelModel.h:68-106), origin = VoxelModel::GetOrigin().  d <= 64. */
+typedef struct osb200_model osb200_model;
+OSB200_API int osb200_model_create(osb200_ctx *ctx, int w, int h, int d, const float origin[3], const uint64_t *solid,
+                                   const uint32_t *colors, osb200_model **out);
+OSB200_API void osb200_model_destroy(osb200_model *model);
+/* SWModel::renderData / renderDataAddr (test hook): returns renderData.size(); copies when the capacities suffice */
+OSB200_API int osb200_model_render_data(const osb200_model *model, uint32_t *data, int dataCap, uint32_t *addr, int addrCap);
+
+/* one IRenderer::RenderModel call: client::ModelRenderParam's matrix (column-major, Matrix4::m) and customColor
+ * (IRenderer.h:39-63; depthHack / ghost / opacity are not read by the software renderer) */
+typedef struct osb200_model_instance {
+	const osb200_model *model;
+	float matrix[16];
+	float customColor[3];
+} osb200_model_instance;
+/* one IRenderer::AddLight call; only point lights are drawn by the software renderer (SWRenderer.cpp:581-585) */
+typedef struct osb200_light {
+	float origin[3];
+	float radius;
+	float color[3];
+} osb200_light;
+/* StartScene + RenderModel x nInst + AddLight x nLights + EndScene for one view: terrain (as osb200_render), then every
+ * model splatted voxel by voxel with the reference's strict depth test and submission order (SWModelRenderer.cpp:46-277),
+ * then the dynamic lights in submission order (SWRenderer::AddLight culls :578-649, ApplyDynamicLight :229-339), then the
+ * fog.  Frame and depth live in the context (persistent depth, see osb200_render) and are copied to the nullable host
+ * pointers; the call synchronises. */
+OSB200_API int osb200_render_scene(osb200_ctx *ctx, const osb200_scene *scene, int w, int h, const float fogColor[3],
+                                   float fogDist, const osb200_model_instance *inst, int nInst, const osb200_light *lights,
+                                   int nLights, uint32_t *host_bgrx, float *host_depth);
+
 /* ---- GameMap::CastRay (GameMap.cpp:208-359), batched: the integer cell-wall walk used by the ambient-occlusion
  *      evaluation and by the game's hit tests.  v0, dir: n x 3 floats; one length for the batch (the walk takes at most
  *      (long)length cell walls); out: n x {hit, hitBlock.x, hitBlock.y, hitBlock.z} int32 (zeros on a miss). ---- */

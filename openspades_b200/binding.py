@@ -13,6 +13,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OSB200_LIB") or os.path.join(_HERE, "lib", "libosb200.so")  # override: kernel A/B experiments
 
 NUM_IEEE, NUM_SSE, NUM_SSE2 = 0, 1, 2
+# osb200_model_instance (pointer + 16 + 3 floats, 4 bytes of tail padding) and osb200_light
+MODEL_INSTANCE_DTYPE = np.dtype({"names": ["model", "matrix", "customColor"], "formats": ["<u8", ("<f4", 16), ("<f4", 3)],
+                                 "offsets": [0, 8, 72], "itemsize": 88})
+LIGHT_DTYPE = np.dtype([("origin", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 3)])
 
 
 class OsbError(RuntimeError):
@@ -86,6 +90,11 @@ def load_library():
     lib.osb200_radiosity_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
     lib.osb200_radiosity_volumes.argtypes = [vp] + [ctypes.POINTER(vp)] * 5
     lib.osb200_castray.argtypes = [vp, vp, vp, fp, vp, sz]
+    lib.osb200_model_create.argtypes = [vp, ci, ci, ci, vp, vp, vp, ctypes.POINTER(vp)]
+    lib.osb200_model_destroy.argtypes = [vp]
+    lib.osb200_model_destroy.restype = None
+    lib.osb200_model_render_data.argtypes = [vp, vp, ci, vp, ci]
+    lib.osb200_render_scene.argtypes = [vp, vp, ci, ci, vp, fp, vp, ci, vp, ci, vp, vp]
     lib.osb200_castray_device.argtypes = [vp, vp, vp, fp, vp, sz]
     lib.osb200_ambient_set_rays.argtypes = [vp, vp]
     lib.osb200_ambient_get_rays.argtypes = [vp, vp]
@@ -266,6 +275,44 @@ class Context:
         self._check(self._lib.osb200_radiosity_evaluate_box(self._h, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
                                                             out.ctypes.data))
         return out
+
+    # ---- voxel models + dynamic lights: the full EndScene ----
+    def model_create(self, w, h, d, origin, solid, colors):
+        """SWModel from VoxelModel arrays: solid uint64[h][w] (index x + y*w), colors uint32[h][w][d]. Returns a handle."""
+        o = np.asarray(origin, np.float32)
+        solid = np.ascontiguousarray(solid, np.uint64)
+        colors = np.ascontiguousarray(colors, np.uint32)
+        assert solid.size == w * h and colors.size == w * h * d
+        m = ctypes.c_void_p()
+        self._check(self._lib.osb200_model_create(self._h, w, h, d, o.ctypes.data, solid.ctypes.data, colors.ctypes.data,
+                                                  ctypes.byref(m)))
+        return m.value
+
+    def model_destroy(self, m):
+        self._lib.osb200_model_destroy(m)
+
+    def model_render_data(self, m, ncols):
+        n = self._lib.osb200_model_render_data(m, None, 0, None, 0)
+        data = np.zeros(n, np.uint32)
+        addr = np.zeros(ncols, np.uint32)
+        self._lib.osb200_model_render_data(m, data.ctypes.data, n, addr.ctypes.data, ncols)
+        return data, addr
+
+    def render_scene(self, scene, w, h, fog_color, fog_dist, instances=None, lights=None, want_depth=True):
+        """One view: terrain + models (MODEL_INSTANCE_DTYPE[n]) + point lights (LIGHT_DTYPE[m]) + fog."""
+        scene = np.ascontiguousarray(np.atleast_1d(scene))
+        assert scene.dtype == SCENE_DTYPE and len(scene) == 1
+        inst = np.zeros(0, MODEL_INSTANCE_DTYPE) if instances is None else np.ascontiguousarray(instances)
+        lg = np.zeros(0, LIGHT_DTYPE) if lights is None else np.ascontiguousarray(lights)
+        assert inst.dtype == MODEL_INSTANCE_DTYPE and lg.dtype == LIGHT_DTYPE
+        fb = np.empty((h, w), np.uint32)
+        dp = np.empty((h, w), np.float32) if want_depth else None
+        fc = np.asarray(fog_color, np.float32)
+        self._check(self._lib.osb200_render_scene(self._h, scene.ctypes.data, w, h, fc.ctypes.data, float(fog_dist),
+                                                  inst.ctypes.data if len(inst) else None, len(inst),
+                                                  lg.ctypes.data if len(lg) else None, len(lg), fb.ctypes.data,
+                                                  None if dp is None else dp.ctypes.data))
+        return fb, dp
 
     # ---- GameMap::CastRay + ambient occlusion ----
     def castray(self, v0, dirs, length):

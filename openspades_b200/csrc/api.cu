@@ -26,7 +26,8 @@ namespace osb {
 	const char *kernel_name(int id) {
 		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_build_lines",
 		                                     "k_gather_fog", "k_castray2", "k_shadow_update", "k_radiosity",
-		                                     "k_rad_select", "k_castray", "k_ao_chunk"};
+		                                     "k_rad_select", "k_castray", "k_ao_chunk", "k_fog", "k_model_setup", "k_model_splat",
+		                                     "k_model_resolve", "k_lights"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
 	KLaunch::KLaunch(osb200_ctx *ctx, int kid, cudaStream_t stream) : c(ctx), slot(-1), st(stream ? stream : ctx->stream) {
@@ -49,6 +50,7 @@ namespace osb {
 	void radiosity_map_replaced(osb200_ctx *ctx);
 	void radiosity_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
 	void ambient_destroy(osb200_ctx *ctx);   // ambient.cu
+	void models_destroy(osb200_ctx *ctx);    // models.cu
 	void ambient_map_replaced(osb200_ctx *ctx);
 	void ambient_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
 } // namespace osb
@@ -269,6 +271,7 @@ void osb200_destroy(osb200_ctx *c) {
 	osb::terrain_destroy(c);
 	osb::radiosity_destroy(c);
 	osb::ambient_destroy(c);
+	osb::models_destroy(c);
 	cudaFree(c->d_solid); // bitmap + colours are one allocation
 	cudaFree(c->d_rcp);
 	cudaFree(c->d_rsqrt);

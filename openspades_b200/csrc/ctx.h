@@ -43,6 +43,11 @@ namespace osb {
 		K_RAD_SELECT,
 		K_CASTRAY,
 		K_AMBIENT,
+		K_FOG,
+		K_MODEL_SETUP,
+		K_MODEL_SPLAT,
+		K_MODEL_RESOLVE,
+		K_LIGHTS,
 		K_COUNT
 	};
 	const char *kernel_name(int id);
@@ -50,10 +55,17 @@ namespace osb {
 	struct TerrainState;   // terrain.cu
 	struct RadiosityState; // radiosity.cu
 	struct AmbientState;   // ambient.cu
+	struct ModelState;     // models.cu
 } // namespace osb
 
 struct osb200_ctx;
 namespace osb {
+	// terrain.cu, shared with models.cu (the full EndScene: terrain -> models -> lights -> fog)
+	int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
+	                float fogDist, uint32_t *d_fb, float *d_depth, uint32_t *host_fb, float *host_depth, bool deferFog);
+	int terrain_out_buffers(osb200_ctx *c, size_t n, uint32_t **fb, float **depth);
+	int terrain_apply_fog(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, const float *d_depth);
+
 	// RAII bracket around one kernel launch: counts it and, when timing is on, records CUDA events
 	// on the context stream before and after it.
 	struct KLaunch {
@@ -111,6 +123,7 @@ struct osb200_ctx {
 	osb::TerrainState *terrain = nullptr;
 	osb::RadiosityState *radiosity = nullptr;
 	osb::AmbientState *ambient = nullptr;
+	osb::ModelState *models = nullptr;
 
 	int ensure_scratch(size_t bytes);
 	int ensure_stage(size_t bytes);

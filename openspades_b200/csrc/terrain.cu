@@ -52,6 +52,7 @@ namespace osb {
 
 	struct FrameGeom {
 		int fw, fh, under, swThreads, sse2Fog, sse2Shade;
+		int noFog; // fog deferred to k_fog (models / dynamic lights are drawn between terrain and fog, SWRenderer.cpp:727-744)
 		int noMap; // no map set: SWRenderer::EndScene still clears and fogs over the stale depth (SWRenderer.cpp:713-744)
 		uint32_t fogB, fogG, fogR;
 	};
@@ -677,7 +678,7 @@ namespace osb {
 #pragma unroll
 					for (int py = 0; py < 8; py++, o += g.fw) {
 						const float dep = dbV[o];
-						fbV[o] = fog_blend<kSse2Fog>(0x7f7f7fu, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8);
+						fbV[o] = g.noFog ? 0x7f7f7fu : fog_blend<kSse2Fog>(0x7f7f7fu, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8);
 					}
 				}
 				continue;
@@ -726,7 +727,7 @@ namespace osb {
 						pitchIndex &= lineRes - 1;
 						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
 						const float dep = __uint_as_float(pix.y);
-						__stcs(fbV + o, fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
+						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
 						__stcs(dbV + o, dep);
 					}
 				} else {
@@ -753,7 +754,7 @@ namespace osb {
 						const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
 						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
 						const float dep = __uint_as_float(pix.y);
-						__stcs(fbV + o, fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
+						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
 						__stcs(dbV + o, dep);
 #pragma unroll
 						for (int k = 0; k < 3; k++)
@@ -765,6 +766,26 @@ namespace osb {
 			for (int k = 0; k < 3; k++)
 				v2[k] = __fadd_rn(v2[k], dDL[k]);
 		}
+	}
+
+	// SWRenderer::ApplyFog as a pass of its own (SWRenderer.cpp:341-516), for frames that draw models / dynamic lights
+	// between terrain and fog.  Same per-4x4-block scale and blend as the fused path in k_gather_fog.
+	template <bool kSse, bool kSse2Fog>
+	__global__ void __launch_bounds__(256)
+	  k_fog(const ViewParams *__restrict__ views, FrameGeom g, const float *__restrict__ tabs, osbn::SseTables sse,
+	        uint32_t *__restrict__ fb, const float *__restrict__ depthBuf) {
+		const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+		if (x >= g.fw || y >= g.fh)
+			return;
+		const ViewParams &V = views[blockIdx.z];
+		osbn::Num<kSse> num{sse};
+		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2);
+		const float vx = vxTab[x >> 2], vy = vyTab[y >> 2];
+		float ds = __fadd_rn(__fadd_rn(1.f, __fmul_rn(vx, vx)), __fmul_rn(vy, vy));
+		ds = __fmul_rn(ds, __fmul_rn(num.rsqrt(ds), V.fogScale));
+		const size_t o = (size_t)blockIdx.z * g.fw * g.fh + (size_t)y * g.fw + x;
+		const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
+		fb[o] = fog_blend<kSse2Fog>(fb[o], __fmul_rn(depthBuf[o], ds), fogBR, fogG8);
 	}
 
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
@@ -959,9 +980,8 @@ namespace osb {
 
 	// host_fb / host_depth (nullable): when given, each chunk's finished frames are copied to the host on a second
 	// stream while the next chunk renders (PCIe overlaps the kernels); the caller synchronises copyDone.
-	static int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
-	                       const float fogColor[3], float fogDist, uint32_t *d_fb, float *d_depth,
-	                       uint32_t *host_fb = nullptr, float *host_depth = nullptr) {
+	int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
+	                float fogDist, uint32_t *d_fb, float *d_depth, uint32_t *host_fb, float *host_depth, bool deferFog) {
 		if (!c) {
 			set_error("osb200_render: no context");
 			return -1;
@@ -992,6 +1012,7 @@ namespace osb {
 		g.swThreads = c->opts.sw_threads;
 		g.sse2Fog = g.sse2Shade = c->opts.numerics == OSB200_NUM_SSE2;
 		g.noMap = c->mapLoaded ? 0 : 1;
+		g.noFog = deferFog ? 1 : 0;
 		auto toFixed8 = [](float v) { // SWUtils.h:68-71
 			int i = static_cast<int>(v * 255.f + .5f);
 			return (uint32_t)std::max(std::min(i, 255), 0);
@@ -1155,6 +1176,59 @@ namespace osb {
 		OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
 		return 0;
 	}
+	// Context-owned frame + depth of the host-pointer entry points.  The depth buffer persists between frames like
+	// SWRenderer::depthBuffer (never cleared, SWRenderer.cpp:83); a fresh one starts at zero like vector::resize.
+	int terrain_out_buffers(osb200_ctx *c, size_t n, uint32_t **fb, float **depth) {
+		if (terrain_init(c))
+			return -2;
+		TerrainState *T = c->terrain;
+		if (n != T->outCap) {
+			cudaFree(T->d_fb);
+			cudaFree(T->d_depth);
+			T->d_fb = nullptr;
+			T->d_depth = nullptr;
+			T->outCap = 0;
+			OSB_CUDA(cudaMalloc(&T->d_fb, n * 4));
+			OSB_CUDA(cudaMalloc(&T->d_depth, n * 4));
+			OSB_CUDA(cudaMemsetAsync(T->d_depth, 0, n * 4, c->stream));
+			T->outCap = n;
+		}
+		// the previous call's copies must not race with this call's kernels overwriting the same device buffers
+		OSB_CUDA(cudaStreamSynchronize(T->copyStream));
+		*fb = T->d_fb;
+		*depth = T->d_depth;
+		return 0;
+	}
+
+	// ApplyFog over the single view last set up by render_impl(.., deferFog = true) on the context stream
+	int terrain_apply_fog(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, const float *d_depth) {
+		TerrainState *T = c->terrain;
+		FrameGeom g;
+		std::memset(&g, 0, sizeof(g));
+		g.fw = w;
+		g.fh = h;
+		g.under = c->opts.undersampling;
+		g.swThreads = c->opts.sw_threads;
+		g.sse2Fog = g.sse2Shade = c->opts.numerics == OSB200_NUM_SSE2;
+		auto toFixed8 = [](float v) {
+			int i = static_cast<int>(v * 255.f + .5f);
+			return (uint32_t)std::max(std::min(i, 255), 0);
+		};
+		g.fogR = toFixed8(fogColor[0]);
+		g.fogG = toFixed8(fogColor[1]);
+		g.fogB = toFixed8(fogColor[2]);
+		osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
+		const dim3 grid((w + 31) / 32, (h + 7) / 8, 1);
+		KLaunch kl(c, K_FOG);
+		if (c->opts.numerics == OSB200_NUM_IEEE)
+			k_fog<false, false><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+		else if (c->opts.numerics == OSB200_NUM_SSE)
+			k_fog<true, false><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+		else
+			k_fog<true, true><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+		OSB_CUDA(cudaGetLastError());
+		return 0;
+	}
 } // namespace osb
 
 extern "C" {
@@ -1172,7 +1246,7 @@ __attribute__((visibility("default"))) int osb200_debug_stats(unsigned long long
 
 int osb200_render_device(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h,
                          const float fogColor[3], float fogDist, uint32_t *d_bgrx, float *d_depth) {
-	return osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, d_bgrx, d_depth);
+	return osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, d_bgrx, d_depth, nullptr, nullptr, false);
 }
 
 int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
@@ -1191,23 +1265,11 @@ int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, 
 	if (osb::terrain_init(c))
 		return -2;
 	osb::TerrainState *T = c->terrain;
-	const size_t n = (size_t)nViews * w * h;
-	if (n != T->outCap) {
-		// the depth buffer persists between frames like SWRenderer::depthBuffer (never cleared, SWRenderer.cpp:83);
-		// a fresh one starts at zero like std::vector<float>::resize
-		cudaFree(T->d_fb);
-		cudaFree(T->d_depth);
-		T->d_fb = nullptr;
-		T->d_depth = nullptr;
-		T->outCap = 0;
-		OSB_CUDA(cudaMalloc(&T->d_fb, n * 4));
-		OSB_CUDA(cudaMalloc(&T->d_depth, n * 4));
-		OSB_CUDA(cudaMemsetAsync(T->d_depth, 0, n * 4, c->stream));
-		T->outCap = n;
-	}
-	// the previous call's copies must not race with this call's kernels overwriting the same device buffers
-	OSB_CUDA(cudaStreamSynchronize(T->copyStream));
-	int rc = osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, T->d_fb, T->d_depth, host_bgrx, host_depth);
+	uint32_t *ofb;
+	float *odp;
+	if (int rc0 = osb::terrain_out_buffers(c, (size_t)nViews * w * h, &ofb, &odp))
+		return rc0;
+	int rc = osb::render_impl(c, scenes, nViews, w, h, fogColor, fogDist, T->d_fb, T->d_depth, host_bgrx, host_depth, false);
 	if (rc)
 		return rc;
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
