@@ -111,15 +111,51 @@ namespace osb200 {
 		duringSceneRendering_ = true;
 	}
 
-	void B200Renderer::AddLight(const void *) {
+	Model::~Model() { osb200_model_destroy(m_); }
+
+	std::unique_ptr<Model> B200Renderer::CreateModel(const VoxelModelData &vm) {
 		EnsureInitialized();
-		EnsureSceneStarted();
+		if (vm.width <= 0 || vm.height <= 0 || vm.depth <= 0 ||
+		    vm.solidBits.size() != (size_t)vm.width * vm.height ||
+		    vm.colors.size() != (size_t)vm.width * vm.height * vm.depth)
+			throw RendererError("invalid voxel model");
+		const float origin[3] = {vm.origin.x, vm.origin.y, vm.origin.z};
+		osb200_model *m = nullptr;
+		if (osb200_model_create(ctx_, vm.width, vm.height, vm.depth, origin, vm.solidBits.data(), vm.colors.data(), &m) != 0)
+			RaiseAbi("osb200_model_create");
+		return std::unique_ptr<Model>(new Model(m, this));
 	}
-	void B200Renderer::RenderModel(const void *model, const void *) {
+
+	void B200Renderer::AddLight(const DynamicLightParam &param) {
+		// SWRenderer.cpp:578-585; the culls and the screen rectangle (:587-649) are evaluated inside osb200_render_scene
 		EnsureInitialized();
 		EnsureSceneStarted();
-		if (!model)
-			throw RendererError("null model"); // SPInvalidArgument("model") for a foreign model in the reference
+		if (param.type != DynamicLightTypePoint)
+			return;
+		osb200_light l;
+		l.origin[0] = param.origin.x;
+		l.origin[1] = param.origin.y;
+		l.origin[2] = param.origin.z;
+		l.radius = param.radius;
+		l.color[0] = param.color.x;
+		l.color[1] = param.color.y;
+		l.color[2] = param.color.z;
+		lights_.push_back(l);
+	}
+	void B200Renderer::RenderModel(Model &model, const ModelRenderParam &param) {
+		// SWRenderer.cpp:565-576
+		EnsureInitialized();
+		EnsureSceneStarted();
+		if (model.owner_ != this)
+			throw RendererError("model"); // SPInvalidArgument("model"): the dynamic_cast<SWModel&> of a foreign model
+		osb200_model_instance inst;
+		inst.model = model.m_;
+		for (int i = 0; i < 16; i++)
+			inst.matrix[i] = param.matrix[i];
+		inst.customColor[0] = param.customColor.x;
+		inst.customColor[1] = param.customColor.y;
+		inst.customColor[2] = param.customColor.z;
+		models_.push_back(inst);
 	}
 	void B200Renderer::AddDebugLine(Vector3, Vector3, const float *) {
 		EnsureInitialized();
@@ -136,7 +172,7 @@ namespace osb200 {
 
 	void B200Renderer::EndScene() {
 		// SWRenderer.cpp:709-745: clear to 0x7f7f7f, flat-map Update (drains dirty columns -> UpdateRle x5),
-		// terrain, [models, lights: not drawn here], fog.  The clear is folded into the kernels: the terrain
+		// terrain, models, lights, fog.  The clear is folded into the kernels: the terrain
 		// pass writes every pixel, or 0x7f7f7f when the eye is inside a solid voxel (SWMapRenderer.cpp:1181-1184).
 		EnsureInitialized();
 		EnsureSceneStarted();
@@ -167,8 +203,14 @@ namespace osb200 {
 		sc.zNear = sceneDef_.zNear;
 		sc.zFar = sceneDef_.zFar;
 		const float fog[3] = {fogColor_.x, fogColor_.y, fogColor_.z};
-		if (osb200_render(ctx_, &sc, 1, w, h, fog, fogDistance_, fb_->GetPixels(), nullptr) != 0)
-			RaiseAbi("osb200_render");
+		// models.clear() / lights.clear() of the reference (:731,737) happen whether or not the draw succeeds
+		std::vector<osb200_model_instance> models;
+		std::vector<osb200_light> lights;
+		models.swap(models_);
+		lights.swap(lights_);
+		if (osb200_render_scene(ctx_, &sc, w, h, fog, fogDistance_, models.data(), (int)models.size(), lights.data(),
+		                        (int)lights.size(), fb_->GetPixels(), nullptr) != 0)
+			RaiseAbi("osb200_render_scene");
 	}
 
 	void B200Renderer::FrameDone() {

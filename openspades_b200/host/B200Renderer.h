@@ -5,11 +5,12 @@
 // (include/osb200.h) to the CUDA kernels.  There is no CPU rendering path in this class.
 //
 // What is mirrored:  Init / Shutdown, SetGameMap (+ listener registration), SetFogDistance / SetFogColor,
-//   StartScene / EndScene (terrain pass + fog of EndScene, SWRenderer.cpp:709-745), FrameDone, Flip, ReadBitmap,
+//   StartScene / EndScene (terrain pass, voxel models, dynamic point lights and fog of EndScene, SWRenderer.cpp:709-745),
+//   CreateModel / RenderModel (SWModel + SWModelRenderer), AddLight (SWRenderer.cpp:578-649), FrameDone, Flip, ReadBitmap,
 //   ScreenWidth / ScreenHeight, GameMapChanged -> dirty-column bitset -> re-upload at the next EndScene
 //   (SWFlatMapRenderer::SetNeedsUpdate / Update, SWFlatMapRenderer.cpp:52-111).
-// What is accepted and NOT drawn (out of scope): RenderModel, AddLight, AddSprite,
-//   AddLongSprite, AddDebugLine and the 2-D DrawImage family; they only enforce the same call-order rules.
+// What is accepted and NOT drawn (out of scope): AddSprite, AddLongSprite, AddDebugLine and the
+//   2-D DrawImage family; they only enforce the same call-order rules.
 // Extension beyond SWRenderer (the CPU halves of GLRenderer's map shadow + radiosity):
 //   UpdateRadiosity(), and of the ray-traced ambient occlusion volume (GLAmbientShadowRenderer): UpdateAmbient().
 //
@@ -94,6 +95,41 @@ namespace osb200 {
 		int radiosityMode = 1;          // r_radiosity
 	};
 
+	// spades::VoxelModel's data as SWModel reads it (Core/VoxelModel.h:68-106): solid[x + y*w] bit z, colors[(x + y*w)*d + z]
+	struct VoxelModelData {
+		int width = 0, height = 0, depth = 0;
+		Vector3 origin{0, 0, 0};
+		std::vector<uint64_t> solidBits;
+		std::vector<uint32_t> colors;
+	};
+	// client::ModelRenderParam (IRenderer.h:39-63): the two fields the software renderer reads
+	struct ModelRenderParam {
+		float matrix[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}; // Matrix4::m, column-major
+		Vector3 customColor{0, 0, 0};
+	};
+	enum DynamicLightType { DynamicLightTypePoint, DynamicLightTypeSpotlight, DynamicLightTypeLinear };
+	// client::DynamicLightParam (IRenderer.h:71-96); only point lights are drawn (SWRenderer.cpp:581-585)
+	struct DynamicLightParam {
+		DynamicLightType type = DynamicLightTypePoint;
+		Vector3 origin{0, 0, 0};
+		float radius = 1.f;
+		Vector3 color{1, 1, 1};
+	};
+	class B200Renderer;
+	// client::IModel as SWRenderer::CreateModel returns it (draw::SWModel): owns the device copy of the render data
+	class Model {
+	public:
+		~Model();
+		Model(const Model &) = delete;
+		Model &operator=(const Model &) = delete;
+
+	private:
+		friend class B200Renderer;
+		Model(osb200_model *m, const B200Renderer *owner) : m_(m), owner_(owner) {}
+		osb200_model *m_;
+		const B200Renderer *owner_;
+	};
+
 	class B200Renderer : public IVoxelMapListener {
 	public:
 		explicit B200Renderer(std::shared_ptr<FramebufferPort> port, const B200RendererOptions &opts = B200RendererOptions());
@@ -107,9 +143,12 @@ namespace osb200 {
 		void SetFogColor(Vector3 v) { fogColor_ = v; }
 
 		void StartScene(const SceneDefinition &def);
+		// SWRenderer::CreateModel (SWRenderer.cpp:142-147): builds SWModel's render data and uploads it
+		std::unique_ptr<Model> CreateModel(const VoxelModelData &vm);
+		// queued until EndScene, drawn in submission order between terrain and fog
+		void AddLight(const DynamicLightParam &param);
+		void RenderModel(Model &model, const ModelRenderParam &param);
 		// accepted, order-checked, not drawn (see header comment)
-		void AddLight(const void *dynamicLightParam);
-		void RenderModel(const void *model, const void *modelRenderParam);
 		void AddDebugLine(Vector3 a, Vector3 b, const float color[4]);
 		void AddSprite(const void *image, Vector3 center, float radius, float rotation);
 		void AddLongSprite(const void *image, Vector3 p1, Vector3 p2, float radius);
@@ -163,6 +202,8 @@ namespace osb200 {
 		float fogDistance_ = 128.f;
 		Vector3 fogColor_{0.f, 0.f, 0.f};
 		int lastFlushed_ = 0;
+		std::vector<osb200_model_instance> models_; // RenderModel calls of the open scene
+		std::vector<osb200_light> lights_;          // AddLight calls of the open scene (point lights)
 		std::mutex dirtyMutex_; // GameMapChanged may arrive from another thread (SWFlatMapRenderer.cpp:107-111)
 	};
 } // namespace osb200

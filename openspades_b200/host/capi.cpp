@@ -142,6 +142,39 @@ OSBH_API int osbh_renderer_update_ambient(void *p, int maxChunks, int *updated) 
 OSBH_API int osbh_renderer_set_ambient_rays(void *p, const float *rays) {
 	return guarded([&] { R(p)->SetAmbientRays(rays); });
 }
+OSBH_API int osbh_renderer_create_model(void *p, int w, int h, int d, const float *origin, const uint64_t *solid,
+                                        const uint32_t *colors, void **out) {
+	return guarded([&] {
+		osb200::VoxelModelData vm;
+		vm.width = w;
+		vm.height = h;
+		vm.depth = d;
+		vm.origin = {origin[0], origin[1], origin[2]};
+		vm.solidBits.assign(solid, solid + (size_t)w * h);
+		vm.colors.assign(colors, colors + (size_t)w * h * d);
+		*out = R(p)->CreateModel(vm).release();
+	});
+}
+OSBH_API void osbh_model_free(void *m) { delete static_cast<osb200::Model *>(m); }
+OSBH_API int osbh_renderer_render_model(void *p, void *model, const float *matrix, const float *customColor) {
+	return guarded([&] {
+		osb200::ModelRenderParam prm;
+		for (int i = 0; i < 16; i++)
+			prm.matrix[i] = matrix[i];
+		prm.customColor = {customColor[0], customColor[1], customColor[2]};
+		R(p)->RenderModel(*static_cast<osb200::Model *>(model), prm);
+	});
+}
+OSBH_API int osbh_renderer_add_light(void *p, int type, const float *origin, float radius, const float *color) {
+	return guarded([&] {
+		osb200::DynamicLightParam prm;
+		prm.type = static_cast<osb200::DynamicLightType>(type);
+		prm.origin = {origin[0], origin[1], origin[2]};
+		prm.radius = radius;
+		prm.color = {color[0], color[1], color[2]};
+		R(p)->AddLight(prm);
+	});
+}
 OSBH_API int osbh_renderer_last_flushed(void *p) { return R(p)->LastFlushedColumns(); }
 OSBH_API void *osbh_renderer_context(void *p) { return R(p)->Context(); }
 OSBH_API int osbh_map_castray2(void *m, void *ctx, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,

@@ -120,6 +120,11 @@ class B200Renderer:
         L.osbh_renderer_screen.argtypes = [vp, ctypes.POINTER(fp), ctypes.POINTER(fp)]
         L.osbh_renderer_update_radiosity.argtypes = [vp, ci, ctypes.POINTER(ci)]
         L.osbh_renderer_update_ambient.argtypes = [vp, ci, ctypes.POINTER(ci)]
+        L.osbh_renderer_create_model.argtypes = [vp, ci, ci, ci, vp, vp, vp, ctypes.POINTER(vp)]
+        L.osbh_model_free.argtypes = [vp]
+        L.osbh_model_free.restype = None
+        L.osbh_renderer_render_model.argtypes = [vp, vp, vp, vp]
+        L.osbh_renderer_add_light.argtypes = [vp, ci, vp, ctypes.c_float, vp]
         L.osbh_renderer_set_ambient_rays.argtypes = [vp, vp]
         L.osbh_map_castray.argtypes = [vp, vp, vp, vp, ctypes.c_float, vp, ctypes.c_size_t]
         L.osbh_map_castray2.argtypes = [vp, vp, vp, vp, ci, vp, ctypes.c_size_t]
@@ -193,6 +198,29 @@ class B200Renderer:
         n = ctypes.c_int()
         self._chk(self._L.osbh_renderer_update_radiosity(self._h, max_chunks, ctypes.byref(n)))
         return n.value
+
+    def create_model(self, w, h, d, origin, solid, colors):
+        """B200Renderer::CreateModel from VoxelModel arrays; returns a Model handle (free with free_model)."""
+        o = np.asarray(origin, np.float32)
+        solid = np.ascontiguousarray(solid, np.uint64)
+        colors = np.ascontiguousarray(colors, np.uint32)
+        m = ctypes.c_void_p()
+        self._chk(self._L.osbh_renderer_create_model(self._h, w, h, d, o.ctypes.data, solid.ctypes.data,
+                                                     colors.ctypes.data, ctypes.byref(m)))
+        return m.value
+
+    def free_model(self, m):
+        self._L.osbh_model_free(m)
+
+    def render_model(self, model, matrix, custom_color=(0, 0, 0)):
+        mt = np.ascontiguousarray(matrix, np.float32)
+        cc = np.asarray(custom_color, np.float32)
+        self._chk(self._L.osbh_renderer_render_model(self._h, model, mt.ctypes.data, cc.ctypes.data))
+
+    def add_light(self, origin, radius, color, light_type=0):
+        o = np.asarray(origin, np.float32)
+        c = np.asarray(color, np.float32)
+        self._chk(self._L.osbh_renderer_add_light(self._h, int(light_type), o.ctypes.data, float(radius), c.ctypes.data))
 
     def update_ambient(self, max_chunks=8):
         n = ctypes.c_int()

@@ -127,3 +127,60 @@ def test_frames_with_edits_match_reference():
         rr.set_map(None)
         rr.close()
         ref.map_free(rm)
+
+
+def test_renderer_draws_models_and_lights_like_the_reference():
+    """IRenderer surface: CreateModel / RenderModel / AddLight between StartScene and EndScene; the queued models and
+    lights are drawn in submission order and the lists are cleared by EndScene (SWRenderer.cpp:565-576,709-745)."""
+    import model_scenes as ms
+    if not oracles.ref_available():
+        pytest.skip("oracle/_ref not present")
+    ref = oracles.Ref("sse2")
+    m = VoxelMap.load_file(oracles.TITLE_VXL)
+    w, h = 256, 160
+    rm = ref.map_from_arrays(m.solid.copy(), m.color.copy())
+    rr = oracles.RefRenderer(ref, w, h, -1, 4)
+    rr.set_map(rm)
+    rr.set_fog(FOG, 128.0)
+    vm = oracles.RefVoxelModel(ref, kv6=open(ms.KV6[0], "rb").read())
+    rmod = rr.create_model(vm)
+    r = B200Renderer(w, h, numerics=osb.NUM_SSE2, sw_threads=4)
+    r.init()
+    r.set_fog(FOG, 128.0)
+    r.set_game_map(m)
+    s, c = vm.arrays()
+    gmod = r.create_model(vm.w, vm.hgt, vm.d, vm.origin, s, c)
+    sc = workloads.title_scene(w, h, 68.0)
+    with pytest.raises(osb.OsbError, match="outside of StartScene"):
+        r.add_light((0, 0, 0), 1.0, (1, 1, 1))
+    pl = ms.placements(sc, 1, 3)
+    par = np.zeros(len(pl), oracles.MODEL_PARAM_DTYPE)
+    lrows = ms.lights(sc, 3)
+    lg = np.zeros(len(lrows), oracles.LIGHT_DTYPE)
+    r.start_scene(sc)
+    for i, (_, mat, cc) in enumerate(pl):
+        r.render_model(gmod, mat, cc)
+        par["matrix"][i], par["customColor"][i] = mat, cc
+    for i, (o, rad, col) in enumerate(lrows):
+        r.add_light(o, rad, col)
+        lg["origin"][i], lg["radius"][i], lg["color"][i] = o, rad, col
+    r.add_light(sc["origin"], 50.0, (1, 1, 1), light_type=1)  # spotlight: ignored like the reference
+    r.end_scene()
+    r.frame_done()
+    wfb, wdp = rr.render_scene(sc, [rmod] * len(pl), par, lg)
+    assert np.array_equal(r.framebuffer() & 0xFFFFFF, wfb & 0xFFFFFF)
+    assert np.array_equal(r.read_depth().view(np.uint32), wdp.view(np.uint32))
+    # the next scene starts with empty lists
+    r.start_scene(sc)
+    r.end_scene()
+    wfb2, _ = rr.render_scene(sc)
+    assert np.array_equal(r.framebuffer() & 0xFFFFFF, wfb2 & 0xFFFFFF)
+    assert not np.array_equal(wfb2 & 0xFFFFFF, wfb & 0xFFFFFF)
+    r.free_model(gmod)
+    r.set_game_map(None)
+    r.close()
+    rr.free_model(rmod)
+    vm.close()
+    rr.set_map(None)
+    rr.close()
+    ref.map_free(rm)
