@@ -109,3 +109,34 @@ def test_cuda_matches_golden(title_arrays):
         ctx.map_upload(solid, color)
         ctx.radiosity_update(-1)
         assert np.array_equal(ctx.radiosity_read_chunk(16, 16, 2), r["chunk_mode2_16_16_2"])
+
+
+@pytest.mark.gpu
+def test_cuda_matches_golden_models(title_arrays):
+    """Frames with voxel models + dynamic lights drawn by the unmodified SWRenderer (make_golden_models.py, V-IEEE)."""
+    import openspades_b200 as osb
+    solid, color = title_arrays
+    g = np.load(os.path.join(GOLD, "models_title.npz"))
+    fog = g["fog"]
+    with osb.Context(0, osb.NUM_IEEE, sw_threads=4) as ctx:
+        ctx.map_upload(solid, color)
+        mods = []
+        for i in range(int(g["n_models"])):
+            w, h, d = (int(v) for v in g[f"m{i}_dims"])
+            mo = ctx.model_create(w, h, d, g[f"m{i}_origin"], g[f"m{i}_solid"], g[f"m{i}_colors"])
+            data, addr = ctx.model_render_data(mo, w * h)
+            assert np.array_equal(data, g[f"m{i}_data"]) and np.array_equal(addr, g[f"m{i}_addr"])
+            mods.append(mo)
+        H, W = g["s0_bgr"].shape
+        for si, sc in enumerate(g["scenes"].view(osb.SCENE_DTYPE).reshape(-1)):
+            idx = g[f"s{si}_model_index"]
+            inst = np.zeros(len(idx), osb.MODEL_INSTANCE_DTYPE)
+            inst["model"] = [mods[int(k)] for k in idx]
+            inst["matrix"] = g[f"s{si}_matrix"]
+            inst["customColor"] = g[f"s{si}_custom"]
+            lg = np.ascontiguousarray(g[f"s{si}_lights"]).view(osb.LIGHT_DTYPE).reshape(-1)
+            fb, dp = ctx.render_scene(sc, W, H, fog[:3], float(fog[3]), inst, lg)
+            assert np.array_equal(fb & 0xFFFFFF, g[f"s{si}_bgr"]), si
+            assert np.array_equal(dp.view(np.uint32), g[f"s{si}_depth"].view(np.uint32)), si
+        for mo in mods:
+            ctx.model_destroy(mo)
