@@ -375,6 +375,42 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                                       "flushed between iterations)", "ms_per_frame": ms,
                           "mpixel_s": w * h / ms / 1e3, "e2e_ms_per_frame": e2e_ms, "e2e_mpixel_s": w * h / e2e_ms / 1e3,
                           "hbm_frac_algorithmic": (BYTES_PER_PIXEL * w * h / (ms * 1e-3) / 1e9) / peak}
+    # ---- the same frame as the game submits it: + 64 voxel models (3 distinct, 24x24x40) + 8 point lights, full EndScene ----
+    handles = [ctx.model_create(*workloads.blob_model(11 + k)) for k in range(3)]
+    inst, lights = workloads.game_frame(sc, handles, 64, 8)
+    ctx.timing_enable(False)
+    for _ in range(3):
+        ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights, to_host=False)
+    tot = 0.0
+    for _ in range(n_it):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights, to_host=False)
+        e1.record(ext)
+        e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    g_ms = tot / n_it
+    ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights, out_bgrx=hfb, out_depth=hdp)
+    t0 = time.perf_counter()
+    for _ in range(n_it):
+        ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights, out_bgrx=hfb, out_depth=hdp)
+    g_e2e = (time.perf_counter() - t0) * 1e3 / n_it
+    ctx.timing_enable(True)
+    ctx.timing_read()
+    for _ in range(5):
+        ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights, to_host=False)
+    g_kt = {k: v[1] / 5 for k, v in ctx.timing_read().items() if v[0]}
+    ctx.timing_enable(False)
+    vox = sum(int(ctx.model_render_data(hd, 24 * 24)[0].size - 24 * 24) for hd in handles)
+    for hd in handles:
+        ctx.model_destroy(hd)
+    out["frame_1080p_game"] = {"workload": "1920x1080 title pose fovY 68, full EndScene: terrain + 64 voxel-model instances (3 models of "
+                                           "24x24x40, 0.1 block per voxel, 4..70 blocks away) + 8 point lights (radius 4..16) + fog "
+                                           "(osb200_render_scene; L2 flushed between iterations)",
+                               "ms_per_frame": g_ms, "e2e_ms_per_frame": g_e2e, "fps_device": 1e3 / g_ms, "fps_e2e": 1e3 / g_e2e,
+                               "surface_voxels_of_the_3_models": vox, "kernel_ms": g_kt}
     del fb, dp, hfb, hdp, flush
 
     # ---- CastRay2, args.rays rays per GPU, maxSteps 256 ----

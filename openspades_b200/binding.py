@@ -183,8 +183,8 @@ class Context:
 
     def timing_read(self):
         """{kernel name: (launches, total_ms)} since the last read (CUDA events on the context stream)."""
-        arr = (KernelTime * 16)()
-        n = self._check(self._lib.osb200_timing_read(self._h, arr, 16))
+        arr = (KernelTime * 32)()
+        n = self._check(self._lib.osb200_timing_read(self._h, arr, 32))
         return {arr[i].name.decode(): (int(arr[i].launches), float(arr[i].total_ms)) for i in range(n)}
 
     # ---- map ----
@@ -298,20 +298,25 @@ class Context:
         self._lib.osb200_model_render_data(m, data.ctypes.data, n, addr.ctypes.data, ncols)
         return data, addr
 
-    def render_scene(self, scene, w, h, fog_color, fog_dist, instances=None, lights=None, want_depth=True):
-        """One view: terrain + models (MODEL_INSTANCE_DTYPE[n]) + point lights (LIGHT_DTYPE[m]) + fog."""
+    def render_scene(self, scene, w, h, fog_color, fog_dist, instances=None, lights=None, want_depth=True,
+                     out_bgrx=None, out_depth=None, to_host=True):
+        """One view: terrain + models (MODEL_INSTANCE_DTYPE[n]) + point lights (LIGHT_DTYPE[m]) + fog.
+        out_bgrx / out_depth: host tensors or arrays to fill (pinned for speed); to_host=False leaves the frame in
+        the context's device buffers (timing of the device leg only)."""
         scene = np.ascontiguousarray(np.atleast_1d(scene))
         assert scene.dtype == SCENE_DTYPE and len(scene) == 1
         inst = np.zeros(0, MODEL_INSTANCE_DTYPE) if instances is None else np.ascontiguousarray(instances)
         lg = np.zeros(0, LIGHT_DTYPE) if lights is None else np.ascontiguousarray(lights)
         assert inst.dtype == MODEL_INSTANCE_DTYPE and lg.dtype == LIGHT_DTYPE
-        fb = np.empty((h, w), np.uint32)
-        dp = np.empty((h, w), np.float32) if want_depth else None
+        fb = dp = None
+        if to_host:
+            fb = np.empty((h, w), np.uint32) if out_bgrx is None else out_bgrx
+            dp = out_depth if out_depth is not None else (np.empty((h, w), np.float32) if want_depth else None)
         fc = np.asarray(fog_color, np.float32)
         self._check(self._lib.osb200_render_scene(self._h, scene.ctypes.data, w, h, fc.ctypes.data, float(fog_dist),
                                                   inst.ctypes.data if len(inst) else None, len(inst),
-                                                  lg.ctypes.data if len(lg) else None, len(lg), fb.ctypes.data,
-                                                  None if dp is None else dp.ctypes.data))
+                                                  lg.ctypes.data if len(lg) else None, len(lg),
+                                                  None if fb is None else _ptr(fb), None if dp is None else _ptr(dp)))
         return fb, dp
 
     # ---- GameMap::CastRay + ambient occlusion ----

@@ -152,3 +152,58 @@ def random_scenes(n, solid, w, h, fov_y_deg=68.0, seed=4321, max_pitch_deg=60.0)
         out[k] = look_at_scene(eye, at, (0.0, 0.0, -1.0), fov_y_deg, w, h)
         k += 1
     return out
+
+
+def blob_model(seed, w=24, h=24, d=40):
+    """Player-sized voxel model for the in-game frame workload: an ellipsoid with a few holes, ~8 % emissive and
+    ~8 % colour-0 (customColor) voxels.  Returns the arrays osb200_model_create takes (VoxelModel layout,
+    Core/VoxelModel.h:68-106): (w, h, d, origin, solid uint64[h][w], colors uint32[h][w][d])."""
+    rng = np.random.default_rng(seed)
+    x, y, z = np.meshgrid(np.arange(w), np.arange(h), np.arange(d), indexing="xy")  # [h][w][d] with "xy"
+    cx, cy, cz = (w - 1) / 2, (h - 1) / 2, (d - 1) / 2
+    r = ((x - cx) / (w / 2)) ** 2 + ((y - cy) / (h / 2)) ** 2 + ((z - cz) / (d / 2)) ** 2
+    filled = (r < 1.0) & (rng.random(r.shape) < 0.95)
+    colors = rng.integers(1, 1 << 24, size=r.shape, dtype=np.uint32)
+    u = rng.random(r.shape)
+    colors[u < 0.08] = 0
+    colors[(u >= 0.08) & (u < 0.16)] |= np.uint32(1 << 24)
+    colors[~filled] = 0
+    solid = (filled.astype(np.uint64) << np.arange(d, dtype=np.uint64)[None, None, :]).sum(axis=2).astype(np.uint64)
+    origin = np.array([-cx - 0.5, -cy - 0.5, -cz - 0.5], np.float32)
+    return w, h, d, origin, solid, colors
+
+
+def game_frame(scene, handles, n_instances, n_lights, seed=99):
+    """In-game frame population in front of `scene`'s camera: n_instances voxel models (handles cycled) at 0.1 block
+    per voxel, 4..70 blocks away inside the view cone, random yaw; n_lights point lights of radius 4..16 near them.
+    Returns (MODEL_INSTANCE_DTYPE[n_instances], LIGHT_DTYPE[n_lights])."""
+    from .binding import LIGHT_DTYPE, MODEL_INSTANCE_DTYPE
+    rng = np.random.default_rng(seed)
+    sc = np.asarray(scene).reshape(-1)[0]
+    o = np.asarray(sc["origin"], np.float64)
+    right, up, front = (np.asarray(sc["axis"][i], np.float64) for i in range(3))
+    tx, ty = math.tan(float(sc["fovX"]) / 2), math.tan(float(sc["fovY"]) / 2)
+    inst = np.zeros(n_instances, MODEL_INSTANCE_DTYPE)
+    spots = []
+    for i in range(n_instances):
+        dist = 4.0 + 66.0 * rng.random() ** 2
+        pos = o + front * dist + right * (rng.uniform(-0.9, 0.9) * tx * dist) + up * (rng.uniform(-0.9, 0.9) * ty * dist)
+        spots.append(pos)
+        ang = rng.uniform(0, 2 * math.pi)
+        c, s = math.cos(ang), math.sin(ang)
+        m = np.zeros(16, np.float32)
+        m[0:3] = (0.1 * c, 0.1 * s, 0)
+        m[4:7] = (-0.1 * s, 0.1 * c, 0)
+        m[8:11] = (0, 0, 0.1)
+        m[12:15] = pos
+        m[15] = 1
+        inst[i]["model"] = handles[i % len(handles)]
+        inst[i]["matrix"] = m
+        inst[i]["customColor"] = rng.random(3)
+    lights = np.zeros(n_lights, LIGHT_DTYPE)
+    for i in range(n_lights):
+        base = spots[i % len(spots)] if spots else o + front * 10
+        lights[i]["origin"] = base + rng.normal(size=3) * 2.0
+        lights[i]["radius"] = rng.uniform(4, 16)
+        lights[i]["color"] = rng.uniform(0.3, 1.0, 3)
+    return inst, lights
