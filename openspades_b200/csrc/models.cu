@@ -10,7 +10,7 @@
 // submission order, voxels in x / y / z order -- i.e. per pixel the winner is the smallest depth and, among equal
 // depths, the earliest splat; the terrain wins ties against every splat.  That is one 64-bit atomicMin per covered
 // pixel on the key (order-preserving depth bits << 32 | sequence number), with the terrain entered as sequence 0,
-// followed by a resolve pass that fetches the winner's colour.  One thread per (instance, model column); the
+// followed by a resolve pass that fetches the winner's colour.  One warp per (instance, model column); the
 // reference's sequential float recurrences (v1 += tAxis1 per x, v2 += tAxis2 per y) are replayed per thread.
 // Lights modify a pixel in submission order, so one thread per pixel walks the light list; the per-row / per-column
 // float recurrences of the reference (and its per-thread row bands) come from small tables built by one thread per light.
@@ -256,13 +256,34 @@ namespace osb {
 			keys[i] = (unsigned long long)depth_key(depth[i]) << 32; // sequence 0: the terrain wins ties
 	}
 
-	// The voxel loop of RenderInner (:184-276).  One thread per (instance, column (x, y)).
+	// strict `zval < *db` on the packed key; the plain load first turns most overdraw into a read (a stale value is
+	// only ever larger than the current one, so it can cause a redundant atomic, never a wrong skip)
+#ifndef OSB_SPLAT_PRETEST
+#define OSB_SPLAT_PRETEST 0 // 0: atomics only (fastest: the loads are latency, the atomics fire-and-forget), 1: L2 load first, 2: L1-cached load first
+#endif
+	__device__ __forceinline__ void key_min(unsigned long long *p, unsigned long long key) {
+#if OSB_SPLAT_PRETEST == 1
+		if (key < __ldcg(p))
+#elif OSB_SPLAT_PRETEST == 2
+		if (key < __ldca(p))
+#endif
+			atomicMin(p, key);
+	}
+
+	// The voxel loop of RenderInner (:184-276).  One WARP per (instance, column (x, y)): lane i takes the column's i-th
+	// surface voxel (projection, cull, shading: the per-voxel float work runs 32 wide), then splats of up to
+	// kOwnLaneArea pixels are written by their own lane and larger ones by the whole warp, one voxel at a time.
+#ifndef OSB_SPLAT_OWN_AREA
+#define OSB_SPLAT_OWN_AREA 16
+#endif
+	constexpr int kOwnLaneArea = OSB_SPLAT_OWN_AREA;
 	template <bool kSse>
 	__global__ void __launch_bounds__(128)
 	  k_model_splat(const SceneMats *__restrict__ mats, const InstanceIn *__restrict__ inst,
 	                const InstanceSetup *__restrict__ setup, int nInst, uint32_t totalCols,
 	                unsigned long long *__restrict__ keys, uint32_t *__restrict__ splatColor, osbn::SseTables sse) {
-		const uint32_t item = blockIdx.x * blockDim.x + threadIdx.x;
+		const uint32_t item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+		const int lane = threadIdx.x & 31;
 		if (item >= totalCols)
 			return;
 		int lo = 0, hi = nInst - 1;
@@ -283,6 +304,10 @@ namespace osb {
 		// traversal order is x outer, y inner (:185-188); item order inside the instance follows it
 		const uint32_t col = item - I.colBase;
 		const int x = (int)(col / (uint32_t)I.model.h), y = (int)(col % (uint32_t)I.model.h);
+		const int ci = x + y * I.model.w, nCols = I.model.w * I.model.h;
+		const int count = (int)I.model.addr[2 * nCols + ci]; // surface voxels of this column
+		if (count == 0)
+			return;
 		float v2[4];
 #pragma unroll
 		for (int k = 0; k < 4; k++) {
@@ -293,44 +318,75 @@ namespace osb {
 				v = __fadd_rn(v, R.tAxis2[k]); // v2 += tAxis2
 			v2[k] = v;
 		}
-		const uint32_t *mp = I.model.data + I.model.addr[x + y * I.model.w];
-		uint32_t seq = I.seqBase + I.model.addr[I.model.w * I.model.h + x + y * I.model.w]; // rank table behind addr
+		const uint32_t *mp = I.model.data + I.model.addr[ci];
+		const uint32_t seq0 = I.seqBase + I.model.addr[nCols + ci]; // rank of the column's first voxel in traversal order
 		const int offX = fw >> 1, offY = fh >> 1;
-		for (; *mp != 0xffffffffu; mp += 2, seq++) {
-			const uint32_t data = mp[0], normal = mp[1];
-			const float zf = (float)(data >> 24);
-			float vv[4];
+		for (int base = 0; base < count; base += 32) {
+			const int vi = base + lane;
+			bool have = vi < count;
+			int minX = 0, minY = 0, rw = 0, rh = 0;
+			unsigned long long key = 0;
+			if (have) {
+				const uint32_t data = mp[2 * vi], normal = mp[2 * vi + 1];
+				const float zf = (float)(data >> 24);
+				float vv[4];
 #pragma unroll
-			for (int k = 0; k < 4; k++)
-				vv[k] = __fadd_rn(v2[k], __fmul_rn(R.tAxis3[k], zf));
-			if (vv[2] < zNear)
-				continue;
-			const float zval = vv[2];
-			const float scl = num.rcp(vv[3]);
-			const int ix = osbn::x86_f2i(__fmul_rn(vv[0], scl)) + offX;
-			const int iy = osbn::x86_f2i(__fmul_rn(vv[1], scl)) + offY;
-			int idm = osbn::x86_f2i(__fadd_rn(__fmul_rn(R.pointDiameter, scl), .99f));
-			idm = max(1, idm);
-			int minX = ix - (idm >> 1), minY = iy - (idm >> 1);
-			if (minX >= fw || minY >= fh)
-				continue;
-			int maxX = (int)((uint32_t)ix + (uint32_t)idm), maxY = (int)((uint32_t)iy + (uint32_t)idm);
-			if (maxX <= 0 || maxY <= 0)
-				continue;
-			minX = max(minX, 0);
-			minY = max(minY, 0);
-			maxX = min(maxX, fw);
-			maxY = min(maxY, fh);
-			uint32_t color = data & 0xffffffu;
-			if (color == 0)
-				color = I.customColor;
-			const uint32_t bright = R.brights[normal < 28 ? normal : 27];
-			color = ((((color & 0xff00u) * bright) & 0xff0000u) | (((color & 0xff00ffu) * bright) & 0xff00ff00u)) >> 8;
-			splatColor[seq] = color;
-			const unsigned long long key = ((unsigned long long)depth_key(zval) << 32) | seq;
-			for (int yy = minY; yy < maxY; yy++)
-				for (int xx = minX; xx < maxX; xx++)
-					atomicMin(keys + (size_t)yy * fw + xx, key);
+				for (int k = 0; k < 4; k++)
+					vv[k] = __fadd_rn(v2[k], __fmul_rn(R.tAxis3[k], zf));
+				have = !(vv[2] < zNear);
+				if (have) {
+					const float scl = num.rcp(vv[3]);
+					const int ix = osbn::x86_f2i(__fmul_rn(vv[0], scl)) + offX;
+					const int iy = osbn::x86_f2i(__fmul_rn(vv[1], scl)) + offY;
+					int idm = osbn::x86_f2i(__fadd_rn(__fmul_rn(R.pointDiameter, scl), .99f));
+					idm = max(1, idm);
+					minX = ix - (idm >> 1);
+					minY = iy - (idm >> 1);
+					int maxX = (int)((uint32_t)ix + (uint32_t)idm), maxY = (int)((uint32_t)iy + (uint32_t)idm);
+					have = !(minX >= fw || minY >= fh) && !(maxX <= 0 || maxY <= 0);
+					if (have) {
+						minX = max(minX, 0);
+						minY = max(minY, 0);
+						rw = min(maxX, fw) - minX;
+						rh = min(maxY, fh) - minY;
+						uint32_t color = data & 0xffffffu;
+						if (color == 0)
+							color = I.customColor;
+						const uint32_t bright = R.brights[normal < 28 ? normal : 27];
+						color = ((((color & 0xff00u) * bright) & 0xff0000u) | (((color & 0xff00ffu) * bright) & 0xff00ff00u)) >> 8;
+						const uint32_t seq = seq0 + (uint32_t)vi;
+						splatColor[seq] = color;
+						key = ((unsigned long long)depth_key(vv[2]) << 32) | seq;
+					}
+				}
+			}
+			const bool own = have && rw * rh <= kOwnLaneArea;
+			if (own) {
+				unsigned long long *row = keys + (size_t)minY * fw + minX;
+				for (int yy = 0; yy < rh; yy++, row += fw)
+					for (int xx = 0; xx < rw; xx++)
+						key_min(row + xx, key);
+			}
+			unsigned big = __ballot_sync(0xffffffffu, have && !own);
+			while (big) {
+				const int src = __ffs(big) - 1;
+				big &= big - 1;
+				const int bx = __shfl_sync(0xffffffffu, minX, src), by = __shfl_sync(0xffffffffu, minY, src);
+				const int bw = __shfl_sync(0xffffffffu, rw, src), bh = __shfl_sync(0xffffffffu, rh, src);
+				const unsigned long long bk = __shfl_sync(0xffffffffu, key, src);
+				unsigned long long *org = keys + (size_t)by * fw + bx;
+				if (bw <= 32) { // lanes tile the rectangle: 2^sh columns x (32 >> sh) rows per pass
+					const int sh = bw <= 1 ? 0 : 32 - __clz(bw - 1);
+					const int lx = lane & ((1 << sh) - 1), ly = lane >> sh, stepY = 32 >> sh;
+					if (lx < bw)
+						for (int yy = ly; yy < bh; yy += stepY)
+							key_min(org + (size_t)yy * fw + lx, bk);
+				} else {
+					for (int yy = 0; yy < bh; yy++, org += fw)
+						for (int xx = lane; xx < bw; xx += 32)
+							key_min(org + xx, bk);
+				}
+			}
 		}
 	}
 
@@ -634,13 +690,14 @@ int osb200_model_create(osb200_ctx *c, int w, int h, int d, const float origin[3
 	osb::build_render_data(*M, solid, colors);
 	// behind the column start table: the rank of each column's first voxel in the renderer's x-outer / y-inner order
 	std::vector<uint32_t> addrAndRank(M->renderDataAddr);
-	addrAndRank.resize((size_t)w * h * 2);
+	addrAndRank.resize((size_t)w * h * 3); // + the number of surface voxels of each column
 	uint32_t rank = 0;
 	for (int x = 0; x < w; x++)
 		for (int y = 0; y < h; y++) {
 			addrAndRank[(size_t)w * h + x + y * w] = rank;
 			const uint32_t a = M->renderDataAddr[x + y * w];
 			const uint32_t e = (x + y * w + 1 < w * h) ? M->renderDataAddr[x + y * w + 1] : (uint32_t)M->renderData.size();
+			addrAndRank[(size_t)w * h * 2 + x + y * w] = (e - a - 1) / 2;
 			rank += (e - a - 1) / 2;
 		}
 	cudaError_t e1 = cudaMalloc(&M->d_data, M->renderData.size() * 4);
@@ -768,10 +825,10 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 			KLaunch kl(c, K_MODEL_SPLAT);
 			k_key_init<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(d_depth, M->d_keys, npix);
 			if (kSseMode)
-				k_model_splat<true><<<(cols + 127) / 128, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
+				k_model_splat<true><<<(cols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
 				                                                               M->d_keys, M->d_splatColor, sse);
 			else
-				k_model_splat<false><<<(cols + 127) / 128, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
+				k_model_splat<false><<<(cols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
 				                                                                M->d_keys, M->d_splatColor, sse);
 		}
 		{
