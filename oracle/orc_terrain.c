@@ -605,9 +605,31 @@ int orc_last_lines(int *lineRes, const uint32_t **combined, const float **depth)
 	return tl_numLines;
 }
 
+/* EndScene up to the fog (clear + terrain), and the fog pass on its own: orc_models.c draws between the two */
+int orc_render_terrain(const uint64_t *solid, const uint32_t *color, const orc_scene *scene, int w, int h, int numerics,
+                       int threads, int under, uint32_t *bgrx, float *depth);
+void orc_apply_fog(const orc_scene *scene, const float fogColor[3], float fogDist, int numerics, int threads, int w, int h,
+                   uint32_t *bgrx, float *depth) {
+	if (threads < 1)
+		threads = 1;
+	if (threads > 32)
+		threads = 32;
+	for (int t = 0; t < threads; t++)
+		apply_fog(scene, fogColor, fogDist, numerics == ORC_NUM_SSE2, t, threads, w, h, bgrx, depth);
+}
+
 int orc_render(const uint64_t *solid, const uint32_t *color, const orc_scene *scene, int w, int h,
                const float fogColor[3], float fogDist, int numerics, int threads, int under, uint32_t *bgrx,
                float *depth) {
+	int rc = orc_render_terrain(solid, color, scene, w, h, numerics, threads, under, bgrx, depth);
+	if (rc)
+		return rc;
+	orc_apply_fog(scene, fogColor, fogDist, numerics, threads, w, h, bgrx, depth);
+	return 0;
+}
+
+int orc_render_terrain(const uint64_t *solid, const uint32_t *color, const orc_scene *scene, int w, int h, int numerics,
+                       int threads, int under, uint32_t *bgrx, float *depth) {
 	static const float pi = M_PI;
 	if ((w & 7) || (h & 7) || w <= 0 || h <= 0)
 		return -1; /* SWRenderer.cpp:105-107 */
@@ -697,7 +719,5 @@ int orc_render(const uint64_t *solid, const uint32_t *color, const orc_scene *sc
 		for (int t = 0; t < threads; t++)
 			render_final(&f, yawMin, yawMax, (unsigned)numLines, t, threads, underT, w, h, bgrx, depth);
 	}
-	for (int t = 0; t < threads; t++)
-		apply_fog(scene, fogColor, fogDist, numerics == ORC_NUM_SSE2, t, threads, w, h, bgrx, depth);
 	return 0;
 }

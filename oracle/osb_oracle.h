@@ -96,6 +96,29 @@ void orc_ao_invalidate(int32_t *state, int x, int y, int z);
 void orc_ao_update_chunk(const uint64_t *solid, const float rays[48], int32_t *state, int cx, int cy, int cz,
                          float *data);
 
+/* ---- voxel models + dynamic lights inside EndScene (orc_models.c) ---- */
+typedef struct orc_model orc_model;
+typedef struct orc_model_instance { /* one SWRenderer::RenderModel call: same layout as osb200_model_instance */
+	const orc_model *model;
+	float matrix[16]; /* Matrix4::m, column-major */
+	float customColor[3];
+} orc_model_instance;
+typedef struct orc_light { /* client::DynamicLightParam of a point light */
+	float origin[3];
+	float radius;
+	float color[3];
+} orc_light;
+/* Draw/SWModel.cpp:25-100; solid[x + y*w] bit z, colors[(x + y*w)*d + z] */
+orc_model *orc_model_create(int w, int h, int d, const float origin[3], const uint64_t *solid, const uint32_t *colors);
+void orc_model_free(orc_model *m);
+/* SWModel::renderData / renderDataAddr; returns the length of renderData */
+int orc_model_render_data(const orc_model *m, uint32_t *data, int dataCap, uint32_t *addr, int addrCap);
+/* Draw/SWRenderer.cpp:709-745 EndScene: clear, terrain (skipped when solid == NULL), models, lights, fog */
+int orc_render_scene(const uint64_t *solid, const uint32_t *color, const orc_scene *scene, int w, int h,
+                     const float fogColor[3], float fogDist, int numerics, int threads, int under,
+                     const orc_model_instance *inst, int nInst, const orc_light *lights, int nLights, uint32_t *bgrx,
+                     float *depth);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,6 +14,8 @@ SCENE_DTYPE = np.dtype([("origin", "<f4", 3), ("axis", "<f4", (3, 3)), ("fovX", 
                         ("zNear", "<f4"), ("zFar", "<f4")])
 MODEL_PARAM_DTYPE = np.dtype([("matrix", "<f4", 16), ("customColor", "<f4", 3)])
 LIGHT_DTYPE = np.dtype([("origin", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 3)])
+ORC_INSTANCE_DTYPE = np.dtype({"names": ["model", "matrix", "customColor"], "formats": ["<u8", ("<f4", 16), ("<f4", 3)],
+                               "offsets": [0, 8, 72], "itemsize": 88})
 RAYHIT_DTYPE = np.dtype([("hit", "u1"), ("startSolid", "u1"), ("pad", "u1", 2), ("hitPos", "<f4", 3),
                          ("hitBlock", "<i4", 3), ("normal", "<i4", 3)])
 
@@ -76,6 +78,54 @@ class Port:
         L.orc_ao_invalidate.restype = None
         L.orc_ao_update_chunk.argtypes = [vp, vp, vp, ci, ci, ci, vp]
         L.orc_ao_update_chunk.restype = None
+        L.orc_model_create.argtypes = [ci, ci, ci, vp, vp, vp]
+        L.orc_model_create.restype = vp
+        L.orc_model_free.argtypes = [vp]
+        L.orc_model_free.restype = None
+        L.orc_model_render_data.argtypes = [vp, vp, ci, vp, ci]
+        L.orc_render_scene.argtypes = [vp, vp, vp, ci, ci, vp, ctypes.c_float, ci, ci, ci, vp, ci, vp, ci, vp, vp]
+
+    # ---- voxel models + dynamic lights (orc_models.c) ----
+    def model_create(self, w, h, d, origin, solid, colors):
+        o = np.asarray(origin, np.float32)
+        solid = np.ascontiguousarray(solid, np.uint64)
+        colors = np.ascontiguousarray(colors, np.uint32)
+        assert solid.size == w * h and colors.size == w * h * d
+        m = self.L.orc_model_create(w, h, d, o.ctypes.data, solid.ctypes.data, colors.ctypes.data)
+        if not m:
+            raise ValueError("orc_model_create failed")
+        return m
+
+    def model_free(self, m):
+        self.L.orc_model_free(m)
+
+    def model_render_data(self, m, ncols):
+        n = self.L.orc_model_render_data(m, None, 0, None, 0)
+        data = np.zeros(n, np.uint32)
+        addr = np.zeros(ncols, np.uint32)
+        self.L.orc_model_render_data(m, data.ctypes.data, n, addr.ctypes.data, ncols)
+        return data, addr
+
+    def render_scene(self, solid, color, scene, w, h, fog_color, fog_dist, numerics, models=(), params=None, lights=None,
+                     threads=4, under=1, depth=None):
+        """EndScene with models (handles + MODEL_PARAM_DTYPE[n]) and point lights (LIGHT_DTYPE[m])."""
+        fb = np.zeros((h, w), np.uint32)
+        dp = np.zeros((h, w), np.float32) if depth is None else depth
+        sc = np.ascontiguousarray(scene)
+        fc = np.asarray(fog_color, np.float32)
+        inst = np.zeros(len(models), ORC_INSTANCE_DTYPE)
+        for i, m in enumerate(models):
+            inst[i]["model"] = m
+            inst[i]["matrix"] = params[i]["matrix"]
+            inst[i]["customColor"] = params[i]["customColor"]
+        lights = np.zeros(0, LIGHT_DTYPE) if lights is None else np.ascontiguousarray(lights)
+        rc = self.L.orc_render_scene(None if solid is None else solid.ctypes.data,
+                                     None if color is None else color.ctypes.data, sc.ctypes.data, w, h, fc.ctypes.data,
+                                     fog_dist, numerics, threads, under, inst.ctypes.data, len(inst), lights.ctypes.data,
+                                     len(lights), fb.ctypes.data, dp.ctypes.data)
+        if rc:
+            raise ValueError("orc_render_scene failed")
+        return fb, dp
 
     def vxl_load(self, data: bytes):
         solid = np.zeros((512, 512), np.uint64)
