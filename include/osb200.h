@@ -211,6 +211,18 @@ OSB200_API int osb200_render_scene(osb200_ctx *ctx, const osb200_scene *scene, i
                                    float fogDist, const osb200_model_instance *inst, int nInst, const osb200_light *lights,
                                    int nLights, uint32_t *host_bgrx, float *host_depth);
 
+/* ---- VXL stream <-> resident map on the device.
+ *      osb200_map_load_vxl replaces GameMap::Load (Client/GameMap.cpp:519-596) + osb200_map_upload: the raw (inflated)
+ *      VXL bytes go to the device (2 MB for Title.vxl instead of 66 MiB of arrays), column starts are found by pointer
+ *      doubling and every column is decoded by its own thread into the resident map.  host_solid / host_color
+ *      (nullable) receive the arrays in GameMap's [x][y] / [x][y][z] order -- what the owner of the map keeps for
+ *      GameMap::Set and osb200_map_flush.  Truncated / malformed input: -1 (the reference throws), no map loaded.
+ *      osb200_map_save_vxl replaces GameMap::Save (:93-160, IsSurface :65-83): returns the stream length and writes
+ *      min(length, cap) bytes to out (out may be NULL with cap 0 to ask for the length). ---- */
+OSB200_API int osb200_map_load_vxl(osb200_ctx *ctx, const uint8_t *data, size_t len, uint64_t *host_solid,
+                                   uint32_t *host_color);
+OSB200_API long long osb200_map_save_vxl(osb200_ctx *ctx, uint8_t *out, size_t cap);
+
 /* ---- GameMap::CastRay (GameMap.cpp:208-359), batched: the integer cell-wall walk used by the ambient-occlusion
  *      evaluation and by the game's hit tests.  v0, dir: n x 3 floats; one length for the batch (the walk takes at most
  *      (long)length cell walls); out: n x {hit, hitBlock.x, hitBlock.y, hitBlock.z} int32 (zeros on a miss). ---- */

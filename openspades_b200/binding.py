@@ -74,6 +74,9 @@ def load_library():
     lib.osb200_timing_read.argtypes = [vp, ctypes.POINTER(KernelTime), ci]
     lib.osb200_map_upload.argtypes = [vp, vp, vp]
     lib.osb200_map_clear.argtypes = [vp]
+    lib.osb200_map_load_vxl.argtypes = [vp, vp, sz, vp, vp]
+    lib.osb200_map_save_vxl.argtypes = [vp, vp, sz]
+    lib.osb200_map_save_vxl.restype = ctypes.c_longlong
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
     lib.osb200_map_flush.argtypes = [vp, vp, vp]
     lib.osb200_map_read_solid.argtypes = [vp, vp]
@@ -193,6 +196,25 @@ class Context:
         color = np.ascontiguousarray(color, np.uint32)
         assert solid.shape == (512, 512) and color.shape == (512, 512, 64)
         self._check(self._lib.osb200_map_upload(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def map_load_vxl(self, data: bytes, want_arrays=True):
+        """GameMap::Load on the device: raw VXL bytes -> resident map; returns (solid, color) host arrays or None."""
+        buf = np.frombuffer(data, np.uint8)
+        solid = np.empty((512, 512), np.uint64) if want_arrays else None
+        color = np.empty((512, 512, 64), np.uint32) if want_arrays else None
+        self._check(self._lib.osb200_map_load_vxl(self._h, buf.ctypes.data, len(buf), _ptr(solid), _ptr(color)))
+        return (solid, color) if want_arrays else None
+
+    def map_save_vxl(self) -> bytes:
+        """GameMap::Save from the resident map."""
+        n = self._lib.osb200_map_save_vxl(self._h, None, 0)
+        if n < 0:
+            raise OsbError(self._lib.osb200_last_error().decode())
+        out = np.empty(n, np.uint8)
+        m = self._lib.osb200_map_save_vxl(self._h, out.ctypes.data, n)
+        if m != n:
+            raise OsbError(self._lib.osb200_last_error().decode() if m < 0 else "osb200_map_save_vxl: length changed")
+        return out.tobytes()
 
     def map_clear(self):
         self._check(self._lib.osb200_map_clear(self._h))

@@ -48,6 +48,9 @@ namespace osb {
 		K_MODEL_SPLAT,
 		K_MODEL_RESOLVE,
 		K_LIGHTS,
+		K_VXL_INDEX,
+		K_VXL_DECODE,
+		K_VXL_ENCODE,
 		K_COUNT
 	};
 	const char *kernel_name(int id);
@@ -56,6 +59,7 @@ namespace osb {
 	struct RadiosityState; // radiosity.cu
 	struct AmbientState;   // ambient.cu
 	struct ModelState;     // models.cu
+	struct VxlState;       // vxl.cu
 } // namespace osb
 
 struct osb200_ctx;
@@ -124,6 +128,7 @@ struct osb200_ctx {
 	osb::RadiosityState *radiosity = nullptr;
 	osb::AmbientState *ambient = nullptr;
 	osb::ModelState *models = nullptr;
+	osb::VxlState *vxl = nullptr;
 
 	int ensure_scratch(size_t bytes);
 	int ensure_stage(size_t bytes);

@@ -92,6 +92,91 @@ int orc_vxl_load(const uint8_t *data, size_t len, uint64_t *solid, uint32_t *col
 #undef RD32
 }
 
+/* GameMap.cpp:65-83 (no wrap: the map edge has no neighbour) */
+static int is_solid(const uint64_t *solid, int x, int y, int z) { return (int)((solid[(size_t)x * H + y] >> z) & 1); }
+static int is_surface(const uint64_t *solid, int x, int y, int z) {
+	if (!is_solid(solid, x, y, z))
+		return 0;
+	if (z == 0)
+		return 1;
+	if (x > 0 && !is_solid(solid, x - 1, y, z))
+		return 1;
+	if (x < W - 1 && !is_solid(solid, x + 1, y, z))
+		return 1;
+	if (y > 0 && !is_solid(solid, x, y - 1, z))
+		return 1;
+	if (y < H - 1 && !is_solid(solid, x, y + 1, z))
+		return 1;
+	if (!is_solid(solid, x, y, z - 1))
+		return 1;
+	if (z < D - 1 && !is_solid(solid, x, y, z + 1))
+		return 1;
+	return 0;
+}
+
+/* GameMap.cpp:93-160 GameMap::Save.  Returns the stream length; writes at most cap bytes. */
+long long orc_vxl_save(const uint64_t *solid, const uint32_t *color, uint8_t *out, size_t cap) {
+	size_t n = 0;
+#define PUT(b)                                                                                     \
+	do {                                                                                           \
+		if (n < cap)                                                                               \
+			out[n] = (uint8_t)(b);                                                                 \
+		n++;                                                                                       \
+	} while (0)
+	for (int y = 0; y < H; y++)
+		for (int x = 0; x < W; x++) {
+			const uint32_t *c = color + ((size_t)x * H + y) * D;
+			int k = 0;
+			while (k < D) {
+				int z;
+				int air_start = k;
+				while (k < D && !is_solid(solid, x, y, k))
+					++k;
+				int top_colors_start = k;
+				while (k < D && is_surface(solid, x, y, k))
+					++k;
+				int top_colors_end = k;
+				while (k < D && is_solid(solid, x, y, k) && !is_surface(solid, x, y, k))
+					++k;
+				int bottom_colors_start = k;
+				z = k;
+				while (z < D && is_surface(solid, x, y, z))
+					++z;
+				if (z != D) {
+					while (is_surface(solid, x, y, k))
+						++k;
+				}
+				int bottom_colors_end = k;
+				int top_colors_len = top_colors_end - top_colors_start;
+				int bottom_colors_len = bottom_colors_end - bottom_colors_start;
+				int colors = top_colors_len + bottom_colors_len;
+				if (k == D)
+					PUT(0);
+				else
+					PUT(colors + 1);
+				PUT(top_colors_start);
+				PUT(top_colors_end - 1);
+				PUT(air_start);
+				for (z = 0; z < top_colors_len; ++z) {
+					uint32_t col = c[top_colors_start + z];
+					PUT(col >> 16);
+					PUT(col >> 8);
+					PUT(col >> 0);
+					PUT(col >> 24);
+				}
+				for (z = 0; z < bottom_colors_len; ++z) {
+					uint32_t col = c[bottom_colors_start + z];
+					PUT(col >> 16);
+					PUT(col >> 8);
+					PUT(col >> 0);
+					PUT(col >> 24);
+				}
+			}
+		}
+#undef PUT
+	return (long long)n;
+}
+
 /* GameMap.cpp:361-507, one ray */
 static void castray2_one(const uint64_t *solid, const float *v0, const float *d, int maxSteps,
                          orc_rayhit *r) {

@@ -41,6 +41,8 @@ enum { ORC_NUM_IEEE = 0, ORC_NUM_SSE = 1, ORC_NUM_SSE2 = 2 };
 
 /* Client/GameMap.cpp:519-596 GameMap::Load.  Returns 0 or <0 on truncated input. */
 int orc_vxl_load(const uint8_t *data, size_t len, uint64_t *solid, uint32_t *color);
+/* Client/GameMap.cpp:93-160 GameMap::Save (IsSurface :65-83).  Returns the stream length, writes <= cap bytes. */
+long long orc_vxl_save(const uint64_t *solid, const uint32_t *color, uint8_t *out, size_t cap);
 
 /* Client/GameMap.cpp:361-507 GameMap::CastRay2 */
 void orc_castray2(const uint64_t *solid, const float *v0, const float *dir, int maxSteps, orc_rayhit *out,

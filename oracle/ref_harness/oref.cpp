@@ -14,6 +14,7 @@
 #include <Core/Bitmap.h>
 #include <Core/Exception.h>
 #include <Core/MemoryStream.h>
+#include <Core/DynamicMemoryStream.h>
 #include <Core/Settings.h>
 #include <Core/StdStream.h>
 #include <Draw/SWFeatureLevel.h>
@@ -86,6 +87,18 @@ void *oref_map_load_vxl_mem(const void *data, size_t len) {
 		MemoryStream s(reinterpret_cast<const char *>(data), len);
 		return client::GameMap::Load(&s);
 	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+
+long long oref_map_save_vxl(void *map, void *out, size_t cap) {
+	try {
+		DynamicMemoryStream s;
+		reinterpret_cast<client::GameMap *>(map)->Save(&s);
+		const uint64_t n = s.GetLength();
+		s.SetPosition(0);
+		if (out && cap)
+			s.Read(out, (size_t)(n < cap ? n : cap));
+		return (long long)n;
+	} catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
 void *oref_map_from_arrays(const uint64_t *solid, const uint32_t *color) {

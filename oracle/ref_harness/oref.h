@@ -37,6 +37,7 @@ OREF_API const char *oref_variant(void); /* "sse2" or "ieee" (compile-time) */
 /* ---- GameMap ---- */
 OREF_API void *oref_map_load_vxl(const char *path);  /* GameMap::Load, GameMap.cpp:519 */
 OREF_API void *oref_map_load_vxl_mem(const void *data, size_t len);
+OREF_API long long oref_map_save_vxl(void *map, void *out, size_t cap); /* GameMap::Save, GameMap.cpp:93-160 */
 OREF_API void *oref_map_from_arrays(const uint64_t *solid /*[x][y]*/, const uint32_t *color /*[x][y][z]*/);
 OREF_API void oref_map_free(void *map);
 OREF_API void oref_map_get_arrays(void *map, uint64_t *solid, uint32_t *color);

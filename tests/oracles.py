@@ -48,6 +48,8 @@ class Port:
             build_port()
         L = self.L = ctypes.CDLL(path)
         L.orc_vxl_load.argtypes = [vp, ctypes.c_size_t, vp, vp]
+        L.orc_vxl_save.argtypes = [vp, vp, vp, ctypes.c_size_t]
+        L.orc_vxl_save.restype = ctypes.c_longlong
         L.orc_castray2.argtypes = [vp, vp, vp, ci, vp, ctypes.c_size_t, ci]
         L.orc_castray2.restype = None
         L.orc_build_rle.argtypes = [vp, ci, ci, vp]
@@ -135,6 +137,12 @@ class Port:
         if rc:
             raise ValueError("truncated VXL")
         return solid, color
+
+    def vxl_save(self, solid, color) -> bytes:
+        n = self.L.orc_vxl_save(solid.ctypes.data, color.ctypes.data, None, 0)
+        buf = np.zeros(n, np.uint8)
+        self.L.orc_vxl_save(solid.ctypes.data, color.ctypes.data, buf.ctypes.data, n)
+        return buf.tobytes()
 
     def castray2(self, solid, v0, dirs, max_steps, threads=1):
         v0 = np.ascontiguousarray(v0, np.float32)
@@ -258,6 +266,8 @@ class Ref:
             getattr(L, f).restype = vp
         L.oref_map_load_vxl_mem.argtypes = [vp, ctypes.c_size_t]
         L.oref_map_from_arrays.argtypes = [vp, vp]
+        L.oref_map_save_vxl.argtypes = [vp, vp, ctypes.c_size_t]
+        L.oref_map_save_vxl.restype = ctypes.c_longlong
         L.oref_map_free.argtypes = [vp]
         L.oref_map_get_arrays.argtypes = [vp, vp, vp]
         L.oref_map_set.argtypes = [vp, ci, ci, ci, ci, ctypes.c_uint32]
@@ -283,6 +293,15 @@ class Ref:
 
     def map_from_arrays(self, solid, color):
         return self.L.oref_map_from_arrays(solid.ctypes.data, color.ctypes.data)
+
+    def map_save_vxl(self, m) -> bytes:
+        """GameMap::Save"""
+        n = self.L.oref_map_save_vxl(m, None, 0)
+        if n < 0:
+            raise ValueError(self.L.oref_last_error().decode())
+        buf = np.zeros(n, np.uint8)
+        self.L.oref_map_save_vxl(m, buf.ctypes.data, n)
+        return buf.tobytes()
 
     def map_arrays(self, m):
         solid = np.zeros((512, 512), np.uint64)

@@ -118,3 +118,32 @@ def test_render_scene_argument_errors(title_map):
         fb, dp = ctx.render_scene(sc, 64, 64, FOG, 128.0, np.zeros(0, osb.MODEL_INSTANCE_DTYPE))  # empty lists
         fb2, dp2 = ctx.render(sc, 64, 64, FOG, 128.0)
         assert np.array_equal(fb & 0xFFFFFF, fb2[0] & 0xFFFFFF) and np.array_equal(dp, dp2[0])
+
+
+def test_bench_game_frame_1080p_matches_port(title_map):
+    """The bench's in-game frame (1080p, 64 instances of 24x24x40 models, 8 lights; bench.py extra frame_1080p_game) and a
+    denser one (256 instances, 32 lights) against the C restatement, bit for bit -- the full-size case of this path."""
+    solid, color = title_map
+    port = oracles.Port()
+    w, h = 1920, 1080
+    sc = workloads.title_scene(w, h, 68.0)
+    mdls = [workloads.blob_model(11 + k) for k in range(3)]
+    pms = [port.model_create(*m) for m in mdls]
+    with osb.Context(0, osb.NUM_SSE2, sw_threads=4) as ctx:
+        ctx.map_upload(solid, color)
+        gms = [ctx.model_create(*m) for m in mdls]
+        for n_inst, n_lights in ((64, 8), (256, 32)):
+            inst, lights = workloads.game_frame(sc, gms, n_inst, n_lights)
+            fb, dp = ctx.render_scene(sc, w, h, (0.1, 0.1, 0.1), 128.0, inst, lights)
+            par = np.zeros(n_inst, oracles.MODEL_PARAM_DTYPE)
+            par["matrix"], par["customColor"] = inst["matrix"], inst["customColor"]
+            wfb, wdp = port.render_scene(solid, color, sc, w, h, (0.1, 0.1, 0.1), 128.0, 2, [pms[i % 3] for i in range(n_inst)],
+                                         par, lights.view(oracles.LIGHT_DTYPE), threads=4)
+            assert np.array_equal(dp.view(np.uint32), wdp.view(np.uint32)), n_inst
+            assert np.array_equal(fb & 0xFFFFFF, wfb & 0xFFFFFF), n_inst
+            terrain_dp = port.render(solid, color, sc, w, h, (0.1, 0.1, 0.1), 128.0, 2, 4, 1)[1]
+            assert (wdp.view(np.uint32) != terrain_dp.view(np.uint32)).sum() > 10000  # the models are on screen
+        for g in gms:
+            ctx.model_destroy(g)
+    for p in pms:
+        port.model_free(p)
