@@ -533,6 +533,40 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
     out["castray"] = {"workload": f"GameMap::CastRay batch, {nr} unit rays of length 128 per GPU, Title.vxl (in 24 B + out 16 B per ray)",
                       "ms_per_batch": cr_ms, "mrays_s": nr / cr_ms / 1e3, "hit_fraction": cr_hits,
                       "hbm_frac_algorithmic": (40 * nr / (cr_ms * 1e-3) / 1e9) / peak}
+    # ---- VXL stream <-> resident map (GameMap::Load / Save): device decode vs host decode + 66 MiB upload ----
+    from openspades_b200.hostlib import VoxelMap
+    vxl = open(workloads.TITLE_VXL, "rb").read()
+    with osb.Context(device=dev.index, numerics=osb.NUM_IEEE) as vc:
+        reps = 10
+        vc.map_load_vxl(vxl, want_arrays=False)
+        vc.timing_enable(True)
+        vc.timing_read()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            vc.map_load_vxl(vxl, want_arrays=False)
+        load_ms = (time.perf_counter() - t0) * 1e3 / reps
+        load_kt = {k: v[1] / reps for k, v in vc.timing_read().items() if v[0]}
+        t0 = time.perf_counter()
+        for _ in range(3):
+            hs, hc = vc.map_load_vxl(vxl, want_arrays=True)
+        load_arrays_ms = (time.perf_counter() - t0) * 1e3 / 3
+        vc.timing_read()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            saved = vc.map_save_vxl()
+        save_ms = (time.perf_counter() - t0) * 1e3 / reps
+        save_kt = {k: v[1] / (2 * reps) for k, v in vc.timing_read().items() if v[0]}  # each save = length query + emit
+        t0 = time.perf_counter()
+        for _ in range(3):
+            hm = VoxelMap.load(vxl)
+            vc.map_upload(hm.solid, hm.color)
+        host_ms = (time.perf_counter() - t0) * 1e3 / 3
+    out["vxl"] = {"workload": f"Title.vxl ({len(vxl)} B stream, 262144 columns): osb200_map_load_vxl (H2D of the stream, column "
+                              "index by pointer doubling, per-column decode into the resident map) and osb200_map_save_vxl, "
+                              "against the host decoder (VoxelMap::Load = GameMap::Load) + osb200_map_upload of the 66 MiB arrays",
+                  "device_load_ms": load_ms, "device_load_with_host_arrays_ms": load_arrays_ms, "device_save_ms": save_ms,
+                  "host_load_plus_upload_ms": host_ms, "saved_bytes": len(saved), "load_kernel_ms": load_kt,
+                  "save_kernel_ms_per_call": save_kt, "columns_per_s_load": 262144 / (load_ms * 1e-3)}
     out["radiosity"] = {"workload": "C5 Title.vxl: all 4096 chunks dirty -> osb200_radiosity_update(all) (16.8 M voxels, <=169 "
                                     "taps each), then 100 frames x 100 random block edits, each frame flush + shadow update + "
                                     "radiosity update of every dirty chunk (host edit generation inside the wall time)",

@@ -94,6 +94,42 @@ namespace osb200 {
 		}
 	}
 
+	std::unique_ptr<VoxelMap> B200Renderer::LoadGameMap(const uint8_t *data, size_t len) {
+		EnsureInitialized();
+		EnsureSceneNotStarted();
+		std::unique_ptr<VoxelMap> map(new VoxelMap());
+		if (map_)
+			map_->RemoveListener(this);
+		map_ = nullptr;
+		if (osb200_map_load_vxl(ctx_, data, len, map->MutableSolidData(), map->MutableColorData()) != 0) {
+			osb200_map_clear(ctx_);
+			RaiseAbi("osb200_map_load_vxl");
+		}
+		map_ = map.get();
+		map_->AddListener(this);
+		return map;
+	}
+
+	std::vector<uint8_t> B200Renderer::SaveGameMap() {
+		EnsureInitialized();
+		EnsureSceneNotStarted();
+		if (!map_)
+			throw RendererError("B200Renderer: no map set");
+		{
+			std::lock_guard<std::mutex> guard(dirtyMutex_);
+			lastFlushed_ = osb200_map_flush(ctx_, map_->SolidData(), map_->ColorData());
+		}
+		if (lastFlushed_ < 0)
+			RaiseAbi("osb200_map_flush");
+		const long long n = osb200_map_save_vxl(ctx_, nullptr, 0);
+		if (n < 0)
+			RaiseAbi("osb200_map_save_vxl");
+		std::vector<uint8_t> out((size_t)n);
+		if (osb200_map_save_vxl(ctx_, out.data(), out.size()) != n)
+			RaiseAbi("osb200_map_save_vxl");
+		return out;
+	}
+
 	void B200Renderer::GameMapChanged(int x, int y, int z, VoxelMap *map) {
 		// SWRenderer.cpp:1148-1154 -> SWFlatMapRenderer::SetNeedsUpdate (mutex-protected bitset)
 		if (map != map_)

@@ -139,6 +139,12 @@ namespace osb200 {
 		void Shutdown();
 
 		void SetGameMap(VoxelMap *map); // nullptr detaches (stmp::optional<GameMap&> in the reference)
+		// GameMap::Load + SetGameMap in one step: the raw VXL stream is decoded on the device (osb200_map_load_vxl), the
+		// returned VoxelMap receives the decoded arrays and becomes the current map without a second upload.
+		// Throws RendererError on a truncated stream (the reference's loader throws as well).
+		std::unique_ptr<VoxelMap> LoadGameMap(const uint8_t *data, size_t len);
+		// GameMap::Save of the current map, encoded on the device (pending edits are flushed first)
+		std::vector<uint8_t> SaveGameMap();
 		void SetFogDistance(float v) { fogDistance_ = v; }
 		void SetFogColor(Vector3 v) { fogColor_ = v; }
 

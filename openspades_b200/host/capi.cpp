@@ -82,6 +82,23 @@ OSBH_API int osbh_renderer_shutdown(void *p) { return guarded([&] { R(p)->Shutdo
 OSBH_API int osbh_renderer_set_map(void *p, void *map) {
 	return guarded([&] { R(p)->SetGameMap(static_cast<osb200::VoxelMap *>(map)); });
 }
+// GameMap::Load on the device + SetGameMap; returns the new VoxelMap (owned by the caller) or NULL
+OSBH_API void *osbh_renderer_load_map(void *p, const uint8_t *data, size_t len) {
+	osb200::VoxelMap *m = nullptr;
+	guarded([&] { m = R(p)->LoadGameMap(data, len).release(); });
+	return m;
+}
+// GameMap::Save on the device: returns the stream length (< 0 on error), copies min(length, cap) bytes
+OSBH_API long long osbh_renderer_save_map(void *p, uint8_t *out, size_t cap) {
+	long long n = -1;
+	guarded([&] {
+		std::vector<uint8_t> v = R(p)->SaveGameMap();
+		if (out && cap)
+			std::memcpy(out, v.data(), v.size() < cap ? v.size() : cap);
+		n = (long long)v.size();
+	});
+	return n;
+}
 OSBH_API int osbh_renderer_set_fog(void *p, float r, float g, float b, float dist) {
 	return guarded([&] {
 		R(p)->SetFogColor(osb200::Vector3{r, g, b});

@@ -112,6 +112,10 @@ class B200Renderer:
             getattr(L, "osbh_renderer_" + f).argtypes = [vp]
         L.osbh_renderer_free.restype = None
         L.osbh_renderer_set_map.argtypes = [vp, vp]
+        L.osbh_renderer_load_map.argtypes = [vp, vp, ctypes.c_size_t]
+        L.osbh_renderer_load_map.restype = vp
+        L.osbh_renderer_save_map.argtypes = [vp, vp, ctypes.c_size_t]
+        L.osbh_renderer_save_map.restype = ctypes.c_longlong
         L.osbh_renderer_set_fog.argtypes = [vp, fp, fp, fp, fp]
         L.osbh_renderer_start_scene.argtypes = [vp, vp]
         L.osbh_renderer_read_bitmap.argtypes = [vp, vp]
@@ -146,6 +150,26 @@ class B200Renderer:
     def set_game_map(self, m):
         self._map = m  # keep the host map alive while it is attached
         self._chk(self._L.osbh_renderer_set_map(self._h, None if m is None else m.handle))
+
+    def load_game_map(self, data: bytes):
+        """B200Renderer::LoadGameMap: GameMap::Load on the device + SetGameMap; returns the VoxelMap."""
+        buf = np.frombuffer(data, np.uint8)
+        h = self._L.osbh_renderer_load_map(self._h, buf.ctypes.data, len(buf))
+        if not h:
+            self._map = None
+            raise OsbError(self._L.osbh_last_error().decode())
+        self._map = VoxelMap(h)
+        return self._map
+
+    def save_game_map(self) -> bytes:
+        """B200Renderer::SaveGameMap: GameMap::Save of the current map, encoded on the device."""
+        n = self._L.osbh_renderer_save_map(self._h, None, 0)
+        if n < 0:
+            raise OsbError(self._L.osbh_last_error().decode())
+        out = np.empty(n, np.uint8)
+        if self._L.osbh_renderer_save_map(self._h, out.ctypes.data, n) != n:
+            raise OsbError(self._L.osbh_last_error().decode())
+        return out.tobytes()
 
     def set_fog(self, color, dist):
         self._chk(self._L.osbh_renderer_set_fog(self._h, color[0], color[1], color[2], dist))

@@ -184,3 +184,41 @@ def test_renderer_draws_models_and_lights_like_the_reference():
     rr.set_map(None)
     rr.close()
     ref.map_free(rm)
+
+
+def test_renderer_loads_and_saves_the_map_on_the_device():
+    """B200Renderer::LoadGameMap (GameMap::Load on the device + SetGameMap) gives the frames of the host-decoded map,
+    the returned VoxelMap takes edits like any other, and SaveGameMap is GameMap::Save of the edited map."""
+    data = open(oracles.TITLE_VXL, "rb").read()
+    port = oracles.Port()
+    w, h = 128, 96
+    sc = workloads.title_scene(w, h, 68.0)
+    frames = []
+    for device_load in (False, True):
+        r = B200Renderer(w, h, numerics=osb.NUM_SSE2)
+        r.init()
+        r.set_fog(FOG, 128.0)
+        if device_load:
+            m = r.load_game_map(data)
+        else:
+            m = VoxelMap.load(data)
+            r.set_game_map(m)
+        out = []
+        for step in range(2):
+            r.start_scene(sc)
+            r.end_scene()
+            r.frame_done()
+            out.append(r.read_bitmap().copy())
+            for z in range(5, 31):  # a tower dead ahead; GameMap::Set -> GameMapChanged -> dirty column, visible next frame
+                m.set(256, 266, z, True, 0x64112233 + z)
+        saved = r.save_game_map()
+        assert saved == port.vxl_save(m.solid.copy(), m.color.copy())
+        frames.append(out)
+        with pytest.raises(osb.OsbError):
+            r.load_game_map(data[:1000])
+        r.set_game_map(None)
+        r.shutdown()
+        r.close()
+    for a, b in zip(*frames):
+        assert np.array_equal(a, b)
+    assert not np.array_equal(frames[0][0], frames[0][1])  # the edit is on screen
