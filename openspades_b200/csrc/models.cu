@@ -788,10 +788,47 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 			int i = static_cast<int>(v * 255.f + .5f);
 			return (uint32_t)std::max(std::min(i, 255), 0);
 		};
+		// The heaviest instances (estimated covered pixels = voxels x (scale / distance)^2) are launched first so that
+		// a near, large-splat instance does not end up as the tail of the splat kernel.  Only the launch order
+		// changes: sequence numbers keep the submission order, which is what decides ties.
+		std::vector<int> order(nInst);
+		std::vector<float> cost(nInst);
+		std::vector<uint32_t> seqBase(nInst);
 		uint32_t seq = 1, cols = 0;
 		for (int i = 0; i < nInst; i++) {
+			const float *m = inst[i].matrix;
+			float s2 = 0.f, d2 = 0.f;
+			for (int a = 0; a < 3; a++)
+				s2 = std::max(s2, m[a * 4] * m[a * 4] + m[a * 4 + 1] * m[a * 4 + 1] + m[a * 4 + 2] * m[a * 4 + 2]);
+			for (int k = 0; k < 3; k++)
+				d2 += (m[12 + k] - scene->origin[k]) * (m[12 + k] - scene->origin[k]);
+			cost[i] = (float)inst[i].model->voxels * s2 / std::max(d2, 1.f);
+			order[i] = i;
+			seqBase[i] = seq;
+			seq += inst[i].model->voxels;
+		}
+		{ // the kHeavyFirst most expensive instances go to the front, the rest keep the submission order (sorting all
+			// of them makes the near, mutually overlapping instances run at the same time and contend in L2: measured
+			// +8 % at 2048 instances, while the front group alone removes the tail: -18 % at 64)
+			constexpr int kHeavyFirst = 16;
+			std::vector<int> byCost(order);
+			const int nh = std::min(kHeavyFirst, nInst);
+			std::partial_sort(byCost.begin(), byCost.begin() + nh, byCost.end(),
+			                  [&](int a, int b) { return cost[a] > cost[b] || (cost[a] == cost[b] && a < b); });
+			std::vector<char> front(nInst, 0);
+			int slot = 0;
+			for (int k = 0; k < nh; k++) {
+				order[slot++] = byCost[k];
+				front[byCost[k]] = 1;
+			}
+			for (int i = 0; i < nInst; i++)
+				if (!front[i])
+					order[slot++] = i;
+		}
+		for (int slot = 0; slot < nInst; slot++) {
+			const int i = order[slot];
 			const osb200_model *mo = inst[i].model;
-			InstanceIn &I = M->h_inst[i];
+			InstanceIn &I = M->h_inst[slot];
 			I.model.data = mo->d_data;
 			I.model.addr = mo->d_addr;
 			I.model.w = mo->w;
@@ -804,9 +841,8 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 			std::memcpy(I.matrix, inst[i].matrix, sizeof(I.matrix));
 			I.customColor = toFixed8(inst[i].customColor[2]) | (toFixed8(inst[i].customColor[1]) << 8) |
 			                (toFixed8(inst[i].customColor[0]) << 16);
-			I.seqBase = seq;
+			I.seqBase = seqBase[i];
 			I.colBase = cols;
-			seq += mo->voxels;
 			cols += (uint32_t)(mo->w * mo->h);
 		}
 		fill_scene_mats(*scene, w, h, *M->h_mats);
