@@ -121,6 +121,20 @@ int orc_render_scene(const uint64_t *solid, const uint32_t *color, const orc_sce
                      const orc_model_instance *inst, int nInst, const orc_light *lights, int nLights, uint32_t *bgrx,
                      float *depth);
 
+/* ---- floating-block detection + minimap (orc_links.c) ---- */
+typedef struct orc_links orc_links;
+orc_links *orc_links_create(void);
+void orc_links_free(orc_links *w);
+/* Client/GameMapWrapper.cpp:50-102 Rebuild */
+void orc_links_rebuild(orc_links *w, const uint64_t *solid);
+/* :104-193 AddBlock (sets the voxel in the caller's arrays like GameMap::Set) */
+void orc_links_add_block(orc_links *w, uint64_t *solid, uint32_t *color, int x, int y, int z, uint32_t col);
+/* :199-361 RemoveBlocks: clears the cells, returns the floating blocks (count; min(count, cap) written, reference order) */
+int orc_links_remove_blocks(orc_links *w, uint64_t *solid, const int16_t *cells, int n, int16_t *out, int cap);
+void orc_links_linked(const orc_links *w, uint64_t *out);
+/* Draw/SWFlatMapRenderer.cpp:94-105 GeneratePixel over the map: out[y * 512 + x] */
+void orc_minimap(const uint64_t *solid, const uint32_t *color, uint32_t *out);
+
 #ifdef __cplusplus
 }
 #endif

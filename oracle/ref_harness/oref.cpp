@@ -10,6 +10,7 @@
 #include <vector>
 
 #include <Client/GameMap.h>
+#include <Client/GameMapWrapper.h>
 #include <Client/SceneDefinition.h>
 #include <Core/Bitmap.h>
 #include <Core/Exception.h>
@@ -19,6 +20,8 @@
 #include <Core/StdStream.h>
 #include <Draw/SWFeatureLevel.h>
 #include <Core/VoxelModel.h>
+#include <Draw/SWFlatMapRenderer.h>
+#include <Draw/SWImage.h>
 #include <Draw/SWMapRenderer.h>
 #include <Draw/SWModel.h>
 #include <Draw/SWPort.h>
@@ -138,6 +141,46 @@ void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps, o
 	}
 }
 
+/* ---- GameMapWrapper (Client/GameMapWrapper.cpp): floating-block detection ---- */
+void *oref_wrapper_create(void *map) {
+	try {
+		auto *w = new client::GameMapWrapper(*reinterpret_cast<client::GameMap *>(map));
+		w->Rebuild();
+		return w;
+	} catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+void oref_wrapper_free(void *w) { delete reinterpret_cast<client::GameMapWrapper *>(w); }
+void oref_wrapper_add_block(void *w, int x, int y, int z, uint32_t color) {
+	reinterpret_cast<client::GameMapWrapper *>(w)->AddBlock(x, y, z, color);
+}
+/* cells: n x {x, y, z} int16; returns the number of floating blocks, writes min(count, cap) of them */
+int oref_wrapper_remove_blocks(void *w, const int16_t *cells, int n, int16_t *out, int cap) {
+	try {
+		std::vector<client::CellPos> in;
+		for (int i = 0; i < n; i++)
+			in.emplace_back(cells[i * 3], cells[i * 3 + 1], cells[i * 3 + 2]);
+		std::vector<client::CellPos> fl = reinterpret_cast<client::GameMapWrapper *>(w)->RemoveBlocks(in);
+		for (size_t i = 0; i < fl.size() && (int)i < cap; i++) {
+			out[i * 3] = fl[i].x;
+			out[i * 3 + 1] = fl[i].y;
+			out[i * 3 + 2] = fl[i].z;
+		}
+		return (int)fl.size();
+	} catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+/* linkMap != Invalid per voxel, as bit z of out[x][y] */
+void oref_wrapper_linked(void *w, uint64_t *out) {
+	auto *gw = reinterpret_cast<client::GameMapWrapper *>(w);
+	for (int x = 0; x < 512; x++)
+		for (int y = 0; y < 512; y++) {
+			uint64_t b = 0;
+			for (int z = 0; z < 64; z++)
+				if (gw->linkMap[(x * 512 + y) * 64 + z] != 0)
+					b |= 1ull << z;
+			out[x * 512 + y] = b;
+		}
+}
+
 /* GameMap::CastRay (GameMap.cpp:208-359) */
 void oref_castray(void *map, const float *v0, const float *dir, float length, int32_t *out, size_t n, int threads) {
 	auto *m = reinterpret_cast<const client::GameMap *>(map);
@@ -189,6 +232,15 @@ void oref_renderer_set_map(void *r, void *map) {
 	auto *R = reinterpret_cast<Renderer *>(r);
 	if (map) R->r->SetGameMap(*reinterpret_cast<client::GameMap *>(map));
 	else R->r->SetGameMap({});
+}
+
+/* SWFlatMapRenderer's image (GeneratePixel per column, SWFlatMapRenderer.cpp:52-105), after draining pending updates */
+int oref_renderer_minimap(void *r, uint32_t *out /*[y][x] 512x512*/) {
+	auto *R = reinterpret_cast<Renderer *>(r);
+	if (!R->r->flatMapRenderer) { g_err = "no map set"; return -1; }
+	R->r->flatMapRenderer->Update();
+	std::memcpy(out, R->r->flatMapRenderer->img->GetRawBitmap(), sizeof(uint32_t) * 512 * 512);
+	return 0;
 }
 
 void oref_renderer_set_fog(void *r, float cr, float cg, float cb, float dist) {

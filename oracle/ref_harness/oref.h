@@ -41,6 +41,12 @@ OREF_API long long oref_map_save_vxl(void *map, void *out, size_t cap); /* GameM
 OREF_API void *oref_map_from_arrays(const uint64_t *solid /*[x][y]*/, const uint32_t *color /*[x][y][z]*/);
 OREF_API void oref_map_free(void *map);
 OREF_API void oref_map_get_arrays(void *map, uint64_t *solid, uint32_t *color);
+/* GameMapWrapper (Client/GameMapWrapper.cpp): create = ctor + Rebuild */
+OREF_API void *oref_wrapper_create(void *map);
+OREF_API void oref_wrapper_free(void *w);
+OREF_API void oref_wrapper_add_block(void *w, int x, int y, int z, uint32_t color);
+OREF_API int oref_wrapper_remove_blocks(void *w, const int16_t *cells, int n, int16_t *out, int cap);
+OREF_API void oref_wrapper_linked(void *w, uint64_t *out /*[x][y], bit z = link != Invalid*/);
 OREF_API void oref_map_set(void *map, int x, int y, int z, int solid, uint32_t color); /* GameMap::Set, notifies listeners */
 OREF_API void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps,
                             oref_rayhit *out, size_t n, int threads); /* GameMap::CastRay2 */
@@ -52,6 +58,7 @@ OREF_API void oref_renderer_free(void *r);
 OREF_API int oref_renderer_level(void *r);
 OREF_API void oref_renderer_set_threads(int threads); /* cvar r_swNumThreads */
 OREF_API void oref_renderer_set_map(void *r, void *map);
+OREF_API int oref_renderer_minimap(void *r, uint32_t *out); /* SWFlatMapRenderer image, [y][x] */
 OREF_API void oref_renderer_set_fog(void *r, float cr, float cg, float cb, float dist);
 /* StartScene + EndScene + FrameDone; copies framebuffer (BGRX) and depth when non-NULL.
    Returns 0, or -1 when the reference threw. */

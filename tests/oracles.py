@@ -80,12 +80,53 @@ class Port:
         L.orc_ao_invalidate.restype = None
         L.orc_ao_update_chunk.argtypes = [vp, vp, vp, ci, ci, ci, vp]
         L.orc_ao_update_chunk.restype = None
+        L.orc_links_create.restype = vp
+        L.orc_links_free.argtypes = [vp]
+        L.orc_links_free.restype = None
+        L.orc_links_rebuild.argtypes = [vp, vp]
+        L.orc_links_rebuild.restype = None
+        L.orc_links_add_block.argtypes = [vp, vp, vp, ci, ci, ci, ctypes.c_uint32]
+        L.orc_links_add_block.restype = None
+        L.orc_links_remove_blocks.argtypes = [vp, vp, vp, ci, vp, ci]
+        L.orc_links_linked.argtypes = [vp, vp]
+        L.orc_links_linked.restype = None
+        L.orc_minimap.argtypes = [vp, vp, vp]
+        L.orc_minimap.restype = None
         L.orc_model_create.argtypes = [ci, ci, ci, vp, vp, vp]
         L.orc_model_create.restype = vp
         L.orc_model_free.argtypes = [vp]
         L.orc_model_free.restype = None
         L.orc_model_render_data.argtypes = [vp, vp, ci, vp, ci]
         L.orc_render_scene.argtypes = [vp, vp, vp, ci, ci, vp, ctypes.c_float, ci, ci, ci, vp, ci, vp, ci, vp, vp]
+
+    # ---- floating blocks + minimap (orc_links.c) ----
+    def links_create(self, solid):
+        w = self.L.orc_links_create()
+        self.L.orc_links_rebuild(w, solid.ctypes.data)
+        return w
+
+    def links_free(self, w):
+        self.L.orc_links_free(w)
+
+    def links_add_block(self, w, solid, color, x, y, z, col):
+        self.L.orc_links_add_block(w, solid.ctypes.data, color.ctypes.data, x, y, z, col)
+
+    def links_remove_blocks(self, w, solid, cells):
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros((1 << 20, 3), np.int16)
+        n = self.L.orc_links_remove_blocks(w, solid.ctypes.data, cells.ctypes.data, len(cells), out.ctypes.data, len(out))
+        assert 0 <= n <= len(out)
+        return out[:n].copy()
+
+    def links_linked(self, w):
+        out = np.zeros((512, 512), np.uint64)
+        self.L.orc_links_linked(w, out.ctypes.data)
+        return out
+
+    def minimap(self, solid, color):
+        out = np.zeros((512, 512), np.uint32)
+        self.L.orc_minimap(solid.ctypes.data, color.ctypes.data, out.ctypes.data)
+        return out
 
     # ---- voxel models + dynamic lights (orc_models.c) ----
     def model_create(self, w, h, d, origin, solid, colors):
@@ -271,6 +312,15 @@ class Ref:
         L.oref_map_free.argtypes = [vp]
         L.oref_map_get_arrays.argtypes = [vp, vp, vp]
         L.oref_map_set.argtypes = [vp, ci, ci, ci, ci, ctypes.c_uint32]
+        L.oref_wrapper_create.argtypes = [vp]
+        L.oref_wrapper_create.restype = vp
+        L.oref_wrapper_free.argtypes = [vp]
+        L.oref_wrapper_free.restype = None
+        L.oref_wrapper_add_block.argtypes = [vp, ci, ci, ci, ctypes.c_uint32]
+        L.oref_wrapper_add_block.restype = None
+        L.oref_wrapper_remove_blocks.argtypes = [vp, vp, ci, vp, ci]
+        L.oref_wrapper_linked.argtypes = [vp, vp]
+        L.oref_wrapper_linked.restype = None
         L.oref_castray2.argtypes = [vp, vp, vp, ci, vp, ctypes.c_size_t, ci]
         L.oref_castray.argtypes = [vp, vp, vp, ctypes.c_float, vp, ctypes.c_size_t, ci]
         L.oref_castray.restype = None
@@ -280,6 +330,7 @@ class Ref:
         L.oref_renderer_set_threads.argtypes = [ci]
         L.oref_renderer_set_map.argtypes = [vp, vp]
         L.oref_renderer_set_fog.argtypes = [vp] + [ctypes.c_float] * 4
+        L.oref_renderer_minimap.argtypes = [vp, vp]
         L.oref_renderer_render.argtypes = [vp, vp, vp, vp]
         L.oref_renderer_rle.argtypes = [vp, ci, ci, vp, ci]
         L.oref_renderer_lines.argtypes = [vp, ctypes.POINTER(ci)]
@@ -308,6 +359,32 @@ class Ref:
         color = np.zeros((512, 512, 64), np.uint32)
         self.L.oref_map_get_arrays(m, solid.ctypes.data, color.ctypes.data)
         return solid, color
+
+    # GameMapWrapper (floating-block detection); create = ctor + Rebuild
+    def wrapper_create(self, m):
+        w = self.L.oref_wrapper_create(m)
+        if not w:
+            raise RuntimeError(self.L.oref_last_error().decode())
+        return w
+
+    def wrapper_free(self, w):
+        self.L.oref_wrapper_free(w)
+
+    def wrapper_add_block(self, w, x, y, z, col):
+        self.L.oref_wrapper_add_block(w, x, y, z, int(col))
+
+    def wrapper_remove_blocks(self, w, cells):
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros((1 << 20, 3), np.int16)
+        n = self.L.oref_wrapper_remove_blocks(w, cells.ctypes.data, len(cells), out.ctypes.data, len(out))
+        if n < 0:
+            raise RuntimeError(self.L.oref_last_error().decode())
+        return out[:n].copy()
+
+    def wrapper_linked(self, w):
+        out = np.zeros((512, 512), np.uint64)
+        self.L.oref_wrapper_linked(w, out.ctypes.data)
+        return out
 
     def map_set(self, m, x, y, z, solid, color):
         self.L.oref_map_set(m, x, y, z, int(solid), int(color))
@@ -560,6 +637,12 @@ class RefRenderer:
         if rc:
             raise RuntimeError(self.ref.L.oref_last_error().decode())
         return fb, dp
+
+    def minimap(self):
+        out = np.zeros((512, 512), np.uint32)
+        if self.ref.L.oref_renderer_minimap(self.r, out.ctypes.data):
+            raise RuntimeError(self.ref.L.oref_last_error().decode())
+        return out
 
     def create_model(self, vmodel: "RefVoxelModel"):
         m = self.ref.L.oref_model_create(self.r, vmodel.h)
