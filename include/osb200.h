@@ -223,6 +223,28 @@ OSB200_API int osb200_map_load_vxl(osb200_ctx *ctx, const uint8_t *data, size_t 
                                    uint32_t *host_color);
 OSB200_API long long osb200_map_save_vxl(osb200_ctx *ctx, uint8_t *out, size_t cap);
 
+/* ---- Floating-block detection: GameMapWrapper (Client/GameMapWrapper.cpp) on the resident map.  State: one "linked"
+ *      bit per voxel (connected to the ground through solid 6-neighbours, no wrap; the z = 63 layer is the root).
+ *      All three calls need a flushed map (osb200_map_flush).
+ *      osb200_links_rebuild        GameMapWrapper::Rebuild (:50-102); returns the number of flood launches (>= 1).
+ *      osb200_links_blocks_added   after voxels were added (GameMapWrapper::AddBlock, :104-193) and flushed.
+ *      osb200_links_remove_blocks  GameMapWrapper::RemoveBlocks (:199-361) for cells {x, y, z} x n (int16) that the
+ *                                  caller has already cleared on the host map and flushed (the reference's
+ *                                  m.Set(.., false) at :214): returns how many solid voxels lost their connection
+ *                                  and writes min(count, cap) of them, sorted by (x, y, z) (the reference returns
+ *                                  the same set in its walk order).  Like the reference it does not remove them.
+ *      osb200_links_read           linked bitmap in [x][y] order, bit z. ---- */
+OSB200_API int osb200_links_rebuild(osb200_ctx *ctx);
+OSB200_API int osb200_links_blocks_added(osb200_ctx *ctx);
+OSB200_API int osb200_links_remove_blocks(osb200_ctx *ctx, const int16_t *cells, int n, int16_t *floating, int cap);
+OSB200_API int osb200_links_read(osb200_ctx *ctx, uint64_t *out);
+OSB200_API int osb200_links_last_rounds(osb200_ctx *ctx); /* flood launches of the last links call (diagnostics) */
+
+/* ---- Minimap: SWFlatMapRenderer::Update / GeneratePixel (Draw/SWFlatMapRenderer.cpp:52-105): colour of the topmost solid
+ *      voxel of every column, 0xffRRGGBB-swizzled like the reference's SWImage, out[y * 512 + x] (nullable); *device
+ *      (nullable) receives the device copy.  Needs a flushed map. ---- */
+OSB200_API int osb200_minimap(osb200_ctx *ctx, uint32_t *out, const uint32_t **device);
+
 /* ---- GameMap::CastRay (GameMap.cpp:208-359), batched: the integer cell-wall walk used by the ambient-occlusion
  *      evaluation and by the game's hit tests.  v0, dir: n x 3 floats; one length for the batch (the walk takes at most
  *      (long)length cell walls); out: n x {hit, hitBlock.x, hitBlock.y, hitBlock.z} int32 (zeros on a miss). ---- */

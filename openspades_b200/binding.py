@@ -77,6 +77,12 @@ def load_library():
     lib.osb200_map_load_vxl.argtypes = [vp, vp, sz, vp, vp]
     lib.osb200_map_save_vxl.argtypes = [vp, vp, sz]
     lib.osb200_map_save_vxl.restype = ctypes.c_longlong
+    lib.osb200_links_rebuild.argtypes = [vp]
+    lib.osb200_links_blocks_added.argtypes = [vp]
+    lib.osb200_links_remove_blocks.argtypes = [vp, vp, ci, vp, ci]
+    lib.osb200_links_read.argtypes = [vp, vp]
+    lib.osb200_links_last_rounds.argtypes = [vp]
+    lib.osb200_minimap.argtypes = [vp, vp, ctypes.POINTER(vp)]
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
     lib.osb200_map_flush.argtypes = [vp, vp, vp]
     lib.osb200_map_read_solid.argtypes = [vp, vp]
@@ -215,6 +221,35 @@ class Context:
         if m != n:
             raise OsbError(self._lib.osb200_last_error().decode() if m < 0 else "osb200_map_save_vxl: length changed")
         return out.tobytes()
+
+    # ---- GameMapWrapper (floating blocks) + minimap ----
+    def links_rebuild(self):
+        return self._check(self._lib.osb200_links_rebuild(self._h))
+
+    def links_blocks_added(self):
+        return self._check(self._lib.osb200_links_blocks_added(self._h))
+
+    def links_remove_blocks(self, cells, cap=1 << 20):
+        """cells: (n, 3) int16 already cleared + flushed; returns the (m, 3) int16 floating blocks sorted by (x, y, z)."""
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros((cap, 3), np.int16)
+        n = self._check(self._lib.osb200_links_remove_blocks(self._h, cells.ctypes.data, len(cells), out.ctypes.data, cap))
+        if n > cap:
+            raise OsbError("links_remove_blocks: more floating blocks than cap")
+        return out[:n].copy()
+
+    def links_read(self):
+        out = np.zeros((512, 512), np.uint64)
+        self._check(self._lib.osb200_links_read(self._h, out.ctypes.data))
+        return out
+
+    def links_last_rounds(self):
+        return self._lib.osb200_links_last_rounds(self._h)
+
+    def minimap(self):
+        out = np.zeros((512, 512), np.uint32)
+        self._check(self._lib.osb200_minimap(self._h, out.ctypes.data, None))
+        return out
 
     def map_clear(self):
         self._check(self._lib.osb200_map_clear(self._h))

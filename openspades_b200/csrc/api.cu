@@ -27,7 +27,7 @@ namespace osb {
 		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_build_lines",
 		                                     "k_gather_fog", "k_castray2", "k_shadow_update", "k_radiosity",
 		                                     "k_rad_select", "k_castray", "k_ao_chunk", "k_fog", "k_model_setup", "k_model_splat",
-		                                     "k_model_resolve", "k_lights", "k_vxl_index", "k_vxl_decode", "k_vxl_encode"};
+		                                     "k_model_resolve", "k_lights", "k_vxl_index", "k_vxl_decode", "k_vxl_encode", "k_links_flood", "k_minimap"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
 	KLaunch::KLaunch(osb200_ctx *ctx, int kid, cudaStream_t stream) : c(ctx), slot(-1), st(stream ? stream : ctx->stream) {
@@ -52,6 +52,8 @@ namespace osb {
 	void ambient_destroy(osb200_ctx *ctx);   // ambient.cu
 	void models_destroy(osb200_ctx *ctx);    // models.cu
 	void vxl_destroy(osb200_ctx *ctx);       // vxl.cu
+	void links_destroy(osb200_ctx *ctx);     // links.cu
+	void links_map_replaced(osb200_ctx *ctx);
 	void ambient_map_replaced(osb200_ctx *ctx);
 	void ambient_mark_dirty(osb200_ctx *ctx, int x, int y, int z);
 	// a whole new map is resident (osb200_map_upload / osb200_map_load_vxl): nothing is dirty, every derived volume is stale
@@ -61,6 +63,7 @@ namespace osb {
 		c->mapLoaded = true;
 		radiosity_map_replaced(c);
 		ambient_map_replaced(c);
+		links_map_replaced(c);
 	}
 } // namespace osb
 
@@ -282,6 +285,7 @@ void osb200_destroy(osb200_ctx *c) {
 	osb::ambient_destroy(c);
 	osb::models_destroy(c);
 	osb::vxl_destroy(c);
+	osb::links_destroy(c);
 	cudaFree(c->d_solid); // bitmap + colours are one allocation
 	cudaFree(c->d_rcp);
 	cudaFree(c->d_rsqrt);

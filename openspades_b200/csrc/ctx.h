@@ -51,6 +51,8 @@ namespace osb {
 		K_VXL_INDEX,
 		K_VXL_DECODE,
 		K_VXL_ENCODE,
+		K_LINKS_FLOOD,
+		K_MINIMAP,
 		K_COUNT
 	};
 	const char *kernel_name(int id);
@@ -60,6 +62,7 @@ namespace osb {
 	struct AmbientState;   // ambient.cu
 	struct ModelState;     // models.cu
 	struct VxlState;       // vxl.cu
+	struct LinksState;     // links.cu
 } // namespace osb
 
 struct osb200_ctx;
@@ -129,6 +132,7 @@ struct osb200_ctx {
 	osb::AmbientState *ambient = nullptr;
 	osb::ModelState *models = nullptr;
 	osb::VxlState *vxl = nullptr;
+	osb::LinksState *links = nullptr;
 
 	int ensure_scratch(size_t bytes);
 	int ensure_stage(size_t bytes);
