@@ -567,6 +567,57 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                   "device_load_ms": load_ms, "device_load_with_host_arrays_ms": load_arrays_ms, "device_save_ms": save_ms,
                   "host_load_plus_upload_ms": host_ms, "saved_bytes": len(saved), "load_kernel_ms": load_kt,
                   "save_kernel_ms_per_call": save_kt, "columns_per_s_load": 262144 / (load_ms * 1e-3)}
+    # ---- floating-block detection (GameMapWrapper) + minimap ----
+    ls, lc = load_map()
+    with osb.Context(device=dev.index, numerics=osb.NUM_IEEE) as lk:
+        lk.map_upload(ls, lc)
+        lk.links_rebuild()
+        t0 = time.perf_counter()
+        for _ in range(10):
+            rounds = lk.links_rebuild()
+        rebuild_ms = (time.perf_counter() - t0) * 1e3 / 10
+        rng = np.random.default_rng(5)
+        n_calls, per_call, fell = 50, 100, 0
+        batches = []
+        for _ in range(n_calls):  # 100 distinct columns per call: the voxel under the surface is dug out (undercut)
+            cols = rng.choice(512 * 512, per_call, replace=False)
+            batches.append([(int(c) >> 9, int(c) & 511) for c in cols])
+        lk.timing_enable(True)
+        lk.timing_read()
+        t0 = time.perf_counter()
+        for cols in batches:
+            cells = []
+            for (x, y) in cols:
+                m_ = int(ls[x, y])
+                z = (m_ & -m_).bit_length() - 1 + 1
+                if z >= 62 or not (m_ >> z) & 1:
+                    continue
+                ls[x, y] &= ~(np.uint64(1) << np.uint64(z))
+                lk.map_mark_dirty(x, y, z)
+                cells.append((x, y, z))
+            lk.map_flush(ls, lc)
+            fl = lk.links_remove_blocks(cells)
+            fell += len(fl)
+            for (x, y, z) in fl:
+                ls[x, y] &= ~(np.uint64(1) << np.uint64(int(z)))
+                lk.map_mark_dirty(int(x), int(y), int(z))
+        lk.map_flush(ls, lc)
+        remove_ms = (time.perf_counter() - t0) * 1e3 / n_calls
+        lkt = lk.timing_read()
+        lk.timing_read()
+        t0 = time.perf_counter()
+        for _ in range(20):
+            lk.minimap()
+        minimap_ms = (time.perf_counter() - t0) * 1e3 / 20
+        mm_k = lk.timing_read()["k_minimap"][1] / 20
+    out["links"] = {"workload": "GameMapWrapper on Title.vxl: Rebuild (flood from the ground over 16.8 M voxels as 64-bit column "
+                                f"masks), then {n_calls} RemoveBlocks calls x {per_call} undercut voxels each (host edit + flush + flood + "
+                                "result read-back inside the wall time); minimap = SWFlatMapRenderer image of the whole map",
+                    "rebuild_ms": rebuild_ms, "rebuild_flood_launches": rounds, "remove_blocks_ms_per_call": remove_ms,
+                    "removed_voxels_per_s": n_calls * per_call / (remove_ms * n_calls * 1e-3), "blocks_fell": fell,
+                    "flood_kernel_ms_per_call": lkt["k_links_flood"][1] / n_calls,
+                    "flood_launches_per_call": lkt["k_links_flood"][0] / n_calls,
+                    "minimap_ms": minimap_ms, "minimap_kernel_ms": mm_k}
     out["radiosity"] = {"workload": "C5 Title.vxl: all 4096 chunks dirty -> osb200_radiosity_update(all) (16.8 M voxels, <=169 "
                                     "taps each), then 100 frames x 100 random block edits, each frame flush + shadow update + "
                                     "radiosity update of every dirty chunk (host edit generation inside the wall time)",

@@ -238,6 +238,8 @@ OSB200_API int osb200_links_rebuild(osb200_ctx *ctx);
 OSB200_API int osb200_links_blocks_added(osb200_ctx *ctx);
 OSB200_API int osb200_links_remove_blocks(osb200_ctx *ctx, const int16_t *cells, int n, int16_t *floating, int cap);
 OSB200_API int osb200_links_read(osb200_ctx *ctx, uint64_t *out);
+/* the result of the last osb200_links_remove_blocks again (for a caller whose buffer was too small): count, min(count, cap) written */
+OSB200_API int osb200_links_last_floating(osb200_ctx *ctx, int16_t *floating, int cap);
 OSB200_API int osb200_links_last_rounds(osb200_ctx *ctx); /* flood launches of the last links call (diagnostics) */
 
 /* ---- Minimap: SWFlatMapRenderer::Update / GeneratePixel (Draw/SWFlatMapRenderer.cpp:52-105): colour of the topmost solid

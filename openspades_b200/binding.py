@@ -81,6 +81,7 @@ def load_library():
     lib.osb200_links_blocks_added.argtypes = [vp]
     lib.osb200_links_remove_blocks.argtypes = [vp, vp, ci, vp, ci]
     lib.osb200_links_read.argtypes = [vp, vp]
+    lib.osb200_links_last_floating.argtypes = [vp, vp, ci]
     lib.osb200_links_last_rounds.argtypes = [vp]
     lib.osb200_minimap.argtypes = [vp, vp, ctypes.POINTER(vp)]
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
@@ -229,13 +230,14 @@ class Context:
     def links_blocks_added(self):
         return self._check(self._lib.osb200_links_blocks_added(self._h))
 
-    def links_remove_blocks(self, cells, cap=1 << 20):
+    def links_remove_blocks(self, cells, cap=4096):
         """cells: (n, 3) int16 already cleared + flushed; returns the (m, 3) int16 floating blocks sorted by (x, y, z)."""
         cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
         out = np.zeros((cap, 3), np.int16)
         n = self._check(self._lib.osb200_links_remove_blocks(self._h, cells.ctypes.data, len(cells), out.ctypes.data, cap))
         if n > cap:
-            raise OsbError("links_remove_blocks: more floating blocks than cap")
+            out = np.zeros((n, 3), np.int16)
+            self._check(self._lib.osb200_links_last_floating(self._h, out.ctypes.data, n))
         return out[:n].copy()
 
     def links_read(self):

@@ -36,6 +36,7 @@ namespace osb {
 		uint32_t *d_minimap = nullptr;
 		bool valid = false;
 		int lastRounds = 0;
+		std::vector<int16_t> lastFloating; // sorted result of the last remove_blocks call (osb200_links_last_floating)
 	};
 
 	// all runs of `within` that contain a bit of r (r is a subset of within)
@@ -158,7 +159,7 @@ namespace osb {
 			const int z = __ffsll((long long)m) - 1;
 			m &= m - 1;
 			const int k = atomicAdd(&flags[1], 1);
-			if (k < cap) {
+			if (out && k < cap) {
 				out[k * 3] = (int16_t)x;
 				out[k * 3 + 1] = (int16_t)y;
 				out[k * 3 + 2] = (int16_t)z;
@@ -340,14 +341,6 @@ int osb200_links_remove_blocks(osb200_ctx *c, const int16_t *cells, int n, int16
 		OSB_CUDA(cudaMalloc(&S->d_cells, ((size_t)n + 1024) * 3 * sizeof(int16_t)));
 		S->cellCap = (size_t)n + 1024;
 	}
-	const size_t wantOut = std::max<size_t>((size_t)cap, 1 << 16);
-	if (wantOut > S->outCap) {
-		cudaFree(S->d_out);
-		S->d_out = nullptr;
-		S->outCap = 0;
-		OSB_CUDA(cudaMalloc(&S->d_out, wantOut * 3 * sizeof(int16_t)));
-		S->outCap = wantOut;
-	}
 	OSB_CUDA(cudaMemcpyAsync(S->d_cells, cells, (size_t)n * 3 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream));
 	if (int rc = ground_flood(c))
 		return rc;
@@ -369,28 +362,58 @@ int osb200_links_remove_blocks(osb200_ctx *c, const int16_t *cells, int n, int16
 		if (int rc = flood(c, d_within2, S->d_reach2))
 			return rc;
 	}
+	// count first, then emit into a buffer that is large enough
 	OSB_CUDA(cudaMemsetAsync(S->d_flags, 0, 4 * sizeof(int), c->stream));
 	k_links_emit<<<nCols / 256, 256, 0, c->stream>>>(S->d_linked, S->d_within, S->d_reach, haveCluster ? S->d_reach2 : nullptr,
-	                                               S->d_out, (int)S->outCap, S->d_flags);
-	k_links_finish<<<nCols / 256, 256, 0, c->stream>>>(S->d_reach, S->d_linked);
-	c->launches += 2;
-	OSB_CUDA(cudaGetLastError());
+	                                               nullptr, 0, S->d_flags);
+	c->launches++;
 	OSB_CUDA(cudaMemcpyAsync(S->h_flags, S->d_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	const int count = S->h_flags[1];
-	const int got = (int)std::min<size_t>((size_t)count, S->outCap);
-	std::vector<int16_t> host((size_t)got * 3);
-	if (got)
-		OSB_CUDA(cudaMemcpy(host.data(), S->d_out, (size_t)got * 3 * sizeof(int16_t), cudaMemcpyDeviceToHost));
+	if ((size_t)count > S->outCap) {
+		cudaFree(S->d_out);
+		S->d_out = nullptr;
+		S->outCap = 0;
+		const size_t want = (size_t)count + ((size_t)count >> 1) + 4096;
+		OSB_CUDA(cudaMalloc(&S->d_out, want * 3 * sizeof(int16_t)));
+		S->outCap = want;
+	}
+	if (count) {
+		OSB_CUDA(cudaMemsetAsync(S->d_flags, 0, 4 * sizeof(int), c->stream));
+		k_links_emit<<<nCols / 256, 256, 0, c->stream>>>(S->d_linked, S->d_within, S->d_reach,
+		                                               haveCluster ? S->d_reach2 : nullptr, S->d_out, (int)S->outCap, S->d_flags);
+		c->launches++;
+	}
+	k_links_finish<<<nCols / 256, 256, 0, c->stream>>>(S->d_reach, S->d_linked);
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	std::vector<int16_t> host((size_t)count * 3);
+	if (count)
+		OSB_CUDA(cudaMemcpyAsync(host.data(), S->d_out, (size_t)count * 3 * sizeof(int16_t), cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	// deterministic order: (x, y, z) ascending, CellPos::operator< (GameMapWrapper.h:35-48)
-	std::vector<int> idx(got);
-	for (int i = 0; i < got; i++)
+	std::vector<int> idx(count);
+	for (int i = 0; i < count; i++)
 		idx[i] = i;
 	std::sort(idx.begin(), idx.end(), [&](int a, int b) {
-		return std::lexicographical_compare(&host[a * 3], &host[a * 3] + 3, &host[b * 3], &host[b * 3] + 3);
+		return std::lexicographical_compare(&host[(size_t)a * 3], &host[(size_t)a * 3] + 3, &host[(size_t)b * 3], &host[(size_t)b * 3] + 3);
 	});
-	for (int i = 0; i < got && i < cap; i++)
-		std::memcpy(floating + (size_t)i * 3, &host[(size_t)idx[i] * 3], 3 * sizeof(int16_t));
+	S->lastFloating.resize((size_t)count * 3);
+	for (int i = 0; i < count; i++)
+		std::memcpy(&S->lastFloating[(size_t)i * 3], &host[(size_t)idx[i] * 3], 3 * sizeof(int16_t));
+	if (cap > 0 && count > 0)
+		std::memcpy(floating, S->lastFloating.data(), (size_t)std::min(count, cap) * 3 * sizeof(int16_t));
+	return count;
+}
+
+int osb200_links_last_floating(osb200_ctx *c, int16_t *floating, int cap) {
+	if (!c || !c->links || cap < 0 || (cap && !floating)) {
+		osb::set_error("osb200_links_last_floating: bad argument");
+		return -1;
+	}
+	const int count = (int)(c->links->lastFloating.size() / 3);
+	if (cap > 0 && count > 0)
+		std::memcpy(floating, c->links->lastFloating.data(), (size_t)std::min(count, cap) * 3 * sizeof(int16_t));
 	return count;
 }
 

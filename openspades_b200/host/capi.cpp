@@ -50,6 +50,7 @@ OSBH_API int osbh_map_set_arrays(void *m, const uint64_t *solid, const uint32_t 
 
 // ---- B200Renderer ----
 #include "B200Renderer.h"
+#include "VoxelMapWrapper.h"
 
 namespace {
 	struct RendererBox {
@@ -206,3 +207,32 @@ OSBH_API int osbh_map_castray(void *m, void *ctx, const float *v0, const float *
 	});
 }
 #undef R
+
+// ---- VoxelMapWrapper (client::GameMapWrapper's surface) ----
+OSBH_API void *osbh_wrapper_new(void *map, void *ctx) {
+	return new osb200::VoxelMapWrapper(*static_cast<osb200::VoxelMap *>(map), static_cast<osb200_ctx *>(ctx));
+}
+OSBH_API void osbh_wrapper_free(void *w) { delete static_cast<osb200::VoxelMapWrapper *>(w); }
+OSBH_API int osbh_wrapper_rebuild(void *w) {
+	return guarded([&] { static_cast<osb200::VoxelMapWrapper *>(w)->Rebuild(); });
+}
+OSBH_API int osbh_wrapper_add_block(void *w, int x, int y, int z, uint32_t color) {
+	return guarded([&] { static_cast<osb200::VoxelMapWrapper *>(w)->AddBlock(x, y, z, color); });
+}
+// cells: n x {x, y, z} int16; returns the number of floating blocks (< 0 on error), writes min(count, cap)
+OSBH_API int osbh_wrapper_remove_blocks(void *w, const int16_t *cells, int n, int16_t *out, int cap) {
+	int count = -1;
+	guarded([&] {
+		std::vector<osb200::CellPos> in;
+		for (int i = 0; i < n; i++)
+			in.emplace_back(cells[i * 3], cells[i * 3 + 1], cells[i * 3 + 2]);
+		std::vector<osb200::CellPos> fl = static_cast<osb200::VoxelMapWrapper *>(w)->RemoveBlocks(in);
+		for (size_t i = 0; i < fl.size() && (int)i < cap; i++) {
+			out[i * 3] = fl[i].x;
+			out[i * 3 + 1] = fl[i].y;
+			out[i * 3 + 2] = fl[i].z;
+		}
+		count = (int)fl.size();
+	});
+	return count;
+}

@@ -285,3 +285,44 @@ class B200Renderer:
             self.close()
         except Exception:
             pass
+
+
+class VoxelMapWrapper:
+    """osb200::VoxelMapWrapper (host/VoxelMapWrapper.h) -- client::GameMapWrapper's surface: Rebuild / AddBlock / RemoveBlocks
+    on a VoxelMap whose device copy lives in `renderer`'s context."""
+
+    def __init__(self, vmap: VoxelMap, renderer: "B200Renderer"):
+        L = self._L = load_host_library()
+        vp = ctypes.c_void_p
+        L.osbh_wrapper_new.argtypes = [vp, vp]
+        L.osbh_wrapper_new.restype = vp
+        L.osbh_wrapper_free.argtypes = [vp]
+        L.osbh_wrapper_free.restype = None
+        L.osbh_wrapper_rebuild.argtypes = [vp]
+        L.osbh_wrapper_add_block.argtypes = [vp] + [ctypes.c_int] * 3 + [ctypes.c_uint32]
+        L.osbh_wrapper_remove_blocks.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int]
+        L.osbh_renderer_context.restype = vp
+        self._map, self._renderer = vmap, renderer  # keep both alive
+        self._h = L.osbh_wrapper_new(vmap.handle, L.osbh_renderer_context(renderer._h))
+
+    def _chk(self, rc):
+        if rc < 0:
+            raise OsbError(self._L.osbh_last_error().decode())
+        return rc
+
+    def rebuild(self):
+        self._chk(self._L.osbh_wrapper_rebuild(self._h))
+
+    def add_block(self, x, y, z, color):
+        self._chk(self._L.osbh_wrapper_add_block(self._h, x, y, z, int(color)))
+
+    def remove_blocks(self, cells):
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros((1 << 16, 3), np.int16)
+        n = self._chk(self._L.osbh_wrapper_remove_blocks(self._h, cells.ctypes.data, len(cells), out.ctypes.data, len(out)))
+        return out[:min(n, len(out))].copy()
+
+    def close(self):
+        if self._h:
+            self._L.osbh_wrapper_free(self._h)
+            self._h = None

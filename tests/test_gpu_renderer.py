@@ -222,3 +222,50 @@ def test_renderer_loads_and_saves_the_map_on_the_device():
     for a, b in zip(*frames):
         assert np.array_equal(a, b)
     assert not np.array_equal(frames[0][0], frames[0][1])  # the edit is on screen
+
+
+def test_voxel_map_wrapper_reports_falling_blocks_like_game_map_wrapper():
+    """host/VoxelMapWrapper (client::GameMapWrapper's surface) on the renderer's context: a tower with an arm is built with
+    AddBlock, cut with RemoveBlocks, and the reported blocks are those of the C restatement; the map edits reach the
+    frame through the renderer's GameMapChanged listener."""
+    from openspades_b200.hostlib import VoxelMapWrapper
+    import links_cases
+    port = oracles.Port()
+    m = VoxelMap.load_file(oracles.TITLE_VXL)
+    ps, pc = m.solid.copy(), m.color.copy()
+    pw = port.links_create(ps)
+    r = B200Renderer(128, 96, numerics=osb.NUM_IEEE)
+    r.init()
+    r.set_fog(FOG, 128.0)
+    r.set_game_map(m)
+    w = VoxelMapWrapper(m, r)
+    w.rebuild()
+    x, y = 256, 266
+    z0 = links_cases.top_of(ps, x, y)
+    tower = [(x, y, z0 - 1 - k) for k in range(10)]
+    arm = [(x + k, y, z0 - 10) for k in range(1, 5)]
+    for c in tower + arm:
+        w.add_block(*c, 0x64aa5511)
+        port.links_add_block(pw, ps, pc, *c, 0x64aa5511)
+    assert np.array_equal(m.solid, ps)
+    sc = workloads.title_scene(128, 96, 68.0)
+    r.start_scene(sc)
+    r.end_scene()
+    r.frame_done()
+    before = r.read_bitmap().copy()
+    got = w.remove_blocks([tower[3]])
+    want = port.links_remove_blocks(pw, ps, [tower[3]])
+    want = want[np.lexsort((want[:, 2], want[:, 1], want[:, 0]))]
+    assert np.array_equal(got, want) and len(got) == 6 + 4
+    for (cx, cy, cz) in got:  # World::ApplyBlockActions: the floating blocks are cleared
+        m.set(int(cx), int(cy), int(cz), False, 0)
+    r.start_scene(sc)
+    r.end_scene()
+    r.frame_done()
+    assert not np.array_equal(before, r.read_bitmap())
+    assert len(w.remove_blocks([tower[0]])) == 2  # what is left above the foot of the tower
+    w.close()
+    port.links_free(pw)
+    r.set_game_map(None)
+    r.shutdown()
+    r.close()
