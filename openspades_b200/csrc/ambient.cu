@@ -143,15 +143,148 @@ namespace osb {
 		return false;
 	}
 
+	// The same walk as a resumable state, for the batch kernel: lanes whose ray has ended pick up new rays while the
+	// others keep walking (rays of one batch end after anything between 0 and ~2 * length cell walls).
+	struct RayWalk {
+		int ax, ay, az, px, py, pz, ix, iy, iz, dx, dy, dz, cx, cz;
+		long long cnt;
+		uint64_t mask;
+	};
+	enum { kRayWalking = 0, kRayHit = 1, kRayMiss = 2 };
+	template <class Columns>
+	__device__ __forceinline__ int ray_init(const Columns &col, const float v0[3], const float dir[3], float length, RayWalk &w) {
+		const float v1[3] = {__fadd_rn(v0[0], __fmul_rn(dir[0], length)), __fadd_rn(v0[1], __fmul_rn(dir[1], length)),
+		                     __fadd_rn(v0[2], __fmul_rn(dir[2], length))};
+		int a[3], c[3], d[3];
+		float f[3], g[3];
+		long long cnt = 0;
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			a[k] = osbn::x86_f2i(floorf(v0[k]));
+			c[k] = osbn::x86_f2i(floorf(v1[k]));
+			if (c[k] < a[k]) {
+				d[k] = -1;
+				f[k] = __fsub_rn(v0[k], (float)a[k]);
+				g[k] = __fmul_rn(__fsub_rn(v0[k], v1[k]), 1024.f);
+				cnt += (long long)a[k] - c[k];
+			} else if (c[k] != a[k]) {
+				d[k] = 1;
+				f[k] = __fsub_rn((float)(a[k] + 1), v0[k]);
+				g[k] = __fmul_rn(__fsub_rn(v1[k], v0[k]), 1024.f);
+				cnt += (long long)c[k] - a[k];
+			} else {
+				d[k] = 0;
+				f[k] = g[k] = 0.f;
+			}
+		}
+		w.px = osbn::x86_f2i(floorf(__fsub_rn(__fmul_rn(f[0], g[2]), __fmul_rn(f[2], g[0]))));
+		w.py = osbn::x86_f2i(floorf(__fsub_rn(__fmul_rn(f[1], g[2]), __fmul_rn(f[2], g[1]))));
+		w.pz = osbn::x86_f2i(floorf(__fsub_rn(__fmul_rn(f[1], g[0]), __fmul_rn(f[0], g[1]))));
+		w.ix = osbn::x86_f2i(floorf(g[0]));
+		w.iy = osbn::x86_f2i(floorf(g[1]));
+		w.iz = osbn::x86_f2i(floorf(g[2]));
+		const long long lim = (length >= -9223372036854775808.f && length < 9223372036854775808.f)
+		                        ? (long long)length
+		                        : (long long)0x8000000000000000ull;
+		w.cnt = cnt > lim ? lim : cnt;
+		w.ax = a[0], w.ay = a[1], w.az = a[2];
+		w.dx = d[0], w.dy = d[1], w.dz = d[2];
+		w.cx = c[0], w.cz = c[2];
+		w.mask = col(w.ax, w.ay);
+		if (w.az < 0 && w.dz < 0)
+			return kRayMiss;
+		if (w.az >= 64)
+			return kRayHit;
+		return w.cnt > 0 ? kRayWalking : kRayMiss;
+	}
+	template <class Columns> __device__ __forceinline__ int ray_step(const Columns &col, RayWalk &w) {
+		const bool above = w.az < 0;
+		if (((w.px | w.py) >= 0) && w.az != w.cz) {
+			w.az += w.dz;
+			w.px -= w.ix;
+			w.py -= w.iy;
+			if (!above) {
+				if (w.az < 0 && w.dz < 0)
+					return kRayMiss;
+				if (w.az >= 64)
+					return kRayHit;
+			}
+		} else {
+			if (w.pz >= 0 && w.ax != w.cx) {
+				w.ax += w.dx;
+				w.px += w.iz;
+				w.pz -= w.iy;
+			} else {
+				w.ay += w.dy;
+				w.py += w.iz;
+				w.pz += w.ix;
+			}
+			if (!above)
+				w.mask = col(w.ax, w.ay);
+		}
+		if (!above && ((w.mask >> w.az) & 1ull))
+			return kRayHit;
+		return --w.cnt > 0 ? kRayWalking : kRayMiss;
+	}
+
+	// Batch kernel: persistent warps over a batch-wide cursor; when half of a warp's lanes have no ray, the idle lanes
+	// fetch the next rays (first version: one ray per thread to completion, 9.9 of 32 lanes busy on average).
+#ifndef OSB_RAY_BURST
+#define OSB_RAY_BURST 8
+#endif
+#ifndef OSB_RAY_REFILL
+#define OSB_RAY_REFILL 24 // refill when at most this many lanes are walking (8 / 16 / 24 / 28 measured: 5.34 / 4.11 / 3.71 / 3.89 ms)
+#endif
+	constexpr int kRayBurst = OSB_RAY_BURST;
 	__global__ void __launch_bounds__(256) k_castray(const uint64_t *__restrict__ solid, const float *__restrict__ v0,
 	                                                const float *__restrict__ dir, float length, int4 *__restrict__ out,
-	                                                size_t n) {
+	                                                size_t n, unsigned long long *__restrict__ cursor) {
 		const GlobalColumns col{solid};
-		for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-			int hx = 0, hy = 0, hz = 0;
-			const bool hit = cast_ray(col, v0[i * 3], v0[i * 3 + 1], v0[i * 3 + 2], dir[i * 3], dir[i * 3 + 1],
-			                          dir[i * 3 + 2], length, hx, hy, hz);
-			out[i] = hit ? make_int4(1, hx, hy, hz) : make_int4(0, 0, 0, 0);
+		const unsigned lane = threadIdx.x & 31;
+		RayWalk w;
+		size_t idx = 0;
+		bool active = false, more = true;
+		for (;;) {
+			unsigned act = __ballot_sync(0xffffffffu, active);
+			if (more && __popc(act) <= OSB_RAY_REFILL) {
+				const unsigned idle = ~act;
+				const int need = __popc(idle);
+				unsigned long long base = 0;
+				if (lane == 0)
+					base = atomicAdd(cursor, (unsigned long long)need);
+				base = __shfl_sync(0xffffffffu, base, 0);
+				more = base + (unsigned long long)need < n;
+				if (!active) {
+					const size_t i = base + __popc(idle & ((1u << lane) - 1u));
+					if (i < n) {
+						const float o[3] = {v0[i * 3], v0[i * 3 + 1], v0[i * 3 + 2]};
+						const float d[3] = {dir[i * 3], dir[i * 3 + 1], dir[i * 3 + 2]};
+						const int st = ray_init(col, o, d, length, w);
+						if (st == kRayWalking) {
+							active = true;
+							idx = i;
+						} else {
+							out[i] = st == kRayHit ? make_int4(1, w.ax, w.ay, w.az) : make_int4(0, 0, 0, 0);
+						}
+					}
+				}
+				act = __ballot_sync(0xffffffffu, active);
+			}
+			if (!act) {
+				if (!more)
+					break;
+				continue;
+			}
+#pragma unroll 1
+			for (int s = 0; s < kRayBurst; s++) {
+				if (active) {
+					const int st = ray_step(col, w);
+					if (st != kRayWalking) {
+						out[idx] = st == kRayHit ? make_int4(1, w.ax, w.ay, w.az) : make_int4(0, 0, 0, 0);
+						active = false;
+					}
+				}
+			}
 		}
 	}
 
@@ -496,10 +629,13 @@ int osb200_castray_device(osb200_ctx *c, const float *d_v0, const float *d_dir, 
 	}
 	OSB_CUDA(cudaSetDevice(c->device));
 	const size_t blocks = std::min<size_t>((size_t)c->smCount * 8, (n + 255) / 256);
+	if (!c->d_rayCursor)
+		OSB_CUDA(cudaMalloc(&c->d_rayCursor, sizeof(unsigned long long)));
+	OSB_CUDA(cudaMemsetAsync(c->d_rayCursor, 0, sizeof(unsigned long long), c->stream));
 	{
 		osb::KLaunch kl(c, osb::K_CASTRAY);
 		osb::k_castray<<<(unsigned)blocks, 256, 0, c->stream>>>(c->d_solid, d_v0, d_dir, length,
-		                                                       reinterpret_cast<int4 *>(d_out), n);
+		                                                       reinterpret_cast<int4 *>(d_out), n, c->d_rayCursor);
 	}
 	OSB_CUDA(cudaGetLastError());
 	return 0;
