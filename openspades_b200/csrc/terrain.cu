@@ -118,8 +118,9 @@ namespace osb {
 		float2 *d_lineDirs = nullptr;
 		int4 *d_lineParams = nullptr;
 		uint2 *d_strips = nullptr;
+		uint32_t *d_lineMask = nullptr; // lineRes bits per line: strip pixels the line wrote
 		float *d_tabs = nullptr;
-		size_t lineCap = 0, lineParamCap = 0, stripCap = 0, tabCap = 0;
+		size_t lineCap = 0, lineParamCap = 0, stripCap = 0, maskCap = 0, tabCap = 0;
 		cudaStream_t stream = nullptr;
 		cudaEvent_t done = nullptr; // last kernel of the newest chunk that used this set
 	};
@@ -236,24 +237,34 @@ namespace osb {
 #ifndef OSB_LINE_MINB
 #define OSB_LINE_MINB 14
 #endif
+#ifndef OSB_STRIP_CLEAR
+#define OSB_STRIP_CLEAR 0
+#endif
+#ifndef OSB_MASK_FIRST
+#define OSB_MASK_FIRST 1 // gather: test the written-pixel mask before loading the strip pixel (1: 1.68 ms) or load both at once (0: 1.91 ms)
+#endif
 	__global__ void __launch_bounds__(kLineThreads, OSB_LINE_MINB)
 	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
 	                const uint64_t *__restrict__ solid, const uint32_t *__restrict__ color,
 	                osbn::SseTables tabs, uint2 *__restrict__ strips, int4 *__restrict__ lineParams,
-	                uint32_t totalLines, int lineRes) {
+	                uint32_t *__restrict__ lineMask, uint32_t totalLines, int lineRes) {
 		extern __shared__ uint32_t s_filled[]; // (lineRes/32) words x kLineThreads
 		const uint32_t lineBase = blockIdx.x * kLineThreads;
 		const uint32_t gl = lineBase + threadIdx.x;
 		const int words = lineRes >> 5;
 
-		// cooperative clear of this CTA's strips: LinePixel::Clear = {0, 10000.f} (:89-92)
+		// LinePixel::Clear = {0, 10000.f} (:89-92).  The strips are NOT cleared in memory: a line publishes the bitmask
+		// of the strip pixels it wrote (lineMask, lineRes bits per line) and the gather substitutes the clear value
+		// for the others -- the clear was 3/4 of this kernel's DRAM writes.  OSB_STRIP_CLEAR=1 restores the clear.
 		{
+#if OSB_STRIP_CLEAR
 			const uint32_t nl = min((uint32_t)kLineThreads, totalLines - lineBase);
 			uint4 *dst = reinterpret_cast<uint4 *>(strips + (size_t)lineBase * lineRes);
 			const uint32_t n4 = nl * (uint32_t)lineRes / 2;
 			const uint4 clr = make_uint4(0u, __float_as_uint(10000.f), 0u, __float_as_uint(10000.f));
 			for (uint32_t i = threadIdx.x; i < n4; i += kLineThreads)
 				__stcs(dst + i, clr);
+#endif
 			for (int w = 0; w < words; w++)
 				s_filled[w * kLineThreads + threadIdx.x] = 0;
 		}
@@ -353,8 +364,12 @@ namespace osb {
 		const float pitchScale = __fdiv_rn((float)lineRes, __fsub_rn(maxTan, minTan));
 		lineParams[gl] = make_int4(__float_as_int(minTan), __float_as_int(pitchScale),
 		                           osbn::x86_f2i(__fmul_rn(minTan, 65536.f)), osbn::x86_f2i(__fmul_rn(pitchScale, 65536.f)));
-		if (minPitch >= maxPitch)
-			return; // culled: strip stays cleared (:387-389)
+		uint32_t *maskOut = lineMask + (size_t)gl * words;
+		if (minPitch >= maxPitch) { // culled: the strip stays cleared (:387-389)
+			for (int w = 0; w < words; w++)
+				maskOut[w] = 0;
+			return;
+		}
 
 		// ---- DDA set-up (:309-351) ----
 		float dirX = hd.x, dirY = hd.y;
@@ -520,6 +535,8 @@ namespace osb {
 				count = 4;
 			}
 		}
+		for (int w = 0; w < words; w++)
+			maskOut[w] = filled[w * kLineThreads];
 	}
 
 	// ---- fastATan / fastATan2 (SWMapRenderer.cpp:697-742); tab = sm | lg | smN | lgN, 5000 each ----
@@ -592,8 +609,9 @@ namespace osb {
 	__global__ void __launch_bounds__(kGatherWarps * 32)
 	  k_gather_fog(const ViewParams *__restrict__ views, int nViews, FrameGeom g, const float *__restrict__ tabs,
 	               const uint64_t *__restrict__ solid, const uint16_t *__restrict__ atanTab, osbn::SseTables sse,
-	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams, int lineRes,
-	               uint32_t *__restrict__ fb, float *__restrict__ depthBuf) {
+	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams,
+	               const uint32_t *__restrict__ lineMask, int lineRes, uint32_t *__restrict__ fb,
+	               float *__restrict__ depthBuf) {
 		__shared__ float s_fog[kGatherWarps][kSegRows * 2][8];
 		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 		const int colBlocks = g.fw >> 3, rowBlocks = g.fh >> 3;
@@ -667,6 +685,8 @@ namespace osb {
 		const int yawMin2 = V.yawMin2;
 		const int lineShift = 31 - __clz(lineRes);
 		const uint2 *stripsV = strips + (size_t)V.lineBase * lineRes;
+		const uint32_t *maskV = lineMask + (size_t)V.lineBase * (lineRes >> 5); // written strip pixels, bit per pixel
+		const uint2 kClearPix = make_uint2(0u, __float_as_uint(10000.f));       // LinePixel::Clear
 		const int4 *lpV = lineParams + V.lineBase;
 		const int blkLane = lane & ~7;
 
@@ -725,7 +745,20 @@ namespace osb {
 						int pitchIndex = (pitC >> 13) - lp.z;
 						pitchIndex = __mulhi(pitchIndex, lp.w);
 						pitchIndex &= lineRes - 1;
+#if OSB_STRIP_CLEAR
 						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+#elif OSB_MASK_FIRST
+						const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
+						uint2 pix = kClearPix;
+						if ((mw >> (pitchIndex & 31)) & 1u)
+							pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+#else
+						uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+						{
+							const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
+							pix = ((mw >> (pitchIndex & 31)) & 1u) ? pix : kClearPix;
+						}
+#endif
 						const float dep = __uint_as_float(pix.y);
 						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
 						__stcs(dbV + o, dep);
@@ -752,7 +785,20 @@ namespace osb {
 						pitch = num.toSpecialTan(pitch);
 						pitch = __fmul_rn(__fsub_rn(pitch, __int_as_float(lp.x)), __int_as_float(lp.y));
 						const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
+#if OSB_STRIP_CLEAR
 						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+#elif OSB_MASK_FIRST
+						const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
+						uint2 pix = kClearPix;
+						if ((mw >> (pitchIndex & 31)) & 1u)
+							pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+#else
+						uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
+						{
+							const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
+							pix = ((mw >> (pitchIndex & 31)) & 1u) ? pix : kClearPix;
+						}
+#endif
 						const float dep = __uint_as_float(pix.y);
 						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
 						__stcs(dbV + o, dep);
@@ -850,6 +896,7 @@ namespace osb {
 			cudaFree(b.d_lineDirs);
 			cudaFree(b.d_lineParams);
 			cudaFree(b.d_strips);
+			cudaFree(b.d_lineMask);
 			cudaFree(b.d_tabs);
 			if (b.done)
 				cudaEventDestroy(b.done);
@@ -1078,7 +1125,8 @@ namespace osb {
 		for (int k = 0; k < (dual ? 2 : 1); k++) {
 			ChunkBufs &B = T->set[k];
 			if (grow(B.d_lineDirs, B.lineCap, maxLines) || grow(B.d_lineParams, B.lineParamCap, maxLines) ||
-			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
+			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) ||
+			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)(lineRes >> 5)) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
 				return -2;
 		}
 		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
@@ -1127,7 +1175,7 @@ namespace osb {
 				smem += sizeof(uint32_t) << c->rcpBits;
 #define LAUNCH_LINES(SSE, SH)                                                                      \
 	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, st>>>(                                 \
-	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, totalLines, lineRes)
+	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, B.d_lineMask, totalLines, lineRes)
 			if (!g.noMap) {
 				KLaunch kl(c, K_BUILD_LINES, st);
 				if (num == OSB200_NUM_IEEE)
@@ -1145,7 +1193,7 @@ namespace osb {
 			float *dbC = d_depth + (size_t)v0 * w * h;
 #define LAUNCH_GATHER(SSE, FOG)                                                                    \
 	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, st>>>(                                  \
-	  dV, nv, g, B.d_tabs, c->d_solid, T->d_atan, sse, B.d_strips, B.d_lineParams, lineRes, fbC, dbC)
+	  dV, nv, g, B.d_tabs, c->d_solid, T->d_atan, sse, B.d_strips, B.d_lineParams, B.d_lineMask, lineRes, fbC, dbC)
 			{
 				KLaunch kl(c, K_GATHER_FOG, st);
 				if (num == OSB200_NUM_IEEE)
