@@ -240,6 +240,9 @@ namespace osb {
 #ifndef OSB_STRIP_CLEAR
 #define OSB_STRIP_CLEAR 0
 #endif
+#ifndef OSB_PAIR_STORE
+#define OSB_PAIR_STORE 0
+#endif
 #ifndef OSB_MASK_FIRST
 #define OSB_MASK_FIRST 1 // gather: test the written-pixel mask before loading the strip pixel (1: 1.68 ms) or load both at once (0: 1.91 ms)
 #endif
@@ -515,6 +518,22 @@ namespace osb {
 							havePx = true;
 						}
 						uint2 *dst = strip + (w << 5);
+#if OSB_PAIR_STORE
+						// two adjacent strip pixels (even-aligned) go out as one 16-byte store
+						uint32_t pairs = todo & (todo >> 1) & 0x55555555u;
+						todo &= ~(pairs | (pairs << 1));
+						const uint4 px2 = make_uint4(px.x, px.y, px.x, px.y);
+						while (pairs) {
+							const int b = __ffs(pairs) - 1;
+							pairs &= pairs - 1;
+							__stcs(reinterpret_cast<uint4 *>(dst + b), px2);
+						}
+						while (todo) {
+							const int b = __ffs(todo) - 1;
+							todo &= todo - 1;
+							__stcs(dst + b, px);
+						}
+#else
 						do {
 							const int b = __ffs(todo) - 1;
 							todo &= todo - 1;
@@ -523,6 +542,7 @@ namespace osb {
 #endif
 							__stcs(dst + b, px);
 						} while (todo);
+#endif
 					}
 				}
 			}
