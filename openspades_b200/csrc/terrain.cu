@@ -626,7 +626,10 @@ namespace osb {
 	// Per block row the 16 block corners (4 blocks x 4) are evaluated by 16 lanes in one instruction stream
 	// and shared by shuffle; per pixel only the reference's integer interpolation, the gather and the blend remain.
 	template <bool kSse, bool kSse2Fog>
-	__global__ void __launch_bounds__(kGatherWarps * 32)
+#ifndef OSB_GATHER_MINB
+#define OSB_GATHER_MINB 1
+#endif
+	__global__ void __launch_bounds__(kGatherWarps * 32, OSB_GATHER_MINB)
 	  k_gather_fog(const ViewParams *__restrict__ views, int nViews, FrameGeom g, const float *__restrict__ tabs,
 	               const uint64_t *__restrict__ solid, const uint16_t *__restrict__ atanTab, osbn::SseTables sse,
 	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams,
