@@ -21,6 +21,7 @@
 #include "numerics.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace osb {
@@ -114,6 +115,17 @@ namespace osb {
 	// Per-chunk working set.  Two of them, each with its own stream: chunk k+1's line build runs beside chunk k's
 	// gather and fills the SMs that chunk k's launch tail leaves idle (a single yaw line is ~150 dependent DDA steps,
 	// so every k_build_lines launch ends in a long low-occupancy tail).
+	// lower bound of lanes per warp for small k_build_lines launches (OSB200_LINE_MIN_LANES, default 4; 32 = off).
+	// One 1080p frame (3.8 k lines): 32 / 16 / 8 / 4 / 2 lanes -> 0.338 / 0.285 / 0.240 / 0.207 / 0.203 ms
+	static int line_min_lanes() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_LINE_MIN_LANES");
+			const int n = e ? atoi(e) : 4;
+			return n >= 32 ? 32 : (n >= 16 ? 16 : (n >= 8 ? 8 : (n >= 4 ? 4 : (n >= 2 ? 2 : 1))));
+		}();
+		return v;
+	}
+
 	struct ChunkBufs {
 		float2 *d_lineDirs = nullptr;
 		int4 *d_lineParams = nullptr;
@@ -250,17 +262,19 @@ namespace osb {
 	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
 	                const uint64_t *__restrict__ solid, const uint32_t *__restrict__ color,
 	                osbn::SseTables tabs, uint2 *__restrict__ strips, int4 *__restrict__ lineParams,
-	                uint32_t *__restrict__ lineMask, uint32_t totalLines, int lineRes) {
+	                uint32_t *__restrict__ lineMask, uint32_t totalLines, int lineRes, int lanesPerWarp) {
 		extern __shared__ uint32_t s_filled[]; // (lineRes/32) words x kLineThreads
-		const uint32_t lineBase = blockIdx.x * kLineThreads;
-		const uint32_t gl = lineBase + threadIdx.x;
+		// lanesPerWarp < 32 (small launches, e.g. one 1080p frame = a few thousand lines): the lines are spread over
+		// more warps and SMs, and a warp's instruction stream is the union of fewer lanes' paths
+		const uint32_t gl = (blockIdx.x * (kLineThreads / 32) + (threadIdx.x >> 5)) * (uint32_t)lanesPerWarp + (threadIdx.x & 31);
 		const int words = lineRes >> 5;
 
 		// LinePixel::Clear = {0, 10000.f} (:89-92).  The strips are NOT cleared in memory: a line publishes the bitmask
 		// of the strip pixels it wrote (lineMask, lineRes bits per line) and the gather substitutes the clear value
 		// for the others -- the clear was 3/4 of this kernel's DRAM writes.  OSB_STRIP_CLEAR=1 restores the clear.
 		{
-#if OSB_STRIP_CLEAR
+#if OSB_STRIP_CLEAR // (needs lanesPerWarp == 32)
+			const uint32_t lineBase = blockIdx.x * kLineThreads;
 			const uint32_t nl = min((uint32_t)kLineThreads, totalLines - lineBase);
 			uint4 *dst = reinterpret_cast<uint4 *>(strips + (size_t)lineBase * lineRes);
 			const uint32_t n4 = nl * (uint32_t)lineRes / 2;
@@ -282,7 +296,7 @@ namespace osb {
 		}
 #endif
 		__syncthreads();
-		if (gl >= totalLines)
+		if ((int)(threadIdx.x & 31) >= lanesPerWarp || gl >= totalLines)
 			return;
 
 		// which view does this line belong to (views are few per chunk: binary search on lineBase)
@@ -1192,13 +1206,19 @@ namespace osb {
 				KLaunch kl(c, K_VIEW_PREP, st);
 				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
-			const unsigned lineBlocks = (totalLines + kLineThreads - 1) / kLineThreads;
+			// small launches use fewer lanes per warp (a line is one long dependent chain: what counts is how many
+			// warps run side by side and how little each warp diverges)
+			int lpw = 32;
+			while (lpw > line_min_lanes() && (size_t)totalLines / lpw < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
+				lpw >>= 1;
+			const unsigned linesPerCta = kLineThreads / 32 * lpw;
+			const unsigned lineBlocks = (totalLines + linesPerCta - 1) / linesPerCta;
 			size_t smem = (size_t)(lineRes >> 5) * kLineThreads * sizeof(uint32_t);
 			if (OSB_RCP_SMEM && num != OSB200_NUM_IEEE && c->rcpBits <= kRcpSmemBits)
 				smem += sizeof(uint32_t) << c->rcpBits;
 #define LAUNCH_LINES(SSE, SH)                                                                      \
 	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, st>>>(                                 \
-	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, B.d_lineMask, totalLines, lineRes)
+	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, B.d_lineMask, totalLines, lineRes, lpw)
 			if (!g.noMap) {
 				KLaunch kl(c, K_BUILD_LINES, st);
 				if (num == OSB200_NUM_IEEE)
