@@ -193,6 +193,10 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # stdout carries the one JSON line: NCCL's "NCCL version ..." banner (printed to stdout at NCCL_DEBUG=VERSION)
+        # goes to a file next to the other per-run logs unless the caller asked for INFO / TRACE output
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     import openspades_b200 as osb
