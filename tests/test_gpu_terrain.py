@@ -3,6 +3,8 @@ restatement (oracle/liboracle.so) and, where it travelled, the unmodified refere
 
 Bar (BASELINE.json north_star): >= 95 % of pixels bit-identical, the rest within +-1 LSB per channel;
 depth ordering bit-exact.  The kernels are written to be bit-identical, so the tests assert 100 %."""
+import os
+
 import numpy as np
 import pytest
 
@@ -115,3 +117,34 @@ def test_eye_inside_solid_and_bad_size(title_map):
         assert np.all((fb & 0xFFFFFF) == 0x7F7F7F) and np.all(dp == 0)
         with pytest.raises(osb.OsbError, match="multiple of 8"):
             ctx.render(sc, 100, 60, FOG, 128.0)
+
+
+def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
+    """k_build_lines deals 4..32 lines to a warp depending on the launch size (OSB200_LINE_MIN_LANES, read once per process):
+    the same views rendered in fresh processes with full warps and with the default give identical frames + depth."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "import openspades_b200 as osb\n"
+        "from openspades_b200 import workloads\n"
+        "from openspades_b200.hostlib import VoxelMap\n"
+        "m = VoxelMap.load_file(workloads.TITLE_VXL)\n"
+        "with osb.Context(0, osb.NUM_SSE2, sw_threads=4) as ctx:\n"
+        "    ctx.map_upload(m.solid.copy(), m.color.copy())\n"
+        "    S = workloads.random_scenes(3, m.solid, 320, 200, seed=9)\n"
+        "    fb, dp = ctx.render(S, 320, 200, (0.8, 1.0, 1.0), 128.0)\n"
+        "    sc = workloads.title_scene(1920, 1080, 68.0)\n"
+        "    fb2, dp2 = ctx.render(sc, 1920, 1080, (0.1, 0.1, 0.1), 128.0)\n"
+        "np.savez(sys.argv[1], fb=fb, dp=dp, fb2=fb2, dp2=dp2)\n")
+    outs = []
+    for lanes in ("32", "4", "1"):
+        out = str(tmp_path / f"lanes{lanes}.npz")
+        env = dict(os.environ, OSB200_LINE_MIN_LANES=lanes)
+        subprocess.run([sys.executable, "-c", code, out], check=True, env=env, timeout=300)
+        outs.append(np.load(out))
+    for other in outs[1:]:
+        for k in ("fb", "dp", "fb2", "dp2"):
+            assert np.array_equal(outs[0][k].view(np.uint32), other[k].view(np.uint32)), k
