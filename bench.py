@@ -177,7 +177,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     return 0
 
 
@@ -193,10 +193,6 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # stdout carries the one JSON line: NCCL's "NCCL version ..." banner (printed to stdout at NCCL_DEBUG=VERSION)
-        # goes to a file next to the other per-run logs unless the caller asked for INFO / TRACE output
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() in ("VERSION", "WARN"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     import openspades_b200 as osb
@@ -333,7 +329,7 @@ def run_b200(args):
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "extra": extra, "result_checksum": checksum,
         }
-        print(json.dumps(line), flush=True)
+        emit_json(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -633,8 +629,30 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
     return out
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly one JSON line.  Libraries that write to file descriptor 1 on their own (NCCL prints its
+    "NCCL version ..." banner there under torchrun) are pointed at stderr; the JSON line goes to the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     args = parse_args()
+    claim_stdout()
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)
