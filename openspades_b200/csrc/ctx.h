@@ -43,7 +43,7 @@ namespace osb {
 		K_RAD_SELECT,
 		K_CASTRAY,
 		K_AMBIENT,
-		K_FOG,
+		K_SCENE_FINISH,
 		K_MODEL_SETUP,
 		K_MODEL_SPLAT,
 		K_MODEL_RESOLVE,
@@ -71,7 +71,26 @@ namespace osb {
 	int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
 	                float fogDist, uint32_t *d_fb, float *d_depth, uint32_t *host_fb, float *host_depth, bool deferFog);
 	int terrain_out_buffers(osb200_ctx *c, size_t n, uint32_t **fb, float **depth);
-	int terrain_apply_fog(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, const float *d_depth);
+
+	// one kept dynamic light of a scene (models.cu fills it: AddLight's culls and rectangle, SWRenderer.cpp:578-649)
+	struct LightDev {
+		int minX, minY, maxX, maxY;
+		float center[3]; // light origin in view space
+		int r, g, b;     // ToFixedFactor8
+		float invRadius2;
+		uint32_t tabBase; // vx[fw] then vy[fh] of this light inside the light table buffer
+	};
+	// The tail of EndScene for a frame with models and / or lights in ONE pass over the frame (terrain.cu): winner of
+	// the splat keys (keys may be null), the lights in submission order (nLights may be 0), then the fog.
+	int terrain_finish_scene(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, float *d_depth,
+	                         const unsigned long long *d_keys, const uint32_t *d_splatColor, const LightDev *d_lights,
+	                         int nLights, const float *d_lightTabs);
+	// order-preserving map float -> uint32 (and back), so that one unsigned atomicMin implements `zval < *db`
+	__device__ __forceinline__ uint32_t depth_key(float f) {
+		const uint32_t u = __float_as_uint(f);
+		return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+	}
+	__device__ __forceinline__ float key_depth(uint32_t k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); }
 
 	// RAII bracket around one kernel launch: counts it and, when timing is on, records CUDA events
 	// on the context stream before and after it.

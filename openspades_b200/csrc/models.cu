@@ -1,10 +1,11 @@
 // Voxel models and dynamic lights of the software renderer's EndScene, between the terrain pass and the fog
 // (SWRenderer::EndScene, Sources/Draw/SWRenderer.cpp:709-745):
 //   SWModel::SWModel                  Sources/Draw/SWModel.cpp:25-100         (build_render_data, host, once per model)
-//   SWModelRenderer::RenderInner      Sources/Draw/SWModelRenderer.cpp:46-277 (k_model_setup, k_model_splat, k_model_resolve)
+//   SWModelRenderer::RenderInner      Sources/Draw/SWModelRenderer.cpp:46-277 (k_model_setup, k_model_splat; winners resolved in
+//                                                                              terrain.cu k_scene_finish)
 //   SWRenderer::StartScene matrices   Sources/Client/SceneDefinition.cpp:26-72, Sources/Core/Math.cpp:108-181 (host)
 //   SWRenderer::AddLight              Sources/Draw/SWRenderer.cpp:578-649     (host: culls + screen rectangle)
-//   SWRenderer::ApplyDynamicLight     Sources/Draw/SWRenderer.cpp:229-339     (k_light_prep, k_lights)
+//   SWRenderer::ApplyDynamicLight     Sources/Draw/SWRenderer.cpp:229-339     (k_light_prep here, the per-pixel part in k_scene_finish)
 //
 // Design: the reference splats every surface voxel as a screen-aligned square with a strict depth test, models in
 // submission order, voxels in x / y / z order -- i.e. per pixel the winner is the smallest depth and, among equal
@@ -111,14 +112,6 @@ namespace osb {
 		float frustum[6][4]; // n.xyz, w
 		float zNear;
 		int fw, fh;
-	};
-
-	struct LightDev {
-		int minX, minY, maxX, maxY;
-		float center[3]; // light origin in view space
-		int r, g, b;     // ToFixedFactor8
-		float invRadius2;
-		uint32_t tabBase; // vx[fw] then vy[fh] of this light inside the light table buffer
 	};
 
 	struct ModelState {
@@ -242,13 +235,6 @@ namespace osb {
 		R.pointDiameter = __fsqrt_rn(largest);
 		out[i] = R;
 	}
-
-	// order-preserving map float -> uint32 (and back), so that one unsigned atomicMin implements `zval < *db`
-	__device__ __forceinline__ uint32_t depth_key(float f) {
-		const uint32_t u = __float_as_uint(f);
-		return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-	}
-	__device__ __forceinline__ float key_depth(uint32_t k) { return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); }
 
 	__global__ void k_key_init(const float *__restrict__ depth, unsigned long long *__restrict__ keys, size_t n) {
 		const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -390,19 +376,6 @@ namespace osb {
 		}
 	}
 
-	__global__ void k_model_resolve(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ splatColor,
-	                                uint32_t *__restrict__ fb, float *__restrict__ depth, size_t n) {
-		const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-		if (i >= n)
-			return;
-		const unsigned long long k = keys[i];
-		const uint32_t seq = (uint32_t)k;
-		if (seq) {
-			fb[i] = splatColor[seq];
-			depth[i] = key_depth((uint32_t)(k >> 32));
-		}
-	}
-
 	// The float recurrences of ApplyDynamicLight (:266-272,327-333): vx restarts at the light's minX and grows by dvx per
 	// pixel; vy restarts at the first row of every emulated worker thread's band and grows by dvy per row.
 	__global__ void k_light_prep(const LightDev *__restrict__ lights, int nLights, int fw, int fh, int swThreads, float fovX,
@@ -429,45 +402,6 @@ namespace osb {
 				vy = __fadd_rn(vy, dvy);
 			}
 		}
-	}
-
-	// ApplyDynamicLight (:283-325) for every light, in submission order, one thread per pixel.
-	__global__ void __launch_bounds__(256)
-	  k_lights(const LightDev *__restrict__ lights, int nLights, int fw, int fh, const float *__restrict__ tabs,
-	           uint32_t *__restrict__ fb, const float *__restrict__ depth) {
-		const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-		if (x >= fw || y >= fh)
-			return;
-		const size_t o = (size_t)y * fw + x;
-		uint32_t color = fb[o];
-		const float z = depth[o];
-		bool touched = false;
-		for (int li = 0; li < nLights; li++) {
-			const LightDev &L = lights[li];
-			if (x < L.minX || x >= L.maxX || y < L.minY || y >= L.maxY)
-				continue;
-			const float *vxT = tabs + L.tabBase, *vyT = vxT + fw;
-			const float px = __fsub_rn(__fmul_rn(vxT[x], z), L.center[0]);
-			const float py = __fsub_rn(__fmul_rn(vyT[y], z), L.center[1]);
-			const float pz = __fsub_rn(z, L.center[2]);
-			float dist = __fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), __fmul_rn(pz, pz));
-			dist = __fmul_rn(dist, L.invRadius2);
-			if (dist < 1.f) {
-				float strength = __fsub_rn(1.f, dist);
-				strength = __fmul_rn(strength, strength);
-				strength = __fmul_rn(strength, 256.f);
-				const int factor = osbn::x86_f2i(strength);
-				const uint32_t sr = (color >> 16) & 0xff, sg = (color >> 8) & 0xff, sb = color & 0xff;
-				const int ar = (int)((uint32_t)(L.r * factor) * sr), ag = (int)((uint32_t)(L.g * factor) * sg),
-				          ab = (int)((uint32_t)(L.b * factor) * sb);
-				const uint32_t dr = min((uint32_t)(ar >> 16) + sr, 255u), dg = min((uint32_t)(ag >> 16) + sg, 255u),
-				               db = min((uint32_t)(ab >> 16) + sb, 255u);
-				color = db | (dg << 8) | (dr << 16);
-				touched = true;
-			}
-		}
-		if (touched)
-			fb[o] = color;
 	}
 
 	template <class T> static int grow_buf(T *&p, size_t &cap, size_t want, bool pinned = false) {
@@ -867,11 +801,7 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 				k_model_splat<false><<<(cols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
 				                                                                M->d_keys, M->d_splatColor, sse);
 		}
-		{
-			KLaunch kl(c, K_MODEL_RESOLVE);
-			k_model_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(M->d_keys, M->d_splatColor, d_fb, d_depth, npix);
-		}
-		c->launches++; // k_key_init rides in the splat bracket
+		c->launches++; // k_key_init rides in the splat bracket; the winners are resolved by the finishing pass below
 	}
 	if (!kept.empty()) {
 		const size_t nl = kept.size();
@@ -888,13 +818,12 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 		KLaunch kl(c, K_LIGHTS);
 		k_light_prep<<<(unsigned)nl, 32, 0, c->stream>>>(M->d_lights, (int)nl, w, h, c->opts.sw_threads, fovX, fovY, dvx, dvy,
 		                                              M->d_lightTabs);
-		k_lights<<<dim3((w + 31) / 32, (h + 7) / 8), 256, 0, c->stream>>>(M->d_lights, (int)nl, w, h, M->d_lightTabs, d_fb,
-		                                                                   d_depth);
-		c->launches++;
 	}
 	OSB_CUDA(cudaEventRecord(M->stageFree, c->stream));
+	// splat winners -> lights in submission order -> fog, one pass over the frame (k_scene_finish, terrain.cu)
 	if (extras)
-		if (int rc = terrain_apply_fog(c, w, h, fogColor, d_fb, d_depth))
+		if (int rc = terrain_finish_scene(c, w, h, fogColor, d_fb, d_depth, nInst > 0 ? M->d_keys : nullptr, M->d_splatColor,
+		                                  M->d_lights, (int)kept.size(), M->d_lightTabs))
 			return rc;
 	OSB_CUDA(cudaGetLastError());
 	if (host_bgrx)

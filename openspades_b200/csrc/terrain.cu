@@ -53,7 +53,7 @@ namespace osb {
 
 	struct FrameGeom {
 		int fw, fh, under, swThreads, sse2Fog, sse2Shade;
-		int noFog; // fog deferred to k_fog (models / dynamic lights are drawn between terrain and fog, SWRenderer.cpp:727-744)
+		int noFog; // fog deferred to k_scene_finish (models / dynamic lights are drawn between terrain and fog, SWRenderer.cpp:727-744)
 		int noMap; // no map set: SWRenderer::EndScene still clears and fogs over the stale depth (SWRenderer.cpp:713-744)
 		uint32_t fogB, fogG, fogR;
 	};
@@ -850,26 +850,6 @@ namespace osb {
 		}
 	}
 
-	// SWRenderer::ApplyFog as a pass of its own (SWRenderer.cpp:341-516), for frames that draw models / dynamic lights
-	// between terrain and fog.  Same per-4x4-block scale and blend as the fused path in k_gather_fog.
-	template <bool kSse, bool kSse2Fog>
-	__global__ void __launch_bounds__(256)
-	  k_fog(const ViewParams *__restrict__ views, FrameGeom g, const float *__restrict__ tabs, osbn::SseTables sse,
-	        uint32_t *__restrict__ fb, const float *__restrict__ depthBuf) {
-		const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-		if (x >= g.fw || y >= g.fh)
-			return;
-		const ViewParams &V = views[blockIdx.z];
-		osbn::Num<kSse> num{sse};
-		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2);
-		const float vx = vxTab[x >> 2], vy = vyTab[y >> 2];
-		float ds = __fadd_rn(__fadd_rn(1.f, __fmul_rn(vx, vx)), __fmul_rn(vy, vy));
-		ds = __fmul_rn(ds, __fmul_rn(num.rsqrt(ds), V.fogScale));
-		const size_t o = (size_t)blockIdx.z * g.fw * g.fh + (size_t)y * g.fw + x;
-		const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
-		fb[o] = fog_blend<kSse2Fog>(fb[o], __fmul_rn(depthBuf[o], ds), fogBR, fogG8);
-	}
-
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
 	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs,
 	                            float *tabs) {
@@ -1291,7 +1271,74 @@ namespace osb {
 	}
 
 	// ApplyFog over the single view last set up by render_impl(.., deferFog = true) on the context stream
-	int terrain_apply_fog(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, const float *d_depth) {
+	// The tail of SWRenderer::EndScene for a frame that drew models and / or dynamic lights, in one pass over the frame:
+	//   winner of the splat keys (SWModelRenderer's depth-tested writes, models.cu)      keys == null: nothing was splatted
+	//   ApplyDynamicLight (SWRenderer.cpp:283-325) for every kept light in submission order, float recurrences from
+	//   the tables of k_light_prep                                                       nLights == 0: no lights
+	//   ApplyFog (SWRenderer.cpp:341-516), same per-4x4-block scale and blend as k_gather_fog
+	template <bool kSse, bool kSse2Fog>
+	__global__ void __launch_bounds__(256)
+	  k_scene_finish(const ViewParams *__restrict__ views, FrameGeom g, const float *__restrict__ tabs, osbn::SseTables sse,
+	                 uint32_t *__restrict__ fb, float *__restrict__ depthBuf, const unsigned long long *__restrict__ keys,
+	                 const uint32_t *__restrict__ splatColor, const LightDev *__restrict__ lights, int nLights,
+	                 const float *__restrict__ lightTabs) {
+		const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+		if (x >= g.fw || y >= g.fh)
+			return;
+		const size_t o = (size_t)y * g.fw + x;
+		uint32_t color;
+		float z;
+		bool splat = false;
+		if (keys) {
+			const unsigned long long k = keys[o];
+			const uint32_t seq = (uint32_t)k;
+			if (seq) {
+				color = splatColor[seq];
+				z = key_depth((uint32_t)(k >> 32));
+				depthBuf[o] = z;
+				splat = true;
+			}
+		}
+		if (!splat) {
+			color = fb[o];
+			z = depthBuf[o];
+		}
+		for (int li = 0; li < nLights; li++) {
+			const LightDev &L = lights[li];
+			if (x < L.minX || x >= L.maxX || y < L.minY || y >= L.maxY)
+				continue;
+			const float *vxT = lightTabs + L.tabBase, *vyT = vxT + g.fw;
+			const float px = __fsub_rn(__fmul_rn(vxT[x], z), L.center[0]);
+			const float py = __fsub_rn(__fmul_rn(vyT[y], z), L.center[1]);
+			const float pz = __fsub_rn(z, L.center[2]);
+			float dist = __fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), __fmul_rn(pz, pz));
+			dist = __fmul_rn(dist, L.invRadius2);
+			if (dist < 1.f) {
+				float strength = __fsub_rn(1.f, dist);
+				strength = __fmul_rn(strength, strength);
+				strength = __fmul_rn(strength, 256.f);
+				const int factor = osbn::x86_f2i(strength);
+				const uint32_t sr = (color >> 16) & 0xff, sg = (color >> 8) & 0xff, sb = color & 0xff;
+				const int ar = (int)((uint32_t)(L.r * factor) * sr), ag = (int)((uint32_t)(L.g * factor) * sg),
+				          ab = (int)((uint32_t)(L.b * factor) * sb);
+				const uint32_t dr = min((uint32_t)(ar >> 16) + sr, 255u), dg = min((uint32_t)(ag >> 16) + sg, 255u),
+				               db = min((uint32_t)(ab >> 16) + sb, 255u);
+				color = db | (dg << 8) | (dr << 16);
+			}
+		}
+		const ViewParams &V = views[0];
+		osbn::Num<kSse> num{sse};
+		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2);
+		const float vx = vxTab[x >> 2], vy = vyTab[y >> 2];
+		float ds = __fadd_rn(__fadd_rn(1.f, __fmul_rn(vx, vx)), __fmul_rn(vy, vy));
+		ds = __fmul_rn(ds, __fmul_rn(num.rsqrt(ds), V.fogScale));
+		const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
+		fb[o] = fog_blend<kSse2Fog>(color, __fmul_rn(z, ds), fogBR, fogG8);
+	}
+
+	int terrain_finish_scene(osb200_ctx *c, int w, int h, const float fogColor[3], uint32_t *d_fb, float *d_depth,
+	                         const unsigned long long *d_keys, const uint32_t *d_splatColor, const LightDev *d_lights,
+	                         int nLights, const float *d_lightTabs) {
 		TerrainState *T = c->terrain;
 		FrameGeom g;
 		std::memset(&g, 0, sizeof(g));
@@ -1309,16 +1356,21 @@ namespace osb {
 		g.fogB = toFixed8(fogColor[2]);
 		osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
 		const dim3 grid((w + 31) / 32, (h + 7) / 8, 1);
-		KLaunch kl(c, K_FOG);
+		KLaunch kl(c, K_SCENE_FINISH);
+#define LAUNCH_FINISH(SSE, FOG)                                                                                        \
+	k_scene_finish<SSE, FOG><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth, d_keys,   \
+	                                                      d_splatColor, d_lights, nLights, d_lightTabs)
 		if (c->opts.numerics == OSB200_NUM_IEEE)
-			k_fog<false, false><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+			LAUNCH_FINISH(false, false);
 		else if (c->opts.numerics == OSB200_NUM_SSE)
-			k_fog<true, false><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+			LAUNCH_FINISH(true, false);
 		else
-			k_fog<true, true><<<grid, 256, 0, c->stream>>>(T->d_views, g, T->set[0].d_tabs, sse, d_fb, d_depth);
+			LAUNCH_FINISH(true, true);
+#undef LAUNCH_FINISH
 		OSB_CUDA(cudaGetLastError());
 		return 0;
 	}
+
 } // namespace osb
 
 extern "C" {

@@ -8,6 +8,6 @@ cat gpurun_out/game_frame_plain.log
 python tools/game_frame_run.py 512 32 4 > gpurun_out/game_frame_plain512.log 2>&1; cat gpurun_out/game_frame_plain512.log
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/r01_launches_game_frame.csv \
   python tools/game_frame_run.py 64 8 2 > gpurun_out/ncu_gf_list.log 2>&1; echo "list rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:'k_model|k_key_init|k_light|k_fog' -s 7 -c 7 \
+ncu --set full --clock-control none --import-source on -k regex:'k_model|k_key_init|k_light|k_scene_finish' -s 7 -c 7 \
   -o gpurun_out/prof_r01_game_frame python tools/game_frame_run.py 64 8 2 > gpurun_out/ncu_gf_full.log 2>&1; echo "full rc=$?"
 tail -2 gpurun_out/ncu_gf_full.log
