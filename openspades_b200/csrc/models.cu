@@ -128,6 +128,8 @@ namespace osb {
 		float *d_lightTabs = nullptr;
 		size_t lightTabCap = 0;
 		cudaEvent_t stageFree = nullptr;
+		cudaStream_t aux = nullptr;   // per-instance set-up and light tables run beside the terrain kernels
+		cudaEvent_t auxDone = nullptr;
 	};
 
 	// ---- small float helpers in the reference's operation order (Core/Math.h, Core/Math.cpp:162-181) ----
@@ -432,6 +434,8 @@ namespace osb {
 		OSB_CUDA(cudaMalloc(&M->d_mats, sizeof(SceneMats)));
 		OSB_CUDA(cudaMallocHost(&M->h_mats, sizeof(SceneMats)));
 		OSB_CUDA(cudaEventCreateWithFlags(&M->stageFree, cudaEventDisableTiming));
+		OSB_CUDA(cudaStreamCreateWithFlags(&M->aux, cudaStreamNonBlocking));
+		OSB_CUDA(cudaEventCreateWithFlags(&M->auxDone, cudaEventDisableTiming));
 		return 0;
 	}
 
@@ -451,6 +455,10 @@ namespace osb {
 		cudaFree(M->d_lightTabs);
 		if (M->stageFree)
 			cudaEventDestroy(M->stageFree);
+		if (M->auxDone)
+			cudaEventDestroy(M->auxDone);
+		if (M->aux)
+			cudaStreamDestroy(M->aux);
 		delete M;
 		c->models = nullptr;
 	}
@@ -713,6 +721,10 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 	osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
 	const bool kSseMode = c->opts.numerics != OSB200_NUM_IEEE;
 	OSB_CUDA(cudaEventSynchronize(M->stageFree)); // pinned staging of the previous call
+	// The terrain kernels are already queued on the context stream; the per-instance set-up and the light tables do not
+	// depend on them and go to a second stream (with per-kernel timing on, everything stays on the context stream).
+	cudaStream_t aux = c->timing ? c->stream : M->aux;
+	uint32_t totalCols = 0;
 	if (nInst > 0) {
 		if (grow_buf(M->h_inst, M->instCap, (size_t)nInst, true))
 			return -2;
@@ -782,26 +794,16 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 		fill_scene_mats(*scene, w, h, *M->h_mats);
 		if (grow_buf(M->d_keys, M->keyCap, npix) || grow_buf(M->d_splatColor, M->splatCap, (size_t)seq))
 			return -2;
-		OSB_CUDA(cudaMemcpyAsync(M->d_mats, M->h_mats, sizeof(SceneMats), cudaMemcpyHostToDevice, c->stream));
-		OSB_CUDA(cudaMemcpyAsync(M->d_inst, M->h_inst, sizeof(InstanceIn) * nInst, cudaMemcpyHostToDevice, c->stream));
+		OSB_CUDA(cudaMemcpyAsync(M->d_mats, M->h_mats, sizeof(SceneMats), cudaMemcpyHostToDevice, aux));
+		OSB_CUDA(cudaMemcpyAsync(M->d_inst, M->h_inst, sizeof(InstanceIn) * nInst, cudaMemcpyHostToDevice, aux));
 		{
-			KLaunch kl(c, K_MODEL_SETUP);
+			KLaunch kl(c, K_MODEL_SETUP, aux);
 			if (kSseMode)
-				k_model_setup<true><<<(nInst + 63) / 64, 64, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, sse);
+				k_model_setup<true><<<(nInst + 63) / 64, 64, 0, aux>>>(M->d_mats, M->d_inst, M->d_setup, nInst, sse);
 			else
-				k_model_setup<false><<<(nInst + 63) / 64, 64, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, sse);
+				k_model_setup<false><<<(nInst + 63) / 64, 64, 0, aux>>>(M->d_mats, M->d_inst, M->d_setup, nInst, sse);
 		}
-		{
-			KLaunch kl(c, K_MODEL_SPLAT);
-			k_key_init<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(d_depth, M->d_keys, npix);
-			if (kSseMode)
-				k_model_splat<true><<<(cols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
-				                                                               M->d_keys, M->d_splatColor, sse);
-			else
-				k_model_splat<false><<<(cols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, cols,
-				                                                                M->d_keys, M->d_splatColor, sse);
-		}
-		c->launches++; // k_key_init rides in the splat bracket; the winners are resolved by the finishing pass below
+		totalCols = cols;
 	}
 	if (!kept.empty()) {
 		const size_t nl = kept.size();
@@ -812,12 +814,27 @@ int osb200_render_scene(osb200_ctx *c, const osb200_scene *scene, int w, int h, 
 		if (grow_buf(M->d_lightTabs, M->lightTabCap, nl * (size_t)(w + h)))
 			return -2;
 		std::memcpy(M->h_lights, kept.data(), nl * sizeof(LightDev));
-		OSB_CUDA(cudaMemcpyAsync(M->d_lights, M->h_lights, nl * sizeof(LightDev), cudaMemcpyHostToDevice, c->stream));
+		OSB_CUDA(cudaMemcpyAsync(M->d_lights, M->h_lights, nl * sizeof(LightDev), cudaMemcpyHostToDevice, aux));
 		const float fovX = tanf(scene->fovX * 0.5f), fovY = tanf(scene->fovY * 0.5f);
 		const float dvx = -fovX * 2.f / static_cast<float>(w), dvy = -fovY * 2.f / static_cast<float>(h);
-		KLaunch kl(c, K_LIGHTS);
-		k_light_prep<<<(unsigned)nl, 32, 0, c->stream>>>(M->d_lights, (int)nl, w, h, c->opts.sw_threads, fovX, fovY, dvx, dvy,
-		                                              M->d_lightTabs);
+		KLaunch kl(c, K_LIGHTS, aux);
+		k_light_prep<<<(unsigned)nl, 32, 0, aux>>>(M->d_lights, (int)nl, w, h, c->opts.sw_threads, fovX, fovY, dvx, dvy,
+		                                        M->d_lightTabs);
+	}
+	if (aux != c->stream) { // join: what follows reads the set-up records / light tables and the terrain's depth
+		OSB_CUDA(cudaEventRecord(M->auxDone, aux));
+		OSB_CUDA(cudaStreamWaitEvent(c->stream, M->auxDone, 0));
+	}
+	if (nInst > 0) {
+		KLaunch kl(c, K_MODEL_SPLAT);
+		k_key_init<<<(unsigned)((npix + 255) / 256), 256, 0, c->stream>>>(d_depth, M->d_keys, npix);
+		if (kSseMode)
+			k_model_splat<true><<<(totalCols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, totalCols,
+			                                                                    M->d_keys, M->d_splatColor, sse);
+		else
+			k_model_splat<false><<<(totalCols + 3) / 4, 128, 0, c->stream>>>(M->d_mats, M->d_inst, M->d_setup, nInst, totalCols,
+			                                                                     M->d_keys, M->d_splatColor, sse);
+		c->launches++; // k_key_init rides in the splat bracket; the winners are resolved by the finishing pass below
 	}
 	OSB_CUDA(cudaEventRecord(M->stageFree, c->stream));
 	// splat winners -> lights in submission order -> fog, one pass over the frame (k_scene_finish, terrain.cu)
