@@ -610,6 +610,20 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
             lk.minimap()
         minimap_ms = (time.perf_counter() - t0) * 1e3 / 20
         mm_k = lk.timing_read()["k_minimap"][1] / 20
+        # World::ClusterizeBlocks: the solid voxels of Title.vxl above z = 48 as one cell set (hills, buildings, bridges)
+        cl_x, cl_y = np.nonzero(ls & np.uint64((1 << 48) - 1))
+        cl_cells = []
+        for z in range(48):
+            sel = ((ls[cl_x, cl_y] >> np.uint64(z)) & np.uint64(1)).astype(bool)
+            cl_cells.append(np.stack([cl_x[sel], cl_y[sel], np.full(int(sel.sum()), z)], 1))
+        cl_cells = np.ascontiguousarray(np.concatenate(cl_cells).astype(np.int16))
+        lk.clusterize_blocks(cl_cells)
+        lk.timing_read()
+        t0 = time.perf_counter()
+        for _ in range(5):
+            cl_k, _lab = lk.clusterize_blocks(cl_cells)
+        cluster_ms = (time.perf_counter() - t0) * 1e3 / 5
+        cluster_k_ms = lk.timing_read()["k_cluster_union"][1] / 5
     out["links"] = {"workload": "GameMapWrapper on Title.vxl: Rebuild (flood from the ground over 16.8 M voxels as 64-bit column "
                                 f"masks), then {n_calls} RemoveBlocks calls x {per_call} undercut voxels each (host edit + flush + flood + "
                                 "result read-back inside the wall time); minimap = SWFlatMapRenderer image of the whole map",
@@ -617,7 +631,12 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                     "removed_voxels_per_s": n_calls * per_call / (remove_ms * n_calls * 1e-3), "blocks_fell": fell,
                     "flood_kernel_ms_per_call": lkt["k_links_flood"][1] / n_calls,
                     "flood_launches_per_call": lkt["k_links_flood"][0] / n_calls,
-                    "minimap_ms": minimap_ms, "minimap_kernel_ms": mm_k}
+                    "minimap_ms": minimap_ms, "minimap_kernel_ms": mm_k,
+                    "clusterize": {"workload": "World::ClusterizeBlocks of every solid voxel of Title.vxl above z = 48 in one call "
+                                               "(host key sort + H2D + union-find kernel + labels D2H inside the wall time)",
+                                   "cells": int(len(cl_cells)), "pieces": int(cl_k), "wall_ms": cluster_ms,
+                                   "union_kernel_ms": cluster_k_ms,
+                                   "mcells_s_kernel": len(cl_cells) / (cluster_k_ms * 1e-3) / 1e6}}
     out["radiosity"] = {"workload": "C5 Title.vxl: all 4096 chunks dirty -> osb200_radiosity_update(all) (16.8 M voxels, <=169 "
                                     "taps each), then 100 frames x 100 random block edits, each frame flush + shadow update + "
                                     "radiosity update of every dirty chunk (host edit generation inside the wall time)",

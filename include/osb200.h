@@ -242,6 +242,13 @@ OSB200_API int osb200_links_read(osb200_ctx *ctx, uint64_t *out);
 OSB200_API int osb200_links_last_floating(osb200_ctx *ctx, int16_t *floating, int cap);
 OSB200_API int osb200_links_last_rounds(osb200_ctx *ctx); /* flood launches of the last links call (diagnostics) */
 
+/* ---- Falling objects: World::ClusterizeBlocks (Client/World.cpp:154-226), the step World::ApplyBlockActions
+ *      (:227-265) runs on RemoveBlocks' result: the 6-connected components of a set of cells {x, y, z} x n (int16,
+ *      inside the map).  cluster[i] = number of the component of cell i; components are numbered 0 .. count-1 by
+ *      their smallest cell in CellPos order (the reference returns them in the iteration order of its
+ *      unordered_map: the same partition).  A cell given twice is one cell.  Needs no map.  Returns count. ---- */
+OSB200_API int osb200_clusterize_blocks(osb200_ctx *ctx, const int16_t *cells, int n, int32_t *cluster);
+
 /* ---- Minimap: SWFlatMapRenderer::Update / GeneratePixel (Draw/SWFlatMapRenderer.cpp:52-105): colour of the topmost solid
  *      voxel of every column, 0xffRRGGBB-swizzled like the reference's SWImage, out[y * 512 + x] (nullable); *device
  *      (nullable) receives the device copy.  Needs a flushed map. ---- */

@@ -83,6 +83,7 @@ def load_library():
     lib.osb200_links_read.argtypes = [vp, vp]
     lib.osb200_links_last_floating.argtypes = [vp, vp, ci]
     lib.osb200_links_last_rounds.argtypes = [vp]
+    lib.osb200_clusterize_blocks.argtypes = [vp, vp, ci, vp]
     lib.osb200_minimap.argtypes = [vp, vp, ctypes.POINTER(vp)]
     lib.osb200_map_mark_dirty.argtypes = [vp, ci, ci, ci]
     lib.osb200_map_flush.argtypes = [vp, vp, vp]
@@ -244,6 +245,14 @@ class Context:
         out = np.zeros((512, 512), np.uint64)
         self._check(self._lib.osb200_links_read(self._h, out.ctypes.data))
         return out
+
+    def clusterize_blocks(self, cells):
+        """World::ClusterizeBlocks (Client/World.cpp:154-226): cells int16 [n, 3] -> (count, int32 [n] component number
+        of every cell, components numbered by their smallest cell)."""
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros(len(cells), np.int32)
+        k = self._check(self._lib.osb200_clusterize_blocks(self._h, cells.ctypes.data, len(cells), out.ctypes.data))
+        return k, out
 
     def links_last_rounds(self):
         return self._lib.osb200_links_last_rounds(self._h)

@@ -53,6 +53,7 @@ namespace osb {
 		K_VXL_ENCODE,
 		K_LINKS_FLOOD,
 		K_MINIMAP,
+		K_CLUSTER_UNION,
 		K_COUNT
 	};
 	const char *kernel_name(int id);

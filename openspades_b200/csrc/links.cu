@@ -196,6 +196,71 @@ namespace osb {
 		out[i] = px;
 	}
 
+	// ---- World::ClusterizeBlocks (Sources/Client/World.cpp:154-226): 6-connected components of a set of cells ----
+	// The reference walks the set breadth-first through an unordered_map, one cell at a time.  Here the cells arrive
+	// as sorted 24-bit keys (x << 15 | y << 6 | z, the order of CellPos::operator<), a thread per cell looks its +x,
+	// +y and +z neighbours up by binary search and joins them in a lock-free union-find whose roots are the smallest
+	// index of a component (a larger root is only ever hooked below a smaller one, with atomicCAS), so the labels do
+	// not depend on the interleaving of the threads.
+	__device__ __forceinline__ int cl_find(int *parent, int i) {
+		for (;;) {
+			const int p = ((volatile int *)parent)[i];
+			if (p == i)
+				return i;
+			const int g = ((volatile int *)parent)[p];
+			if (g != p)
+				atomicMin(&parent[i], g); // path halving; parents only move towards smaller indices
+			i = p;
+		}
+	}
+	__device__ __forceinline__ void cl_union(int *parent, int a, int b) {
+		for (;;) {
+			a = cl_find(parent, a);
+			b = cl_find(parent, b);
+			if (a == b)
+				return;
+			const int hi = max(a, b), lo = min(a, b);
+			if (atomicCAS(&parent[hi], hi, lo) == hi)
+				return;
+		}
+	}
+	__device__ __forceinline__ int cl_lookup(const uint32_t *__restrict__ keys, int n, uint32_t k) {
+		int lo = 0, hi = n;
+		while (lo < hi) {
+			const int mid = (lo + hi) >> 1;
+			if (__ldg(&keys[mid]) < k)
+				lo = mid + 1;
+			else
+				hi = mid;
+		}
+		return lo < n && __ldg(&keys[lo]) == k ? lo : -1;
+	}
+	__global__ void k_cluster_init(int *__restrict__ parent, int n) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i < n)
+			parent[i] = i;
+	}
+	__global__ void k_cluster_union(const uint32_t *__restrict__ keys, int n, int *parent) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n)
+			return;
+		const uint32_t k = keys[i];
+		if (i > 0 && keys[i - 1] == k) // the same cell twice is one cell (the reference's map holds it once)
+			cl_union(parent, i, i - 1);
+		int j;
+		if ((k & 63u) != 63u && i + 1 < n && keys[i + 1] == k + 1) // +z is the next key when it is there
+			cl_union(parent, i, i + 1);
+		if (((k >> 6) & 511u) != 511u && (j = cl_lookup(keys, n, k + (1u << 6))) >= 0)
+			cl_union(parent, i, j);
+		if ((k >> 15) != 511u && (j = cl_lookup(keys, n, k + (1u << 15))) >= 0)
+			cl_union(parent, i, j);
+	}
+	__global__ void k_cluster_label(int *parent, int n) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i < n)
+			parent[i] = cl_find(parent, i); // roots are fixed by now: only pointers below them are rewritten
+	}
+
 	static int links_init(osb200_ctx *c) {
 		if (c->links)
 			return 0;
@@ -435,6 +500,65 @@ int osb200_links_read(osb200_ctx *c, uint64_t *out) {
 	OSB_CUDA(cudaMemcpyAsync(out, tmp, (size_t)nCols * 8, cudaMemcpyDeviceToHost, c->stream));
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
 	return 0;
+}
+
+int osb200_clusterize_blocks(osb200_ctx *c, const int16_t *cells, int n, int32_t *cluster) {
+	using namespace osb;
+	if (!c || n < 0 || (n && (!cells || !cluster))) {
+		set_error("osb200_clusterize_blocks: bad argument");
+		return -1;
+	}
+	if (n == 0)
+		return 0;
+	// sorted keys; order[] remembers which input cell a sorted slot came from
+	std::vector<uint32_t> keys((size_t)n);
+	std::vector<int> order((size_t)n);
+	for (int i = 0; i < n; i++) {
+		const int x = cells[i * 3], y = cells[i * 3 + 1], z = cells[i * 3 + 2];
+		if (x < 0 || x >= OSB200_MAP_W || y < 0 || y >= OSB200_MAP_H || z < 0 || z >= OSB200_MAP_D) {
+			set_error("osb200_clusterize_blocks: cell %d outside the map", i);
+			return -1;
+		}
+		keys[i] = (uint32_t)x << 15 | (uint32_t)y << 6 | (uint32_t)z;
+		order[i] = i;
+	}
+	std::sort(order.begin(), order.end(), [&](int a, int b) { return keys[a] != keys[b] ? keys[a] < keys[b] : a < b; });
+	std::vector<uint32_t> sorted((size_t)n);
+	for (int i = 0; i < n; i++)
+		sorted[i] = keys[order[i]];
+	OSB_CUDA(cudaSetDevice(c->device));
+	if (c->ensure_scratch((size_t)n * 8))
+		return -2;
+	uint32_t *d_keys = reinterpret_cast<uint32_t *>(c->d_scratch);
+	int *d_parent = reinterpret_cast<int *>(c->d_scratch) + n;
+	OSB_CUDA(cudaMemcpyAsync(d_keys, sorted.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+	const int grid = (n + 255) / 256;
+	k_cluster_init<<<grid, 256, 0, c->stream>>>(d_parent, n);
+	{
+		KLaunch kl(c, K_CLUSTER_UNION);
+		k_cluster_union<<<grid, 256, 0, c->stream>>>(d_keys, n, d_parent);
+	}
+	k_cluster_label<<<grid, 256, 0, c->stream>>>(d_parent, n);
+	c->launches += 2;
+	OSB_CUDA(cudaGetLastError());
+	std::vector<int> root((size_t)n);
+	OSB_CUDA(cudaMemcpyAsync(root.data(), d_parent, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	// a root is the smallest sorted slot of its cluster: numbering the roots in slot order numbers the clusters by
+	// their smallest cell
+	std::vector<int> number((size_t)n, -1);
+	int count = 0;
+	for (int i = 0; i < n; i++)
+		if (root[i] == i)
+			number[i] = count++;
+	for (int i = 0; i < n; i++) {
+		if (root[i] < 0 || root[i] > i || number[root[i]] < 0) {
+			set_error("osb200_clusterize_blocks: inconsistent labels from the device");
+			return -2;
+		}
+		cluster[order[i]] = number[root[i]];
+	}
+	return count;
 }
 
 int osb200_links_last_rounds(osb200_ctx *c) { return c && c->links ? c->links->lastRounds : -1; }

@@ -1,5 +1,6 @@
 #include "VoxelMapWrapper.h"
 
+#include <algorithm>
 #include <stdexcept>
 
 namespace osb200 {
@@ -62,5 +63,27 @@ namespace osb200 {
 		for (int i = 0; i < n; i++)
 			res.emplace_back(out[i * 3], out[i * 3 + 1], out[i * 3 + 2]);
 		return res;
+	}
+	std::vector<std::vector<CellPos>> VoxelMapWrapper::ClusterizeBlocks(const std::vector<CellPos> &blocks) {
+		if (blocks.empty())
+			return {};
+		std::vector<int16_t> flat;
+		flat.reserve(blocks.size() * 3);
+		for (const CellPos &p : blocks) {
+			flat.push_back(p.x);
+			flat.push_back(p.y);
+			flat.push_back(p.z);
+		}
+		std::vector<int32_t> id(blocks.size());
+		const int k = osb200_clusterize_blocks(ctx_, flat.data(), (int)blocks.size(), id.data());
+		Check(k);
+		std::vector<std::vector<CellPos>> ret((size_t)k);
+		for (size_t i = 0; i < blocks.size(); i++)
+			ret[(size_t)id[i]].push_back(blocks[i]);
+		for (auto &piece : ret) {
+			std::sort(piece.begin(), piece.end());
+			piece.erase(std::unique(piece.begin(), piece.end()), piece.end()); // a cell named twice is one cell
+		}
+		return ret;
 	}
 } // namespace osb200

@@ -34,6 +34,11 @@ namespace osb200 {
 		// CellPos::operator<; the reference returns the same set in walk order).  It does not remove them.
 		std::vector<CellPos> RemoveBlocks(const std::vector<CellPos> &cells);
 
+		// World::ClusterizeBlocks (World.cpp:154-226), the next step of World::ApplyBlockActions (:249): the floating
+		// set split into its 6-connected pieces, one falling object each.  Pieces come ordered by their smallest cell,
+		// cells inside a piece sorted (the reference: unordered_map iteration order / walk order; the same partition).
+		std::vector<std::vector<CellPos>> ClusterizeBlocks(const std::vector<CellPos> &blocks);
+
 	private:
 		void Flush();
 		VoxelMap &map_;

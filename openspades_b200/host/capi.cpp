@@ -2,6 +2,7 @@
 // can drive the same objects a C++ integrator would use.  Not part of the osb200 C ABI proper.
 #include <cstring>
 #include <exception>
+#include <stdexcept>
 #include <string>
 
 #include "../../include/osb200.h"
@@ -218,6 +219,31 @@ OSBH_API int osbh_wrapper_rebuild(void *w) {
 }
 OSBH_API int osbh_wrapper_add_block(void *w, int x, int y, int z, uint32_t color) {
 	return guarded([&] { static_cast<osb200::VoxelMapWrapper *>(w)->AddBlock(x, y, z, color); });
+}
+// World::ClusterizeBlocks through the wrapper: pieces written back to back into out (n cells), sizes[k] cells each;
+// returns the number of pieces (< 0 on error, or when more than capPieces)
+OSBH_API int osbh_wrapper_clusterize(void *w, const int16_t *cells, int n, int16_t *out, int32_t *sizes, int capPieces) {
+	int count = -1;
+	guarded([&] {
+		std::vector<osb200::CellPos> in;
+		for (int i = 0; i < n; i++)
+			in.emplace_back(cells[i * 3], cells[i * 3 + 1], cells[i * 3 + 2]);
+		auto pieces = static_cast<osb200::VoxelMapWrapper *>(w)->ClusterizeBlocks(in);
+		if ((int)pieces.size() > capPieces)
+			throw std::length_error("osbh_wrapper_clusterize: more pieces than capPieces");
+		size_t o = 0;
+		for (size_t k = 0; k < pieces.size(); k++) {
+			sizes[k] = (int32_t)pieces[k].size();
+			for (const auto &p : pieces[k]) {
+				out[o * 3] = p.x;
+				out[o * 3 + 1] = p.y;
+				out[o * 3 + 2] = p.z;
+				o++;
+			}
+		}
+		count = (int)pieces.size();
+	});
+	return count;
 }
 // cells: n x {x, y, z} int16; returns the number of floating blocks (< 0 on error), writes min(count, cap)
 OSBH_API int osbh_wrapper_remove_blocks(void *w, const int16_t *cells, int n, int16_t *out, int cap) {

@@ -301,6 +301,7 @@ class VoxelMapWrapper:
         L.osbh_wrapper_rebuild.argtypes = [vp]
         L.osbh_wrapper_add_block.argtypes = [vp] + [ctypes.c_int] * 3 + [ctypes.c_uint32]
         L.osbh_wrapper_remove_blocks.argtypes = [vp, vp, ctypes.c_int, vp, ctypes.c_int]
+        L.osbh_wrapper_clusterize.argtypes = [vp, vp, ctypes.c_int, vp, vp, ctypes.c_int]
         L.osbh_renderer_context.restype = vp
         self._map, self._renderer = vmap, renderer  # keep both alive
         self._h = L.osbh_wrapper_new(vmap.handle, L.osbh_renderer_context(renderer._h))
@@ -321,6 +322,16 @@ class VoxelMapWrapper:
         out = np.zeros((1 << 16, 3), np.int16)
         n = self._chk(self._L.osbh_wrapper_remove_blocks(self._h, cells.ctypes.data, len(cells), out.ctypes.data, len(out)))
         return out[:min(n, len(out))].copy()
+
+    def clusterize_blocks(self, cells):
+        """World::ClusterizeBlocks (World.cpp:154-226): list of (m, 3) int16 arrays, one per 6-connected piece."""
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros((max(len(cells), 1), 3), np.int16)
+        sizes = np.zeros(max(len(cells), 1), np.int32)
+        k = self._chk(self._L.osbh_wrapper_clusterize(self._h, cells.ctypes.data, len(cells), out.ctypes.data,
+                                                      sizes.ctypes.data, len(sizes)))
+        ends = np.cumsum(sizes[:k])
+        return [out[e - s:e].copy() for s, e in zip(sizes[:k], ends)]
 
     def close(self):
         if self._h:

@@ -299,3 +299,64 @@ void orc_minimap(const uint64_t *solid, const uint32_t *color, uint32_t *out) {
 			out[(size_t)y * W + x] = px;
 		}
 }
+
+/* ---- World::ClusterizeBlocks (Client/World.cpp:154-226) ----
+ * The reference puts the cells into an unordered_map<CellPos, bool> (:156-159), then for every still-true entry walks
+ * breadth-first (:176-217) over the six neighbours in the order -x +x -y +y -z +z, clearing the flag of each cell it
+ * takes (:187).  The outer loop follows the map's iteration order; here it follows the input order, so the pieces are
+ * the same and only their numbering differs.  cluster[i] = piece of cell i, returns the number of pieces. */
+static int cmp_u32(const void *a, const void *b) {
+	const uint32_t x = *(const uint32_t *)a, y = *(const uint32_t *)b;
+	return x < y ? -1 : x > y;
+}
+static int key_slot(const uint32_t *keys, int n, int x, int y, int z) {
+	if (x < 0 || y < 0 || z < 0 || x > 0x7fff || y > 0x7fff || z > 0x7fff)
+		return -1;
+	const uint32_t k = ((uint32_t)x << 20) | ((uint32_t)y << 8) | (uint32_t)z; /* x < 4096, y < 4096, z < 256 */
+	const uint32_t *p = (const uint32_t *)bsearch(&k, keys, (size_t)n, sizeof(uint32_t), cmp_u32);
+	return p ? (int)(p - keys) : -1;
+}
+int orc_clusterize_blocks(const int16_t *cells, int n, int32_t *cluster) {
+	if (n <= 0)
+		return 0;
+	uint32_t *keys = (uint32_t *)malloc((size_t)n * sizeof(uint32_t));
+	int m = 0;
+	for (int i = 0; i < n; i++)
+		keys[i] = ((uint32_t)cells[i * 3] << 20) | ((uint32_t)cells[i * 3 + 1] << 8) | (uint32_t)cells[i * 3 + 2];
+	qsort(keys, (size_t)n, sizeof(uint32_t), cmp_u32);
+	for (int i = 0; i < n; i++) /* the map holds a cell once (:157-159) */
+		if (i == 0 || keys[i] != keys[i - 1])
+			keys[m++] = keys[i];
+	int32_t *piece = (int32_t *)malloc((size_t)m * sizeof(int32_t)); /* -1 = flag still true */
+	int *queue = (int *)malloc((size_t)m * 6 * sizeof(int) + sizeof(int));
+	for (int i = 0; i < m; i++)
+		piece[i] = -1;
+	int count = 0;
+	for (int s = 0; s < n; s++) {
+		const int start = key_slot(keys, m, cells[s * 3], cells[s * 3 + 1], cells[s * 3 + 2]);
+		if (piece[start] >= 0) /* :173-174 */
+			continue;
+		int head = 0, tail = 0;
+		queue[tail++] = start;
+		while (head < tail) {
+			const int c = queue[head++];
+			if (piece[c] >= 0) /* :181-182 */
+				continue;
+			piece[c] = count; /* :185-187 */
+			const int x = (int)(keys[c] >> 20), y = (int)((keys[c] >> 8) & 0xfff), z = (int)(keys[c] & 0xff);
+			const int nb[6][3] = {{x - 1, y, z}, {x + 1, y, z}, {x, y - 1, z}, {x, y + 1, z}, {x, y, z - 1}, {x, y, z + 1}};
+			for (int k = 0; k < 6; k++) { /* :191-214 */
+				const int j = key_slot(keys, m, nb[k][0], nb[k][1], nb[k][2]);
+				if (j >= 0 && piece[j] < 0)
+					queue[tail++] = j;
+			}
+		}
+		count++; /* :219-221 */
+	}
+	for (int i = 0; i < n; i++)
+		cluster[i] = piece[key_slot(keys, m, cells[i * 3], cells[i * 3 + 1], cells[i * 3 + 2])];
+	free(queue);
+	free(piece);
+	free(keys);
+	return count;
+}

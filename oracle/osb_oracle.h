@@ -132,6 +132,9 @@ void orc_links_add_block(orc_links *w, uint64_t *solid, uint32_t *color, int x, 
 /* :199-361 RemoveBlocks: clears the cells, returns the floating blocks (count; min(count, cap) written, reference order) */
 int orc_links_remove_blocks(orc_links *w, uint64_t *solid, const int16_t *cells, int n, int16_t *out, int cap);
 void orc_links_linked(const orc_links *w, uint64_t *out);
+/* Client/World.cpp:154-226 ClusterizeBlocks: cells n x {x, y, z} (0 <= x, y < 4096, 0 <= z < 256); cluster[i] = piece of
+ * cell i, pieces numbered in order of their first cell in the input; returns the number of pieces */
+int orc_clusterize_blocks(const int16_t *cells, int n, int32_t *cluster);
 /* Draw/SWFlatMapRenderer.cpp:94-105 GeneratePixel over the map: out[y * 512 + x] */
 void orc_minimap(const uint64_t *solid, const uint32_t *color, uint32_t *out);
 

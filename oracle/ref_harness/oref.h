@@ -47,6 +47,8 @@ OREF_API void oref_wrapper_free(void *w);
 OREF_API void oref_wrapper_add_block(void *w, int x, int y, int z, uint32_t color);
 OREF_API int oref_wrapper_remove_blocks(void *w, const int16_t *cells, int n, int16_t *out, int cap);
 OREF_API void oref_wrapper_linked(void *w, uint64_t *out /*[x][y], bit z = link != Invalid*/);
+/* World::ClusterizeBlocks (Client/World.cpp:154-226, oref_world.cpp): cluster[i] = index of the returned piece holding cell i */
+OREF_API int oref_clusterize_blocks(const int16_t *cells, int n, int32_t *cluster);
 OREF_API void oref_map_set(void *map, int x, int y, int z, int solid, uint32_t color); /* GameMap::Set, notifies listeners */
 OREF_API void oref_castray2(void *map, const float *v0, const float *dir, int maxSteps,
                             oref_rayhit *out, size_t n, int threads); /* GameMap::CastRay2 */

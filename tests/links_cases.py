@@ -67,3 +67,61 @@ def script(solid, seed=0, n_random=150):
                     cells.append((x0 + dx, y0 + dy, z + dz))
     ops.append(("remove", cells))
     return ops
+
+
+def canonical_partition(cells, labels):
+    """A labelling as a sorted list of sorted tuples of cells: what World::ClusterizeBlocks returns, without its order."""
+    pieces = {}
+    for c, l in zip(np.asarray(cells).reshape(-1, 3).tolist(), np.asarray(labels).tolist()):
+        pieces.setdefault(l, set()).add(tuple(c))
+    return sorted(tuple(sorted(p)) for p in pieces.values())
+
+
+def cluster_cases(seed=0):
+    """Cell sets for World::ClusterizeBlocks: name -> int16 [n, 3]."""
+    rng = np.random.default_rng(seed)
+    cases = {}
+    cases["single"] = [[7, 9, 3]]
+    cases["two_apart"] = [[1, 1, 1], [3, 1, 1]]
+    cases["diagonal_is_not_connected"] = [[4, 4, 4], [5, 5, 4], [6, 6, 5], [5, 4, 5]]
+    cases["corners_of_the_map"] = [[0, 0, 0], [511, 511, 63], [0, 511, 0], [511, 0, 63], [0, 0, 1], [511, 511, 62],
+                                   [511, 510, 63], [510, 511, 63]]
+    # keys that differ by one in the packed order but are not neighbours: (x, y, 63) and (x, y + 1, 0), (x, 511, z) and (x + 1, 0, z)
+    cases["no_wrap_between_columns"] = [[10, 10, 63], [10, 11, 0], [20, 511, 5], [21, 0, 5], [30, 511, 63], [31, 0, 0]]
+    line = [[x, 100, 20] for x in range(50, 300)]
+    cases["long_line_shuffled"] = rng.permutation(np.array(line)).tolist()
+    # a winding path: worst case for label propagation, nothing special for union-find
+    snake = []
+    for row in range(0, 40, 2):
+        xs = range(100, 180) if (row // 2) % 2 == 0 else range(179, 99, -1)
+        snake += [[x, 200 + row, 30] for x in xs]
+        snake.append([179 if (row // 2) % 2 == 0 else 100, 200 + row + 1, 30])
+    cases["snake"] = rng.permutation(np.array(snake)).tolist()
+    box = [[x, y, z] for x in range(300, 312) for y in range(300, 310) for z in range(10, 18)]
+    shell = [c for c in box if c[0] in (300, 311) or c[1] in (300, 309) or c[2] in (10, 17)]
+    cases["hollow_box_with_core"] = shell + [[305, 305, 13], [305, 305, 14], [306, 305, 14]]
+    cases["duplicates"] = [[5, 5, 5], [5, 5, 6], [5, 5, 5], [9, 9, 9], [9, 9, 9], [5, 6, 6]]
+    pts = rng.integers(0, [24, 24, 16], size=(3000, 3)) + [400, 60, 40]  # ~33 % fill: many pieces of all sizes
+    cases["random_cloud"] = np.unique(pts, axis=0)[rng.permutation(len(np.unique(pts, axis=0)))].tolist()
+    towers = [[x, y, z] for x in range(0, 512, 37) for y in range(0, 512, 41) for z in range(0, 64)]
+    cases["towers_full_height"] = towers
+    return {k: np.array(v, np.int16).reshape(-1, 3) for k, v in cases.items()}
+
+
+def brute_partition(cells):
+    """Connected components by definition (pure Python flood over a set), for small cases."""
+    todo = {tuple(c) for c in np.asarray(cells).reshape(-1, 3).tolist()}
+    out = []
+    while todo:
+        stack = [todo.pop()]
+        piece = []
+        while stack:
+            c = stack.pop()
+            piece.append(c)
+            for d in ((1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1)):
+                nb = (c[0] + d[0], c[1] + d[1], c[2] + d[2])
+                if nb in todo:
+                    todo.remove(nb)
+                    stack.append(nb)
+        out.append(tuple(sorted(piece)))
+    return sorted(out)

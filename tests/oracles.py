@@ -100,6 +100,12 @@ class Port:
         L.orc_render_scene.argtypes = [vp, vp, vp, ci, ci, vp, ctypes.c_float, ci, ci, ci, vp, ci, vp, ci, vp, vp]
 
     # ---- floating blocks + minimap (orc_links.c) ----
+    def clusterize_blocks(self, cells):
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.zeros(len(cells), np.int32)
+        self.L.orc_clusterize_blocks.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        return self.L.orc_clusterize_blocks(cells.ctypes.data, len(cells), out.ctypes.data), out
+
     def links_create(self, solid):
         w = self.L.orc_links_create()
         self.L.orc_links_rebuild(w, solid.ctypes.data)
@@ -369,6 +375,13 @@ class Ref:
 
     def wrapper_free(self, w):
         self.L.oref_wrapper_free(w)
+
+    # World::ClusterizeBlocks, the unmodified static function of Client/World.cpp (oref_world.cpp)
+    def clusterize_blocks(self, cells):
+        cells = np.ascontiguousarray(cells, np.int16).reshape(-1, 3)
+        out = np.full(len(cells), -1, np.int32)
+        self.L.oref_clusterize_blocks.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        return self.L.oref_clusterize_blocks(cells.ctypes.data, len(cells), out.ctypes.data), out
 
     def wrapper_add_block(self, w, x, y, z, col):
         self.L.oref_wrapper_add_block(w, x, y, z, int(col))

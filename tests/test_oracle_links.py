@@ -85,3 +85,19 @@ def test_minimap_matches_reference_flat_map_renderer(port):
     rr.set_map(None)
     rr.close()
     ref.map_free(m)
+
+
+def test_clusterize_blocks_port_matches_reference_and_definition(port):
+    """orc_clusterize_blocks against World::ClusterizeBlocks itself (the unmodified static function of Client/World.cpp
+    compiled into oracle/_ref) and against the definition of a connected component."""
+    ref = oracles.Ref("ieee") if oracles.ref_available("ieee") else None
+    for name, cells in links_cases.cluster_cases().items():
+        k, lab = port.clusterize_blocks(cells)
+        got = links_cases.canonical_partition(cells, lab)
+        assert len(got) == k, name
+        assert got == links_cases.brute_partition(cells), name
+        if ref is not None:
+            rk, rlab = ref.clusterize_blocks(cells)
+            assert (rlab >= 0).all(), name
+            assert rk == k and links_cases.canonical_partition(cells, rlab) == got, name
+    assert port.clusterize_blocks(np.zeros((0, 3), np.int16))[0] == 0
