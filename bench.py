@@ -633,7 +633,7 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                     "flood_launches_per_call": lkt["k_links_flood"][0] / n_calls,
                     "minimap_ms": minimap_ms, "minimap_kernel_ms": mm_k,
                     "clusterize": {"workload": "World::ClusterizeBlocks of every solid voxel of Title.vxl above z = 48 in one call "
-                                               "(host key sort + H2D + union-find kernel + labels D2H inside the wall time)",
+                                               "(H2D of the cells, device key sort, union-find, piece numbering, labels D2H inside the wall time)",
                                    "cells": int(len(cl_cells)), "pieces": int(cl_k), "wall_ms": cluster_ms,
                                    "union_kernel_ms": cluster_k_ms,
                                    "mcells_s_kernel": len(cl_cells) / (cluster_k_ms * 1e-3) / 1e6}}

@@ -19,6 +19,9 @@
 // voxels).  The result is returned sorted by (x, y, z); the reference returns the same set in breadth-first order.
 #include "ctx.h"
 
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -198,8 +201,8 @@ namespace osb {
 
 	// ---- World::ClusterizeBlocks (Sources/Client/World.cpp:154-226): 6-connected components of a set of cells ----
 	// The reference walks the set breadth-first through an unordered_map, one cell at a time.  Here the cells arrive
-	// as sorted 24-bit keys (x << 15 | y << 6 | z, the order of CellPos::operator<), a thread per cell looks its +x,
-	// +y and +z neighbours up by binary search and joins them in a lock-free union-find whose roots are the smallest
+	// become 24-bit keys (x << 15 | y << 6 | z, the order of CellPos::operator<) sorted on the device (cub radix sort,
+	// three 8-bit passes), a thread per cell looks its +x, +y and +z neighbours up by binary search and joins them in a lock-free union-find whose roots are the smallest
 	// index of a component (a larger root is only ever hooked below a smaller one, with atomicCAS), so the labels do
 	// not depend on the interleaving of the threads.
 	__device__ __forceinline__ int cl_find(int *parent, int i) {
@@ -255,10 +258,37 @@ namespace osb {
 		if ((k >> 15) != 511u && (j = cl_lookup(keys, n, k + (1u << 15))) >= 0)
 			cl_union(parent, i, j);
 	}
-	__global__ void k_cluster_label(int *parent, int n) {
+	__global__ void k_cluster_label(int *parent, int n, int *__restrict__ isRoot) {
 		const int i = blockIdx.x * blockDim.x + threadIdx.x;
-		if (i < n)
-			parent[i] = cl_find(parent, i); // roots are fixed by now: only pointers below them are rewritten
+		if (i < n) {
+			const int r = cl_find(parent, i); // roots are fixed by now: only pointers below them are rewritten
+			parent[i] = r;
+			isRoot[i] = r == i;
+		}
+	}
+	// cells -> 24-bit keys + the slot they came from; flags[0] = smallest index of a cell outside the map
+	__global__ void k_cluster_keys(const int16_t *__restrict__ cells, int n, uint32_t *__restrict__ keys,
+	                               uint32_t *__restrict__ slot, int *__restrict__ flags) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n)
+			return;
+		const int x = cells[i * 3], y = cells[i * 3 + 1], z = cells[i * 3 + 2];
+		const bool ok = x >= 0 && x < OSB200_MAP_W && y >= 0 && y < OSB200_MAP_H && z >= 0 && z < OSB200_MAP_D;
+		if (!ok)
+			atomicMin(&flags[0], i);
+		keys[i] = ok ? ((uint32_t)x << 15 | (uint32_t)y << 6 | (uint32_t)z) : 0u;
+		slot[i] = (uint32_t)i;
+	}
+	// label[input cell] = number of its root; flags[1] = number of pieces
+	__global__ void k_cluster_scatter(const int *__restrict__ root, const int *__restrict__ number,
+	                                  const int *__restrict__ isRoot, const uint32_t *__restrict__ slot, int n,
+	                                  int *__restrict__ label, int *__restrict__ count) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n)
+			return;
+		label[slot[i]] = number[root[i]];
+		if (i == n - 1)
+			*count = number[i] + isRoot[i];
 	}
 
 	static int links_init(osb200_ctx *c) {
@@ -510,55 +540,54 @@ int osb200_clusterize_blocks(osb200_ctx *c, const int16_t *cells, int n, int32_t
 	}
 	if (n == 0)
 		return 0;
-	// sorted keys; order[] remembers which input cell a sorted slot came from
-	std::vector<uint32_t> keys((size_t)n);
-	std::vector<int> order((size_t)n);
-	for (int i = 0; i < n; i++) {
-		const int x = cells[i * 3], y = cells[i * 3 + 1], z = cells[i * 3 + 2];
-		if (x < 0 || x >= OSB200_MAP_W || y < 0 || y >= OSB200_MAP_H || z < 0 || z >= OSB200_MAP_D) {
-			set_error("osb200_clusterize_blocks: cell %d outside the map", i);
-			return -1;
-		}
-		keys[i] = (uint32_t)x << 15 | (uint32_t)y << 6 | (uint32_t)z;
-		order[i] = i;
-	}
-	std::sort(order.begin(), order.end(), [&](int a, int b) { return keys[a] != keys[b] ? keys[a] < keys[b] : a < b; });
-	std::vector<uint32_t> sorted((size_t)n);
-	for (int i = 0; i < n; i++)
-		sorted[i] = keys[order[i]];
 	OSB_CUDA(cudaSetDevice(c->device));
-	if (c->ensure_scratch((size_t)n * 8))
+	cudaStream_t st = c->stream;
+	// scratch: cells | keys x2 | slots x2 (which input cell a sorted slot came from) | parent | number | labels | flags | cub
+	const size_t N = ((size_t)n + 63) & ~(size_t)63;
+	size_t sortBytes = 0, scanBytes = 0;
+	OSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sortBytes, (const uint32_t *)nullptr, (uint32_t *)nullptr,
+	                                         (const uint32_t *)nullptr, (uint32_t *)nullptr, n, 0, 24, st));
+	OSB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, (const int *)nullptr, (int *)nullptr, n, st));
+	const size_t tempBytes = (std::max(sortBytes, scanBytes) + 255) & ~(size_t)255;
+	if (c->ensure_scratch(N * 8 + N * 4 * 8 + 256 + tempBytes))
 		return -2;
-	uint32_t *d_keys = reinterpret_cast<uint32_t *>(c->d_scratch);
-	int *d_parent = reinterpret_cast<int *>(c->d_scratch) + n;
-	OSB_CUDA(cudaMemcpyAsync(d_keys, sorted.data(), (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+	uint8_t *base = reinterpret_cast<uint8_t *>(c->d_scratch);
+	int16_t *d_cells = reinterpret_cast<int16_t *>(base);
+	uint32_t *d_keysIn = reinterpret_cast<uint32_t *>(base + N * 8);
+	uint32_t *d_keys = d_keysIn + N, *d_slotIn = d_keys + N, *d_slot = d_slotIn + N;
+	int *d_parent = reinterpret_cast<int *>(d_slot + N), *d_number = d_parent + N, *d_label = d_number + N;
+	int *d_isRoot = d_label + N;
+	int *d_flags = d_isRoot + N; // [0] smallest index of a cell outside the map, [1] number of pieces
+	void *d_temp = reinterpret_cast<uint8_t *>(d_flags) + 256;
+	OSB_CUDA(cudaMemcpyAsync(d_cells, cells, (size_t)n * 3 * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+	OSB_CUDA(cudaMemsetAsync(d_flags, 0x7f, sizeof(int), st));
 	const int grid = (n + 255) / 256;
-	k_cluster_init<<<grid, 256, 0, c->stream>>>(d_parent, n);
+	k_cluster_keys<<<grid, 256, 0, st>>>(d_cells, n, d_keysIn, d_slotIn, d_flags);
+	size_t tb = tempBytes;
+	OSB_CUDA(cub::DeviceRadixSort::SortPairs(d_temp, tb, d_keysIn, d_keys, d_slotIn, d_slot, n, 0, 24, st));
+	k_cluster_init<<<grid, 256, 0, st>>>(d_parent, n);
 	{
 		KLaunch kl(c, K_CLUSTER_UNION);
-		k_cluster_union<<<grid, 256, 0, c->stream>>>(d_keys, n, d_parent);
+		k_cluster_union<<<grid, 256, 0, st>>>(d_keys, n, d_parent);
 	}
-	k_cluster_label<<<grid, 256, 0, c->stream>>>(d_parent, n);
-	c->launches += 2;
+	k_cluster_label<<<grid, 256, 0, st>>>(d_parent, n, d_isRoot);
+	// a root is the smallest sorted slot of its piece: numbering the roots in slot order numbers the pieces by their
+	// smallest cell
+	tb = tempBytes;
+	OSB_CUDA(cub::DeviceScan::ExclusiveSum(d_temp, tb, d_isRoot, d_number, n, st));
+	k_cluster_scatter<<<grid, 256, 0, st>>>(d_parent, d_number, d_isRoot, d_slot, n, d_label, d_flags + 1);
+	c->launches += 4;
 	OSB_CUDA(cudaGetLastError());
-	std::vector<int> root((size_t)n);
-	OSB_CUDA(cudaMemcpyAsync(root.data(), d_parent, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
-	OSB_CUDA(cudaStreamSynchronize(c->stream));
-	// a root is the smallest sorted slot of its cluster: numbering the roots in slot order numbers the clusters by
-	// their smallest cell
-	std::vector<int> number((size_t)n, -1);
-	int count = 0;
-	for (int i = 0; i < n; i++)
-		if (root[i] == i)
-			number[i] = count++;
-	for (int i = 0; i < n; i++) {
-		if (root[i] < 0 || root[i] > i || number[root[i]] < 0) {
-			set_error("osb200_clusterize_blocks: inconsistent labels from the device");
-			return -2;
-		}
-		cluster[order[i]] = number[root[i]];
+	int flags[2] = {0, 0};
+	OSB_CUDA(cudaMemcpyAsync(flags, d_flags, sizeof(flags), cudaMemcpyDeviceToHost, st));
+	OSB_CUDA(cudaStreamSynchronize(st));
+	if (flags[0] < n) {
+		set_error("osb200_clusterize_blocks: cell %d outside the map", flags[0]);
+		return -1;
 	}
-	return count;
+	OSB_CUDA(cudaMemcpyAsync(cluster, d_label, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+	OSB_CUDA(cudaStreamSynchronize(st));
+	return flags[1];
 }
 
 int osb200_links_last_rounds(osb200_ctx *c) { return c && c->links ? c->links->lastRounds : -1; }
