@@ -35,7 +35,7 @@ namespace osb {
 		K_MAP_REPACK = 0,
 		K_MAP_SCATTER,
 		K_VIEW_PREP,
-		K_BUILD_LINES,
+		K_WALK_LINES,
 		K_GATHER_FOG,
 		K_CASTRAY2,
 		K_SHADOW_BITMAP,
@@ -46,7 +46,7 @@ namespace osb {
 		K_SCENE_FINISH,
 		K_MODEL_SETUP,
 		K_MODEL_SPLAT,
-		K_MODEL_RESOLVE,
+		K_LINE_SETUP,
 		K_LIGHTS,
 		K_VXL_INDEX,
 		K_VXL_DECODE,

@@ -1,122 +1,35 @@
 // Software-renderer terrain pass + fog on the GPU, reproducing the reference's results:
 //   SWRenderer::EndScene / BuildFrustrum   Sources/Draw/SWRenderer.cpp:207-227,709-745
-//   SWMapRenderer::RenderInner             Sources/Draw/SWMapRenderer.cpp:1045-1174  (per-view set-up)
-//   SWMapRenderer::BuildLine               Sources/Draw/SWMapRenderer.cpp:219-671    (k_build_lines)
+//   SWMapRenderer::RenderInner             Sources/Draw/SWMapRenderer.cpp:1045-1174  (fill_view + k_view_prep)
+//   SWMapRenderer::BuildLine               Sources/Draw/SWMapRenderer.cpp:219-671    (k_line_setup + k_walk_lines)
 //   SWMapRenderer::RenderFinal             Sources/Draw/SWMapRenderer.cpp:744-1043   (k_gather_fog)
 //   SWRenderer::ApplyFog                   Sources/Draw/SWRenderer.cpp:341-516       (fused into k_gather_fog)
 //
-// Design: the reference renders a view as ~2.5-5k vertical "yaw lines", each a 1-D strip
-// of (colour, depth) built by a 2-D DDA through map columns, then gathers every screen pixel from
-// (line, pitch index).  Here
-//   * one thread builds one line; the six per-column RLE z-lists of the reference are never stored --
-//     tops/bottoms/walls are bit expressions of the 64-bit column mask and of the mask of the cell the
-//     DDA just left, so a step costs one 8-byte load from the 2 MiB tiled bitmap;
-//   * "first writer wins" along a strip is kept in a per-thread bitmask in shared memory, so strip
-//     pixels are written once, write-only, and colours are fetched only for spans that land;
-//   * gather and fog are one kernel: each warp owns an 8-pixel-wide column of 8x8 blocks, replays the
-//     reference's per-thread float recurrences for its start vectors and writes BGRX + depth once.
+// Design: the reference renders a view as ~0.6-5k vertical "yaw lines", each a 1-D strip of
+// (colour, depth) built by a 2-D DDA through map columns, then gathers every screen pixel from (line, pitch index).
+// The per-lane arithmetic lives in terrain_core.cuh (shared with the CPU emulation of tests/native); this file is
+// the launch structure around it:
+//   k_view_prep    one warp per view: the reference's sequential float recurrences (line directions, fog / v1 tables)
+//   k_line_setup   one thread per yaw line: pitch cull against the frustum (glibc-exact atanf / tanf), line records,
+//                  and warp-aggregated COMPACTION of the surviving lines into the chunk's active list -- a line's
+//                  position in that list is its strip slot, culled lines own no strip memory at all
+//   k_walk_lines   persistent grid; a lane walks one active line (DDA + spans), and when enough lanes of a warp have
+//                  finished, the warp fetches the next lines from the chunk-wide cursor with one atomic (ballot +
+//                  prefix rank) -- no launch tail per chunk, no lanes parked on culled or short lines
+//   k_gather_fog   one warp per (view, 32-pixel column group, 8 block rows): RenderFinal + ApplyFog, frame written once
 // All float arithmetic is separate IEEE mul/add (--fmad=false) in the reference's evaluation order.
 #include "ctx.h"
-#include "libm_f32.cuh"
-#include "numerics.cuh"
+#include "terrain_core.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
 
 namespace osb {
 
-	// Per-view constants.  Everything that the reference computes once per frame with libm
-	// (tanf/atanf/asinf/atan2l/cosf/sinf, SWMapRenderer.cpp:1057-1133, SWRenderer.cpp:207-227,345-357)
-	// is evaluated on the host with the same libm and shipped here.
-	struct ViewParams {
-		float origin[3];
-		float right[3], up[3], front[3];
-		float frN[4][3]; // frustum side-plane normals, SWRenderer::frustrum[2..5].n
-		float fovXt, fovYt;
-		float yawMin, yawMax;
-		float cosYawMin, sinYawMin, cosScl, sinScl;
-		int numLines, lineRes;
-		int yawScale2, yawMin2;
-		uint32_t lineBase;  // first line slot of this view inside the chunk
-		uint32_t tabBase;   // first float of this view's recurrence tables
-		float fogScale;     // 255 / fogDistance
-		float dvx, dvy;     // ApplyFog steps
-		uint32_t pad;
-	};
-
-	// Recurrence tables of one view, laid out at tabs + tabBase:
-	//   vx[fw/4]            ApplyFog per-4-pixel-column vx          (SWRenderer.cpp:372,409)
-	//   vy[fh/4]            ApplyFog per-4-row vy, per emulated thread band (:365-369,412)
-	//   v1[fw/8][3]         RenderFinal per-8-pixel-column start vector, per emulated thread (:757,789,1040)
-	__host__ __device__ inline uint32_t tab_floats(int fw, int fh) { return fw / 4 + fh / 4 + (fw / 8) * 3; }
-
-	struct FrameGeom {
-		int fw, fh, under, swThreads, sse2Fog, sse2Shade;
-		int noFog; // fog deferred to k_scene_finish (models / dynamic lights are drawn between terrain and fog, SWRenderer.cpp:727-744)
-		int noMap; // no map set: SWRenderer::EndScene still clears and fogs over the stale depth (SWRenderer.cpp:713-744)
-		uint32_t fogB, fogG, fogR;
-	};
-
-	// One sequential float recurrence per role; the same code runs on the host (few views) or on one
-	// lane per role on the device (many views).
-	__host__ __device__ inline void prep_line_dirs(const ViewParams &v, float2 *dirs) {
-		// SWMapRenderer.cpp:1129-1143
-		float hx = v.cosYawMin, hy = v.sinYawMin;
-		const float c = v.cosScl, s = v.sinScl;
-		for (int i = 0; i < v.numLines; i++) {
-			dirs[i] = make_float2(hx, hy);
-			const float x = osbm::subf(osbm::mulf(hx, c), osbm::mulf(hy, s));
-			const float y = osbm::addf(osbm::mulf(hx, s), osbm::mulf(hy, c));
-			hx = x;
-			hy = y;
-		}
-	}
-	__host__ __device__ inline void prep_fog_vx(const ViewParams &v, const FrameGeom &g, float *vx) {
-		float x = v.fovXt;
-		for (int i = 0; i < g.fw / 4; i++) {
-			vx[i] = x;
-			x = osbm::addf(x, v.dvx);
-		}
-	}
-	__host__ __device__ inline void prep_fog_vy(const ViewParams &v, const FrameGeom &g, int t, float *vy) {
-		// band of emulated thread t, SWRenderer.cpp:359-369
-		int startY = (int)((unsigned)g.fh * (unsigned)t / (unsigned)g.swThreads) & ~3;
-		int endY = (int)((unsigned)g.fh * (unsigned)(t + 1) / (unsigned)g.swThreads) & ~3;
-		float y = osbm::addf(v.fovYt, osbm::mulf(v.dvy, (float)(startY >> 2)));
-		for (int r = startY; r < endY; r += 4) {
-			vy[r >> 2] = y;
-			y = osbm::addf(y, v.dvy);
-		}
-	}
-	__host__ __device__ inline void prep_v1(const ViewParams &v, const FrameGeom &g, int t, float *v1tab) {
-		// SWMapRenderer.cpp:757-759,774-781,789,1040
-		const float fx = v.fovXt, fy = v.fovYt;
-		float v1[3], dR[3], dRL[3];
-		const float sR = osbm::mulf(osbm::divf(osbm::mulf(fx, 2.f), (float)g.fw), (float)g.under);
-		unsigned startX = (unsigned)t * (unsigned)g.fw / (unsigned)g.swThreads;
-		unsigned endX = (unsigned)(t + 1) * (unsigned)g.fw / (unsigned)g.swThreads;
-		startX = (startX / 8) * 8;
-		endX = (endX / 8) * 8;
-		for (int k = 0; k < 3; k++) {
-			v1[k] = osbm::addf(osbm::subf(v.front[k], osbm::mulf(v.right[k], fx)), osbm::mulf(v.up[k], fy));
-			dR[k] = osbm::mulf(v.right[k], sR);
-			dRL[k] = osbm::mulf(dR[k], (float)(8 / g.under));
-			v1[k] = osbm::addf(v1[k], osbm::mulf(dR[k], (float)(startX / (unsigned)g.under)));
-		}
-		for (unsigned x = startX; x < endX; x += 8) {
-			for (int k = 0; k < 3; k++) {
-				v1tab[(x >> 3) * 3 + k] = v1[k];
-				v1[k] = osbm::addf(v1[k], dRL[k]);
-			}
-		}
-	}
-
-	// Per-chunk working set.  Two of them, each with its own stream: chunk k+1's line build runs beside chunk k's
-	// gather and fills the SMs that chunk k's launch tail leaves idle (a single yaw line is ~150 dependent DDA steps,
-	// so every k_build_lines launch ends in a long low-occupancy tail).
-	// lower bound of lanes per warp for small k_build_lines launches (OSB200_LINE_MIN_LANES, default 4; 32 = off).
-	// One 1080p frame (3.8 k lines): 32 / 16 / 8 / 4 / 2 lanes -> 0.338 / 0.285 / 0.240 / 0.207 / 0.203 ms
+	// lower bound of lanes per warp for small k_walk_lines launches (OSB200_LINE_MIN_LANES, default 4; 32 = off).
+	// One 1080p frame (3.8 k lines) with the round-1 kernel: 32 / 16 / 8 / 4 / 2 lanes -> 0.338 / 0.285 / 0.240 / 0.207 / 0.203 ms
 	static int line_min_lanes() {
 		static const int v = [] {
 			const char *e = getenv("OSB200_LINE_MIN_LANES");
@@ -125,14 +38,28 @@ namespace osb {
 		}();
 		return v;
 	}
+	// a warp of k_walk_lines fetches new lines when at least this many of its lanes are idle (OSB200_REFILL_AT, 1..32)
+	static int refill_at() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_REFILL_AT");
+			const int n = e ? atoi(e) : 8;
+			return n < 1 ? 1 : (n > 32 ? 32 : n);
+		}();
+		return v;
+	}
 
+	// Per-chunk working set.  Two of them, each with its own stream, when a batch is cut into chunks (frames going
+	// back to the host: the PCIe copy of chunk k overlaps the kernels of chunk k+1).
 	struct ChunkBufs {
 		float2 *d_lineDirs = nullptr;
-		int4 *d_lineParams = nullptr;
+		float2 *d_lineTan = nullptr;
+		LineRec *d_lineRecs = nullptr;
+		uint32_t *d_active = nullptr;   // compacted list of the lines that survived the pitch cull
+		uint32_t *d_counters = nullptr; // [0] number of active lines, [1] work cursor of k_walk_lines
 		uint2 *d_strips = nullptr;
-		uint32_t *d_lineMask = nullptr; // lineRes bits per line: strip pixels the line wrote
+		uint32_t *d_lineMask = nullptr; // lineRes bits per strip slot: strip pixels the line wrote
 		float *d_tabs = nullptr;
-		size_t lineCap = 0, lineParamCap = 0, stripCap = 0, maskCap = 0, tabCap = 0;
+		size_t lineCap = 0, tanCap = 0, recCap = 0, activeCap = 0, stripCap = 0, maskCap = 0, tabCap = 0;
 		cudaStream_t stream = nullptr;
 		cudaEvent_t done = nullptr; // last kernel of the newest chunk that used this set
 	};
@@ -153,706 +80,21 @@ namespace osb {
 		cudaEvent_t stageFree = nullptr;
 		cudaStream_t copyStream = nullptr; // D2H of finished chunks, overlapped with the next chunk's kernels
 		cudaEvent_t fork = nullptr, copyDone = nullptr;
-	};
-} // namespace osb
-
-namespace osb {
-
-	#ifndef OSB_LINE_THREADS
-#define OSB_LINE_THREADS 64
-#endif
-	constexpr int kLineThreads = OSB_LINE_THREADS; // lines per CTA of k_build_lines
-#ifndef OSB_COLOR_EARLY
-#define OSB_COLOR_EARLY 0
-#endif
-#ifndef OSB_EXP
-#define OSB_EXP 0
-#endif
-#ifndef OSB_RCP_SMEM
-#define OSB_RCP_SMEM 0 // measured on B200: no gain over the L1-cached global table (3.79 vs 3.76 ms), left as a knob
-#endif
-#ifndef OSB_TRANSFORM_BRANCHY
-#define OSB_TRANSFORM_BRANCHY 1
-#endif
-#ifdef OSB_STATS
-	__device__ unsigned long long g_stats[16];
-#define STAT(i, n) atomicAdd(&g_stats[i], (unsigned long long)(n))
-#else
-#define STAT(i, n)
-#endif
-	enum { F_POSX = 0, F_NEGX = 1, F_POSY = 2, F_NEGY = 3, F_POSZ = 4, F_NEGZ = 5 }; // SWMapRenderer.cpp:68
-
-	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map; mode 0 = NegY walls and
-	// tops (NegZ), 1 = PosX/PosY/NegX walls, 2 = undersides (PosZ).  All four 8-bit lanes are shaded in one
-	// register: (x>>1)+(x>>2) <= 190 never carries into the neighbouring lane.
-	template <bool kSse2Shade> __device__ __forceinline__ uint32_t shade(uint32_t col, int mode) {
-		if (kSse2Shade) {
-			// 16-bit lanes B,G,R,H: PosZ >>1; PosX/PosY/NegX (>>1)+(>>2); health<100 >>1; pack; filled bit
-			const bool weak = (col >> 24) < 100u;
-			const uint32_t half = (col >> 1) & 0x7f7f7f7fu, quarter = (col >> 2) & 0x3f3f3f3fu;
-			uint32_t v = mode == 2 ? half : (mode == 1 ? half + quarter : col);
-			v = weak ? (v >> 1) & 0x7f7f7f7fu : v;
-			return __byte_perm(v, 0u, 0x3012) | (1u << 24); // H B G R -> H R G B
-		} else {
-			uint32_t c = __byte_perm(col, 0u, 0x4012); // 0 R G B
-			c = mode == 2 ? (c & 0xfcfcfcu) >> 2 : (mode == 1 ? (c & 0xfefefeu) >> 1 : c);
-			return c | (1u << 24);
-		}
-	}
-
-	constexpr int kRcpSmemBits = 12; // rcpss tables up to 4096 entries (16 KB) are copied into shared memory per CTA
-
-	template <bool kSse> struct LineCtx {
-		osbn::Num<kSse> num;
-		float cz, transScale, transOffset, vmax;
-		uint32_t srcp; // shared-window address of the CTA's copy of the rcpss table, 0 = use the global one
-		// reciprocal for the two hot uses (DDA distance, ToSpecialTan beyond the seam): same value as Num::rcpBig,
-		// table entry fetched with ld.shared when the CTA holds a copy (keeps it out of the thrashed L1)
-		__device__ __forceinline__ float rcpBig(float b) const {
-#if OSB_RCP_SMEM
-			if (kSse && srcp) {
-				const uint32_t u = __float_as_uint(b), e = (u >> 23) & 0xff;
-				uint32_t r;
-				asm volatile("ld.shared.u32 %0, [%1];" : "=r"(r) : "r"(srcp + (((u & 0x7fffff) >> (23 - num.t.rcpBits)) << 2)));
-				if (e >= 253u)
-					return osbn::rcpss(b, num.t);
-				return __uint_as_float((u & 0x80000000u) | (r + ((127u - e) << 23)));
-			}
-#endif
-			return num.rcpBig(b);
-		}
-		// transform lambda, SWMapRenderer.cpp:395-401 (ToSpecialTan :59-66 inlined).  Branch-free: the reciprocal is
-		// always formed and selected by |v| > 1, so lanes on different sides of the seam share one instruction stream.
-		__device__ __forceinline__ int transform(float invDist, int z) const {
-			const float zv = __fsub_rn((float)z, cz);
-			const float v = __fmul_rn(invDist, zv);
-#if OSB_TRANSFORM_BRANCHY
-			float t = v;
-			if (fabsf(v) > 1.f)
-				t = __fsub_rn(v < 0.f ? -2.f : 2.f, rcpBig(v));
-#else
-			const float r = rcpBig(v);
-			float t = v;
-			t = v < -1.f ? __fsub_rn(-2.f, r) : t;
-			t = v > 1.f ? __fsub_rn(2.f, r) : t;
-#endif
-			float p = __fadd_rn(__fmul_rn(t, transScale), transOffset);
-			// p < 0 ? 0 : p;  vmax < p ? vmax : p;  truncation.  p is never NaN here (finite * finite), and a NaN
-			// would end as 0 either way (cvttss2si of the clamp result vs fmaxf dropping the NaN).
-			p = fminf(fmaxf(p, 0.f), vmax);
-			return __float2int_rz(p);
-		}
+		size_t walkSmem[3] = {0, 0, 0};
+		int walkBlocksPerSm[3] = {0, 0, 0}; // resident CTAs of k_walk_lines per SM, per numerics variant (occupancy API)
 	};
 
-	// One thread = one yaw line (SWMapRenderer::BuildLine, SWMapRenderer.cpp:219-671).
-	template <bool kSse, bool kSse2Shade>
-#ifndef OSB_LINE_MINB
-#define OSB_LINE_MINB 14
+#ifndef OSB_WALK_THREADS
+#define OSB_WALK_THREADS 128
 #endif
-#ifndef OSB_STRIP_CLEAR
-#define OSB_STRIP_CLEAR 0
+#ifndef OSB_WALK_MINB
+#define OSB_WALK_MINB 7
 #endif
-#ifndef OSB_PAIR_STORE
-#define OSB_PAIR_STORE 0
-#endif
-#ifndef OSB_MASK_FIRST
-#define OSB_MASK_FIRST 1 // gather: test the written-pixel mask before loading the strip pixel (1: 1.68 ms) or load both at once (0: 1.91 ms)
-#endif
-	__global__ void __launch_bounds__(kLineThreads, OSB_LINE_MINB)
-	  k_build_lines(const ViewParams *__restrict__ views, int nViews, const float2 *__restrict__ lineDirs,
-	                const uint64_t *__restrict__ solid, const uint32_t *__restrict__ color,
-	                osbn::SseTables tabs, uint2 *__restrict__ strips, int4 *__restrict__ lineParams,
-	                uint32_t *__restrict__ lineMask, uint32_t totalLines, int lineRes, int lanesPerWarp) {
-		extern __shared__ uint32_t s_filled[]; // (lineRes/32) words x kLineThreads
-		// lanesPerWarp < 32 (small launches, e.g. one 1080p frame = a few thousand lines): the lines are spread over
-		// more warps and SMs, and a warp's instruction stream is the union of fewer lanes' paths
-		const uint32_t gl = (blockIdx.x * (kLineThreads / 32) + (threadIdx.x >> 5)) * (uint32_t)lanesPerWarp + (threadIdx.x & 31);
-		const int words = lineRes >> 5;
-
-		// LinePixel::Clear = {0, 10000.f} (:89-92).  The strips are NOT cleared in memory: a line publishes the bitmask
-		// of the strip pixels it wrote (lineMask, lineRes bits per line) and the gather substitutes the clear value
-		// for the others -- the clear was 3/4 of this kernel's DRAM writes.  OSB_STRIP_CLEAR=1 restores the clear.
-		{
-#if OSB_STRIP_CLEAR // (needs lanesPerWarp == 32)
-			const uint32_t lineBase = blockIdx.x * kLineThreads;
-			const uint32_t nl = min((uint32_t)kLineThreads, totalLines - lineBase);
-			uint4 *dst = reinterpret_cast<uint4 *>(strips + (size_t)lineBase * lineRes);
-			const uint32_t n4 = nl * (uint32_t)lineRes / 2;
-			const uint4 clr = make_uint4(0u, __float_as_uint(10000.f), 0u, __float_as_uint(10000.f));
-			for (uint32_t i = threadIdx.x; i < n4; i += kLineThreads)
-				__stcs(dst + i, clr);
-#endif
-			for (int w = 0; w < words; w++)
-				s_filled[w * kLineThreads + threadIdx.x] = 0;
-		}
-		// CTA copy of the rcpss table (SSE numerics, table small enough), behind the fill masks
-		uint32_t srcp = 0;
-#if OSB_RCP_SMEM
-		if (kSse && tabs.rcpBits <= kRcpSmemBits) {
-			uint32_t *s_rcp = s_filled + words * kLineThreads;
-			for (int i = threadIdx.x; i < (1 << tabs.rcpBits); i += kLineThreads)
-				s_rcp[i] = __ldg(tabs.rcp + i);
-			srcp = (uint32_t)__cvta_generic_to_shared(s_rcp);
-		}
-#endif
-		__syncthreads();
-		if ((int)(threadIdx.x & 31) >= lanesPerWarp || gl >= totalLines)
-			return;
-
-		// which view does this line belong to (views are few per chunk: binary search on lineBase)
-		int lo = 0, hi = nViews - 1;
-		while (lo < hi) {
-			const int mid = (lo + hi + 1) >> 1;
-			if (views[mid].lineBase <= gl)
-				lo = mid;
-			else
-				hi = mid - 1;
-		}
-		const ViewParams &V = views[lo];
-		uint32_t *filled = s_filled + threadIdx.x;
-		uint2 *strip = strips + (size_t)gl * lineRes;
-		const float2 hd = lineDirs[gl];
-		const float pi = 3.14159274101257324f; // static const float pi = M_PI
-
-		// ---- pitch culling against the four side planes (:232-289) ----
-		osbn::Num<kSse> num{tabs};
-		float minPitch = -pi * 0.4999f, maxPitch = pi * 0.4999f;
-#pragma unroll 1
-		for (int k = 0; k < 4; k++) {
-			const float px = V.frN[k][0], py = V.frN[k][1], pz = V.frN[k][2];
-			if (px == 0.f && py == 0.f) {
-				if (pz > 0.f)
-					minPitch = minPitch < 0.f ? 0.f : minPitch;
-				else
-					maxPitch = 0.f < maxPitch ? 0.f : maxPitch;
-			} else if (pz == 0.f) {
-				// Vector3::Dot(plane, horz) with horz.z = 0: x*x' + y*y' + z*0
-				const float d = __fadd_rn(__fadd_rn(__fmul_rn(px, hd.x), __fmul_rn(py, hd.y)), __fmul_rn(pz, 0.f));
-				if (d < 0.f) {
-					minPitch = 2.f;
-					maxPitch = -2.f;
-				}
-			} else {
-				// prj = (px,py,0).Normalize()
-				float sc = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), 0.f));
-				if (sc != 0.f)
-					sc = __fdiv_rn(1.f, sc);
-				const float qx = __fmul_rn(px, sc), qy = __fmul_rn(py, sc), qz = __fmul_rn(0.f, sc);
-				const float zv = fabsf(pz);
-				const float cs = __fadd_rn(__fadd_rn(__fmul_rn(qx, hd.x), __fmul_rn(qy, hd.y)), __fmul_rn(qz, 0.f));
-				const float cs2 = __fmul_rn(cs, cs);
-				float ang = __fdiv_rn(__fmul_rn(__fmul_rn(zv, zv), __fsub_rn(1.f, cs2)), cs2);
-				ang = __fmul_rn(-cs, num.sqrt(__fadd_rn(1.f, ang)));
-				ang = __fdiv_rn(zv, ang);
-				if (isnan(ang) || isinf(ang) || ang == 0.f)
-					continue;
-				ang = __fdiv_rn(num.sqrt(__fsub_rn(1.f, __fmul_rn(ang, ang))), ang);
-				ang = osbm::atanf_glibc(ang);
-				if (isnan(ang) || isinf(ang))
-					continue;
-				if (pz > 0.f) {
-					const float c = __fsub_rn(ang, 0.01f);
-					minPitch = minPitch < c ? c : minPitch;
-				} else {
-					const float c = __fadd_rn(-ang, 0.01f);
-					maxPitch = c < maxPitch ? c : maxPitch;
-				}
-			}
-		}
-		// SpecialTan (:43-57)
-		auto specialTan = [&](float v) -> float {
-			if (v <= -pi * 0.5f)
-				return -2.f;
-			else if (v < -pi * 0.25f)
-				return __fsub_rn(-2.f, __fdiv_rn(1.f, osbm::tanf_glibc(v)));
-			else if (v < pi * 0.25f)
-				return osbm::tanf_glibc(v);
-			else if (v < pi * 0.5f)
-				return __fsub_rn(2.f, __fdiv_rn(1.f, osbm::tanf_glibc(v)));
-			return 2.f;
-		};
-		const float minTan = specialTan(minPitch);
-		float maxTan = specialTan(maxPitch);
-		{
-			const float minDiff = __fdiv_rn((float)lineRes, 10000.f);
-			if (maxTan < __fadd_rn(minTan, minDiff))
-				maxTan = __fadd_rn(minTan, minDiff);
-		}
-		const float pitchScale = __fdiv_rn((float)lineRes, __fsub_rn(maxTan, minTan));
-		lineParams[gl] = make_int4(__float_as_int(minTan), __float_as_int(pitchScale),
-		                           osbn::x86_f2i(__fmul_rn(minTan, 65536.f)), osbn::x86_f2i(__fmul_rn(pitchScale, 65536.f)));
-		uint32_t *maskOut = lineMask + (size_t)gl * words;
-		if (minPitch >= maxPitch) { // culled: the strip stays cleared (:387-389)
-			for (int w = 0; w < words; w++)
-				maskOut[w] = 0;
-			return;
-		}
-
-		// ---- DDA set-up (:309-351) ----
-		float dirX = hd.x, dirY = hd.y;
-		if (fabsf(dirY) < 1.e-4f)
-			dirY = 1.e-4f;
-		if (fabsf(dirX) < 1.e-4f)
-			dirX = 1.e-4f;
-		const float invDirX = __fdiv_rn(1.f, dirX), invDirY = __fdiv_rn(1.f, dirY);
-		const bool posX = dirX > 0.f, posY = dirY > 0.f;
-		const int invDirXI = abs(osbn::x86_f2i(__fmul_rn(invDirX, 256.f)));
-		const int invDirYI = abs(osbn::x86_f2i(__fmul_rn(invDirY, 256.f)));
-		const uint32_t dirXI = (uint32_t)abs(osbn::x86_f2i(__fmul_rn(dirX, 512.f)));
-		const uint32_t dirYI = (uint32_t)abs(osbn::x86_f2i(__fmul_rn(dirY, 512.f)));
-
-		const float cx = V.origin[0], cy = V.origin[1], cz = V.origin[2];
-		const int icz = osbn::x86_f2i(floorf(cz));
-		int rx = osbn::x86_f2i(__fmul_rn(cx, 512.f)), ry = osbn::x86_f2i(__fmul_rn(cy, 512.f));
-		int irx = rx >> 9, iry = ry >> 9;
-
-		const float fogDist = 128.f;
-		float distance = 1.e-20f;
-		float invDist = __fdiv_rn(1.f, distance);
-
-		LineCtx<kSse> L;
-		L.num = num;
-		L.cz = cz;
-		L.transScale = pitchScale; // same expression as line.pitchScale (:303,358)
-		L.transOffset = __fmul_rn(-minTan, L.transScale);
-		L.vmax = __fadd_rn((float)lineRes, 0.5f);
-		L.srcp = srcp;
-
-		// zscale = Dot(horizonDir, viewAxis[2]) (horizonDir.z = 0), heightScale, depthBias (:403-414)
-		const float zscale = __fadd_rn(__fadd_rn(__fmul_rn(hd.x, V.front[0]), __fmul_rn(hd.y, V.front[1])),
-		                               __fmul_rn(0.f, V.front[2]));
-		const float heightScale = V.front[2];
-		const float depthBias = __fmul_rn(-cz, heightScale);
-
-		// z > icz / z < icz as bit masks
-		const uint64_t belowEye = icz >= 63 ? 0ull : (icz < 0 ? ~0ull : (~0ull << (icz + 1)));
-		const uint64_t aboveEye = icz <= 0 ? 0ull : (icz >= 64 ? ~0ull : ((1ull << icz) - 1ull));
-
-		uint32_t tOld = tiled_index(irx & 511, iry & 511);
-		uint64_t sOld = solid[tOld];
-		int count = 1;
-		uint32_t cnt2 = 1024; // static_cast<int>(fogDist * 8.f)
-
-		// One DDA step (:426-522) depends only on (rx, ry), never on map data, so the step after the current
-		// one is computed ahead and its column mask is requested before the current step's spans are
-		// processed: the dependent 8-byte load is off the critical path.  Both crossing cases are formed with
-		// selects so that lanes crossing x and lanes crossing y stay in one instruction stream.
-		struct Step {
-			int rx, ry, irx, iry, wallMode;
-			float distance;
-			uint32_t t;
-		};
-		const int sx = posX ? 1 : -1, sy = posY ? 1 : -1;
-		const int edgeX = posX ? 0 : 1, edgeY = posY ? 0 : 1;
-		// wall face of an x crossing is NegX / PosX (both 3/4-shaded, mode 1); of a y crossing NegY (mode 0) / PosY (1)
-		const int wallModeY = posY ? 0 : 1;
-		auto advance = [&](int rx0, int ry0, int irx0, int iry0, float dist0) -> Step {
-			Step n;
-			const uint32_t tx = (uint32_t)((posX ? 512 - (rx0 & 511) : (rx0 & 511)) * invDirXI);
-			const uint32_t ty = (uint32_t)((posY ? 512 - (ry0 & 511) : (ry0 & 511)) * invDirYI);
-			const bool xs = tx < ty;
-			const uint32_t tt = xs ? tx : ty;
-			const int d = (int)(((xs ? dirYI : dirXI) * tt) >> 17);
-			n.irx = irx0 + (xs ? sx : 0);
-			n.iry = iry0 + (xs ? 0 : sy);
-			n.rx = xs ? (n.irx << 9) - edgeX : rx0 + sx * d;
-			n.ry = xs ? ry0 + sy * d : (n.iry << 9) - edgeY;
-			n.distance = __fadd_rn(dist0, __fmul_rn((float)tt, 1.f / 512.f / 256.f));
-			n.wallMode = xs ? 1 : wallModeY;
-			n.t = tiled_index(n.irx & 511, n.iry & 511);
-			return n;
-		};
-		Step nx = advance(rx, ry, irx, iry, distance);
-		uint64_t sNext = solid[nx.t];
-
-		while (distance < fogDist && (--cnt2) > 0) {
-			// ---- take the precomputed step, start the one after it ----
-			const Step cur = nx;
-			const uint64_t sNew = sNext;
-			STAT(0, 1);
-			distance = cur.distance;
-			nx = advance(cur.rx, cur.ry, cur.irx, cur.iry, cur.distance);
-			sNext = solid[nx.t];
-			const uint32_t tNew = cur.t;
-
-			const float oldInvDist = invDist;
-			invDist = L.rcpBig(distance); // distance is in [1e-20, ~200]
-			const float medDist = __fadd_rn(__fmul_rn(distance, zscale), depthBias);
-
-			// ---- spans of this step, one merged work list per lane, in the reference's order:
-			//   floor tops of the cell being left (ascending z, :584-603), its ceilings (descending z, :604-622),
-			//   then the walls of the cell being entered for the crossed face (ascending z, :627-657).
-			// One loop body serves all three kinds (ceilings are kept bit-reversed so that "next" is always the
-			// lowest set bit), and everything up to the landing test is straight-line code.
-			uint64_t tops = sOld & ~(sOld << 1) & belowEye;                                // solid, air above, below the eye
-			uint64_t botsR = __brevll(sOld & ~(sOld >> 1) & ~(1ull << 63) & aboveEye);      // solid, air below, above the eye
-			uint64_t walls = sNew & ~sOld;                                                  // solid there, air in the cell left
-			while (tops | botsR | walls) {
-				const bool isTop = tops != 0, isBot = !isTop && botsR != 0;
-				const uint64_t src = isTop ? tops : (isBot ? botsR : walls);
-				const int bit = __ffsll((long long)src) - 1;
-				const uint64_t rest = src & (src - 1);
-				tops = isTop ? rest : tops;
-				botsR = isBot ? rest : botsR;
-				walls = (isTop || isBot) ? walls : rest;
-				const int z = isBot ? 63 - bit : bit;
-				const bool isWall = !(isTop || isBot);
-#if OSB_COLOR_EARLY
-				// colour is requested before the projection math; it is only used when the span lands
-				const uint32_t rawCol = color[(size_t)(isWall ? tNew : tOld) * 64 + z];
-#endif
-				const int zA = isBot ? z + 1 : z;      // first transform: (invDist, zA)
-				const int zB = isTop ? z : z + 1;      // second: (oldInvDist or invDist, zB)
-				const int pA = L.transform(invDist, zA);
-				const int pB = L.transform(isWall ? invDist : oldInvDist, zB);
-				const int from = isBot ? pB : pA, to = isBot ? pA : pB;
-				if (from < to) {
-					const int w0 = from >> 5, w1 = (to - 1) >> 5;
-					const uint32_t mFirst = 0xffffffffu << (from & 31), mLast = 0xffffffffu >> (31 - ((to - 1) & 31));
-					uint2 px;
-					bool havePx = false;
-					for (int w = w0; w <= w1; w++) {
-						uint32_t m = 0xffffffffu;
-						m = w == w0 ? m & mFirst : m;
-						m = w == w1 ? m & mLast : m;
-						const uint32_t curMask = filled[w * kLineThreads];
-						uint32_t todo = m & ~curMask;
-						if (!todo)
-							continue;
-						filled[w * kLineThreads] = curMask | todo;
-						if (!havePx) {
-#if OSB_EXP == 1
-							const uint32_t rawCol = 0x64000000u | (uint32_t)z * 0x030201u;
-#elif !OSB_COLOR_EARLY
-							const uint32_t rawCol = color[(size_t)(isWall ? tNew : tOld) * 64 + z];
-#endif
-							const int mode = isTop ? 0 : (isBot ? 2 : cur.wallMode);
-							px = make_uint2(shade<kSse2Shade>(rawCol, mode),
-							                __float_as_uint(__fadd_rn(medDist, __fmul_rn((float)zA, heightScale))));
-							havePx = true;
-						}
-						uint2 *dst = strip + (w << 5);
-#if OSB_PAIR_STORE
-						// two adjacent strip pixels (even-aligned) go out as one 16-byte store
-						uint32_t pairs = todo & (todo >> 1) & 0x55555555u;
-						todo &= ~(pairs | (pairs << 1));
-						const uint4 px2 = make_uint4(px.x, px.y, px.x, px.y);
-						while (pairs) {
-							const int b = __ffs(pairs) - 1;
-							pairs &= pairs - 1;
-							__stcs(reinterpret_cast<uint4 *>(dst + b), px2);
-						}
-						while (todo) {
-							const int b = __ffs(todo) - 1;
-							todo &= todo - 1;
-							__stcs(dst + b, px);
-						}
-#else
-						do {
-							const int b = __ffs(todo) - 1;
-							todo &= todo - 1;
-#if OSB_EXP == 2
-							if (px.x == 0xdeadbeefu)
-#endif
-							__stcs(dst + b, px);
-						} while (todo);
-#endif
-					}
-				}
-			}
-			sOld = sNew;
-			tOld = tNew;
-			// ---- pitch cull every 4th step (:661-667) ----
-			if ((--count) == 0) {
-				if ((L.transform(invDist, 0) >= lineRes - 1 && icz >= 0) || L.transform(invDist, 63) <= 0)
-					break;
-				count = 4;
-			}
-		}
-		for (int w = 0; w < words; w++)
-			maskOut[w] = filled[w * kLineThreads];
-	}
-
-	// ---- fastATan / fastATan2 (SWMapRenderer.cpp:697-742); tab = sm | lg | smN | lgN, 5000 each ----
-	template <bool kSse>
-	__device__ __forceinline__ uint32_t fast_atan(const osbn::Num<kSse> &num, const uint16_t *__restrict__ tab, float v) {
-		int idx, base;
-		if (v < 0.f) {
-			if (v > -1.f) {
-				idx = osbn::x86_f2i(__fmul_rn(v, -4096.f));
-				base = 10000;
-			} else {
-				idx = osbn::x86_f2i(num.div(-4096.f, v));
-				base = 15000;
-			}
-		} else {
-			if (v < 1.f) {
-				idx = osbn::x86_f2i(__fmul_rn(v, 4096.f));
-				base = 0;
-			} else {
-				idx = osbn::x86_f2i(num.div(4096.f, v));
-				base = 5000;
-			}
-		}
-		idx = min(max(idx, 0), 4999); // memory safety only; in range for every finite input
-		return __ldg(tab + base + idx);
-	}
-	template <bool kSse>
-	__device__ __forceinline__ uint32_t fast_atan2(const osbn::Num<kSse> &num, const uint16_t *__restrict__ tab, float y,
-	                                               float x) {
-		if (x == 0.f)
-			return y > 0.f ? 16384u : 49152u; // (uint16_t)-16384
-		else if (x > 0.f)
-			return fast_atan(num, tab, num.div(y, x));
-		return (fast_atan(num, tab, num.div(y, x)) + 32768u) & 0xffffu;
-	}
-
-	constexpr int kGatherWarps = 4;
-	constexpr int kSegRows = 8; // 8x8 blocks per warp task (vertical)
-
-	// truncating (C) division by 2^sh without the 40-instruction generic idiv
-	__device__ __forceinline__ int tdiv_pow2(int x, int sh) { return (x + ((x >> 31) & ((1 << sh) - 1))) >> sh; }
-
-	// ApplyFog blend of one pixel (SWRenderer.cpp:381-407 scalar, :462-510 SSE2).  col = B | G<<8 | R<<16 | X<<24.
-	// B and R share one multiply: each 8-bit channel times a factor <= 256 stays below 2^16.
-	template <bool kSse2Fog>
-	__device__ __forceinline__ uint32_t fog_blend(uint32_t col, float dist, uint32_t fogBR, uint32_t fogG8) {
-		int factor;
-		if (kSse2Fog) {
-			float d = dist > 0.f ? dist : 0.f; // maxps / minps return the 2nd operand on NaN
-			d = d < 256.f ? d : 256.f;
-			factor = osbn::x86_f2i_rn(d);
-		} else {
-			factor = min(osbn::x86_f2i(dist), 256);
-			factor = max(0, factor);
-		}
-		const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
-		const uint32_t br = (((col & 0x00ff00ffu) * f2 + fogBR * f1) >> 8) & 0x00ff00ffu;
-		const uint32_t gg = (((col & 0x0000ff00u) * f2 + fogG8 * f1) >> 8) & 0x0000ff00u;
-		uint32_t out = br | gg;
-		if (kSse2Fog) // lane 3 of the SSE2 path keeps (X * f2) >> 8
-			out |= (((col >> 24) * f2) << 16) & 0xff000000u;
-		return out;
-	}
-
-	// RenderFinal + ApplyFog.  One warp per (view, 32-pixel column group = four 8x8 block columns, segment of
-	// kSegRows block rows); one lane per pixel column, so every row is written as one 128-byte run per buffer.
-	// Per block row the 16 block corners (4 blocks x 4) are evaluated by 16 lanes in one instruction stream
-	// and shared by shuffle; per pixel only the reference's integer interpolation, the gather and the blend remain.
-	template <bool kSse, bool kSse2Fog>
-	// (a min-blocks bound was measured and is not used: 10 / 12 / 16 CTAs per SM spill, 1.85 / 1.94 / 2.04 ms; and an explicit
-	// bound of 1 lets ptxas take more registers than the plain form below: 1.90 vs 1.68 ms)
-	__global__ void __launch_bounds__(kGatherWarps * 32)
-	  k_gather_fog(const ViewParams *__restrict__ views, int nViews, FrameGeom g, const float *__restrict__ tabs,
-	               const uint64_t *__restrict__ solid, const uint16_t *__restrict__ atanTab, osbn::SseTables sse,
-	               const uint2 *__restrict__ strips, const int4 *__restrict__ lineParams,
-	               const uint32_t *__restrict__ lineMask, int lineRes, uint32_t *__restrict__ fb,
-	               float *__restrict__ depthBuf) {
-		__shared__ float s_fog[kGatherWarps][kSegRows * 2][8];
-		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-		const int colBlocks = g.fw >> 3, rowBlocks = g.fh >> 3;
-		const int colGroups = (colBlocks + 3) >> 2;
-		const int segs = (rowBlocks + kSegRows - 1) / kSegRows;
-		const uint32_t task = blockIdx.x * kGatherWarps + wid;
-		const uint32_t perView = (uint32_t)colGroups * segs;
-		if (task >= perView * (uint32_t)nViews)
-			return;
-		const int vi = task / perView;
-		const uint32_t rem = task - (uint32_t)vi * perView;
-		const int seg = rem / colGroups, cg = rem - seg * colGroups;
-		const ViewParams &V = views[vi];
-		osbn::Num<kSse> num{sse};
-		const float *vxTab = tabs + V.tabBase, *vyTab = vxTab + (g.fw >> 2), *v1Tab = vyTab + (g.fh >> 2);
-		uint32_t *fbV = fb + (size_t)vi * g.fw * g.fh;
-		float *dbV = depthBuf + (size_t)vi * g.fw * g.fh;
-		const int by0 = seg * kSegRows, by1 = min(by0 + kSegRows, rowBlocks);
-
-		const int bx = (cg << 2) + (lane >> 3);  // this lane's block column
-		const bool colValid = bx < colBlocks;    // a partial last group when fw is not a multiple of 32
-		const int bxc = colValid ? bx : colBlocks - 1;
-		const int px = lane & 7;                 // pixel column inside the block
-		const int x = (bxc << 3) + px;
-
-		// SWMapRenderer::Render :1181-1184: eye inside a solid voxel (or no map at all) -> terrain skipped, fb keeps
-		// the clear colour and the depth buffer keeps its previous contents
-		bool skip;
-		{
-			const int ex = osbn::x86_f2i(floorf(V.origin[0])), ey = osbn::x86_f2i(floorf(V.origin[1])),
-			          ez = osbn::x86_f2i(floorf(V.origin[2]));
-			skip = g.noMap || ez >= 64 || (ez >= 0 && ((solid[tiled_index(ex & 511, ey & 511)] >> ez) & 1ull));
-		}
-
-		// ---- fog scale of every 4x4 pixel block this task covers (SWRenderer.cpp:372-380) ----
-		{
-			const int nRows4 = (by1 - by0) * 2;
-			for (int i = lane; i < nRows4 * 8; i += 32) {
-				const int r4 = i >> 3, c4 = i & 7;
-				const int cx4 = min((cg << 3) + c4, (g.fw >> 2) - 1);
-				const float vx = vxTab[cx4], vy = vyTab[(by0 << 1) + r4];
-				float ds = __fadd_rn(__fadd_rn(1.f, __fmul_rn(vx, vx)), __fmul_rn(vy, vy));
-				ds = __fmul_rn(ds, __fmul_rn(num.rsqrt(ds), V.fogScale));
-				s_fog[wid][r4][c4] = ds;
-			}
-			__syncwarp();
-		}
-		const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
-
-		// per-view deltas (:757-775)
-		const int under = g.under, hSh = under == 1 ? 3 : (under == 2 ? 2 : 1); // log2(8 / under)
-		const int pxq = px - (px % under), xs = pxq / under; // undersampling: pixels share their group leader's sample
-		const float sD = __fdiv_rn(__fmul_rn(V.fovYt, 2.f), (float)g.fh);
-		const float sR = __fmul_rn(__fdiv_rn(__fmul_rn(V.fovXt, 2.f), (float)g.fw), (float)under);
-		float dD[3], dR[3], dDL[3], dRL[3], v2[3];
-#pragma unroll
-		for (int k = 0; k < 3; k++) {
-			dD[k] = __fmul_rn(-V.up[k], sD);
-			dR[k] = __fmul_rn(V.right[k], sR);
-			dDL[k] = __fmul_rn(dD[k], 8.f);
-			dRL[k] = __fmul_rn(dR[k], (float)(8 / under));
-			v2[k] = v1Tab[bxc * 3 + k];
-		}
-		for (int i = 0; i < by0; i++) { // replay v2 += deltaDownLarge (:1037)
-#pragma unroll
-			for (int k = 0; k < 3; k++)
-				v2[k] = __fadd_rn(v2[k], dDL[k]);
-		}
-		const uint32_t numLines = (uint32_t)V.numLines;
-		const uint32_t yawScale2 = (uint32_t)V.yawScale2;
-		const int yawMin2 = V.yawMin2;
-		const int lineShift = 31 - __clz(lineRes);
-		const uint2 *stripsV = strips + (size_t)V.lineBase * lineRes;
-		const uint32_t *maskV = lineMask + (size_t)V.lineBase * (lineRes >> 5); // written strip pixels, bit per pixel
-		const uint2 kClearPix = make_uint2(0u, __float_as_uint(10000.f));       // LinePixel::Clear
-		const int4 *lpV = lineParams + V.lineBase;
-		const int blkLane = lane & ~7;
-
-		for (int by = by0; by < by1; by++) {
-			size_t o = (size_t)(by * 8) * g.fw + x;
-			const float *fogRow = &s_fog[wid][(by - by0) * 2][lane >> 2];
-			if (skip) {
-				if (colValid) {
-#pragma unroll
-					for (int py = 0; py < 8; py++, o += g.fw) {
-						const float dep = dbV[o];
-						fbV[o] = g.noFog ? 0x7f7f7fu : fog_blend<kSse2Fog>(0x7f7f7fu, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8);
-					}
-				}
-				continue;
-			}
-			const bool slow = v2[2] > 0.99f || v2[2] < -0.99f; // uniform within a block (8 lanes)
-			// ---- block corners: lanes 0..3 of every block (:810-835) ----
-			int yaw = 0, pit = 0;
-			if (px < 4 && !slow) {
-				const int cr = px & 1, cd = (px >> 1) & 1;
-				float c[3];
-#pragma unroll
-				for (int k = 0; k < 3; k++) {
-					c[k] = v2[k];
-					if (cr)
-						c[k] = __fadd_rn(c[k], dRL[k]);
-					if (cd)
-						c[k] = __fadd_rn(c[k], dDL[k]);
-				}
-				yaw = (int)((((int)fast_atan2(num, atanTab, c[1], c[0]) - yawMin2) & 0xffff) << 8);
-				float pitch = __fmul_rn(c[2], num.rsqrt(__fadd_rn(__fmul_rn(c[0], c[0]), __fmul_rn(c[1], c[1]))));
-				pitch = num.toSpecialTan(pitch);
-				pit = osbn::x86_f2i(__fmul_rn(pitch, 65536.f * 8192.f));
-			}
-			const int yaw1 = __shfl_sync(0xffffffffu, yaw, blkLane), yaw2 = __shfl_sync(0xffffffffu, yaw, blkLane + 1);
-			const int yaw3 = __shfl_sync(0xffffffffu, yaw, blkLane + 2), yaw4 = __shfl_sync(0xffffffffu, yaw, blkLane + 3);
-			const int pit1 = __shfl_sync(0xffffffffu, pit, blkLane), pit2 = __shfl_sync(0xffffffffu, pit, blkLane + 1);
-			const int pit3 = __shfl_sync(0xffffffffu, pit, blkLane + 2), pit4 = __shfl_sync(0xffffffffu, pit, blkLane + 3);
-			if (colValid) {
-				if (!slow) {
-					// bilinear interpolation in integers; `<<8>>8` is the reference's phase unwrap (:837-881)
-					const int yawDiff1 = tdiv_pow2(((yaw2 - yaw1) << 8) >> 8, hSh), yawDiff2 = tdiv_pow2(((yaw4 - yaw3) << 8) >> 8, hSh);
-					const int pitDiff1 = tdiv_pow2(pit2 - pit1, hSh), pitDiff2 = tdiv_pow2(pit4 - pit3, hSh);
-					const int yawA = yaw1 + xs * yawDiff1, yawB = yaw3 + xs * yawDiff2;
-					const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
-					const int dYaw = tdiv_pow2(((yawB - yawA) << 8) >> 8, 3), dPit = tdiv_pow2(pitB - pitA, 3);
-					int yawC = yawA, pitC = pitA;
-#pragma unroll
-					for (int py = 0; py < 8; py++, o += g.fw, yawC += dYaw, pitC += dPit) {
-						uint32_t yawIndex = (uint32_t)((yawC << 8) >> 16);
-						yawIndex = (yawIndex * yawScale2) >> 16;
-						yawIndex = (yawIndex * numLines) >> 16;
-						yawIndex = min(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
-						const int4 lp = __ldg(lpV + yawIndex);
-						int pitchIndex = (pitC >> 13) - lp.z;
-						pitchIndex = __mulhi(pitchIndex, lp.w);
-						pitchIndex &= lineRes - 1;
-#if OSB_STRIP_CLEAR
-						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-#elif OSB_MASK_FIRST
-						const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
-						uint2 pix = kClearPix;
-						if ((mw >> (pitchIndex & 31)) & 1u)
-							pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-#else
-						uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-						{
-							const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
-							pix = ((mw >> (pitchIndex & 31)) & 1u) ? pix : kClearPix;
-						}
-#endif
-						const float dep = __uint_as_float(pix.y);
-						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
-						__stcs(dbV + o, dep);
-					}
-				} else {
-					// exact per-pixel path near the poles (:940-1033)
-					float v4[3];
-#pragma unroll
-					for (int k = 0; k < 3; k++)
-						v4[k] = v2[k];
-					for (int i = 0; i < xs; i++) {
-#pragma unroll
-						for (int k = 0; k < 3; k++)
-							v4[k] = __fadd_rn(v4[k], dR[k]);
-					}
-#pragma unroll 1
-					for (int py = 0; py < 8; py++, o += g.fw) {
-						uint32_t yawIndex = (uint32_t)(((int)fast_atan2(num, atanTab, v4[1], v4[0]) - yawMin2) & 0xffff);
-						yawIndex = (yawIndex * yawScale2) >> 16;
-						yawIndex = (yawIndex * numLines) >> 16;
-						yawIndex = min(yawIndex, numLines - 1);
-						const int4 lp = __ldg(lpV + yawIndex);
-						float pitch = __fmul_rn(v4[2], num.rsqrt(__fadd_rn(__fmul_rn(v4[0], v4[0]), __fmul_rn(v4[1], v4[1]))));
-						pitch = num.toSpecialTan(pitch);
-						pitch = __fmul_rn(__fsub_rn(pitch, __int_as_float(lp.x)), __int_as_float(lp.y));
-						const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
-#if OSB_STRIP_CLEAR
-						const uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-#elif OSB_MASK_FIRST
-						const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
-						uint2 pix = kClearPix;
-						if ((mw >> (pitchIndex & 31)) & 1u)
-							pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-#else
-						uint2 pix = __ldg(stripsV + (((size_t)yawIndex << lineShift) + pitchIndex));
-						{
-							const uint32_t mw = __ldg(maskV + (((size_t)yawIndex << (lineShift - 5)) + (pitchIndex >> 5)));
-							pix = ((mw >> (pitchIndex & 31)) & 1u) ? pix : kClearPix;
-						}
-#endif
-						const float dep = __uint_as_float(pix.y);
-						__stcs(fbV + o, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, __fmul_rn(dep, fogRow[(py >> 2) * 8]), fogBR, fogG8));
-						__stcs(dbV + o, dep);
-#pragma unroll
-						for (int k = 0; k < 3; k++)
-							v4[k] = __fadd_rn(v4[k], dD[k]);
-					}
-				}
-			}
-#pragma unroll
-			for (int k = 0; k < 3; k++)
-				v2[k] = __fadd_rn(v2[k], dDL[k]);
-		}
-	}
+	constexpr int kWalkThreads = OSB_WALK_THREADS; // lanes (= lines in flight) per CTA of k_walk_lines
+	constexpr int kSetupThreads = 128;
 
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
-	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs,
-	                            float *tabs) {
+	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs, float *tabs) {
 		const int vi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 		const int lane = threadIdx.x & 31;
 		if (vi >= nViews)
@@ -868,6 +110,106 @@ namespace osb {
 			prep_fog_vy(V, g, t, vy);
 		for (int t = 31 - lane; t < g.swThreads; t += 32)
 			prep_v1(V, g, t, v1);
+	}
+
+	// One thread per yaw line (blockIdx.y = view): pitch cull, records, compaction of the surviving lines.
+	template <bool kSse>
+	__global__ void __launch_bounds__(kSetupThreads)
+	  k_line_setup(const ViewParams *__restrict__ views, const float2 *__restrict__ lineDirs, osbn::SseTables tabs, int lineRes,
+	               int noMap, LineRec *__restrict__ lineRecs, float2 *__restrict__ lineTan, uint32_t *__restrict__ active,
+	               uint32_t *__restrict__ counters) {
+		const int vi = blockIdx.y;
+		const ViewParams &V = views[vi];
+		const int l = blockIdx.x * kSetupThreads + threadIdx.x;
+		const bool valid = l < V.numLines;
+		const uint32_t gl = V.lineBase + (uint32_t)(valid ? l : 0);
+		LineSetupOut o;
+		o.minTan = 0.f;
+		o.pitchScale = 0.f;
+		o.culled = true;
+		if (valid && !noMap) {
+			osbn::Num<kSse> num{tabs};
+			o = line_setup<kSse>(V, lineDirs[gl], lineRes, num);
+		}
+		// surviving lines of the warp take consecutive strip slots: one atomic per warp
+		const unsigned live = __ballot_sync(0xffffffffu, valid && !o.culled);
+		const int lane = threadIdx.x & 31;
+		uint32_t base = 0;
+		if (live && lane == 0)
+			base = atomicAdd(counters, (uint32_t)__popc(live));
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if (!valid)
+			return;
+		int slot = -1;
+		if (!o.culled) {
+			slot = (int)(base + (uint32_t)__popc(live & ((1u << lane) - 1u)));
+			active[slot] = gl;
+		}
+		lineRecs[gl] = make_line_rec(o, slot, vi);
+		lineTan[gl] = make_float2(o.minTan, o.pitchScale);
+	}
+
+	// Persistent line walker.  Lane = one yaw line at a time; the warp refills its idle lanes from the chunk-wide cursor.
+	template <bool kSse, bool kSse2Shade>
+	__global__ void __launch_bounds__(kWalkThreads, OSB_WALK_MINB)
+	  k_walk_lines(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, uint32_t *__restrict__ counters,
+	               int laneLimit, int refillAt) {
+		extern __shared__ uint32_t s_filled[]; // (lineRes/32 + kWalkExtraWords) words x kWalkThreads, word-major: bank = lane
+		uint32_t *filled = s_filled + threadIdx.x;
+		const int lane = threadIdx.x & 31;
+		const osbn::Num<kSse> num{tabs};
+		const uint32_t count = counters[0]; // written by k_line_setup, earlier on this stream
+		const unsigned workMask = laneLimit >= 32 ? 0xffffffffu : ((1u << laneLimit) - 1u);
+		LineWalker<kSse, kSse2Shade> W;
+		bool alive = false, exhausted = false;
+		for (;;) {
+			unsigned live = __ballot_sync(0xffffffffu, alive);
+			if (!exhausted) {
+				const unsigned idle = ~live & workMask;
+				const int n = __popc(idle);
+				if (n && (live == 0 || n >= refillAt)) {
+					uint32_t base = 0;
+					if (lane == 0)
+						base = atomicAdd(counters + 1, (uint32_t)n);
+					base = __shfl_sync(0xffffffffu, base, 0);
+					exhausted = base + (uint32_t)n >= count;
+					if ((idle >> lane) & 1u) {
+						const uint32_t idx = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
+						if (idx < count) {
+							W.init(io, __ldg(active + idx), idx, filled, kWalkThreads);
+							alive = true;
+						}
+					}
+					live = __ballot_sync(0xffffffffu, alive);
+				}
+			}
+			if (live == 0)
+				break;
+			if (alive)
+				alive = W.step(io, num, filled, kWalkThreads);
+		}
+	}
+
+	// RenderFinal + ApplyFog, see GatherLane in terrain_core.cuh
+	template <bool kSse, bool kSse2Fog>
+	__global__ void __launch_bounds__(kGatherWarps * 32) k_gather_fog(GatherIO io, osbn::SseTables tabs) {
+		__shared__ GatherShared s_g[kGatherWarps];
+		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+		const uint32_t task = blockIdx.x * kGatherWarps + wid;
+		const osbn::Num<kSse> num{tabs};
+		GatherShared &sm = s_g[wid];
+		GatherLane<kSse, kSse2Fog> L;
+		if (!L.init(io, task, lane)) // whole warp
+			return;
+		L.fog_phase(io, num, sm, lane);
+		__syncwarp();
+		for (int by = L.by0; by < L.by1; by += 2) {
+			L.corner_phase(io, num, sm, lane, by);
+			__syncwarp();
+			L.pixel_phase(io, num, sm, 0, by);
+			L.pixel_phase(io, num, sm, 1, by);
+			__syncwarp();
+		}
 	}
 
 	static int terrain_init(osb200_ctx *c) {
@@ -910,7 +252,10 @@ namespace osb {
 		cudaFreeHost(T->h_views);
 		for (ChunkBufs &b : T->set) {
 			cudaFree(b.d_lineDirs);
-			cudaFree(b.d_lineParams);
+			cudaFree(b.d_lineTan);
+			cudaFree(b.d_lineRecs);
+			cudaFree(b.d_active);
+			cudaFree(b.d_counters);
 			cudaFree(b.d_strips);
 			cudaFree(b.d_lineMask);
 			cudaFree(b.d_tabs);
@@ -936,70 +281,6 @@ namespace osb {
 		c->terrain = nullptr;
 	}
 
-	// Host half of RenderInner (SWMapRenderer.cpp:1057-1133) + BuildFrustrum (SWRenderer.cpp:207-227) +
-	// ApplyFog's scalars (SWRenderer.cpp:345-357) for one view, with the host libm.
-	static void fill_view(const osb200_scene &s, int fw, int fh, int under, float fogDist, ViewParams &v) {
-		static const float pi = M_PI;
-		std::memset(&v, 0, sizeof(v));
-		for (int k = 0; k < 3; k++) {
-			v.origin[k] = s.origin[k];
-			v.right[k] = s.axis[0][k];
-			v.up[k] = s.axis[1][k];
-			v.front[k] = s.axis[2][k];
-		}
-		const float xCos = cosf(s.fovX * .5f), xSin = sinf(s.fovX * .5f);
-		const float yCos = cosf(s.fovY * .5f), ySin = sinf(s.fovY * .5f);
-		for (int k = 0; k < 3; k++) {
-			v.frN[0][k] = v.front[k] * xSin - v.right[k] * xCos;
-			v.frN[1][k] = v.front[k] * xSin + v.right[k] * xCos;
-			v.frN[2][k] = v.front[k] * ySin - v.up[k] * yCos;
-			v.frN[3][k] = v.front[k] * ySin + v.up[k] * yCos;
-		}
-		const float fovX = tanf(s.fovX * 0.5f), fovY = tanf(s.fovY * 0.5f);
-		v.fovXt = fovX;
-		v.fovYt = fovY;
-		const float fovDiag = sqrtf(fovX * fovX + fovY * fovY);
-		const float fovDiagAng = atanf(fovDiag);
-		const float pitch = asinf(v.front[2]);
-		float yawMin, yawMax;
-		if (fabsf(pitch) >= pi * 0.49f - fovDiagAng) { // pole is visible
-			yawMin = 0.f;
-			yawMax = pi * 2.f;
-		} else {
-			const float yaw = atan2l(v.front[1], v.front[0]);
-			yawMin = yaw - pi * .5f;
-			yawMax = yaw + pi * .5f;
-		}
-		float interval = static_cast<float>(fh);
-		interval = fovY * 2.f / interval;
-		int lineRes = fh;
-		for (int i = lineRes, j = 1; j <= i; j <<= 1)
-			lineRes = j;
-		size_t numLines = static_cast<size_t>((yawMax - yawMin) / interval);
-		numLines /= under;
-		if (numLines < 8)
-			numLines = 8;
-		if (numLines > 65536)
-			numLines = 65536;
-		v.yawMin = yawMin;
-		v.yawMax = yawMax;
-		v.numLines = (int)numLines;
-		v.lineRes = lineRes;
-		const float scl = (yawMax - yawMin) / numLines;
-		v.cosYawMin = cosf(yawMin);
-		v.sinYawMin = sinf(yawMin);
-		v.cosScl = cosf(scl);
-		v.sinScl = sinf(scl);
-		const float yawScale = 65536.f / (pi * 2.f);
-		v.yawScale2 = static_cast<int32_t>(pi * 2.f / (yawMax - yawMin) * 65536.f);
-		v.yawMin2 = static_cast<int32_t>(yawMin * yawScale);
-		v.fogScale = 255.f / fogDist;
-		v.dvx = -fovX * 2.f / static_cast<float>(fw / 4);
-		v.dvy = -fovY * 2.f / static_cast<float>(fh / 4);
-	}
-} // namespace osb
-
-namespace osb {
 	template <class T> static int grow(T *&p, size_t &cap, size_t want, bool pinned = false) {
 		if (want <= cap)
 			return 0;
@@ -1011,7 +292,7 @@ namespace osb {
 		}
 		p = nullptr;
 		cap = 0;
-		size_t n = want + (want >> 2);
+		size_t n = want + (want >> 3);
 		if (pinned)
 			OSB_CUDA(cudaMallocHost((void **)&p, n * sizeof(T)));
 		else
@@ -1025,11 +306,11 @@ namespace osb {
 		long mb = e ? atol(e) : 0;
 		return (size_t)(mb > 0 ? mb : dflt) << 20;
 	}
-	// Strip bytes per chunk.  Measured on B200: every launch ends in a latency-bound tail, so chunks must be large
-	// for the tail to be small against the launch, and there must be several of them for the two streams to overlap
-	// one chunk's tail with the other chunk's kernels.
+	// Strip bytes per chunk, sized for the worst case (every yaw line of the chunk survives the pitch cull; on the
+	// headline batch about 40 % do, and only those pages are ever touched).  A 4096-view batch of 256x256 is 6.7 GB of
+	// strip address space: one chunk on a 180 GB part.
 	static size_t strip_budget_bytes() {
-		static size_t v = env_mb("OSB200_STRIP_MB", 3072);
+		static size_t v = env_mb("OSB200_STRIP_MB", 12288);
 		return v;
 	}
 	static bool dual_stream() {
@@ -1039,6 +320,15 @@ namespace osb {
 			v = e ? atoi(e) != 0 : 1;
 		}
 		return v != 0;
+	}
+
+	template <class K> static int resident_blocks(K kernel, int threads, size_t smem) {
+		int nb = 0;
+		if (smem > 48 * 1024) // strips of 2048+ pixels (frames 2048+ rows high)
+			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, smem) != cudaSuccess || nb < 1)
+			nb = 1;
+		return nb;
 	}
 
 	// host_fb / host_depth (nullable): when given, each chunk's finished frames are copied to the host on a second
@@ -1096,16 +386,14 @@ namespace osb {
 			fill_view(scenes[i], w, h, under, fogDist, T->h_views[i]);
 			lineRes = T->h_views[i].lineRes;
 		}
-		// ---- chunking: strips of one chunk must fit the budget; chunks are made equal (the two streams overlap
-		// best with equal partners), and a large batch is split in two even when it would fit one chunk ----
+		const int words = lineRes >> 5;
+		// ---- chunking: the strips of one chunk must fit the budget; chunks are made equal ----
 		size_t budgetLines = std::max<size_t>(strip_budget_bytes() / ((size_t)lineRes * 8), 65536);
 		{
 			size_t total = 0;
 			for (int i = 0; i < nViews; i++)
 				total += (size_t)T->h_views[i].numLines;
 			size_t want = (total + budgetLines - 1) / budgetLines;
-			if (want < 2 && nViews >= 512 && dual_stream())
-				want = 2;
 			// frames going back to the host: the PCIe copy (4-8 B/pixel) is the long pole, so start it early --
 			// more, smaller chunks cost kernel time that hides under the copy of the previous chunk
 			if ((host_fb || host_depth) && nViews >= 1024 && want < 8)
@@ -1133,6 +421,10 @@ namespace osb {
 			}
 			chunkStart.push_back(nViews);
 		}
+		if (maxLines * (size_t)lineRes >= ((size_t)1 << 32)) { // strip pixels are indexed with 32 bits inside a chunk
+			set_error("osb200_render: OSB200_STRIP_MB too large for %d-pixel strips (a chunk must stay below 2^32 strip pixels)", lineRes);
+			return -1;
+		}
 		const bool hostPrep = nViews <= 8;
 		const size_t nChunks = chunkStart.size() - 1;
 		// one chunk (or the host-prep path with its shared pinned staging): everything on the context stream
@@ -1140,10 +432,13 @@ namespace osb {
 		const bool dual = dual_stream() && nChunks > 1 && !hostPrep && !c->timing;
 		for (int k = 0; k < (dual ? 2 : 1); k++) {
 			ChunkBufs &B = T->set[k];
-			if (grow(B.d_lineDirs, B.lineCap, maxLines) || grow(B.d_lineParams, B.lineParamCap, maxLines) ||
+			if (grow(B.d_lineDirs, B.lineCap, maxLines) || grow(B.d_lineTan, B.tanCap, maxLines) ||
+			    grow(B.d_lineRecs, B.recCap, maxLines) || grow(B.d_active, B.activeCap, maxLines) ||
 			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) ||
-			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)(lineRes >> 5)) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
+			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)words) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
 				return -2;
+			if (!B.d_counters)
+				OSB_CUDA(cudaMalloc(&B.d_counters, 2 * sizeof(uint32_t)));
 		}
 		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
 		                         c->stream));
@@ -1160,6 +455,16 @@ namespace osb {
 		}
 		osbn::SseTables sse{c->d_rcp, c->d_rsqrt, c->rcpBits, c->rsqrtBits};
 		const int num = c->opts.numerics;
+		const size_t walkSmem = (size_t)(words + kWalkExtraWords) * kWalkThreads * sizeof(uint32_t);
+		if (!T->walkBlocksPerSm[num] || T->walkSmem[num] != walkSmem) {
+			T->walkSmem[num] = walkSmem;
+			if (num == OSB200_NUM_IEEE)
+				T->walkBlocksPerSm[num] = resident_blocks(k_walk_lines<false, false>, kWalkThreads, walkSmem);
+			else if (num == OSB200_NUM_SSE)
+				T->walkBlocksPerSm[num] = resident_blocks(k_walk_lines<true, false>, kWalkThreads, walkSmem);
+			else
+				T->walkBlocksPerSm[num] = resident_blocks(k_walk_lines<true, true>, kWalkThreads, walkSmem);
+		}
 		for (size_t ci = 0; ci < nChunks; ci++) {
 			ChunkBufs &B = T->set[dual ? (ci & 1) : 0];
 			const cudaStream_t st = dual ? B.stream : c->stream;
@@ -1167,6 +472,10 @@ namespace osb {
 			const ViewParams &last = T->h_views[v0 + nv - 1];
 			const uint32_t totalLines = last.lineBase + (uint32_t)last.numLines;
 			const ViewParams *dV = T->d_views + v0;
+			int maxViewLines = 0;
+			for (int i = 0; i < nv; i++)
+				maxViewLines = std::max(maxViewLines, T->h_views[v0 + i].numLines);
+			OSB_CUDA(cudaMemsetAsync(B.d_counters, 0, 2 * sizeof(uint32_t), st));
 			if (hostPrep) {
 				for (int i = 0; i < nv; i++) {
 					const ViewParams &V = T->h_views[v0 + i];
@@ -1185,47 +494,52 @@ namespace osb {
 				KLaunch kl(c, K_VIEW_PREP, st);
 				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
-			// small launches use fewer lanes per warp (a line is one long dependent chain: what counts is how many
-			// warps run side by side and how little each warp diverges)
-			int lpw = 32;
-			while (lpw > line_min_lanes() && (size_t)totalLines / lpw < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
-				lpw >>= 1;
-			const unsigned linesPerCta = kLineThreads / 32 * lpw;
-			const unsigned lineBlocks = (totalLines + linesPerCta - 1) / linesPerCta;
-			size_t smem = (size_t)(lineRes >> 5) * kLineThreads * sizeof(uint32_t);
-			if (OSB_RCP_SMEM && num != OSB200_NUM_IEEE && c->rcpBits <= kRcpSmemBits)
-				smem += sizeof(uint32_t) << c->rcpBits;
-#define LAUNCH_LINES(SSE, SH)                                                                      \
-	k_build_lines<SSE, SH><<<lineBlocks, kLineThreads, smem, st>>>(                                 \
-	  dV, nv, B.d_lineDirs, c->d_solid, c->d_color, sse, B.d_strips, B.d_lineParams, B.d_lineMask, totalLines, lineRes, lpw)
-			if (!g.noMap) {
-				KLaunch kl(c, K_BUILD_LINES, st);
+			{
+				KLaunch kl(c, K_LINE_SETUP, st);
+				const dim3 grid((maxViewLines + kSetupThreads - 1) / kSetupThreads, nv, 1);
 				if (num == OSB200_NUM_IEEE)
-					LAUNCH_LINES(false, false);
-				else if (num == OSB200_NUM_SSE)
-					LAUNCH_LINES(true, false);
+					k_line_setup<false><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineRecs,
+					                                                    B.d_lineTan, B.d_active, B.d_counters);
 				else
-					LAUNCH_LINES(true, true);
+					k_line_setup<true><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineRecs,
+					                                                   B.d_lineTan, B.d_active, B.d_counters);
 			}
-#undef LAUNCH_LINES
+			if (!g.noMap) {
+				// small launches use fewer lanes per warp (a line is one long dependent chain: what counts is how many
+				// warps run side by side and how little each warp diverges)
+				int lpw = 32;
+				while (lpw > line_min_lanes() && (size_t)totalLines / lpw < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
+					lpw >>= 1;
+				const size_t wantWarps = ((size_t)totalLines + lpw - 1) / lpw;
+				const size_t resident = (size_t)c->smCount * T->walkBlocksPerSm[num];
+				const unsigned blocks = (unsigned)std::min<size_t>((wantWarps + kWalkThreads / 32 - 1) / (kWalkThreads / 32), resident);
+				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
+				// a warp refills when this many of its working lanes are idle (small launches: as soon as a lane is free)
+				const int refillAt = std::min(refill_at(), std::max(1, lpw / 4));
+				KLaunch kl(c, K_WALK_LINES, st);
+#define LAUNCH_WALK(SSE, SH) k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, B.d_counters, lpw, refillAt)
+				if (num == OSB200_NUM_IEEE)
+					LAUNCH_WALK(false, false);
+				else if (num == OSB200_NUM_SSE)
+					LAUNCH_WALK(true, false);
+				else
+					LAUNCH_WALK(true, true);
+#undef LAUNCH_WALK
+			}
 			const int segs = ((h >> 3) + kSegRows - 1) / kSegRows;
 			const size_t tasks = (size_t)nv * (((w >> 3) + 3) >> 2) * segs;
 			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
-			uint32_t *fbC = d_fb + (size_t)v0 * w * h;
-			float *dbC = d_depth + (size_t)v0 * w * h;
-#define LAUNCH_GATHER(SSE, FOG)                                                                    \
-	k_gather_fog<SSE, FOG><<<gBlocks, kGatherWarps * 32, 0, st>>>(                                  \
-	  dV, nv, g, B.d_tabs, c->d_solid, T->d_atan, sse, B.d_strips, B.d_lineParams, B.d_lineMask, lineRes, fbC, dbC)
+			GatherIO gio{dV,           nv,      g, B.d_tabs, c->d_solid, T->d_atan, B.d_strips, B.d_lineRecs, B.d_lineTan, B.d_lineMask,
+			             lineRes, d_fb + (size_t)v0 * w * h, d_depth + (size_t)v0 * w * h};
 			{
 				KLaunch kl(c, K_GATHER_FOG, st);
 				if (num == OSB200_NUM_IEEE)
-					LAUNCH_GATHER(false, false);
+					k_gather_fog<false, false><<<gBlocks, kGatherWarps * 32, 0, st>>>(gio, sse);
 				else if (num == OSB200_NUM_SSE)
-					LAUNCH_GATHER(true, false);
+					k_gather_fog<true, false><<<gBlocks, kGatherWarps * 32, 0, st>>>(gio, sse);
 				else
-					LAUNCH_GATHER(true, true);
+					k_gather_fog<true, true><<<gBlocks, kGatherWarps * 32, 0, st>>>(gio, sse);
 			}
-#undef LAUNCH_GATHER
 			OSB_CUDA(cudaEventRecord(B.done, st));
 			if (host_fb || host_depth) {
 				const size_t off = (size_t)v0 * w * h, cnt = (size_t)nv * w * h;

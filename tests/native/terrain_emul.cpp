@@ -1,0 +1,224 @@
+// CPU lock-step emulation of the terrain kernels (TEST INFRASTRUCTURE, never part of the product).
+//
+// openspades_b200/csrc/terrain_core.cuh holds the per-lane code of k_line_setup, k_walk_lines and k_gather_fog; this
+// file compiles that very header with g++ and runs the lanes one after the other in the kernels' launch structure
+// (per-view set-up, pitch cull + compaction of the surviving lines, one LineWalker per active line, one GatherLane x 32
+// per warp task with the corner / pixel phases in kernel order).  tests/test_terrain_emul.py compares the frames with
+// the oracle, so control-flow and arithmetic mistakes in the core are found in the CPU container (no GPU here).
+//
+// g++ -O2 -ffp-contract=off -shared -fPIC terrain_emul.cpp ../../openspades_b200/csrc/sse_calibrate.cpp
+#include <cstdarg>
+#include <cstdio>
+#include <vector>
+
+#include "../../openspades_b200/csrc/terrain_core.cuh"
+
+namespace osb {
+	void set_error(const char *fmt, ...) {
+		va_list ap;
+		va_start(ap, fmt);
+		vfprintf(stderr, fmt, ap);
+		va_end(ap);
+		fputc('\n', stderr);
+	}
+} // namespace osb
+
+extern "C" int osb200_calibrate_sse(uint32_t *rcp_table, int *rcp_bits, uint32_t *rsqrt_table, int *rsqrt_bits, int max_bits);
+
+namespace {
+	using namespace osb;
+
+	struct Tables {
+		std::vector<uint32_t> rcp, rsqrt;
+		int rcpBits = 0, rsqrtBits = 0;
+		bool ok = false;
+	};
+	Tables &tables() {
+		static Tables t = [] {
+			Tables x;
+			x.rcp.resize(1 << 16);
+			x.rsqrt.resize(2 << 16);
+			x.ok = osb200_calibrate_sse(x.rcp.data(), &x.rcpBits, x.rsqrt.data(), &x.rsqrtBits, 16) == 0;
+			return x;
+		}();
+		return t;
+	}
+
+	std::vector<uint16_t> atan_table() { // AtanTable (SWMapRenderer.cpp:673-696), as terrain.cu builds it
+		std::vector<uint16_t> tab(20000);
+		auto toFixed = [](float v) -> uint16_t {
+			v /= (M_PI * 2.f);
+			v *= 65536.f;
+			int i = static_cast<int>(v);
+			return static_cast<uint16_t>(i & 65535);
+		};
+		for (int i = 0; i < 5000; i++) {
+			tab[i] = toFixed(atanf(i / 4096.f));
+			tab[5000 + i] = toFixed(atanf(1.f / ((i + .5f) / 4096.f)));
+			tab[10000 + i] = toFixed(-atanf(i / 4096.f));
+			tab[15000 + i] = toFixed(-atanf(1.f / ((i + .5f) / 4096.f)));
+		}
+		return tab;
+	}
+
+	struct Stats {
+		unsigned long long lines, active, steps;
+	};
+
+	template <bool kSse, bool kSse2> int run(const uint64_t *solidT, const uint32_t *colorT, const osb200_scene *scenes, int nViews, int w,
+	                                         int h, const float fog[3], float fogDist, int threads, int under, int noMap, int noFog,
+	                                         uint32_t *fb, float *depth, Stats *stats) {
+		Tables &T = tables();
+		if (kSse && !T.ok)
+			return -4;
+		osbn::SseTables sse{T.rcp.data(), T.rsqrt.data(), T.rcpBits, T.rsqrtBits};
+		osbn::Num<kSse> num{sse};
+		FrameGeom g{};
+		g.fw = w;
+		g.fh = h;
+		g.under = under;
+		g.swThreads = threads;
+		g.sse2Fog = g.sse2Shade = kSse2;
+		g.noMap = noMap;
+		g.noFog = noFog;
+		auto toFixed8 = [](float v) {
+			int i = static_cast<int>(v * 255.f + .5f);
+			return (uint32_t)std::max(std::min(i, 255), 0);
+		};
+		g.fogR = toFixed8(fog[0]);
+		g.fogG = toFixed8(fog[1]);
+		g.fogB = toFixed8(fog[2]);
+
+		// ---- per-view set-up (host half + k_view_prep) ----
+		std::vector<ViewParams> views(nViews);
+		const uint32_t tabF = tab_floats(w, h);
+		size_t lines = 0;
+		for (int i = 0; i < nViews; i++) {
+			fill_view(scenes[i], w, h, under, fogDist, views[i]);
+			views[i].lineBase = (uint32_t)lines;
+			views[i].tabBase = (uint32_t)i * tabF;
+			lines += views[i].numLines;
+		}
+		const int lineRes = views[0].lineRes, words = lineRes >> 5;
+		std::vector<float2> lineDirs(lines), lineTan(lines);
+		std::vector<float> tabs((size_t)nViews * tabF);
+		for (int i = 0; i < nViews; i++) {
+			const ViewParams &V = views[i];
+			float *vx = tabs.data() + V.tabBase, *vy = vx + (w >> 2), *v1 = vy + (h >> 2);
+			prep_line_dirs(V, lineDirs.data() + V.lineBase);
+			prep_fog_vx(V, g, vx);
+			for (int t = 0; t < threads; t++) {
+				prep_fog_vy(V, g, t, vy);
+				prep_v1(V, g, t, v1);
+			}
+		}
+		// ---- k_line_setup: pitch cull, records, compaction ----
+		std::vector<LineRec> recs(lines);
+		std::vector<uint32_t> active;
+		if (!noMap) {
+			for (int i = 0; i < nViews; i++) {
+				const ViewParams &V = views[i];
+				for (int l = 0; l < V.numLines; l++) {
+					const uint32_t gl = V.lineBase + l;
+					const LineSetupOut o = line_setup<kSse>(V, lineDirs[gl], lineRes, num);
+					lineTan[gl] = make_float2(o.minTan, o.pitchScale);
+					int slot = -1;
+					if (!o.culled) {
+						slot = (int)active.size();
+						active.push_back(gl);
+					}
+					recs[gl] = make_line_rec(o, slot, i);
+				}
+			}
+		} else {
+			for (size_t gl = 0; gl < lines; gl++)
+				recs[gl] = LineRec{0, 0, -1, 0};
+		}
+		// strips are deliberately filled with garbage: the walker never clears them, the gather must not read an
+		// unwritten pixel
+		std::vector<uint2> strips(active.size() * (size_t)lineRes, make_uint2(0xdeadbeefu, 0x7fc00000u));
+		std::vector<uint32_t> mask(active.size() * (size_t)words, 0xffffffffu);
+		// ---- k_walk_lines ----
+		WalkIO wio{views.data(), lineDirs.data(), lineTan.data(), recs.data(), solidT, colorT, strips.data(), mask.data(), lineRes};
+		unsigned long long steps = 0;
+		for (size_t s = 0; s < active.size(); s++) {
+			uint32_t filled[128 + kWalkExtraWords];
+			LineWalker<kSse, kSse2> W;
+			W.init(wio, active[s], (uint32_t)s, filled, 1);
+			while (W.step(wio, num, filled, 1))
+				steps++;
+		}
+		if (stats) {
+			stats->lines = lines;
+			stats->active = active.size();
+			stats->steps = steps;
+		}
+		// ---- k_gather_fog ----
+		const std::vector<uint16_t> atanTab = atan_table();
+		GatherIO gio{views.data(), nViews,       g,         tabs.data(), solidT, atanTab.data(), strips.data(), recs.data(),
+		             lineTan.data(), mask.data(), lineRes, fb,          depth};
+		const int colGroups = ((w >> 3) + 3) >> 2, segs = ((h >> 3) + kSegRows - 1) / kSegRows;
+		const uint32_t tasks = (uint32_t)nViews * colGroups * segs;
+		for (uint32_t task = 0; task < tasks; task++) {
+			GatherLane<kSse, kSse2> L[32];
+			GatherShared sm;
+			for (int l = 0; l < 32; l++)
+				if (!L[l].init(gio, task, l))
+					return -9;
+			for (int l = 0; l < 32; l++)
+				L[l].fog_phase(gio, num, sm, l);
+			for (int by = L[0].by0; by < L[0].by1; by += 2) {
+				for (int l = 0; l < 32; l++)
+					L[l].corner_phase(gio, num, sm, l, by);
+				for (int r = 0; r < 2; r++)
+					for (int l = 0; l < 32; l++)
+						L[l].pixel_phase(gio, num, sm, r, by);
+			}
+		}
+		return 0;
+	}
+} // namespace
+
+extern "C" {
+// solid uint64[512][512] ([x][y]), color uint32[512][512][64]: the GameMap arrays; tiled here like osb200_map_upload
+__attribute__((visibility("default"))) int emul_render(const uint64_t *solid, const uint32_t *color, const osb200_scene *scenes,
+                                                       int nViews, int w, int h, const float fog[3], float fogDist, int numerics,
+                                                       int threads, int under, int noMap, int noFog, uint32_t *fb, float *depth,
+                                                       unsigned long long *stats3, int mapKey) {
+	// mapKey: the tiled copy of the map is rebuilt whenever the key differs from the previous call's
+	static std::vector<uint64_t> solidT;
+	static std::vector<uint32_t> colorT;
+	static int lastKey = -1;
+	if (!noMap && (mapKey != lastKey || solidT.empty())) {
+		solidT.resize(512 * 512);
+		colorT.resize((size_t)512 * 512 * 64);
+		for (uint32_t x = 0; x < 512; x++)
+			for (uint32_t y = 0; y < 512; y++) {
+				const uint32_t t = tiled_xy(x, y);
+				solidT[t] = solid[x * 512 + y];
+				std::memcpy(&colorT[(size_t)t * 64], &color[((size_t)x * 512 + y) * 64], 64 * 4);
+			}
+		lastKey = mapKey;
+	}
+	if (noMap && solidT.empty()) {
+		solidT.assign(512 * 512, 0);
+		colorT.assign((size_t)512 * 512 * 64, 0);
+	}
+	Stats st{};
+	int rc;
+#define RUN(SSE, SSE2) rc = run<SSE, SSE2>(solidT.data(), colorT.data(), scenes, nViews, w, h, fog, fogDist, threads, under, noMap, noFog, fb, depth, &st)
+	if (numerics == 0)
+		RUN(false, false);
+	else if (numerics == 1)
+		RUN(true, false);
+	else
+		RUN(true, true);
+#undef RUN
+	if (stats3) {
+		stats3[0] = st.lines;
+		stats3[1] = st.active;
+		stats3[2] = st.steps;
+	}
+	return rc;
+}
+}
