@@ -38,28 +38,20 @@ namespace osb {
 		}();
 		return v;
 	}
-	// a warp of k_walk_lines fetches new lines when at least this many of its lanes are idle (OSB200_REFILL_AT, 1..32)
-	static int refill_at() {
-		static const int v = [] {
-			const char *e = getenv("OSB200_REFILL_AT");
-			const int n = e ? atoi(e) : 8;
-			return n < 1 ? 1 : (n > 32 ? 32 : n);
-		}();
-		return v;
-	}
-
 	// Per-chunk working set.  Two of them, each with its own stream, when a batch is cut into chunks (frames going
 	// back to the host: the PCIe copy of chunk k overlaps the kernels of chunk k+1).
 	struct ChunkBufs {
 		float2 *d_lineDirs = nullptr;
 		float2 *d_lineTan = nullptr;
 		LineRec *d_lineRecs = nullptr;
-		uint32_t *d_active = nullptr;   // compacted list of the lines that survived the pitch cull
-		uint32_t *d_counters = nullptr; // [0] number of active lines, [1] work cursor of k_walk_lines
+		uint32_t *d_active = nullptr;   // strip slot -> line: the surviving lines of every view, compacted in yaw order
+		uint32_t *d_liveBits = nullptr; // per view, per 32 lines: ballot of the lines that survived the pitch cull
+		uint32_t *d_tasks = nullptr;    // walker tasks: (first slot << 5) | (lines - 1)
+		uint32_t *d_counters = nullptr; // [0] number of tasks, [1] work cursor of k_walk_lines
 		uint2 *d_strips = nullptr;
 		uint32_t *d_lineMask = nullptr; // lineRes bits per strip slot: strip pixels the line wrote
 		float *d_tabs = nullptr;
-		size_t lineCap = 0, tanCap = 0, recCap = 0, activeCap = 0, stripCap = 0, maskCap = 0, tabCap = 0;
+		size_t lineCap = 0, tanCap = 0, recCap = 0, activeCap = 0, liveCap = 0, taskCap = 0, stripCap = 0, maskCap = 0, tabCap = 0;
 		cudaStream_t stream = nullptr;
 		cudaEvent_t done = nullptr; // last kernel of the newest chunk that used this set
 	};
@@ -92,6 +84,7 @@ namespace osb {
 #endif
 	constexpr int kWalkThreads = OSB_WALK_THREADS; // lanes (= lines in flight) per CTA of k_walk_lines
 	constexpr int kSetupThreads = 128;
+	constexpr int kMinTaskLines = 1; // smallest walker task (OSB200_LINE_MIN_LANES)
 
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
 	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs, float *tabs) {
@@ -112,12 +105,12 @@ namespace osb {
 			prep_v1(V, g, t, v1);
 	}
 
-	// One thread per yaw line (blockIdx.y = view): pitch cull, records, compaction of the surviving lines.
+	// One thread per yaw line (blockIdx.y = view): pitch cull against the frustum side planes.  Writes the line's
+	// {pitchTanMin, pitchScale} and, per warp, the ballot of the lines that survive (liveBits[view * wordsPerView + w]).
 	template <bool kSse>
 	__global__ void __launch_bounds__(kSetupThreads)
 	  k_line_setup(const ViewParams *__restrict__ views, const float2 *__restrict__ lineDirs, osbn::SseTables tabs, int lineRes,
-	               int noMap, LineRec *__restrict__ lineRecs, float2 *__restrict__ lineTan, uint32_t *__restrict__ active,
-	               uint32_t *__restrict__ counters) {
+	               int noMap, float2 *__restrict__ lineTan, uint32_t *__restrict__ liveBits, int wordsPerView) {
 		const int vi = blockIdx.y;
 		const ViewParams &V = views[vi];
 		const int l = blockIdx.x * kSetupThreads + threadIdx.x;
@@ -131,62 +124,116 @@ namespace osb {
 			osbn::Num<kSse> num{tabs};
 			o = line_setup<kSse>(V, lineDirs[gl], lineRes, num);
 		}
-		// surviving lines of the warp take consecutive strip slots: one atomic per warp
 		const unsigned live = __ballot_sync(0xffffffffu, valid && !o.culled);
-		const int lane = threadIdx.x & 31;
-		uint32_t base = 0;
-		if (live && lane == 0)
-			base = atomicAdd(counters, (uint32_t)__popc(live));
-		base = __shfl_sync(0xffffffffu, base, 0);
-		if (!valid)
-			return;
-		int slot = -1;
-		if (!o.culled) {
-			slot = (int)(base + (uint32_t)__popc(live & ((1u << lane) - 1u)));
-			active[slot] = gl;
-		}
-		lineRecs[gl] = make_line_rec(o, slot, vi);
-		lineTan[gl] = make_float2(o.minTan, o.pitchScale);
+		if ((threadIdx.x & 31) == 0)
+			liveBits[(size_t)vi * wordsPerView + (l >> 5)] = live;
+		if (valid)
+			lineTan[gl] = make_float2(o.minTan, o.pitchScale);
 	}
 
-	// Persistent line walker.  Lane = one yaw line at a time; the warp refills its idle lanes from the chunk-wide cursor.
+	// One CTA per view: order-preserving compaction of the view's surviving lines.  Their strip slots are
+	// lineBase + rank (contiguous, in yaw order), the line records are written, and the view's lines are cut into
+	// tasks of <= taskLines consecutive slots for the walker: a walker warp always gets ADJACENT lines of ONE view, which
+	// walk almost the same cells (measured: with slots handed out in atomic order across views a warp mixed two or
+	// three views and ran at 16.8 of 32 lanes).
+	constexpr int kCompactThreads = 256;
+	constexpr int kMaxLineWords = 65536 / 32; // numLines <= 65536 (SWMapRenderer.cpp:1116-1119)
+	__global__ void __launch_bounds__(kCompactThreads)
+	  k_line_compact(const ViewParams *__restrict__ views, const float2 *__restrict__ lineTan, const uint32_t *__restrict__ liveBits,
+	                 int wordsPerView, int taskLines, LineRec *__restrict__ lineRecs, uint32_t *__restrict__ active,
+	                 uint32_t *__restrict__ tasks, uint32_t *__restrict__ counters) {
+		__shared__ uint32_t s_prefix[kMaxLineWords]; // exclusive prefix of the survivor counts per 32-line word
+		__shared__ uint32_t s_warpSum[kCompactThreads / 32];
+		__shared__ uint32_t s_base, s_taskBase;
+		const int vi = blockIdx.x;
+		const ViewParams &V = views[vi];
+		const int nWords = (V.numLines + 31) >> 5;
+		const uint32_t *bits = liveBits + (size_t)vi * wordsPerView;
+		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+		if (threadIdx.x == 0)
+			s_base = 0;
+		__syncthreads();
+		for (int c = 0; c < nWords; c += kCompactThreads) { // block scan, kCompactThreads words at a time
+			const int j = c + threadIdx.x;
+			const uint32_t cnt = j < nWords ? (uint32_t)__popc(bits[j]) : 0u;
+			uint32_t incl = cnt;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) {
+				const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+				if (lane >= d)
+					incl += up;
+			}
+			if (lane == 31)
+				s_warpSum[wid] = incl;
+			__syncthreads();
+			uint32_t before = s_base;
+			for (int w = 0; w < wid; w++)
+				before += s_warpSum[w];
+			if (j < nWords)
+				s_prefix[j] = before + incl - cnt;
+			__syncthreads();
+			if (threadIdx.x == kCompactThreads - 1)
+				s_base = before + incl;
+			__syncthreads();
+		}
+		const uint32_t nLive = s_base;
+		for (int j = wid; j < nWords; j += kCompactThreads / 32) { // one warp per word: lane = line
+			const uint32_t b = bits[j];
+			const int l = (j << 5) + lane;
+			if (l >= V.numLines)
+				continue;
+			const uint32_t gl = V.lineBase + (uint32_t)l;
+			const float2 tn = lineTan[gl];
+			LineSetupOut o;
+			o.minTan = tn.x;
+			o.pitchScale = tn.y;
+			o.culled = !((b >> lane) & 1u);
+			int slot = -1;
+			if (!o.culled) {
+				slot = (int)(V.lineBase + s_prefix[j] + (uint32_t)__popc(b & ((1u << lane) - 1u)));
+				active[slot] = gl;
+			}
+			lineRecs[gl] = make_line_rec(o, slot, vi);
+		}
+		const uint32_t nTasks = (nLive + (uint32_t)taskLines - 1) / (uint32_t)taskLines;
+		if (threadIdx.x == 0)
+			s_taskBase = nTasks ? atomicAdd(counters, nTasks) : 0u;
+		__syncthreads();
+		for (uint32_t i = threadIdx.x; i < nTasks; i += kCompactThreads) {
+			const uint32_t first = i * (uint32_t)taskLines;
+			const uint32_t n = min((uint32_t)taskLines, nLive - first);
+			tasks[s_taskBase + i] = ((V.lineBase + first) << 5) | (n - 1u); // slot of the first line, lines - 1
+		}
+	}
+
+	// Persistent line walker.  A warp takes one task (<= 32 adjacent surviving lines of one view) at a time from the
+	// chunk-wide cursor; lane = one yaw line.
 	template <bool kSse, bool kSse2Shade>
 	__global__ void __launch_bounds__(kWalkThreads, OSB_WALK_MINB)
-	  k_walk_lines(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, uint32_t *__restrict__ counters,
-	               int laneLimit, int refillAt) {
+	  k_walk_lines(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, const uint32_t *__restrict__ tasks,
+	               uint32_t *__restrict__ counters) {
 		extern __shared__ uint32_t s_filled[]; // (lineRes/32 + kWalkExtraWords) words x kWalkThreads, word-major: bank = lane
 		uint32_t *filled = s_filled + threadIdx.x;
 		const int lane = threadIdx.x & 31;
 		const osbn::Num<kSse> num{tabs};
-		const uint32_t count = counters[0]; // written by k_line_setup, earlier on this stream
-		const unsigned workMask = laneLimit >= 32 ? 0xffffffffu : ((1u << laneLimit) - 1u);
+		const uint32_t nTasks = counters[0]; // written by k_line_compact, earlier on this stream
 		LineWalker<kSse, kSse2Shade> W;
-		bool alive = false, exhausted = false;
 		for (;;) {
-			unsigned live = __ballot_sync(0xffffffffu, alive);
-			if (!exhausted) {
-				const unsigned idle = ~live & workMask;
-				const int n = __popc(idle);
-				if (n && (live == 0 || n >= refillAt)) {
-					uint32_t base = 0;
-					if (lane == 0)
-						base = atomicAdd(counters + 1, (uint32_t)n);
-					base = __shfl_sync(0xffffffffu, base, 0);
-					exhausted = base + (uint32_t)n >= count;
-					if ((idle >> lane) & 1u) {
-						const uint32_t idx = base + (uint32_t)__popc(idle & ((1u << lane) - 1u));
-						if (idx < count) {
-							W.init(io, __ldg(active + idx), idx, filled, kWalkThreads);
-							alive = true;
-						}
-					}
-					live = __ballot_sync(0xffffffffu, alive);
-				}
-			}
-			if (live == 0)
+			uint32_t t = 0;
+			if (lane == 0)
+				t = atomicAdd(counters + 1, 1u);
+			t = __shfl_sync(0xffffffffu, t, 0);
+			if (t >= nTasks)
 				break;
+			const uint32_t task = __ldg(tasks + t);
+			const uint32_t slot = (task >> 5) + (uint32_t)lane;
+			bool alive = (uint32_t)lane <= (task & 31u);
 			if (alive)
-				alive = W.step(io, num, filled, kWalkThreads);
+				W.init(io, __ldg(active + slot), slot, filled, kWalkThreads);
+			while (__any_sync(0xffffffffu, alive)) {
+				if (alive)
+					alive = W.step(io, num, filled, kWalkThreads);
+			}
 		}
 	}
 
@@ -206,8 +253,9 @@ namespace osb {
 		for (int by = L.by0; by < L.by1; by += 2) {
 			L.corner_phase(io, num, sm, lane, by);
 			__syncwarp();
-			L.pixel_phase(io, num, sm, 0, by);
-			L.pixel_phase(io, num, sm, 1, by);
+			OSB_PRAGMA(unroll OSB_GATHER_ROW_UNROLL)
+			for (int r = 0; r < 2; r++)
+				L.pixel_phase(io, num, sm, r, by);
 			__syncwarp();
 		}
 	}
@@ -255,6 +303,8 @@ namespace osb {
 			cudaFree(b.d_lineTan);
 			cudaFree(b.d_lineRecs);
 			cudaFree(b.d_active);
+			cudaFree(b.d_liveBits);
+			cudaFree(b.d_tasks);
 			cudaFree(b.d_counters);
 			cudaFree(b.d_strips);
 			cudaFree(b.d_lineMask);
@@ -425,6 +475,11 @@ namespace osb {
 			set_error("osb200_render: OSB200_STRIP_MB too large for %d-pixel strips (a chunk must stay below 2^32 strip pixels)", lineRes);
 			return -1;
 		}
+		int maxViewLinesAll = 0;
+		for (int i = 0; i < nViews; i++)
+			maxViewLinesAll = std::max(maxViewLinesAll, T->h_views[i].numLines);
+		// words of the per-view survivor ballots: the k_line_setup grid covers whole CTAs of lines
+		const int maxWordsPerView = (maxViewLinesAll + kSetupThreads - 1) / kSetupThreads * (kSetupThreads / 32);
 		const bool hostPrep = nViews <= 8;
 		const size_t nChunks = chunkStart.size() - 1;
 		// one chunk (or the host-prep path with its shared pinned staging): everything on the context stream
@@ -434,6 +489,8 @@ namespace osb {
 			ChunkBufs &B = T->set[k];
 			if (grow(B.d_lineDirs, B.lineCap, maxLines) || grow(B.d_lineTan, B.tanCap, maxLines) ||
 			    grow(B.d_lineRecs, B.recCap, maxLines) || grow(B.d_active, B.activeCap, maxLines) ||
+			    grow(B.d_liveBits, B.liveCap, maxViews * (size_t)maxWordsPerView) ||
+			    grow(B.d_tasks, B.taskCap, maxLines / kMinTaskLines + maxViews) ||
 			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) ||
 			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)words) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
 				return -2;
@@ -494,30 +551,32 @@ namespace osb {
 				KLaunch kl(c, K_VIEW_PREP, st);
 				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
+			// small launches cut a view's lines into smaller tasks (a line is one long dependent chain: what counts is
+			// how many warps run side by side and how little each warp diverges)
+			int taskLines = 32;
+			while (taskLines > line_min_lanes() && (size_t)totalLines / taskLines < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
+				taskLines >>= 1;
+			taskLines = std::max(taskLines, kMinTaskLines);
 			{
 				KLaunch kl(c, K_LINE_SETUP, st);
 				const dim3 grid((maxViewLines + kSetupThreads - 1) / kSetupThreads, nv, 1);
 				if (num == OSB200_NUM_IEEE)
-					k_line_setup<false><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineRecs,
-					                                                    B.d_lineTan, B.d_active, B.d_counters);
+					k_line_setup<false><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineTan,
+					                                                    B.d_liveBits, maxWordsPerView);
 				else
-					k_line_setup<true><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineRecs,
-					                                                   B.d_lineTan, B.d_active, B.d_counters);
+					k_line_setup<true><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineTan,
+					                                                   B.d_liveBits, maxWordsPerView);
+				k_line_compact<<<nv, kCompactThreads, 0, st>>>(dV, B.d_lineTan, B.d_liveBits, maxWordsPerView, taskLines,
+				                                              B.d_lineRecs, B.d_active, B.d_tasks, B.d_counters);
+				c->launches++;
 			}
 			if (!g.noMap) {
-				// small launches use fewer lanes per warp (a line is one long dependent chain: what counts is how many
-				// warps run side by side and how little each warp diverges)
-				int lpw = 32;
-				while (lpw > line_min_lanes() && (size_t)totalLines / lpw < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
-					lpw >>= 1;
-				const size_t wantWarps = ((size_t)totalLines + lpw - 1) / lpw;
+				const size_t wantWarps = ((size_t)totalLines + taskLines - 1) / taskLines;
 				const size_t resident = (size_t)c->smCount * T->walkBlocksPerSm[num];
 				const unsigned blocks = (unsigned)std::min<size_t>((wantWarps + kWalkThreads / 32 - 1) / (kWalkThreads / 32), resident);
 				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
-				// a warp refills when this many of its working lanes are idle (small launches: as soon as a lane is free)
-				const int refillAt = std::min(refill_at(), std::max(1, lpw / 4));
 				KLaunch kl(c, K_WALK_LINES, st);
-#define LAUNCH_WALK(SSE, SH) k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, B.d_counters, lpw, refillAt)
+#define LAUNCH_WALK(SSE, SH) k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, B.d_tasks, B.d_counters)
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_WALK(false, false);
 				else if (num == OSB200_NUM_SSE)

@@ -17,6 +17,15 @@
 #include <cstdlib>
 #include <cstring>
 
+#define OSB_PRAGMA_(x) _Pragma(#x)
+#define OSB_PRAGMA(x) OSB_PRAGMA_(x)
+#ifndef OSB_GATHER_HALF_UNROLL
+#define OSB_GATHER_HALF_UNROLL 1 // 1 = the two 4-row halves of a block row share one copy of the pixel code; 2 = unrolled
+#endif
+#ifndef OSB_GATHER_ROW_UNROLL
+#define OSB_GATHER_ROW_UNROLL 1 // same for the two block rows of a pass
+#endif
+
 namespace osb {
 
 	// Per-view constants.  Everything that the reference computes once per frame with libm
@@ -775,16 +784,18 @@ namespace osb {
 				v2c[k] = fadd(fadd(v2c[k], dDL[k]), dDL[k]);
 		}
 
-		// LinePixel of (line yawIndex of this view, strip index pitchIndex)
-		OSB_HDM uint2 fetch(const GatherIO &io, const LineRec &lp, int pitchIndex) const {
-			using namespace osbc;
-			uint2 pix = make_uint2(0u, f2u(10000.f)); // LinePixel::Clear (:89-92)
-			if (lp.slot >= 0) {
-				const uint32_t slot = (uint32_t)lp.slot;
-				const uint32_t mw = ldg(io.lineMask + (slot * (uint32_t)(io.lineRes >> 5) + ((uint32_t)pitchIndex >> 5)));
-				if ((mw >> (pitchIndex & 31)) & 1u)
-					pix = ldg(io.strips + (slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex));
-			}
+		// LinePixel of (strip slot, strip index pitchIndex): two predicated loads, no nested branch, so that the loads of
+		// the pixels of a batch can be in flight together.  mask word first: unwritten strip memory is never read.
+		OSB_HDM uint32_t fetch_mask(const GatherIO &io, int slot, int pitchIndex) const {
+			uint32_t mw = 0u; // culled line: every strip pixel is LinePixel::Clear
+			if (slot >= 0)
+				mw = osbc::ldg(io.lineMask + ((uint32_t)slot * (uint32_t)(io.lineRes >> 5) + ((uint32_t)pitchIndex >> 5)));
+			return mw;
+		}
+		OSB_HDM uint2 fetch_pixel(const GatherIO &io, int slot, int pitchIndex, uint32_t mw) const {
+			uint2 pix = make_uint2(0u, osbc::f2u(10000.f)); // LinePixel::Clear (:89-92)
+			if ((mw >> (pitchIndex & 31)) & 1u)
+				pix = osbc::ldg(io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex));
 			return pix;
 		}
 
@@ -828,26 +839,51 @@ namespace osb {
 				const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
 				const int dYaw = tdiv_pow2(((yawB - yawA) << 8) >> 8, 3), dPit = tdiv_pow2(pitB - pitA, 3);
 				int yawC = yawA, pitC = pitA;
+				// four pixel rows per batch, stage by stage: the four line records, then the four mask words, then the
+				// four strip pixels are requested together (each stage depends on the one before it)
+				// (the two halves and the two block rows of a pass share ONE copy of this code: fully unrolled the kernel
+				// was 4096 instructions and stalled 6 cycles per issue on instruction fetch)
+#if defined(__CUDA_ARCH__)
+				OSB_PRAGMA(unroll OSB_GATHER_HALF_UNROLL)
+#endif
+				for (int half = 0; half < 2; half++) {
+					int slot[4], pitchIndex[4];
+					int4 lpw[4];
+					uint32_t mw[4];
+					uint2 pix[4];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-				for (int py = 0; py < 8; py++, oo += g.fw, yawC += dYaw, pitC += dPit) {
-					uint32_t yawIndex = (uint32_t)((yawC << 8) >> 16);
-					yawIndex = (yawIndex * yawScale2) >> 16;
-					yawIndex = (yawIndex * numLines) >> 16;
-					yawIndex = osbc::uminu(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
-					const int4 lpw = ldg(reinterpret_cast<const int4 *>(lpV + yawIndex));
-					LineRec lp;
-					lp.pitchTanMinI = lpw.x;
-					lp.pitchScaleI = lpw.y;
-					lp.slot = lpw.z;
-					int pitchIndex = (pitC >> 13) - lp.pitchTanMinI;
-					pitchIndex = mulhi(pitchIndex, lp.pitchScaleI);
-					pitchIndex &= lineRes - 1;
-					const uint2 pix = fetch(io, lp, pitchIndex);
-					const float dep = u2f(pix.y);
-					stcs(fbV + oo, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, fmul(dep, py < 4 ? fog0 : fog1), fogBR, fogG8));
-					stcs(dbV + oo, dep);
+					for (int j = 0; j < 4; j++, yawC += dYaw) {
+						uint32_t yawIndex = (uint32_t)((yawC << 8) >> 16);
+						yawIndex = (yawIndex * yawScale2) >> 16;
+						yawIndex = (yawIndex * numLines) >> 16;
+						yawIndex = uminu(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
+						lpw[j] = ldg(reinterpret_cast<const int4 *>(lpV + yawIndex));
+					}
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+					for (int j = 0; j < 4; j++, pitC += dPit) {
+						int pi = (pitC >> 13) - lpw[j].x; // LineRec::pitchTanMinI
+						pi = mulhi(pi, lpw[j].y);         // LineRec::pitchScaleI
+						pitchIndex[j] = pi & (lineRes - 1);
+						slot[j] = lpw[j].z;
+						mw[j] = fetch_mask(io, slot[j], pitchIndex[j]);
+					}
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+					for (int j = 0; j < 4; j++)
+						pix[j] = fetch_pixel(io, slot[j], pitchIndex[j], mw[j]);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+					for (int j = 0; j < 4; j++, oo += g.fw) {
+						const float dep = u2f(pix[j].y);
+						stcs(fbV + oo, g.noFog ? pix[j].x : fog_blend<kSse2Fog>(pix[j].x, fmul(dep, half ? fog1 : fog0), fogBR, fogG8));
+						stcs(dbV + oo, dep);
+					}
 				}
 			} else {
 				// exact per-pixel path near the poles (:940-1033)
@@ -878,7 +914,7 @@ namespace osb {
 					pitch = num.toSpecialTan(pitch);
 					pitch = fmul(fsub(pitch, lt.x), lt.y);
 					const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
-					const uint2 pix = fetch(io, lp, pitchIndex);
+					const uint2 pix = fetch_pixel(io, lp.slot, pitchIndex, fetch_mask(io, lp.slot, pitchIndex));
 					const float dep = u2f(pix.y);
 					stcs(fbV + oo, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, fmul(dep, py < 4 ? fog0 : fog1), fogBR, fogG8));
 					stcs(dbV + oo, dep);

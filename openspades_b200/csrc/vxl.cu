@@ -90,8 +90,8 @@ namespace osb {
 			return;
 		const int x = k & 511, y = k >> 9;
 		const uint32_t s0 = start[k], s1 = start[k + 1];
-		if (s0 == kBad || s1 == kBad) {
-			atomicExch(err, 1); // truncated or malformed input
+		if (s0 == kBad || s1 == kBad || s0 >= nWords || s1 > nWords || s1 <= s0) {
+			atomicExch(err, 1); // truncated or malformed input (never read the stream outside [0, nWords) words)
 			return;
 		}
 		const uint32_t t = tiled_index(x, y);
@@ -373,6 +373,9 @@ int osb200_map_load_vxl(osb200_ctx *c, const uint8_t *data, size_t len, uint64_t
 	cudaStream_t st = c->stream;
 	OSB_CUDA(cudaMemcpyAsync(V->d_file, data, len, cudaMemcpyHostToDevice, st));
 	OSB_CUDA(cudaMemsetAsync(V->d_err, 0, sizeof(int), st));
+	// every column start is "unknown" (kBad) until a doubling round writes it: a short stream leaves most of them that
+	// way (the rounds only run nWords + 1 threads), and the decoder must see kBad there, not stale or uninitialised words
+	OSB_CUDA(cudaMemsetAsync(V->d_start, 0xff, (kCols + 1) * sizeof(uint32_t), st));
 	OSB_CUDA(cudaMemsetAsync(V->d_start, 0, sizeof(uint32_t), st)); // column 0 starts at word 0
 	OSB_CUDA(cudaMemsetAsync(c->d_color, 0, (size_t)kCols * 64 * 4, st));
 	const unsigned blocks = (nWords + 1 + 255) / 256;

@@ -50,37 +50,47 @@ namespace osb200 {
 				uint64_t bits = ~0ull; // everything solid until a span says otherwise
 				uint32_t *col = &map->color_[Idx(x, y) * 64];
 				int airFrom = 0;
-				for (;;) {
+				// VXL maps arrive over the network: every z the stream names is range-checked (the reference only
+				// SPAsserts, GameMap.h:104-110; the device decoder k_vxl_decode rejects the same streams)
+				auto put = [&](int z, uint32_t c) {
+					if (z < 0 || z > 63)
+						throw std::runtime_error("VXL stream malformed: voxel z outside 0..63");
+					col[z] = c;
+					bits |= 1ull << z;
+				};
+				for (int span = 0;; span++) {
+					if (span >= 64)
+						throw std::runtime_error("VXL stream malformed: more than 64 spans in one column");
 					const int chunks = rd.s8(pos);
 					const int topStart = rd.s8(pos + 1);
 					const int topEnd = rd.s8(pos + 2);
-					for (int z = airFrom; z < topStart; z++)
+					if (chunks < 0)
+						throw std::runtime_error("VXL stream malformed: negative span length");
+					for (int z = airFrom; z < topStart; z++) {
+						if (z < 0 || z > 63)
+							throw std::runtime_error("VXL stream malformed: air run outside 0..63");
 						bits &= ~(1ull << z);
+					}
 					size_t cpos = pos + 4;
-					for (int z = topStart; z <= topEnd; z++, cpos += 4) {
-						col[z] = FileColorToMap(rd.u32(cpos));
-						bits |= 1ull << z;
-					}
-					if (topEnd == 62) { // the water floor copies the voxel above it
-						col[63] = col[62];
-						bits |= 1ull << 63;
-					}
+					for (int z = topStart; z <= topEnd; z++, cpos += 4)
+						put(z, FileColorToMap(rd.u32(cpos)));
+					if (topEnd == 62) // the water floor copies the voxel above it
+						put(63, col[62]);
 					const int topLen = topEnd - topStart + 1;
 					if (chunks == 0) { // last span of the column
-						pos += 4 * (size_t)(topLen + 1);
+						pos += 4 * (size_t)(topLen < 0 ? 0 : topLen) + 4;
 						break;
 					}
 					const int bottomLen = (chunks - 1) - topLen;
-					pos += (size_t)chunks * 4;
-					const int bottomEnd = rd.s8(pos + 3); // next span's air start
-					for (int z = bottomEnd - bottomLen; z < bottomEnd; z++, cpos += 4) {
-						col[z] = FileColorToMap(rd.u32(cpos));
-						bits |= 1ull << z;
-					}
-					if (bottomEnd == 63) {
-						col[63] = col[62];
-						bits |= 1ull << 63;
-					}
+					const size_t next = pos + (size_t)chunks * 4;
+					const int bottomEnd = rd.s8(next + 3); // next span's air start
+					if (bottomLen < 0 || cpos + (size_t)bottomLen * 4 > next)
+						throw std::runtime_error("VXL stream malformed: colour run crosses the next span header");
+					pos = next;
+					for (int z = bottomEnd - bottomLen; z < bottomEnd; z++, cpos += 4)
+						put(z, FileColorToMap(rd.u32(cpos)));
+					if (bottomEnd == 63)
+						put(63, col[62]);
 					airFrom = bottomEnd;
 				}
 				map->solid_[Idx(x, y)] = bits;

@@ -202,6 +202,11 @@ void oref_renderer_set_threads(int threads) {
 	h = threads;
 }
 
+void oref_renderer_set_undersampling(int under) { /* cvar r_swUndersampling (SWMapRenderer.cpp:37), read on every frame */
+	Settings::ItemHandle h("r_swUndersampling", nullptr);
+	h = under;
+}
+
 void *oref_renderer_create(int w, int h, int level, int threads) {
 	try {
 		oref_renderer_set_threads(threads);

@@ -59,6 +59,7 @@ OREF_API void *oref_renderer_create(int w, int h, int level, int threads);
 OREF_API void oref_renderer_free(void *r);
 OREF_API int oref_renderer_level(void *r);
 OREF_API void oref_renderer_set_threads(int threads); /* cvar r_swNumThreads */
+OREF_API void oref_renderer_set_undersampling(int under); /* cvar r_swUndersampling, 0 = off */
 OREF_API void oref_renderer_set_map(void *r, void *map);
 OREF_API int oref_renderer_minimap(void *r, uint32_t *out); /* SWFlatMapRenderer image, [y][x] */
 OREF_API void oref_renderer_set_fog(void *r, float cr, float cg, float cb, float dist);

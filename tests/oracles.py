@@ -624,9 +624,11 @@ class RefVoxelModel:
 
 
 class RefRenderer:
-    def __init__(self, ref: Ref, w, h, level=-1, threads=4):
+    def __init__(self, ref: Ref, w, h, level=-1, threads=4, under=0):
+        """threads / under set the process-wide cvars r_swNumThreads / r_swUndersampling (read on every frame)"""
         self.ref, self.w, self.h = ref, w, h
         L = ref.L
+        L.oref_renderer_set_undersampling(under)
         L.oref_model_create.restype = vp
         L.oref_model_create.argtypes = [vp, vp]
         L.oref_model_free.argtypes = [vp]

@@ -67,3 +67,31 @@ def test_host_voxelmap_set_and_listener_contract():
     assert int(m.solid[5, 6]) == before
     with pytest.raises(osb.OsbError):
         m.set(512, 0, 0, True, 0)
+
+
+def test_host_vxl_loader_rejects_malformed_streams():
+    """VoxelMap::Load (GameMap::Load, GameMap.cpp:519-596) takes untrusted network input: every malformed stream must end in
+    an exception, never in a write outside the 64-entry column or an endless walk (z / chunk checks)."""
+    import oracles
+    from openspades_b200.binding import OsbError
+    data = open(oracles.TITLE_VXL, "rb").read()
+    VoxelMap = hostlib.VoxelMap
+    good = VoxelMap.load(data)
+    ps, pc = oracles.Port().vxl_load(data)
+    assert np.array_equal(good.solid, ps)
+    named = ps[:, :, None] >> np.arange(64, dtype=np.uint64) & np.uint64(1) != 0
+    surface_equal = (good.color == pc) | ~named
+    assert surface_equal.mean() > 0.99  # colours the stream names agree (the rest is the reference's random default)
+    col = lambda *spans: b"".join(bytes(s) for s in spans)  # noqa: E731
+    bad_streams = {
+        "truncated half": data[:len(data) // 2],
+        "two bytes": b"\x00\x00",
+        "z beyond 63": col([0, 60, 70, 0] + [1, 2, 3, 4] * 11) * 10,
+        "negative topStart": col([0, 0x90, 3, 0] + [0] * 4 * 120) * 4,
+        "negative chunks": col([0x80, 0, 0, 0, 1, 2, 3, 4]) * 8,
+        "colour run crosses header": col([2, 0, 5, 0, 9, 9, 9, 9, 0, 20, 20, 20, 1, 1, 1, 1]) * 8,
+        "endless spans": col([1, 0, -1 & 0xff, 0]) * 4096,
+    }
+    for name, bad in bad_streams.items():
+        with pytest.raises(OsbError):
+            VoxelMap.load(bad)

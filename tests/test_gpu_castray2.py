@@ -88,3 +88,25 @@ def test_castray2_synthetic_and_edit(ctx, port):
     assert np.array_equal(ctx.map_read_solid(), solid)
     assert _same(ctx.castray2(v0, d, 256), port.castray2(solid, v0, d, 256, threads=8))
     assert ctx.map_flush(solid, color) == 0
+
+
+def test_castray2_16_mi_rays_bit_exact(ctx, port, title_map):
+    """north_star verbatim: GameMap::CastRay2 bit-exact on 16 M rays -- 2^24 rays, seed 1234, maxSteps 256, every field of
+    RayCastResult against the oracle on all host cores (and the first 2^20 against the unmodified reference)."""
+    import os
+    ctx.map_upload(title_map.solid, title_map.color)
+    n = 1 << 24
+    v0, d = workloads.random_rays(n, seed=1234)
+    got = ctx.castray2(v0, d, 256)
+    threads = max(1, len(os.sched_getaffinity(0)))
+    solid = title_map.solid.copy()
+    chunk = 1 << 22
+    for s in range(0, n, chunk):
+        want = port.castray2(solid, v0[s:s + chunk], d[s:s + chunk], 256, threads=threads)
+        assert _same(got[s:s + chunk], want), s
+    if oracles.ref_available():
+        ref = oracles.Ref("sse2")
+        m = ref.map_from_arrays(solid, title_map.color.copy())
+        k = 1 << 20
+        assert _same(got[:k], ref.castray2(m, v0[:k], d[:k], 256, threads=threads))
+        ref.map_free(m)

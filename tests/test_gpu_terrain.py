@@ -148,3 +148,95 @@ def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
     for other in outs[1:]:
         for k in ("fb", "dp", "fb2", "dp2"):
             assert np.array_equal(outs[0][k].view(np.uint32), other[k].view(np.uint32)), k
+
+
+@pytest.mark.parametrize("under", [2, 4])
+@pytest.mark.parametrize("size", [(800, 600, 30.0), (256, 256, 68.0)])
+def test_undersampling_matches_reference(port, title_map, under, size):
+    """r_swUndersampling 2 / 4 (SWMapRenderer.cpp:37,1110-1112: numLines /= under; store replication :889-911,987-1009):
+    osb200_opts.undersampling against the unmodified SWRenderer with the cvar set (when oracle/_ref travelled) and the port."""
+    w, h, fov = size
+    solid, color = title_map.solid.copy(), title_map.color.copy()
+    scenes = [workloads.title_scene(w, h, fov)] + list(workloads.random_scenes(3, solid, w, h, fov, seed=21))
+    ref = oracles.Ref("sse2") if oracles.ref_available("sse2") else None
+    with osb.Context(0, osb.NUM_SSE2, sw_threads=4, undersampling=under) as ctx:
+        ctx.map_upload(solid, color)
+        fbs, dps = ctx.render(np.stack(scenes), w, h, FOG, 128.0)
+    if ref is not None:
+        m = ref.map_from_arrays(solid, color)
+        r = oracles.RefRenderer(ref, w, h, -1, 4, under)
+        r.set_map(m)
+        r.set_fog(FOG, 128.0)
+    for i, sc in enumerate(scenes):
+        pfb, pdp = port.render(solid, color, sc, w, h, FOG, 128.0, osb.NUM_SSE2, 4, under)
+        assert _report(f"under {under} {w}x{h} #{i} vs port", fbs[i], dps[i], pfb, pdp) == (1.0, 1.0)
+        if ref is not None:
+            rfb, rdp = r.render(sc)
+            assert _report(f"under {under} {w}x{h} #{i} vs ref", fbs[i], dps[i], rfb, rdp) == (1.0, 1.0)
+    if ref is not None:
+        r.set_map(None)
+        r.close()
+        oracles.RefRenderer(ref, 8, 8, -1, 4, 0).close()  # leave the process-wide cvar at its default
+        ref.map_free(m)
+
+
+@pytest.mark.parametrize("threads", [1, 8, 32])
+def test_sw_threads_matches_reference(port, title_map, threads):
+    """r_swNumThreads (SWRenderer.cpp:41, SWUtils.h:49-56) changes the per-thread float recurrences of RenderFinal and
+    ApplyFog: osb200_opts.sw_threads replays them for 1, 8 and 32 workers (4 is the default every other test uses)."""
+    solid, color = title_map.solid.copy(), title_map.color.copy()
+    ref = oracles.Ref("sse2") if oracles.ref_available("sse2") else None
+    for (w, h, fov) in ((800, 600, 30.0), (256, 256, 68.0)):
+        scenes = [workloads.title_scene(w, h, fov)] + list(workloads.random_scenes(2, solid, w, h, fov, seed=22))
+        with osb.Context(0, osb.NUM_SSE2, sw_threads=threads) as ctx:
+            ctx.map_upload(solid, color)
+            fbs, dps = ctx.render(np.stack(scenes), w, h, FOG, 128.0)
+        if ref is not None:
+            m = ref.map_from_arrays(solid, color)
+            r = oracles.RefRenderer(ref, w, h, -1, threads, 0)
+            r.set_map(m)
+            r.set_fog(FOG, 128.0)
+        for i, sc in enumerate(scenes):
+            pfb, pdp = port.render(solid, color, sc, w, h, FOG, 128.0, osb.NUM_SSE2, threads, 1)
+            assert _report(f"threads {threads} {w}x{h} #{i} vs port", fbs[i], dps[i], pfb, pdp) == (1.0, 1.0)
+            if ref is not None:
+                rfb, rdp = r.render(sc)
+                assert _report(f"threads {threads} {w}x{h} #{i} vs ref", fbs[i], dps[i], rfb, rdp) == (1.0, 1.0)
+        if ref is not None:
+            r.set_map(None)
+            r.close()
+            ref.map_free(m)
+    if ref is not None:
+        ref.L.oref_renderer_set_threads(4)
+
+
+def test_ceilings_hall(port, title_map):
+    """a hall under a solid roof (undersides, pillars with several tops and bottoms per column): the ceilings list of
+    BuildRle (SWMapRenderer.cpp:604-622), which outdoor cameras on Title.vxl never reach"""
+    solid, color = title_map.solid.copy(), title_map.color.copy()
+    rng = np.random.default_rng(3)
+    x0, y0 = 200, 200
+    for x in range(x0, x0 + 96):
+        for y in range(y0, y0 + 96):
+            m = (1 << 64) - 1
+            m &= ~((1 << 5) - 1)
+            m &= ~(((1 << 22) - 1) << 14)
+            if rng.random() < 0.08:
+                m |= ((1 << 6) - 1) << int(rng.integers(14, 30))
+            if rng.random() < 0.05:
+                m &= ~(((1 << 9) - 1) << 5)
+            solid[x, y] = np.uint64(m)
+            color[x, y, :] = (0x64000000 | rng.integers(0, 1 << 24, 64)).astype(np.uint32)
+    w = h = 256
+    scenes = []
+    for k, (pitch, yaw) in enumerate([(0.0, 0.3), (-0.7, 2.0), (0.6, 4.0), (-1.2, 5.5), (1.3, 1.0)]):
+        eye = np.array([x0 + 48.3, y0 + 47.6, 30.2 - k])
+        d = np.array([np.cos(yaw) * np.cos(pitch), np.sin(yaw) * np.cos(pitch), np.sin(pitch)])
+        scenes.append(workloads.look_at_scene(eye, eye + d, (0, 0, -1), 68.0, w, h))
+    for mode in ("ieee", "sse2"):
+        with osb.Context(0, NUMERICS[mode], sw_threads=4) as ctx:
+            ctx.map_upload(solid, color)
+            fbs, dps = ctx.render(np.stack(scenes), w, h, FOG, 128.0)
+        for i, sc in enumerate(scenes):
+            rfb, rdp = port.render(solid, color, sc, w, h, FOG, 128.0, NUMERICS[mode], 4, 1)
+            assert _report(f"hall {mode} #{i}", fbs[i], dps[i], rfb, rdp) == (1.0, 1.0)

@@ -90,3 +90,16 @@ def test_truncated_and_malformed_streams_are_rejected():
         ctx.map_load_vxl(data)  # and a good stream still loads afterwards
         fb2, _ = ctx.render(sc, 64, 64, FOG, 128.0)
         assert not np.array_equal(fb, fb2)
+
+
+def test_short_stream_as_first_load_on_a_fresh_context():
+    """a stream shorter than the column count leaves most column starts unwritten by the doubling rounds; they
+    must read as 'unknown' (not as uninitialised device memory) and the load must fail cleanly, also as the very first
+    load of a context, and leave the context usable."""
+    data = open(oracles.TITLE_VXL, "rb").read()
+    for bad in (b"\x00\x05\x03\x00" * 10, b"\x00\x3e\x3e\x00\x01\x02\x03\x04" * 1000, data[:4096]):
+        with osb.Context(0, osb.NUM_IEEE) as ctx:
+            with pytest.raises(osb.OsbError, match="malformed|truncated"):
+                ctx.map_load_vxl(bad)
+            ctx.map_load_vxl(data)
+            ctx.sync()

@@ -24,16 +24,16 @@ def title_arrays(port):
     return port.vxl_load(open(oracles.TITLE_VXL, "rb").read())
 
 
-def _compare(ref_lib, level, num, solid, color, scenes, w, h, threads, port, fog=FOG):
+def _compare(ref_lib, level, num, solid, color, scenes, w, h, threads, port, fog=FOG, under=1):
     ref = oracles.Ref(ref_lib)
     m = ref.map_from_arrays(solid, color)
-    r = oracles.RefRenderer(ref, w, h, level, threads)
+    r = oracles.RefRenderer(ref, w, h, level, threads, under if under > 1 else 0)
     r.set_map(m)
     r.set_fog(fog, 128.0)
     depth = np.zeros((h, w), np.float32)  # the reference never clears its depth buffer: carry ours along too
     for i, sc in enumerate(scenes):
         wfb, wdp = r.render(sc)
-        fb, dp = port.render(solid, color, sc, w, h, fog, 128.0, num, threads, 1, depth=depth)
+        fb, dp = port.render(solid, color, sc, w, h, fog, 128.0, num, threads, under, depth=depth)
         assert np.array_equal(fb & 0xFFFFFF, wfb & 0xFFFFFF), (i, ((fb & 0xFFFFFF) == (wfb & 0xFFFFFF)).mean())
         assert np.array_equal(dp.view(np.uint32), wdp.view(np.uint32)), i
         if num == 2:
@@ -41,6 +41,7 @@ def _compare(ref_lib, level, num, solid, color, scenes, w, h, threads, port, fog
     r.set_map(None)
     r.close()
     ref.map_free(m)
+    ref.L.oref_renderer_set_undersampling(0)  # process-wide cvar: back to the default
 
 
 @pytest.mark.parametrize("variant", ["sse2", "sse", "ieee"])
@@ -75,3 +76,16 @@ def test_synthetic_map_and_eye_inside_solid(port):
     buried["origin"] = (100.5, 100.5, 62.5)
     scenes.insert(2, buried)  # keeps the previous frame's depth, clear colour fogged over it
     _compare("sse2", -1, 2, solid, color, scenes, 256, 256, 4, port)
+
+
+@pytest.mark.parametrize("under", [2, 4])
+@pytest.mark.parametrize("variant", ["sse2", "ieee"])
+def test_undersampling_port_follows_the_cvar(port, title_arrays, under, variant):
+    """r_swUndersampling 2 / 4 (SWMapRenderer.cpp:37,1110-1112,889-911,987-1009): fewer yaw lines, pixels replicated
+    horizontally; 1, 4 and 8 worker threads (the replication interacts with the per-thread start columns)."""
+    lib, level, num = VARIANTS[variant]
+    solid, color = title_arrays
+    for (w, h, fov) in ((800, 600, 30.0), (256, 256, 68.0), (320, 200, 68.0)):
+        scenes = [workloads.title_scene(w, h, fov)] + list(workloads.random_scenes(2, solid, w, h, fov, seed=31))
+        for threads in (4, 1, 8):
+            _compare(lib, level, num, solid, color, scenes, w, h, threads, port, fog=(0.8, 1.0, 1.0), under=under)
