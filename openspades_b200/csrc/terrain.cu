@@ -193,7 +193,8 @@ namespace osb {
 				slot = (int)(V.lineBase + s_prefix[j] + (uint32_t)__popc(b & ((1u << lane) - 1u)));
 				active[slot] = gl;
 			}
-			lineRecs[gl] = make_line_rec(o, slot, vi);
+			// (a culled line never reaches the walker: its record carries the empty hull from the start)
+			lineRecs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : vi);
 		}
 		const uint32_t nTasks = (nLive + (uint32_t)taskLines - 1) / (uint32_t)taskLines;
 		if (threadIdx.x == 0)
@@ -239,7 +240,10 @@ namespace osb {
 
 	// RenderFinal + ApplyFog, see GatherLane in terrain_core.cuh
 	template <bool kSse, bool kSse2Fog>
-	__global__ void __launch_bounds__(kGatherWarps * 32) k_gather_fog(GatherIO io, osbn::SseTables tabs) {
+#ifndef OSB_GATHER_MINB
+#define OSB_GATHER_MINB 8 // <= 64 registers: measured 1.24 ms per 4096 views against 1.29 ms unbounded (72 registers)
+#endif
+	__global__ void __launch_bounds__(kGatherWarps * 32, OSB_GATHER_MINB) k_gather_fog(GatherIO io, osbn::SseTables tabs) {
 		__shared__ GatherShared s_g[kGatherWarps];
 		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 		const uint32_t task = blockIdx.x * kGatherWarps + wid;
@@ -363,6 +367,25 @@ namespace osb {
 		static size_t v = env_mb("OSB200_STRIP_MB", 12288);
 		return v;
 	}
+	// experiment knobs: OSB200_MIN_CHUNKS cuts a large device-output batch into at least that many chunks (alternating on
+	// two streams: chunk k's gather runs beside chunk k+1's walker); OSB200_WALK_BLOCKS caps the walker's resident CTAs per
+	// SM so that gather CTAs of the other stream find registers on the same SM.
+	static int min_chunks() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_MIN_CHUNKS");
+			const int n = e ? atoi(e) : 1;
+			return n < 1 ? 1 : n;
+		}();
+		return v;
+	}
+	static int walk_blocks_cap() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_WALK_BLOCKS");
+			const int n = e ? atoi(e) : 0;
+			return n < 0 ? 0 : n;
+		}();
+		return v;
+	}
 	static bool dual_stream() {
 		static int v = -1;
 		if (v < 0) {
@@ -448,6 +471,8 @@ namespace osb {
 			// more, smaller chunks cost kernel time that hides under the copy of the previous chunk
 			if ((host_fb || host_depth) && nViews >= 1024 && want < 8)
 				want = 8;
+			if (nViews >= 512 && want < (size_t)min_chunks())
+				want = (size_t)min_chunks();
 			budgetLines = std::max<size_t>((total + want - 1) / want + 65536 / 32, 65536);
 		}
 		std::vector<int> chunkStart;
@@ -499,6 +524,10 @@ namespace osb {
 		}
 		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
 		                         c->stream));
+		// the pinned view staging is free again once this copy has run: the host prepares the NEXT call's views while
+		// this call's kernels execute (waiting for the end of the call here cost 0.45 ms per 4096-view step)
+		if (nViews > 8)
+			OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
 		if (hostPrep) {
 			if (grow(T->h_lineDirs, T->hLineCap, maxLines, true))
 				return -2;
@@ -572,7 +601,10 @@ namespace osb {
 			}
 			if (!g.noMap) {
 				const size_t wantWarps = ((size_t)totalLines + taskLines - 1) / taskLines;
-				const size_t resident = (size_t)c->smCount * T->walkBlocksPerSm[num];
+				int perSm = T->walkBlocksPerSm[num];
+				if (walk_blocks_cap() && nChunks > 1)
+					perSm = std::min(perSm, walk_blocks_cap());
+				const size_t resident = (size_t)c->smCount * perSm;
 				const unsigned blocks = (unsigned)std::min<size_t>((wantWarps + kWalkThreads / 32 - 1) / (kWalkThreads / 32), resident);
 				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
 				KLaunch kl(c, K_WALK_LINES, st);
@@ -616,7 +648,8 @@ namespace osb {
 				OSB_CUDA(cudaStreamWaitEvent(c->stream, B.done, 0));
 		}
 		OSB_CUDA(cudaGetLastError());
-		OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
+		if (hostPrep) // line directions / tables were staged in pinned memory as well
+			OSB_CUDA(cudaEventRecord(T->stageFree, c->stream));
 		return 0;
 	}
 	// Context-owned frame + depth of the host-pointer entry points.  The depth buffer persists between frames like

@@ -22,6 +22,14 @@
 #ifndef OSB_GATHER_HALF_UNROLL
 #define OSB_GATHER_HALF_UNROLL 1 // 1 = the two 4-row halves of a block row share one copy of the pixel code; 2 = unrolled
 #endif
+#ifndef OSB_STRIP_HULL
+#define OSB_STRIP_HULL 1 // 1: a finished line publishes the hull [first, last] of its written strip pixels in its LineRec and
+                         //    stores LinePixel::Clear into the (rare) holes inside it: the gather needs no mask word;
+                         // 0: the line publishes its written-pixel bitmask, the gather tests the bit before loading a pixel
+#endif
+#ifndef OSB_GATHER_BATCH
+#define OSB_GATHER_BATCH 4 // pixel rows whose loads are in flight together (4 or 8)
+#endif
 #ifndef OSB_GATHER_ROW_UNROLL
 #define OSB_GATHER_ROW_UNROLL 1 // same for the two block rows of a pass
 #endif
@@ -189,8 +197,10 @@ namespace osb {
 		int pitchTanMinI; // static_cast<int>(minTan * 65536.f)        (SWMapRenderer.cpp:305)
 		int pitchScaleI;  // static_cast<int>(pitchScale * 65536.f)    (:306)
 		int slot;         // strip slot (index in the active list), -1 = culled line: its strip is all LinePixel::Clear
-		int view;         // view index inside the chunk
+		int view;         // view index inside the chunk until the walker has finished the line; then (OSB_STRIP_HULL)
+		                  // first | count << 16: the hull [first, first + count) of the strip pixels the line wrote
 	};
+	constexpr int kEmptyHull = 0; // count = 0
 	static_assert(sizeof(LineRec) == 16, "LineRec is loaded as one int4");
 
 	struct LineSetupOut {
@@ -305,7 +315,7 @@ namespace osb {
 		const ViewParams *views;
 		const float2 *lineDirs;   // horizonDir per line of the chunk
 		const float2 *lineTan;    // {pitchTanMin, pitchScale} per line of the chunk
-		const LineRec *lineRecs;
+		LineRec *lineRecs;        // read at init (view); the hull is written back when the line ends
 		const uint64_t *solid;    // [tiled_xy(x, y)]
 		const uint32_t *color;    // [tiled_xy(x, y) * 64 + z]
 		uint2 *strips;            // [slot * lineRes + i]  LinePixel {combined, depth bits}
@@ -346,7 +356,7 @@ namespace osb {
 		// projection
 		float cz, transScale, transOffset, zscale, heightScale, depthBias;
 		int icz;
-		uint32_t stripBase, maskBase; // slot * lineRes, slot * words
+		uint32_t stripBase, maskBase; // slot * lineRes; slot * words (mask scheme) or the line's index (hull scheme)
 		uint32_t cnt2;
 		int count;
 
@@ -396,7 +406,11 @@ namespace osb {
 			for (int w = 0; w < words; w++)
 				filled[w * fstride] = 0;
 			stripBase = slot * (uint32_t)lineRes;
+#if OSB_STRIP_HULL
+			maskBase = gl;
+#else
 			maskBase = slot * (uint32_t)words;
+#endif
 
 			// ---- DDA set-up (:309-351) ----
 			float dirX = hd.x, dirY = hd.y;
@@ -449,12 +463,44 @@ namespace osb {
 			sNext = io.solid[nT];
 		}
 
-		// publish the written-pixel mask of the finished line
+		// the line has ended: publish what it wrote
 		OSB_HDM void finish(const WalkIO &io, const uint32_t *filled, int fstride) const {
 			const int words = io.lineRes >> 5;
+#if OSB_STRIP_HULL
+			// hull [first, last] of the written strip pixels; the holes inside it (sky seen under an overhang, a bridge,
+			// a floating block) get LinePixel::Clear, so that the gather reads the strip inside the hull and nothing else
+			int first = 1, last = 0, w0 = 0, w1 = -1;
+			for (int w = 0; w < words; w++) {
+				const uint32_t m = filled[w * fstride];
+				if (m) {
+					if (w1 < 0) {
+						w0 = w;
+						first = (w << 5) + osbc::ffs32(m);
+					}
+					w1 = w;
+					last = (w << 5) + 31 - osbc::clz32(m);
+				}
+			}
+			const uint2 clearPix = make_uint2(0u, osbc::f2u(10000.f)); // LinePixel::Clear (:89-92)
+			for (int w = w0; w <= w1; w++) {
+				uint32_t holes = ~filled[w * fstride];
+				if (w == w0)
+					holes &= 0xffffffffu << (first & 31);
+				if (w == w1)
+					holes &= 0xffffffffu >> (31 - (last & 31));
+				uint2 *dst = io.strips + (stripBase + ((uint32_t)w << 5));
+				while (holes) {
+					const int b = osbc::ffs32(holes);
+					holes &= holes - 1;
+					osbc::stcs(dst + b, clearPix);
+				}
+			}
+			io.lineRecs[maskBase].view = first | ((last - first + 1) << 16);
+#else
 			uint32_t *out = io.lineMask + maskBase;
 			for (int w = 0; w < words; w++)
 				out[w] = filled[w * fstride];
+#endif
 		}
 
 		// one candidate span: strip indices [from, to) get {colour of (cell, z) shaded by mode, depth of zA} where still empty
@@ -784,6 +830,17 @@ namespace osb {
 				v2c[k] = fadd(fadd(v2c[k], dDL[k]), dDL[k]);
 		}
 
+#if OSB_STRIP_HULL
+		// LinePixel of (line record, strip index): one predicated load inside the line's hull, LinePixel::Clear outside
+		OSB_HDM uint32_t fetch_mask(const GatherIO &, int, int) const { return 0u; }
+		OSB_HDM uint2 fetch_pixel(const GatherIO &io, int slot, int pitchIndex, uint32_t hull) const {
+			uint2 pix = make_uint2(0u, osbc::f2u(10000.f)); // LinePixel::Clear (:89-92)
+			// first <= pitchIndex < first + count as one unsigned compare; a culled line carries count = 0
+			if ((uint32_t)(pitchIndex - (int)(hull & 0xffffu)) < (hull >> 16))
+				pix = osbc::ldg(io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex));
+			return pix;
+		}
+#else
 		// LinePixel of (strip slot, strip index pitchIndex): two predicated loads, no nested branch, so that the loads of
 		// the pixels of a batch can be in flight together.  mask word first: unwritten strip memory is never read.
 		OSB_HDM uint32_t fetch_mask(const GatherIO &io, int slot, int pitchIndex) const {
@@ -798,6 +855,7 @@ namespace osb {
 				pix = osbc::ldg(io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex));
 			return pix;
 		}
+#endif
 
 		// the 8 pixel rows of block row by + r for this lane's pixel column
 		OSB_HDM void pixel_phase(const GatherIO &io, const osbn::Num<kSse> &num, const GatherShared &sm, int r, int by) {
@@ -839,22 +897,23 @@ namespace osb {
 				const int pitA = pit1 + xs * pitDiff1, pitB = pit3 + xs * pitDiff2;
 				const int dYaw = tdiv_pow2(((yawB - yawA) << 8) >> 8, 3), dPit = tdiv_pow2(pitB - pitA, 3);
 				int yawC = yawA, pitC = pitA;
-				// four pixel rows per batch, stage by stage: the four line records, then the four mask words, then the
+				constexpr int kB = OSB_GATHER_BATCH;
+				// kB (four) pixel rows per batch, stage by stage: the four line records, then the four mask words, then the
 				// four strip pixels are requested together (each stage depends on the one before it)
 				// (the two halves and the two block rows of a pass share ONE copy of this code: fully unrolled the kernel
 				// was 4096 instructions and stalled 6 cycles per issue on instruction fetch)
 #if defined(__CUDA_ARCH__)
 				OSB_PRAGMA(unroll OSB_GATHER_HALF_UNROLL)
 #endif
-				for (int half = 0; half < 2; half++) {
-					int slot[4], pitchIndex[4];
-					int4 lpw[4];
-					uint32_t mw[4];
-					uint2 pix[4];
+				for (int half = 0; half < 8 / kB; half++) {
+					int slot[kB], pitchIndex[kB];
+					int4 lpw[kB];
+					uint32_t mw[kB];
+					uint2 pix[kB];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-					for (int j = 0; j < 4; j++, yawC += dYaw) {
+					for (int j = 0; j < kB; j++, yawC += dYaw) {
 						uint32_t yawIndex = (uint32_t)((yawC << 8) >> 16);
 						yawIndex = (yawIndex * yawScale2) >> 16;
 						yawIndex = (yawIndex * numLines) >> 16;
@@ -864,24 +923,28 @@ namespace osb {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-					for (int j = 0; j < 4; j++, pitC += dPit) {
+					for (int j = 0; j < kB; j++, pitC += dPit) {
 						int pi = (pitC >> 13) - lpw[j].x; // LineRec::pitchTanMinI
 						pi = mulhi(pi, lpw[j].y);         // LineRec::pitchScaleI
 						pitchIndex[j] = pi & (lineRes - 1);
 						slot[j] = lpw[j].z;
+#if OSB_STRIP_HULL
+						mw[j] = (uint32_t)lpw[j].w;
+#else
 						mw[j] = fetch_mask(io, slot[j], pitchIndex[j]);
+#endif
 					}
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-					for (int j = 0; j < 4; j++)
+					for (int j = 0; j < kB; j++)
 						pix[j] = fetch_pixel(io, slot[j], pitchIndex[j], mw[j]);
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
-					for (int j = 0; j < 4; j++, oo += g.fw) {
+					for (int j = 0; j < kB; j++, oo += g.fw) {
 						const float dep = u2f(pix[j].y);
-						stcs(fbV + oo, g.noFog ? pix[j].x : fog_blend<kSse2Fog>(pix[j].x, fmul(dep, half ? fog1 : fog0), fogBR, fogG8));
+						stcs(fbV + oo, g.noFog ? pix[j].x : fog_blend<kSse2Fog>(pix[j].x, fmul(dep, (half * kB + j) < 4 ? fog0 : fog1), fogBR, fogG8));
 						stcs(dbV + oo, dep);
 					}
 				}
@@ -914,7 +977,11 @@ namespace osb {
 					pitch = num.toSpecialTan(pitch);
 					pitch = fmul(fsub(pitch, lt.x), lt.y);
 					const int pitchIndex = osbn::x86_f2i(pitch) & (lineRes - 1);
+#if OSB_STRIP_HULL
+					const uint2 pix = fetch_pixel(io, lp.slot, pitchIndex, (uint32_t)lp.view);
+#else
 					const uint2 pix = fetch_pixel(io, lp.slot, pitchIndex, fetch_mask(io, lp.slot, pitchIndex));
+#endif
 					const float dep = u2f(pix.y);
 					stcs(fbV + oo, g.noFog ? pix.x : fog_blend<kSse2Fog>(pix.x, fmul(dep, py < 4 ? fog0 : fog1), fogBR, fogG8));
 					stcs(dbV + oo, dep);

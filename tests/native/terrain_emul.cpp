@@ -127,12 +127,12 @@ namespace {
 						slot = (int)active.size();
 						active.push_back(gl);
 					}
-					recs[gl] = make_line_rec(o, slot, i);
+					recs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : i);
 				}
 			}
 		} else {
 			for (size_t gl = 0; gl < lines; gl++)
-				recs[gl] = LineRec{0, 0, -1, 0};
+				recs[gl] = LineRec{0, 0, -1, kEmptyHull};
 		}
 		// strips are deliberately filled with garbage: the walker never clears them, the gather must not read an
 		// unwritten pixel
