@@ -33,6 +33,9 @@ FOG = (0.8, 1.0, 1.0)  # Client.cpp:112-113
 FOG_DIST = 128.0
 BYTES_PER_PIXEL = 8  # 4 B BGRX + 4 B f32 depth written once per pixel
 BYTES_PER_RAY = 64   # 24 B in + 40 B RayCastResult out
+CPU_VIEWS_PER_WORKER = 256  # CPU sample of both arms: views per worker process per step
+STRONG_VIEWS_TOTAL = 4096   # BASELINE.json configs[3]: 4096 views sharded by view across 1/2/4/8 GPUs
+FLOP_PER_TAP = 42           # one executed radiosity tap (GLRadiosityRenderer.cpp:216-262), sqrt and each divide counted as 1
 
 
 def parse_args():
@@ -125,15 +128,18 @@ def read_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def read_traffic(kernel, workload):
-    """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json)."""
+def read_traffic(kernel, workload, views_per_launch):
+    """dram bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json): NOT a live
+    counter -- a profiler cannot run inside the timed region.  Returns (bytes scaled to this run's launch size, label)."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get(workload, {}).get(kernel)
+            t = json.load(open(p)).get(workload, {})
+            if kernel in t:
+                return t[kernel] * views_per_launch / t.get("views_per_launch", views_per_launch), t.get("source")
         except ValueError:
             pass
-    return None
+    return None, None
 
 
 def cpu_views_sample(args, solid, color, S, per_worker):
@@ -155,8 +161,9 @@ def run_reference(args):
     from oracle import cpu_bench
     S = args.size
     solid, color = load_map_cpu_only()
-    # bounded sample: 32 views per worker process per step (~0.2 s of work per core per step)
-    pool, n = cpu_views_sample(args, solid, color, S, 32)
+    # bounded sample: 256 views per worker process per step (~1 s of work per core per step) -- the same sample, pose
+    # seed and worker layout as the cpu_baseline leg of the GPU arm, so that the two CPU numbers of one box agree
+    pool, n = cpu_views_sample(args, solid, color, S, CPU_VIEWS_PER_WORKER)
     with pool:
         for _ in range(args.warmup):
             pool.step()
@@ -172,13 +179,65 @@ def run_reference(args):
         "config": {"workload": f"C4 batched {S}x{S} views, fovY 68, fog (0.8,1,1)/128, Title.vxl",
                    "views_per_step": n, "width": S, "height": S},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": pool.workers, "kind": pool.kind,
-                         "sample": f"{n} views per step = 32 per worker process x {pool.workers} processes, each a private "
+                         "sample": f"{n} views per step = {CPU_VIEWS_PER_WORKER} per worker process x {pool.workers} processes, each a private "
                                    "SWRenderer (V-SSE2, r_swNumThreads=1), StartScene+EndScene+FrameDone"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit_json(line)
     return 0
+
+
+def parity_views(ctx, scenes, d_fb, d_dp, solid, color, S, n_sample=64, seed=7):
+    """Compares a seeded sample of the views the timed steps rendered (frames + depth still on the device) with the
+    unmodified reference SWRenderer (oracle/_ref, V-SSE2, r_swNumThreads = 4) or, where it did not travel, the oracle
+    port.  Checker only: runs after the timed regions."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracles
+    rng = np.random.default_rng(seed)
+    idx = np.sort(rng.choice(len(scenes), size=min(n_sample, len(scenes)), replace=False))
+    fb = d_fb[idx.tolist()].cpu().numpy().view(np.uint32)
+    dp = d_dp[idx.tolist()].cpu().numpy()
+    use_ref = oracles.ref_available("sse2") and os.path.exists(os.path.join(oracles.ORACLE_DIR, "_ref", "liboref_sse2.so"))
+    same_px = same_dp = within1 = 0
+    total = 0
+    if use_ref:
+        ref = oracles.Ref("sse2")
+        m = ref.map_from_arrays(solid, color)
+        r = oracles.RefRenderer(ref, S, S, -1, 4)
+        r.set_map(m)
+        r.set_fog(FOG, FOG_DIST)
+    else:
+        port = oracles.Port()
+    for k, i in enumerate(idx):
+        if use_ref:
+            rfb, rdp = r.render(scenes[i])
+        else:
+            rfb, rdp = port.render(solid, color, scenes[i], S, S, FOG, FOG_DIST, 2, 4, 1)
+        a, b = fb[k] & 0xFFFFFF, rfb & 0xFFFFFF
+        same_px += int((a == b).sum())
+        d = np.abs(((a[..., None] >> np.array([0, 8, 16], np.uint32)) & 0xFF).astype(int)
+                   - ((b[..., None] >> np.array([0, 8, 16], np.uint32)) & 0xFF).astype(int)).max(axis=-1)
+        within1 += int((d <= 1).sum())
+        same_dp += int((dp[k].view(np.uint32) == rdp.view(np.uint32)).sum())
+        total += a.size
+    if use_ref:
+        r.set_map(None)
+        r.close()
+        ref.map_free(m)
+    return {"views": int(len(idx)), "against": "oracle/_ref SWRenderer (unmodified reference)" if use_ref else "oracle port",
+            "identical": same_px / total, "within_1_lsb": within1 / total, "depth_identical": same_dp / total}
+
+
+def parity_rays(d_out, v0, d, solid, n_sample=1 << 20):
+    """First n_sample rays of the timed CastRay2 batch against the oracle on all host cores: every field bit-exact."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracles
+    from oracle import cpu_bench
+    n = min(n_sample, len(v0))
+    got = d_out[:n].cpu().numpy().view(np.uint8).reshape(n, 40)
+    want = oracles.Port().castray2(solid, v0[:n], d[:n], 256, threads=cpu_bench.usable_cores())
+    return {"rays": int(n), "bit_exact": bool(got.tobytes() == want.tobytes())}
 
 
 def run_b200(args):
@@ -217,13 +276,13 @@ def run_b200(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
-            pool, n_cpu = cpu_views_sample(args, solid, color, S, 256)
+            pool, n_cpu = cpu_views_sample(args, solid, color, S, CPU_VIEWS_PER_WORKER)
             with pool:
                 pool.step()  # warm
                 r = pool.step()
             cpu_baseline = {
                 "value": n_cpu * S * S / r["seconds"] / 1e6, "unit": UNIT, "cores": pool.workers, "kind": pool.kind,
-                "sample": f"{n_cpu} of the same {S}x{S} views (256 per worker process x {pool.workers} processes, each a "
+                "sample": f"{n_cpu} of the same {S}x{S} views ({CPU_VIEWS_PER_WORKER} per worker process x {pool.workers} processes, each a "
                           f"private SWRenderer V-SSE2 r_swNumThreads=1), {r['seconds']:.2f} s wall"}
         except Exception as e:  # the baseline is a reported extra; never let it sink the GPU numbers
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(e)}
@@ -296,14 +355,118 @@ def run_b200(args):
     clocks = sampler.summary(t_wall0, t_wall2)
     checksum = int(h_fb.view(-1)[:: 4099].to(torch.int64).sum().item())  # the step's result was read on the host
 
+    # ---- the headline number carries its own correctness: a seeded sample of the rendered views vs the reference ----
+    parity = None
+    if rank == 0:
+        step_device()
+        ctx.sync()
+        try:
+            parity = parity_views(ctx, scenes, d_fb, d_dp, solid, color, S)
+        except Exception as e:  # a checker problem must not sink the measurement; it is reported
+            parity = {"error": repr(e)}
+
+    # ---- strong scaling: BASELINE.json's config is 4096 views TOTAL, sharded by view over the N GPUs ----
+    from openspades_b200 import sharding
+    sv = STRONG_VIEWS_TOTAL
+    lo, hi = sharding.shard_range(sv, rank, world)
+    if world == 1 and nv == sv:
+        strong_ms = ms_per_step
+    else:
+        sc_all = workloads.random_scenes(sv, solid, S, S, 68.0, seed=4321)
+        mine = np.ascontiguousarray(sc_all[lo:hi])
+        s_fb, s_dp = d_fb[:hi - lo], d_dp[:hi - lo]
+        for _ in range(W):
+            ctx.render_device(mine, S, S, FOG, FOG_DIST, s_fb, s_dp)
+        ctx.sync()
+        barrier()
+        e0.record(ext)
+        for _ in range(K):
+            ctx.render_device(mine, S, S, FOG, FOG_DIST, s_fb, s_dp)
+        e1.record(ext)
+        e1.synchronize()
+        barrier()
+        strong_ms = max_over_ranks(e0.elapsed_time(e1)) / K
+    t1_equiv = ms_per_step * sv / nv  # one GPU rendering all sv views (the weak run's per-GPU load, scaled if --views differs)
+    strong = {"views_total": sv, "views_per_gpu": hi - lo, "ms_per_step": strong_ms,
+              "mpixel_s": sv * S * S / (strong_ms * 1e-3) / 1e6,
+              "efficiency_vs_n1": (t1_equiv / strong_ms) / world,
+              "note": "efficiency = (ms of one GPU rendering all 4096 views, from this run's weak step) / (N x ms of N GPUs "
+                      "rendering 4096 / N each); a launch of few hundred views per GPU is dominated by fixed costs (per-call "
+                      "host set-up of the views, five launches, the latency of the longest yaw lines)"}
+
+    # ---- the one collective of the design (control path): edit broadcast + dirty-column flush; optional gather to rank 0 ----
+    multi_gpu = None
+    if world > 1:
+        solid_w, color_w = solid.copy(), color.copy()
+        with osb.Context(device=local, numerics=osb.NUM_SSE2, sw_threads=4) as ec:
+            ec.map_upload(solid_w, color_w)
+            rng = np.random.default_rng(99)
+            frames, per_frame = 20, 100
+            ed_frames = []
+            for _ in range(frames):
+                xs, ys = rng.integers(0, 512, per_frame), rng.integers(0, 512, per_frame)
+                ed = []
+                for x, y in zip(xs, ys):
+                    col = int(solid[x, y])
+                    top = (col & -col).bit_length() - 1
+                    ed.append((x, y, max(top - 1, 0), 1, 0x64000000 | int(rng.integers(0, 1 << 24))))
+                ed_frames.append(sharding.make_edits(*zip(*ed)))
+            barrier()
+            t0 = time.perf_counter()
+            t_bcast = 0.0
+            for f in range(frames):
+                tb = time.perf_counter()
+                e = sharding.broadcast_edits(ed_frames[f] if rank == 0 else None, 0, dev)
+                t_bcast += time.perf_counter() - tb
+                sharding.apply_edits_arrays(solid_w, color_w, e, ec)
+                ec.map_flush(solid_w, color_w)
+            ec.sync()
+            barrier()
+            edit_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / frames
+            bcast_ms = max_over_ranks(t_bcast * 1e3) / frames
+            digest = sharding.map_digest(solid_w, color_w)
+        dig = [None] * world
+        dist.all_gather_object(dig, digest)
+        # gather of the finished frames to rank 0: grouped send / recv (not an all_gather: only the root receives)
+        reps = 3
+        gb = d_fb.numel() * 4 / 1e9
+        bufs = [torch.empty_like(d_fb) for _ in range(world - 1)] if rank == 0 else None
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            if rank == 0:
+                ops = [dist.P2POp(dist.irecv, bufs[r - 1], r) for r in range(1, world)]
+            else:
+                ops = [dist.P2POp(dist.isend, d_fb, 0)]
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+            torch.cuda.synchronize()
+        barrier()
+        gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / reps
+        del bufs
+        multi_gpu = {"edit_broadcast": {"edits_per_frame": per_frame, "frames": frames, "ms_per_frame_total": edit_ms,
+                                        "ms_per_frame_broadcast": bcast_ms, "replicas_identical": len(set(dig)) == 1,
+                                        "what": "rank 0's edit list (12 B per GameMap::Set) broadcast over NCCL, applied to every "
+                                                "rank's host map, dirty columns flushed to its GPU"},
+                     "gather_to_rank0": {"gb_per_rank": gb, "ms": gather_ms,
+                                         "root_ingress_gb_s": gb * (world - 1) / (gather_ms * 1e-3),
+                                         "value_with_gather_mpixel_s": world * pixels_per_step / ((ms_per_step + gather_ms) * 1e-3) / 1e6,
+                                         "what": "BGRX frames of every rank sent to rank 0 (grouped isend / irecv), after the "
+                                                 "render; not part of `value`"}}
+
     # ---- roofline of the dominant kernel (CUDA events around every launch, on the launching stream) ----
     peak, peak_src = read_peaks()
     dom = max(ktimes, key=lambda k: ktimes[k][1])
     dl, dms = ktimes[dom]
     bytes_per_launch = BYTES_PER_PIXEL * pixels_per_step * K / max(dl, 1)
     achieved = bytes_per_launch / (dms / max(dl, 1) * 1e-3) / 1e9
+    traffic, traffic_src = read_traffic(dom, "views256", nv / max(dl / K, 1))
+    step_bytes = BYTES_PER_PIXEL * pixels_per_step
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": read_traffic(dom, "views256"), "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                "step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_per_step * 1e-3) / 1e9,
+                         "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
+                         "note": "the whole step (all kernels + gaps) against the same 8 B/pixel"},
                 "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": dms / max(dl, 1),
                 "kernel_timing": "separate pass of the same K steps, chunks serialised on one stream, CUDA events "
                                  "around every launch (the timed region overlaps chunks on two streams)",
@@ -312,9 +475,11 @@ def run_b200(args):
 
     extra = {}
     if not args.no_extra:
-        extra = run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
+        extra = run_extras(args, ctx, ext, solid, color, dev, world, barrier, max_over_ranks, peak)
     sampler.stop()
 
+    if rank == 0 and isinstance(parity, dict) and isinstance(extra.get("castray2", {}).get("parity"), dict):
+        parity.update(extra["castray2"]["parity"])
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -327,7 +492,8 @@ def run_b200(args):
                              "buffers, far beyond the 126 MB L2; the 2 MiB map bitmap is L2-resident by design"
                              % (pixels_per_step / 1e9, pixels_per_step * 8 / 1e9)},
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "extra": extra, "result_checksum": checksum,
+            "cpu_baseline": cpu_baseline, "parity_sample": parity, "strong": strong, "multi_gpu": multi_gpu,
+            "extra": extra, "result_checksum": checksum,
         }
         emit_json(line)
     ctx.close()
@@ -336,13 +502,59 @@ def run_b200(args):
     return 0
 
 
-def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak):
+def run_extras(args, ctx, ext, solid, color, dev, world, barrier, max_over_ranks, peak):
     """configs[1] (1920x1080 single view; replicas only, rank-local) and configs[2] (CastRay2 batch,
     rays sharded by ray, aggregate over ranks).  Same timing rules: warm-up, events on the context stream."""
     import torch
     from openspades_b200 import workloads
     import openspades_b200 as osb
     out = {}
+    rank = int(os.environ.get("RANK", "0"))
+    do_cpu = rank == 0 and world == 1 and not args.no_cpu
+    if do_cpu:
+        from oracle import cpu_bench
+    # ---- C1: 800x600, the title-screen camera of the bundled map (fovY 30, fog (0.1,0.1,0.1)/128), the reference's own
+    # CPU-runnable case: SWRenderer with its default 4 worker threads beside it ----
+    w, h = 800, 600
+    sc = workloads.title_scene(w, h, 30.0)
+    fb = torch.empty((1, h, w), dtype=torch.int32, device=dev)
+    dp = torch.zeros((1, h, w), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    n_it = 20
+    for _ in range(3):
+        ctx.render_device(sc, w, h, (0.1, 0.1, 0.1), 128.0, fb, dp)
+    ctx.sync()
+    tot = 0.0
+    for _ in range(n_it):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        ctx.render_device(sc, w, h, (0.1, 0.1, 0.1), 128.0, fb, dp)
+        e1.record(ext)
+        e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    c1_ms = tot / n_it
+    hfb = torch.empty((1, h, w), dtype=torch.int32, pin_memory=True)
+    ctx.render(sc, w, h, (0.1, 0.1, 0.1), 128.0, want_depth=False, out_bgrx=hfb)
+    t0 = time.perf_counter()
+    for _ in range(n_it):
+        ctx.render(sc, w, h, (0.1, 0.1, 0.1), 128.0, want_depth=False, out_bgrx=hfb)
+    c1_e2e = (time.perf_counter() - t0) * 1e3 / n_it
+    out["frame_800x600_title"] = {"workload": "C1 800x600 single view, title-screen camera fovY 30, fog (0.1,0.1,0.1)/128, Title.vxl, "
+                                              "V-SSE2 (L2 flushed between iterations)", "ms_per_frame": c1_ms,
+                                  "mpixel_s": w * h / c1_ms / 1e3, "e2e_ms_per_frame": c1_e2e, "e2e_mpixel_s": w * h / c1_e2e / 1e3,
+                                  "hbm_frac_algorithmic": (BYTES_PER_PIXEL * w * h / (c1_ms * 1e-3) / 1e9) / peak}
+    if do_cpu:
+        try:
+            cms = cpu_bench.single_view_ms(solid, color, sc, w, h, (0.1, 0.1, 0.1), 128.0, threads=4, reps=10)
+            out["frame_800x600_title"]["cpu_baseline"] = {"value": w * h / cms / 1e3, "unit": "Mpixel/s", "ms_per_frame": cms,
+                                                          "cores": 4, "kind": cpu_bench.kind(),
+                                                          "sample": "the same frame, one SWRenderer, r_swNumThreads = 4 (the reference's "
+                                                                    "default), best of 10"}
+        except Exception as e:
+            out["frame_800x600_title"]["cpu_baseline"] = {"value": None, "kind": "unavailable", "sample": repr(e)}
+    del fb, dp, hfb, flush
     # ---- 1920x1080 single view, title pose + fog (0.1,0.1,0.1)/128 ----
     w, h = 1920, 1080
     sc = workloads.title_scene(w, h, 68.0)
@@ -375,6 +587,14 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                                       "flushed between iterations)", "ms_per_frame": ms,
                           "mpixel_s": w * h / ms / 1e3, "e2e_ms_per_frame": e2e_ms, "e2e_mpixel_s": w * h / e2e_ms / 1e3,
                           "hbm_frac_algorithmic": (BYTES_PER_PIXEL * w * h / (ms * 1e-3) / 1e9) / peak}
+    if do_cpu:
+        try:
+            cms = cpu_bench.single_view_ms(solid, color, sc, w, h, (0.1, 0.1, 0.1), 128.0, threads=4, reps=5)
+            out["frame_1080p"]["cpu_baseline"] = {"value": w * h / cms / 1e3, "unit": "Mpixel/s", "ms_per_frame": cms, "cores": 4,
+                                                  "kind": cpu_bench.kind(),
+                                                  "sample": "the same frame, one SWRenderer, r_swNumThreads = 4, best of 5"}
+        except Exception as e:
+            out["frame_1080p"]["cpu_baseline"] = {"value": None, "kind": "unavailable", "sample": repr(e)}
     # ---- the same frame as the game submits it: + 64 voxel models (3 distinct, 24x24x40) + 8 point lights, full EndScene ----
     handles = [ctx.model_create(*workloads.blob_model(11 + k)) for k in range(3)]
     inst, lights = workloads.game_frame(sc, handles, 64, 8)
@@ -444,6 +664,48 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                        "ms_per_batch": ms, "mrays_s": world * n / ms / 1e3, "hit_fraction": hits / n,
                        "hbm_frac_algorithmic": (BYTES_PER_RAY * n / (ms * 1e-3) / 1e9) / peak,
                        "e2e_mrays_s": world * ne / e2e_ms / 1e3, "e2e_rays": ne}
+    if rank == 0:
+        try:
+            out["castray2"]["parity"] = parity_rays(d_out, v0, d, solid)
+        except Exception as e:
+            out["castray2"]["parity"] = {"error": repr(e)}
+    # strong scaling of C3: 2^24 rays TOTAL split over the ranks
+    total_rays = 1 << 24
+    if world > 1:
+        from openspades_b200 import sharding
+        lo, hi = sharding.shard_range(total_rays, rank, world)
+        m = min(hi - lo, n)
+        for _ in range(2):
+            ctx.castray2_device(d_v0, d_d, 256, d_out, m)
+        ctx.sync()
+        barrier()
+        e0.record(ext)
+        for _ in range(K):
+            ctx.castray2_device(d_v0, d_d, 256, d_out, m)
+        e1.record(ext)
+        e1.synchronize()
+        barrier()
+        sms = max_over_ranks(e0.elapsed_time(e1)) / K
+        out["castray2"]["strong"] = {"rays_total": total_rays, "rays_per_gpu": m, "ms_per_batch": sms,
+                                     "mrays_s": total_rays / sms / 1e3,
+                                     "efficiency_vs_n1": (ms * total_rays / n / sms) / world}
+    if do_cpu:
+        try:
+            cores = cpu_bench.usable_cores()
+            per = 250_000  # ~0.5 s per core at the reference's ~0.5 Mrays/s/core
+            with cpu_bench.Pool("rays", solid, color, (v0[:cores * per], d[:cores * per]), workers=cores, max_steps=256) as pool:
+                pool.step()
+                r_all = pool.step()
+            with cpu_bench.Pool("rays", solid, color, (v0[:per], d[:per]), workers=1, max_steps=256) as pool:
+                pool.step()
+                r_one = pool.step()
+            out["castray2"]["cpu_baseline"] = {"value": r_all["units"] / r_all["seconds"] / 1e6, "unit": "Mrays/s", "cores": cores,
+                                               "kind": cpu_bench.kind(), "one_core_mrays_s": r_one["units"] / r_one["seconds"] / 1e6,
+                                               "sample": f"{cores * per} of the same rays (GameMap::CastRay2, maxSteps 256), {per} per "
+                                                         f"worker process x {cores} processes, {r_all['seconds']:.2f} s wall; and {per} "
+                                                         "rays on one core"}
+        except Exception as e:
+            out["castray2"]["cpu_baseline"] = {"value": None, "kind": "unavailable", "sample": repr(e)}
     del d_v0, d_d, d_out
 
     # ---- C5: full-map radiosity + incremental edits (GLRadiosityRenderer CPU half) ----
@@ -459,6 +721,7 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
         full_wall_ms = (time.perf_counter() - t0) * 1e3
         kt = rc.timing_read()
         full_ms = kt["k_radiosity"][1]
+        taps_done, taps_all = rc.radiosity_count_taps()
         # 100 frames x 100 random dig/build edits: mark_dirty -> flush -> shadow update -> radiosity(all dirty)
         rng = np.random.default_rng(99)
         frames, per_frame = 100, 100
@@ -642,9 +905,34 @@ def run_extras(args, ctx, ext, solid, dev, world, barrier, max_over_ranks, peak)
                                     "radiosity update of every dirty chunk (host edit generation inside the wall time)",
                         "full_map_chunks": n_chunks, "full_map_kernel_ms": full_ms, "full_map_wall_ms": full_wall_ms,
                         "full_map_mvoxels_s": 512 * 512 * 64 / full_ms / 1e3,
-                        "hbm_frac_algorithmic": (16 * 512 * 512 * 64 / (full_ms * 1e-3) / 1e9) / peak,
                         "edits_per_s": frames * per_frame / inc_s, "chunk_updates": upd,
                         "incremental_kernel_ms_per_frame": {k: v[1] / frames for k, v in kt2.items() if v[0]}}
+    # C5 is bound by FP32 issue, not by HBM: achieved FP32 rate from the EXECUTED taps (those that pass
+    # Evaluate's normal cull, counted by a separate kernel) against SMs x 128 lanes x clock; the code is built without FMA
+    # contraction (bit parity with the x86 reference), so its ceiling is one operation per lane per clock, half the FMA peak.
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    clk_ghz = 1.965
+    flops = taps_done * FLOP_PER_TAP
+    achieved_tf = flops / (full_ms * 1e-3) / 1e12
+    peak_nofma = sm_count * 128 * clk_ghz / 1e3
+    out["radiosity"]["roofline"] = {"bound": "fp32 issue (CUDA cores), no tensor cores: nothing here is a contraction",
+                                    "executed_taps": taps_done, "tap_slots": taps_all, "executed_fraction": taps_done / taps_all,
+                                    "flop_per_tap": FLOP_PER_TAP, "achieved": achieved_tf, "unit": "TFLOP/s",
+                                    "peak_no_fma": peak_nofma, "peak_fma": 2 * peak_nofma, "frac_of_no_fma_peak": achieved_tf / peak_nofma,
+                                    "frac_of_fma_peak": achieved_tf / (2 * peak_nofma),
+                                    "peak_source": f"{sm_count} SMs x 128 FP32 lanes x {clk_ghz} GHz (x 2 with FMA)"}
+    if do_cpu:
+        try:
+            cores = cpu_bench.usable_cores()
+            s1, v1 = cpu_bench.radiosity_sample(solid, color, 32, 1)
+            sa, va = cpu_bench.radiosity_sample(solid, color, max(64, 8 * cores), cores)
+            out["radiosity"]["cpu_baseline"] = {"value": va / sa / 1e6, "unit": "Mvoxel/s", "cores": cores, "kind": cpu_bench.kind(),
+                                                "one_core_mvoxel_s": v1 / s1 / 1e6,
+                                                "full_map_seconds_extrapolated": 512 * 512 * 64 / (va / sa),
+                                                "sample": f"GLRadiosityRenderer::UpdateChunk over {va // 4096} of the 4096 chunks (even "
+                                                          f"spread, all four z layers) on {cores} threads, {sa:.2f} s wall; 32 chunks on one"}
+        except Exception as e:
+            out["radiosity"]["cpu_baseline"] = {"value": None, "kind": "unavailable", "sample": repr(e)}
     return out
 
 

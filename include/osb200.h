@@ -175,6 +175,9 @@ OSB200_API int osb200_radiosity_evaluate_box(osb200_ctx *ctx, int x0, int y0, in
                                              float *out);
 /* device pointers of the four resident 512x512x64 RGB10A2 volumes ([z][y][x], the layout of the reference's
  * 3-D textures, GLRadiosityRenderer.cpp:120-129) and of the 512x512 shadow bitmap; any may be NULL */
+/* Measurement hook: number of (voxel, tap) pairs of a full-map Evaluate that pass the normal cull
+ * (GLRadiosityRenderer.cpp:199-214) and execute the float work; total = 512*512*64*169.  Used for the FP32 figure of C5. */
+OSB200_API int osb200_radiosity_count_taps(osb200_ctx *ctx, unsigned long long *executed, unsigned long long *total);
 OSB200_API int osb200_radiosity_volumes(osb200_ctx *ctx, const uint32_t **flat, const uint32_t **x,
                                         const uint32_t **y, const uint32_t **z, const uint32_t **shadow);
 

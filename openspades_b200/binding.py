@@ -100,6 +100,7 @@ def load_library():
     lib.osb200_radiosity_read_chunk.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp]
     lib.osb200_radiosity_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
     lib.osb200_radiosity_volumes.argtypes = [vp] + [ctypes.POINTER(vp)] * 5
+    lib.osb200_radiosity_count_taps.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong)]
     lib.osb200_castray.argtypes = [vp, vp, vp, fp, vp, sz]
     lib.osb200_model_create.argtypes = [vp, ci, ci, ci, vp, vp, vp, ctypes.POINTER(vp)]
     lib.osb200_model_destroy.argtypes = [vp]
@@ -325,6 +326,12 @@ class Context:
     def radiosity_update(self, max_chunks=-1, eye=None):
         e = None if eye is None else np.ascontiguousarray(eye, np.float32)
         return self._check(self._lib.osb200_radiosity_update(self._h, int(max_chunks), None if e is None else e.ctypes.data))
+
+    def radiosity_count_taps(self):
+        """(executed, total) taps of a full-map Evaluate: measurement hook for the FP32 roofline of C5"""
+        a, t = ctypes.c_ulonglong(0), ctypes.c_ulonglong(0)
+        self._check(self._lib.osb200_radiosity_count_taps(self._h, ctypes.byref(a), ctypes.byref(t)))
+        return int(a.value), int(t.value)
 
     def radiosity_chunk_info(self, cx, cy, cz):
         out = np.zeros(7, np.int32)

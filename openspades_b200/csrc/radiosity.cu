@@ -328,6 +328,38 @@ namespace osb {
 		}
 	}
 
+	// Measurement hook: how many of the 169 taps per voxel pass Evaluate's normal cull (GLRadiosityRenderer.cpp:199-214) and
+	// do the float work -- the executed-tap count behind bench.py's FP32 figure for C5.  One CTA per 16^3 chunk.
+	__global__ void __launch_bounds__(256) k_radiosity_count_taps(const uint32_t *__restrict__ bitmap, unsigned long long *out) {
+		__shared__ uint32_t tile[kTileW * kTileH];
+		__shared__ unsigned int s_sum;
+		const int ci = blockIdx.x;
+		const int cz = ci & 3, cx = (ci >> 2) & 31, cy = ci >> 7;
+		const int X0 = cx * 16, Y0 = cy * 16, Z0 = cz * 16;
+		const int tx0 = X0 - kEnv, ty0 = Y0 - Z0 - (kChunk - 1) - kEnv;
+		if (threadIdx.x == 0)
+			s_sum = 0;
+		load_tile(tile, bitmap, tx0, ty0);
+		__syncthreads();
+		unsigned int mine = 0;
+		for (int i = threadIdx.x; i < 4096; i += blockDim.x) {
+			const int vx = X0 + (i & 15), vy = Y0 + ((i >> 4) & 15), vz = Z0 + (i >> 8);
+			const int ccx = vx, ccy = vy - vz;
+			const uint32_t *base = tile + (ccy - kEnv - ty0) * kTileW + (ccx - kEnv - tx0);
+			for (int dx = -kEnv; dx <= kEnv; dx++)
+				for (int dy = -kEnv; dy <= kEnv; dy++) {
+					const uint32_t pixel = base[(dy + kEnv) * kTileW + (dx + kEnv)];
+					const int depth = (int)(pixel >> 24);
+					const int wy = ccy + dy + depth, wz = depth;
+					mine += (pixel & 0x80u) ? (wy > vy) : (wz > vz);
+				}
+		}
+		atomicAdd(&s_sum, mine);
+		__syncthreads();
+		if (threadIdx.x == 0)
+			atomicAdd(out, (unsigned long long)s_sum);
+	}
+
 	__global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v) {
 		for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
 			p[i] = v;
@@ -574,6 +606,29 @@ int osb200_radiosity_evaluate_box(osb200_ctx *c, int x0, int y0, int z0, int x1,
 	OSB_CUDA(cudaGetLastError());
 	OSB_CUDA(cudaMemcpyAsync(out, c->d_scratch, bytes, cudaMemcpyDeviceToHost, c->stream));
 	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return 0;
+}
+
+int osb200_radiosity_count_taps(osb200_ctx *c, unsigned long long *executed, unsigned long long *total) {
+	if (!c || !c->mapLoaded || !executed) {
+		osb::set_error("osb200_radiosity_count_taps: bad argument or no map");
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	int rc = osb::shadow_sync(c);
+	if (rc)
+		return rc;
+	if (c->ensure_scratch(sizeof(unsigned long long)))
+		return -2;
+	OSB_CUDA(cudaMemsetAsync(c->d_scratch, 0, sizeof(unsigned long long), c->stream));
+	osb::k_radiosity_count_taps<<<osb::kNumChunks, 256, 0, c->stream>>>(c->radiosity->d_bitmap,
+	                                                                  reinterpret_cast<unsigned long long *>(c->d_scratch));
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	OSB_CUDA(cudaMemcpyAsync(executed, c->d_scratch, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	if (total)
+		*total = 512ull * 512ull * 64ull * 169ull;
 	return 0;
 }
 

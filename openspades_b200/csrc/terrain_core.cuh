@@ -17,6 +17,9 @@
 #include <cstdlib>
 #include <cstring>
 
+#ifndef OSB_STAT
+#define OSB_STAT(what, n) // emulation-only counters (tests/native/terrain_emul.cpp)
+#endif
 #define OSB_PRAGMA_(x) _Pragma(#x)
 #define OSB_PRAGMA(x) OSB_PRAGMA_(x)
 #ifndef OSB_GATHER_HALF_UNROLL
@@ -526,10 +529,12 @@ namespace osb {
 					havePx = true;
 				}
 				uint2 *dst = io.strips + (stripBase + ((uint32_t)w << 5));
+				OSB_STAT(1, 1); // word with landing pixels
 				do {
 					const int b = ffs32(todo);
 					todo &= todo - 1;
 					stcs(dst + b, px);
+					OSB_STAT(2, 1); // strip pixel stored
 				} while (todo);
 			}
 		}
@@ -605,6 +610,7 @@ namespace osb {
 					z = 32 + ffs32(cHi);
 					cHi &= cHi - 1;
 				}
+				OSB_STAT(0, 1); // span candidate
 				const int pA = transform(num, invDist, z, vmax);
 				const int pB = transform(num, phase ? invDist : oldInvDist, z + phase, vmax);
 				if (pA < pB)

@@ -132,6 +132,85 @@ def _worker(spec_path, idx):
         print(json.dumps({"idx": idx, "n": n, "start": t_start, "end": t_end}), file=proto, flush=True)
 
 
+def single_view_ms(solid, color, scene, w, h, fog, fog_dist, threads=4, reps=10):
+    """One view, the way the game renders it: a single SWRenderer with r_swNumThreads = threads (default 4,
+    SWRenderer.cpp:41); best of `reps` wall times around StartScene .. EndScene .. FrameDone, in ms."""
+    solid, color = np.ascontiguousarray(solid), np.ascontiguousarray(color)
+    sc = np.ascontiguousarray(np.atleast_1d(scene))
+    fb = np.zeros((h, w), np.uint32)
+    dp = np.zeros((h, w), np.float32)
+    if kind() == "reference":
+        L = _load_ref()
+        m = L.oref_map_from_arrays(solid.ctypes.data, color.ctypes.data)
+        r = L.oref_renderer_create(w, h, -1, threads)
+        L.oref_renderer_set_map(r, m)
+        L.oref_renderer_set_fog(r, fog[0], fog[1], fog[2], fog_dist)
+
+        def run():
+            L.oref_renderer_render(r, sc.ctypes.data, fb.ctypes.data, dp.ctypes.data)
+    else:
+        L = _load_port()
+        fc = np.asarray(fog, np.float32)
+
+        def run():
+            L.orc_render(solid.ctypes.data, color.ctypes.data, sc.ctypes.data, w, h, fc.ctypes.data, fog_dist, 2, threads, 1,
+                         fb.ctypes.data, dp.ctypes.data)
+    run()
+    best = 1e9
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        run()
+        best = min(best, time.perf_counter() - t0)
+    return best * 1e3
+
+
+def radiosity_sample(solid, color, n_chunks=64, threads=1):
+    """GLRadiosityRenderer::UpdateChunk (Evaluate x 4096 + EncodeValue x 4, GLRadiosityRenderer.cpp:517-543) over a
+    deterministic spread of `n_chunks` of the 4096 chunks of the map, `threads` chunks at a time (the function is
+    independent per chunk).  Returns (seconds, voxels)."""
+    from concurrent.futures import ThreadPoolExecutor
+    solid, color = np.ascontiguousarray(solid), np.ascontiguousarray(color)
+    # chunk index = (cx + cy * 32) * 4 + cz: an even spread over the map that also cycles through the four z layers
+    ids = [((i * 4096 // n_chunks) & ~3) | (i & 3) for i in range(n_chunks)]
+    todo = [((ci >> 2) & 31, ci >> 7, ci & 3) for ci in ids]
+    vp, ci_ = ctypes.c_void_p, ctypes.c_int
+    if kind() == "reference":
+        L = _load_ref()
+        L.oref_rad_create.restype = vp
+        L.oref_rad_create.argtypes = [vp, ci_]
+        L.oref_rad_shadow_update.argtypes = [vp]
+        L.oref_rad_update_chunk.argtypes = [vp, ci_, ci_, ci_]
+        m = L.oref_map_from_arrays(solid.ctypes.data, color.ctypes.data)
+        hnd = L.oref_rad_create(m, 1)
+        L.oref_rad_shadow_update(hnd)
+
+        def one(c):
+            L.oref_rad_update_chunk(hnd, c[0], c[1], c[2])
+    else:
+        L = _load_port()
+        L.orc_shadow_bitmap.argtypes = [vp, vp, vp]
+        L.orc_shadow_bitmap.restype = None
+        L.orc_radiosity_box.argtypes = [vp] + [ci_] * 7 + [vp, vp, ci_]
+        L.orc_radiosity_box.restype = None
+        bitmap = np.zeros((512, 512), np.uint32)
+        L.orc_shadow_bitmap(solid.ctypes.data, color.ctypes.data, bitmap.ctypes.data)
+        outs = {}
+
+        def one(c):
+            enc = outs.setdefault(c, np.zeros(4096 * 4, np.uint32))
+            L.orc_radiosity_box(bitmap.ctypes.data, c[0] * 16, c[1] * 16, c[2] * 16, c[0] * 16 + 15, c[1] * 16 + 15,
+                                c[2] * 16 + 15, 1, None, enc.ctypes.data, 1)
+    one(todo[0])
+    t0 = time.perf_counter()
+    if threads <= 1:
+        for c in todo:
+            one(c)
+    else:
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(one, todo))
+    return time.perf_counter() - t0, len(todo) * 4096
+
+
 class Pool:
     """P persistent worker processes, each with a private copy of the reference objects and a fixed share
     of the units; step() runs every share once from a common wall-clock tick."""

@@ -16,6 +16,7 @@
 #include <Client/IRenderer.h>
 #include <Client/SceneDefinition.h>
 #include <Core/Bitmap.h>
+#include <Core/Debug.h>
 #include <Core/Exception.h>
 #include <Core/MemoryStream.h>
 #include <Core/Settings.h>
@@ -95,6 +96,9 @@ __attribute__((visibility("default"))) const char *adapter_last_error(void) { re
 __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t vxlLen, int w, int h, int numerics, int threads,
                                                        const void *scenesRaw, int nScenes, int editsPerFrame, int withModels,
                                                        uint32_t seed, uint32_t *outB200, uint32_t *outSW, int *info) {
+	// the game's main() does this before anything can throw: spades::Exception's constructor dereferences the
+	// thread's backtrace object (Core/Exception.cpp:42, Core/Debug.cpp:64-73)
+	reflection::Backtrace::StartBacktrace();
 	try {
 		{
 			Settings::ItemHandle th("r_swNumThreads", nullptr);

@@ -11,6 +11,10 @@
 #include <cstdio>
 #include <vector>
 
+// per-lane counters of the current step (span candidates, landing words, stored pixels): the warp model below turns them
+// into what a 32-lane warp would execute
+static thread_local unsigned g_stat[4];
+#define OSB_STAT(what, n) (g_stat[what] += (n))
 #include "../../openspades_b200/csrc/terrain_core.cuh"
 
 namespace osb {
@@ -64,10 +68,13 @@ namespace {
 	struct Stats {
 		unsigned long long lines, active, steps;
 	};
+	template <bool kSse, bool kSse2> void warp_model(WalkIO wio, const osbn::Num<kSse> &num, const std::vector<ViewParams> &views,
+	                                                 const std::vector<LineRec> &recs, const std::vector<uint32_t> &active,
+	                                                 unsigned long long *out);
 
 	template <bool kSse, bool kSse2> int run(const uint64_t *solidT, const uint32_t *colorT, const osb200_scene *scenes, int nViews, int w,
 	                                         int h, const float fog[3], float fogDist, int threads, int under, int noMap, int noFog,
-	                                         uint32_t *fb, float *depth, Stats *stats) {
+	                                         uint32_t *fb, float *depth, Stats *stats, unsigned long long *modelOut = nullptr) {
 		Tables &T = tables();
 		if (kSse && !T.ok)
 			return -4;
@@ -140,6 +147,13 @@ namespace {
 		std::vector<uint32_t> mask(active.size() * (size_t)words, 0xffffffffu);
 		// ---- k_walk_lines ----
 		WalkIO wio{views.data(), lineDirs.data(), lineTan.data(), recs.data(), solidT, colorT, strips.data(), mask.data(), lineRes};
+		if (modelOut) { // lock-step warp statistics instead of a frame (on copies: the walk rewrites the records)
+			std::vector<LineRec> recs2 = recs;
+			WalkIO wio2 = wio;
+			wio2.lineRecs = recs2.data();
+			warp_model<kSse, kSse2>(wio2, num, views, recs, active, modelOut);
+			return 0;
+		}
 		unsigned long long steps = 0;
 		for (size_t s = 0; s < active.size(); s++) {
 			uint32_t filled[128 + kWalkExtraWords];
@@ -176,6 +190,60 @@ namespace {
 			}
 		}
 		return 0;
+	}
+} // namespace
+
+namespace {
+	// Lock-step model of k_walk_lines' warps on one view batch: tasks of 32 adjacent surviving lines of a view, all lanes
+	// step together until the last one ends.  Reports where lanes idle: out[0] warp-steps, [1] lane-steps, [2] sum over
+	// warp-steps of the MAX span candidates of a lane (= iterations of the span loop), [3] sum of candidates, [4] warp-level
+	// fill events (iterations with >= 1 landing lane) approximated per step by max landing words, [5] landing words,
+	// [6] sum of max stored pixels, [7] stored pixels, [8] tasks, [9] lines.
+	template <bool kSse, bool kSse2> void warp_model(WalkIO wio, const osbn::Num<kSse> &num, const std::vector<ViewParams> &views,
+	                                                 const std::vector<LineRec> &recs, const std::vector<uint32_t> &active,
+	                                                 unsigned long long *out) {
+		size_t a = 0;
+		while (a < active.size()) {
+			const int view = recs[active[a]].view;
+			size_t b = a;
+			while (b < active.size() && b - a < 32 && recs[active[b]].view == view)
+				b++;
+			const int n = (int)(b - a);
+			std::vector<LineWalker<kSse, kSse2>> W(n);
+			std::vector<std::vector<uint32_t>> filled(n, std::vector<uint32_t>(128 + kWalkExtraWords));
+			std::vector<char> alive(n, 1);
+			for (int i = 0; i < n; i++)
+				W[i].init(wio, active[a + i], (uint32_t)(a + i), filled[i].data(), 1);
+			out[8]++;
+			out[9] += n;
+			for (;;) {
+				unsigned maxC = 0, sumC = 0, maxW = 0, sumW = 0, maxP = 0, sumP = 0, lanes = 0;
+				for (int i = 0; i < n; i++) {
+					if (!alive[i])
+						continue;
+					g_stat[0] = g_stat[1] = g_stat[2] = 0;
+					alive[i] = W[i].step(wio, num, filled[i].data(), 1);
+					lanes++;
+					maxC = std::max(maxC, g_stat[0]);
+					sumC += g_stat[0];
+					maxW = std::max(maxW, g_stat[1]);
+					sumW += g_stat[1];
+					maxP = std::max(maxP, g_stat[2]);
+					sumP += g_stat[2];
+				}
+				if (!lanes)
+					break;
+				out[0]++;
+				out[1] += lanes;
+				out[2] += maxC;
+				out[3] += sumC;
+				out[4] += maxW;
+				out[5] += sumW;
+				out[6] += maxP;
+				out[7] += sumP;
+			}
+			a = b;
+		}
 	}
 } // namespace
 
@@ -220,5 +288,21 @@ __attribute__((visibility("default"))) int emul_render(const uint64_t *solid, co
 		stats3[2] = st.steps;
 	}
 	return rc;
+}
+// lock-step warp statistics of the walker for a batch of views (V-SSE2): out[10], see warp_model
+__attribute__((visibility("default"))) int emul_warp_model(const uint64_t *solid, const uint32_t *color, const osb200_scene *scenes,
+                                                           int nViews, int w, int h, unsigned long long *out) {
+	std::vector<uint64_t> solidT(512 * 512);
+	std::vector<uint32_t> colorT((size_t)512 * 512 * 64);
+	for (uint32_t x = 0; x < 512; x++)
+		for (uint32_t y = 0; y < 512; y++) {
+			const uint32_t t = tiled_xy(x, y);
+			solidT[t] = solid[x * 512 + y];
+			std::memcpy(&colorT[(size_t)t * 64], &color[((size_t)x * 512 + y) * 64], 64 * 4);
+		}
+	const float fog[3] = {0.8f, 1.f, 1.f};
+	for (int i = 0; i < 10; i++)
+		out[i] = 0;
+	return run<true, true>(solidT.data(), colorT.data(), scenes, nViews, w, h, fog, 128.f, 4, 1, 0, 0, nullptr, nullptr, nullptr, out);
 }
 }

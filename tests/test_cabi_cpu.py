@@ -95,3 +95,35 @@ def test_host_vxl_loader_rejects_malformed_streams():
     for name, bad in bad_streams.items():
         with pytest.raises(OsbError):
             VoxelMap.load(bad)
+
+
+def test_reference_side_adapter_links_and_fails_loudly_without_a_gpu():
+    """oracle/_ref/libadapter_sse2.so = openspades_b200/host/ref_adapter/B200Renderer.cpp (class B200Renderer : public
+    client::IRenderer, public client::IGameMapListener) compiled against the reference headers and linked with the reference
+    translation units.  Without a CUDA device constructing it must raise the reference's own exception type with the
+    library's "no CPU fallback" message (the frames themselves are compared on the GPU: tests/test_gpu_adapter.py)."""
+    import oracles
+    from openspades_b200 import workloads
+    lib = os.path.join(oracles.ORACLE_DIR, "_ref", "libadapter_sse2.so")
+    if not os.path.exists(lib):
+        pytest.skip("adapter not built (needs the reference checkout: make -C oracle adapter)")
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present: covered by tests/test_gpu_adapter.py")
+    except ImportError:
+        pass
+    L = ctypes.CDLL(lib)
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    L.adapter_run.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci, vp, ci, ci, ci, ctypes.c_uint32, vp, vp, vp]
+    L.adapter_last_error.restype = ctypes.c_char_p
+    vxl = np.frombuffer(open(oracles.TITLE_VXL, "rb").read(), np.uint8)
+    sc = np.ascontiguousarray(np.atleast_1d(workloads.title_scene(64, 64, 68.0)))
+    a = np.zeros((1, 64, 64), np.uint32)
+    b = np.zeros((1, 64, 64), np.uint32)
+    info = np.zeros(4, np.int32)
+    rc = L.adapter_run(vxl.ctypes.data, len(vxl), 64, 64, 2, 4, sc.ctypes.data, 1, 0, 0, 1, a.ctypes.data, b.ctypes.data,
+                       info.ctypes.data)
+    assert rc == -1
+    msg = L.adapter_last_error().decode()
+    assert "no CPU fallback" in msg and "B200Renderer" in msg
