@@ -290,6 +290,32 @@ OSB200_API int osb200_ambient_evaluate_box(osb200_ctx *ctx, int x0, int y0, int 
 OSB200_API int osb200_ambient_volume(osb200_ctx *ctx, const float **d_volume);
 
 
+/* ---- several GPUs of one box from one process (the reference has nothing distributed) ----
+ * A group owns one context per listed device and a NCCL communicator over them (libnccl.so.2 is bound at run time and
+ * only when nDevices > 1).  The map is replicated: uploaded over PCIe once and copied to the peers with ncclBroadcast
+ * over NVLink; edits likewise (the dirty columns are uploaded once, their records broadcast, every device scatters them).
+ * Views and rays are independent units: they are sharded by contiguous range [i*n/G, (i+1)*n/G) with no collective on
+ * the data path, one host thread per device.  Results are bit-identical to a single-device call on the same inputs. */
+typedef struct osb200_group osb200_group;
+OSB200_API int osb200_group_create(const osb200_opts *opts /* device field ignored */, const int *devices, int nDevices,
+                                   osb200_group **out);
+OSB200_API void osb200_group_destroy(osb200_group *g);
+OSB200_API int osb200_group_size(const osb200_group *g);
+OSB200_API osb200_ctx *osb200_group_ctx(osb200_group *g, int i); /* for the per-device calls (radiosity, timing ...) */
+OSB200_API int osb200_group_map_upload(osb200_group *g, const uint64_t *solid, const uint32_t *color);
+OSB200_API int osb200_group_map_mark_dirty(osb200_group *g, int x, int y, int z);
+/* returns the number of columns flushed (on every device) */
+OSB200_API int osb200_group_map_flush(osb200_group *g, const uint64_t *solid, const uint32_t *color);
+OSB200_API int osb200_group_render(osb200_group *g, const osb200_scene *scenes, int nViews, int w, int h,
+                                   const float fogColor[3], float fogDist, uint32_t *host_bgrx, float *host_depth);
+/* same views, the finished frames gathered on device `root` over NVLink (grouped ncclSend / ncclRecv: only the root
+ * receives); d_bgrx_root / d_depth_root (nullable) are device pointers on the root's device, nViews * w * h words */
+OSB200_API int osb200_group_render_gather(osb200_group *g, const osb200_scene *scenes, int nViews, int w, int h,
+                                          const float fogColor[3], float fogDist, int root, uint32_t *d_bgrx_root,
+                                          float *d_depth_root);
+OSB200_API int osb200_group_castray2(osb200_group *g, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
+                                     size_t n);
+
 #ifdef __cplusplus
 }
 #endif

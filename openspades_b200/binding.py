@@ -115,6 +115,18 @@ def load_library():
     lib.osb200_ambient_read_chunk.argtypes = [vp, ci, ci, ci, vp]
     lib.osb200_ambient_evaluate_box.argtypes = [vp] + [ci] * 6 + [vp]
     lib.osb200_ambient_volume.argtypes = [vp, ctypes.POINTER(vp)]
+    lib.osb200_group_create.argtypes = [ctypes.POINTER(Opts), ctypes.POINTER(ci), ci, ctypes.POINTER(vp)]
+    lib.osb200_group_destroy.argtypes = [vp]
+    lib.osb200_group_destroy.restype = None
+    lib.osb200_group_size.argtypes = [vp]
+    lib.osb200_group_ctx.argtypes = [vp, ci]
+    lib.osb200_group_ctx.restype = vp
+    lib.osb200_group_map_upload.argtypes = [vp, vp, vp]
+    lib.osb200_group_map_mark_dirty.argtypes = [vp, ci, ci, ci]
+    lib.osb200_group_map_flush.argtypes = [vp, vp, vp]
+    lib.osb200_group_render.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
+    lib.osb200_group_render_gather.argtypes = [vp, vp, ci, ci, ci, vp, fp, ci, vp, vp]
+    lib.osb200_group_castray2.argtypes = [vp, vp, vp, ci, vp, sz]
     _lib = lib
     return lib
 
@@ -280,15 +292,21 @@ class Context:
         return out
 
     # ---- GameMap::CastRay2 ----
-    def castray2(self, v0, dirs, max_steps):
-        """Host arrays in, host structured array (RAYHIT_DTYPE) out."""
-        v0 = np.ascontiguousarray(v0, np.float32)
-        dirs = np.ascontiguousarray(dirs, np.float32)
-        n = v0.shape[0]
-        assert v0.shape == (n, 3) and dirs.shape == (n, 3)
-        out = np.zeros(n, RAYHIT_DTYPE)
-        self._check(self._lib.osb200_castray2(self._h, v0.ctypes.data, dirs.ctypes.data, int(max_steps),
-                                              out.ctypes.data, n))
+    def castray2(self, v0, dirs, max_steps, out=None):
+        """Host arrays in, host structured array (RAYHIT_DTYPE) out.  v0 / dirs / out may be pinned-memory buffers (e.g.
+        torch pin_memory tensors viewed as numpy): the chunk pipeline behind the call then runs at PCIe speed."""
+        if hasattr(v0, "data_ptr"):
+            n = v0.shape[0]
+            pv, pd = v0.data_ptr(), dirs.data_ptr()
+        else:
+            v0 = np.ascontiguousarray(v0, np.float32)
+            dirs = np.ascontiguousarray(dirs, np.float32)
+            n = v0.shape[0]
+            assert v0.shape == (n, 3) and dirs.shape == (n, 3)
+            pv, pd = v0.ctypes.data, dirs.ctypes.data
+        if out is None:
+            out = np.zeros(n, RAYHIT_DTYPE)
+        self._check(self._lib.osb200_castray2(self._h, pv, pd, int(max_steps), _ptr(out), n))
         return out
 
     def castray2_device(self, d_v0, d_dir, max_steps, d_out, n):
@@ -451,3 +469,83 @@ class Context:
         p = [ctypes.c_void_p() for _ in range(5)]
         self._check(self._lib.osb200_radiosity_volumes(self._h, *[ctypes.byref(v) for v in p]))
         return [v.value for v in p]
+
+
+class Group:
+    """osb200_group: one context per listed GPU of this process, map replicated (PCIe once + NCCL broadcast), views and
+    rays sharded by contiguous range.  Mirrors the osb200_group_* C entry points one to one."""
+
+    def __init__(self, devices, numerics=NUM_SSE2, sw_threads=4, undersampling=1, radiosity_mode=1):
+        self._lib = load_library()
+        self._h = ctypes.c_void_p()
+        o = Opts(device=0, numerics=numerics, sw_threads=sw_threads, undersampling=undersampling,
+                 radiosity_mode=radiosity_mode, rcp_table=None, rcp_bits=0, rsqrt_table=None, rsqrt_bits=0)
+        devs = (ctypes.c_int * len(devices))(*devices)
+        rc = self._lib.osb200_group_create(ctypes.byref(o), devs, len(devices), ctypes.byref(self._h))
+        if rc:
+            raise OsbError(f"osb200_group_create failed ({rc}): {self._lib.osb200_last_error().decode()}")
+        self.devices = list(devices)
+
+    def _check(self, rc):
+        if rc < 0:
+            raise OsbError(f"osb200 error {rc}: {self._lib.osb200_last_error().decode()}")
+        return rc
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.osb200_group_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def size(self):
+        return self._lib.osb200_group_size(self._h)
+
+    def map_upload(self, solid, color):
+        solid = np.ascontiguousarray(solid, np.uint64)
+        color = np.ascontiguousarray(color, np.uint32)
+        self._check(self._lib.osb200_group_map_upload(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def map_mark_dirty(self, x, y, z):
+        self._check(self._lib.osb200_group_map_mark_dirty(self._h, int(x), int(y), int(z)))
+
+    def map_flush(self, solid, color):
+        return self._check(self._lib.osb200_group_map_flush(self._h, solid.ctypes.data, color.ctypes.data))
+
+    def render(self, scenes, w, h, fog_color, fog_dist, want_depth=True, out_bgrx=None, out_depth=None):
+        scenes = np.ascontiguousarray(np.atleast_1d(scenes))
+        assert scenes.dtype == SCENE_DTYPE
+        n = len(scenes)
+        fb = np.empty((n, h, w), np.uint32) if out_bgrx is None else out_bgrx
+        dp = (np.empty((n, h, w), np.float32) if out_depth is None else out_depth) if want_depth else None
+        fc = np.asarray(fog_color, np.float32)
+        self._check(self._lib.osb200_group_render(self._h, scenes.ctypes.data, n, w, h, fc.ctypes.data, float(fog_dist),
+                                                  _ptr(fb), _ptr(dp)))
+        return fb, dp
+
+    def render_gather(self, scenes, w, h, fog_color, fog_dist, root, d_bgrx, d_depth=None):
+        """frames of all shards end on device `root` (torch CUDA tensors or raw device pointers)"""
+        scenes = np.ascontiguousarray(np.atleast_1d(scenes))
+        fc = np.asarray(fog_color, np.float32)
+        self._check(self._lib.osb200_group_render_gather(self._h, scenes.ctypes.data, len(scenes), w, h, fc.ctypes.data,
+                                                         float(fog_dist), int(root), _ptr(d_bgrx), _ptr(d_depth)))
+
+    def castray2(self, v0, dirs, max_steps, out=None):
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n = v0.shape[0]
+        if out is None:
+            out = np.zeros(n, RAYHIT_DTYPE)
+        self._check(self._lib.osb200_group_castray2(self._h, v0.ctypes.data, dirs.ctypes.data, int(max_steps), _ptr(out), n))
+        return out

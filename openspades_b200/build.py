@@ -23,7 +23,7 @@ CUFLAGS += os.environ.get("OSB200_NVCC_EXTRA", "").split()
 if os.environ.get("OSB200_LIB_OUT"):  # experiment builds: a differently named library next to the default one
     LIB = os.environ["OSB200_LIB_OUT"]
     OBJ_DIR = LIB + ".obj"
-CU_SOURCES = ["api.cu", "castray2.cu", "terrain.cu", "radiosity.cu", "ambient.cu", "models.cu", "vxl.cu", "links.cu", "sse_calibrate.cpp"]
+CU_SOURCES = ["api.cu", "castray2.cu", "terrain.cu", "radiosity.cu", "ambient.cu", "models.cu", "vxl.cu", "links.cu", "group.cu", "sse_calibrate.cpp"]
 
 
 def _newer(src_list, target):
@@ -59,7 +59,7 @@ def build(force=False, verbose=False):
     if failed:
         raise RuntimeError("nvcc compilation failed")
     if force or procs or _newer(objs, LIB):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-ccbin", "/usr/bin/g++"]
+        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-ccbin", "/usr/bin/g++", "-ldl"]
         if verbose:
             print(" ".join(cmd), flush=True)
         subprocess.check_call(cmd)

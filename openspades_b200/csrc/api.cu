@@ -154,6 +154,24 @@ __global__ void k_map_untile_solid(const uint64_t *__restrict__ solidT, uint64_t
 		solidXY[col] = solidT[osb::tiled_index(col >> 9, col & 511)];
 }
 
+namespace osb {
+	// group.cu: the tiled arrays of `c` were filled by a broadcast from a peer device
+	void map_mark_resident(osb200_ctx *c) { map_replaced_hooks(c); }
+	size_t dirty_record_bytes() { return sizeof(DirtyColumn); }
+	// group.cu: n dirty-column records arrived in c->d_stage by broadcast: scatter them, the host marks are settled
+	int map_scatter_staged(osb200_ctx *c, int n) {
+		if (n > 0) {
+			KLaunch kl(c, K_MAP_SCATTER);
+			k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n, c->d_solid,
+			                                                    c->d_color);
+		}
+		std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
+		c->anyDirty = false;
+		OSB_CUDA(cudaGetLastError());
+		return 0;
+	}
+} // namespace osb
+
 // ---- C ABI ------------------------------------------------------------------------------------
 
 extern "C" {
@@ -291,6 +309,16 @@ void osb200_destroy(osb200_ctx *c) {
 	cudaFree(c->d_rsqrt);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_rayCursor);
+	if (c->rayPipe) {
+		cudaStreamDestroy(c->rayPipe->in);
+		cudaStreamDestroy(c->rayPipe->out);
+		for (int i = 0; i < osb::kPipeSlots; i++) {
+			cudaEventDestroy(c->rayPipe->uploaded[i]);
+			cudaEventDestroy(c->rayPipe->computed[i]);
+			cudaEventDestroy(c->rayPipe->downloaded[i]);
+		}
+		delete c->rayPipe;
+	}
 	cudaFree(c->d_stage);
 	if (c->h_stage)
 		cudaFreeHost(c->h_stage);

@@ -211,6 +211,12 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	return 0;
 }
 
+// Host-buffer entry point.  The batch is cut into chunks of kPipeRays rays that flow through three stages on three
+// streams -- H2D of chunk k+1, the kernel of chunk k, D2H of chunk k-1 -- over a ring of kPipeSlots device slots, so the
+// call runs at the speed of the slower PCIe direction (40 B/ray out) instead of copy + kernel + copy in series.
+// With pinned host buffers every copy is truly asynchronous; with pageable buffers the driver stages each copy and
+// blocks the host meanwhile, so the issue order below (upload and launch chunk k+1 BEFORE downloading chunk k) is
+// what keeps the GPU busy during the download.
 int osb200_castray2(osb200_ctx *c, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
                     size_t n) {
 	if (!c || !c->mapLoaded) {
@@ -224,20 +230,66 @@ int osb200_castray2(osb200_ctx *c, const float *v0, const float *dir, int maxSte
 		return -1;
 	}
 	OSB_CUDA(cudaSetDevice(c->device));
-	const size_t inB = n * 12, outB = n * sizeof(osb200_rayhit);
-	const size_t inPad = (inB + 255) & ~(size_t)255;
-	if (c->ensure_scratch(2 * inPad + outB))
+	if (!c->rayPipe) {
+		auto *P = new osb::RayPipe();
+		c->rayPipe = P;
+		OSB_CUDA(cudaStreamCreateWithFlags(&P->in, cudaStreamNonBlocking));
+		OSB_CUDA(cudaStreamCreateWithFlags(&P->out, cudaStreamNonBlocking));
+		for (int i = 0; i < osb::kPipeSlots; i++) {
+			OSB_CUDA(cudaEventCreateWithFlags(&P->uploaded[i], cudaEventDisableTiming));
+			OSB_CUDA(cudaEventCreateWithFlags(&P->computed[i], cudaEventDisableTiming));
+			OSB_CUDA(cudaEventCreateWithFlags(&P->downloaded[i], cudaEventDisableTiming));
+		}
+	}
+	osb::RayPipe *P = c->rayPipe;
+	const size_t chunk = osb::kPipeRays;
+	const size_t inPad = (chunk * 12 + 255) & ~(size_t)255, outPad = (chunk * sizeof(osb200_rayhit) + 255) & ~(size_t)255;
+	const size_t slotBytes = 2 * inPad + outPad;
+	if (c->ensure_scratch(slotBytes * osb::kPipeSlots))
 		return -2;
-	char *p = reinterpret_cast<char *>(c->d_scratch);
-	float *dv = reinterpret_cast<float *>(p), *dd = reinterpret_cast<float *>(p + inPad);
-	auto *dout = reinterpret_cast<osb200_rayhit *>(p + 2 * inPad);
-	OSB_CUDA(cudaMemcpyAsync(dv, v0, inB, cudaMemcpyHostToDevice, c->stream));
-	OSB_CUDA(cudaMemcpyAsync(dd, dir, inB, cudaMemcpyHostToDevice, c->stream));
-	int rc = osb200_castray2_device(c, dv, dd, maxSteps, dout, n);
-	if (rc)
+	char *base = reinterpret_cast<char *>(c->d_scratch);
+	const size_t nChunks = (n + chunk - 1) / chunk;
+	// the scratch area may still be read by earlier work of the context stream
+	OSB_CUDA(cudaEventRecord(P->computed[0], c->stream));
+	OSB_CUDA(cudaStreamWaitEvent(P->in, P->computed[0], 0));
+	auto upload = [&](size_t k) -> int {
+		const int s = (int)(k % osb::kPipeSlots);
+		const size_t lo = k * chunk, m = std::min(chunk, n - lo);
+		char *p = base + slotBytes * s;
+		if (k >= (size_t)osb::kPipeSlots) // the slot's previous results must have left the device
+			OSB_CUDA(cudaStreamWaitEvent(P->in, P->downloaded[s], 0));
+		OSB_CUDA(cudaMemcpyAsync(p, v0 + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
+		OSB_CUDA(cudaMemcpyAsync(p + inPad, dir + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
+		OSB_CUDA(cudaEventRecord(P->uploaded[s], P->in));
+		OSB_CUDA(cudaStreamWaitEvent(c->stream, P->uploaded[s], 0));
+		int rc = osb200_castray2_device(c, reinterpret_cast<float *>(p), reinterpret_cast<float *>(p + inPad), maxSteps,
+		                                reinterpret_cast<osb200_rayhit *>(p + 2 * inPad), m);
+		if (rc)
+			return rc;
+		OSB_CUDA(cudaEventRecord(P->computed[s], c->stream));
+		return 0;
+	};
+	auto download = [&](size_t k) -> int {
+		const int s = (int)(k % osb::kPipeSlots);
+		const size_t lo = k * chunk, m = std::min(chunk, n - lo);
+		char *p = base + slotBytes * s;
+		OSB_CUDA(cudaStreamWaitEvent(P->out, P->computed[s], 0));
+		OSB_CUDA(cudaMemcpyAsync(out + lo, p + 2 * inPad, m * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, P->out));
+		OSB_CUDA(cudaEventRecord(P->downloaded[s], P->out));
+		return 0;
+	};
+	if (int rc = upload(0))
 		return rc;
-	OSB_CUDA(cudaMemcpyAsync(out, dout, outB, cudaMemcpyDeviceToHost, c->stream));
-	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	for (size_t k = 0; k < nChunks; k++) {
+		if (k + 1 < nChunks)
+			if (int rc = upload(k + 1))
+				return rc;
+		if (int rc = download(k))
+			return rc;
+	}
+	OSB_CUDA(cudaStreamSynchronize(P->out));
+	// later work on the context stream must not overwrite the scratch area before the last download has read it
+	OSB_CUDA(cudaStreamWaitEvent(c->stream, P->downloaded[(nChunks - 1) % osb::kPipeSlots], 0));
 	return 0;
 }
 

@@ -58,6 +58,13 @@ namespace osb {
 	};
 	const char *kernel_name(int id);
 
+	// osb200_castray2's chunk pipeline (castray2.cu)
+	constexpr int kPipeSlots = 3;
+	constexpr size_t kPipeRays = (size_t)1 << 20; // rays per chunk: 64 MB per slot
+	struct RayPipe {
+		cudaStream_t in = nullptr, out = nullptr;
+		cudaEvent_t uploaded[kPipeSlots] = {}, computed[kPipeSlots] = {}, downloaded[kPipeSlots] = {};
+	};
 	struct TerrainState;   // terrain.cu
 	struct RadiosityState; // radiosity.cu
 	struct AmbientState;   // ambient.cu
@@ -142,6 +149,7 @@ struct osb200_ctx {
 	int rsqrtBits = 0;
 
 	unsigned long long *d_rayCursor = nullptr; // batch-wide work cursor of k_castray2
+	osb::RayPipe *rayPipe = nullptr;           // streams / events of the host-buffer ray pipeline
 
 	// ---- scratch for host-pointer convenience entry points ----
 	void *d_scratch = nullptr;

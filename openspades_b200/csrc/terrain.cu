@@ -825,6 +825,23 @@ int osb200_render(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, 
 	return 0;
 }
 
+} // extern "C"
+namespace osb {
+	// group.cu: render into the context-owned device buffers and hand them out (no host copy, no sync)
+	int render_device_frames(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
+	                         float fogDist, uint32_t **d_fb, float **d_depth) {
+		if (!c) {
+			set_error("osb200_render: no context");
+			return -1;
+		}
+		OSB_CUDA(cudaSetDevice(c->device));
+		if (int rc = terrain_out_buffers(c, (size_t)nViews * w * h, d_fb, d_depth))
+			return rc;
+		return render_impl(c, scenes, nViews, w, h, fogColor, fogDist, *d_fb, *d_depth, nullptr, nullptr, false);
+	}
+} // namespace osb
+extern "C" {
+
 int osb200_read_depth(osb200_ctx *c, float *out, size_t n) {
 	if (!c || !out) {
 		osb::set_error("osb200_read_depth: null argument");

@@ -1,5 +1,5 @@
 """Multi-GPU plumbing for the voxel hot path: one process per GPU, the map replicated,
-independent units (views, rays, radiosity chunks) split into contiguous ranges per rank, and NO collective on the
+independent units (views, rays) split into contiguous ranges per rank, and NO collective on the
 data path.  The only exchange step is the control path of map edits: rank 0's per-frame edit list is broadcast
 (NCCL over NVLink on a GPU box, gloo in the CPU tests) and every rank applies it to its own host map, which fires
 the same GameMapChanged -> dirty-column -> osb200_map_flush sequence everywhere, so replicas stay bit-identical.
@@ -19,11 +19,6 @@ def shard_range(n, rank, world):
     if world <= 0 or not (0 <= rank < world):
         raise ValueError("bad rank/world")
     return (n * rank) // world, (n * (rank + 1)) // world
-
-
-def chunk_stripe(rank, world):
-    """Radiosity chunks striped by cx (32 columns of chunks): the cx range owned by `rank`."""
-    return shard_range(32, rank, world)
 
 
 def make_edits(xs, ys, zs, solids, colors):
@@ -86,15 +81,25 @@ def apply_edits_arrays(solid, color, edits, ctx=None):
     return changed
 
 
-def gather_frames(t, group=None):
-    """Optional all-gather of per-rank result tensors (frames, depth, ray hits); off the timed data path.
-    Returns the list of per-rank tensors (rank order)."""
+def gather_frames(t, dst=0, group=None):
+    """Optional gather of per-rank result tensors (frames, depth, ray hits) to rank `dst`; off the timed data path.
+    Only the root receives (grouped send / recv, not an all-gather: at 8 ranks that is an eighth of the traffic).
+    Returns the list of per-rank tensors (rank order) on `dst`, None elsewhere.  Every rank's tensor must have the
+    same shape and dtype."""
     import torch
     import torch.distributed as dist
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return [t]
-    out = [torch.empty_like(t) for _ in range(dist.get_world_size(group))]
-    dist.all_gather(out, t.contiguous(), group=group)
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    t = t.contiguous()
+    if rank == dst:
+        out = [t if r == dst else torch.empty_like(t) for r in range(world)]
+        ops = [dist.P2POp(dist.irecv, out[r], r, group) for r in range(world) if r != dst]
+    else:
+        out = None
+        ops = [dist.P2POp(dist.isend, t, dst, group)]
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
     return out
 
 

@@ -24,7 +24,6 @@ def test_shard_range_partitions_exactly():
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         sharding.shard_range(10, 2, 2)
-    assert [sharding.chunk_stripe(k, 8) for k in range(8)] == [(4 * k, 4 * k + 4) for k in range(8)]
 
 
 def test_apply_edits_follows_gamemap_set_semantics():
