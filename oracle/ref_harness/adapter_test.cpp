@@ -6,6 +6,7 @@
  * EndScene / FrameDone / ReadBitmap / Flip -- the head-less pattern of Client/HitTestDebugger.cpp:38-57,147-305.
  * tests/test_gpu_adapter.py compares what the two ReadBitmap calls return.
  */
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <random>
@@ -92,10 +93,11 @@ __attribute__((visibility("default"))) const char *adapter_last_error(void) { re
 /* Renders nScenes frames with both renderers; between frames editsPerFrame random GameMap::Set calls (dig / build) hit
  * the shared map.  withModels: every frame also submits 3 RenderModel calls and 2 AddLight calls.
  * outB200 / outSW: nScenes x h x w RGBA words as ReadBitmap returns them.  info: [0] listener calls seen by the B200
- * renderer's last flush (columns), [1] port swaps of the B200 port, [2] total edits applied. */
+ * renderer's last flush (columns), [1] port swaps of the B200 port, [2] total edits applied.
+ * numerics < 0: only SWRenderer runs (usable without a GPU: the harness then serves to pin the oracle port on edited maps). */
 __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t vxlLen, int w, int h, int numerics, int threads,
                                                        const void *scenesRaw, int nScenes, int editsPerFrame, int withModels,
-                                                       uint32_t seed, uint32_t *outB200, uint32_t *outSW, int *info) {
+                                                       uint32_t seed, uint32_t *outB200, uint32_t *outSW, int *info, int32_t *editsOut /* nullable: 6 ints per edit {frame, x, y, z, solid, colour} */) {
 	// the game's main() does this before anything can throw: spades::Exception's constructor dereferences the
 	// thread's backtrace object (Core/Exception.cpp:42, Core/Debug.cpp:64-73)
 	reflection::Backtrace::StartBacktrace();
@@ -113,13 +115,15 @@ __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t v
 		auto portB = Handle<Port>::New(w, h), portS = Handle<Port>::New(w, h);
 		// one interface type for both; the concrete classes appear only in these two lines
 		Handle<client::IRenderer> rs[2];
-		rs[0] = Handle<draw::B200Renderer>::New(portB.Cast<draw::SWPort>(), numerics, 0).Cast<client::IRenderer>();
+		const int k0 = numerics < 0 ? 1 : 0;
+		if (!k0)
+			rs[0] = Handle<draw::B200Renderer>::New(portB.Cast<draw::SWPort>(), numerics, 0).Cast<client::IRenderer>();
 		rs[1] = Handle<draw::SWRenderer>::New(portS.Cast<draw::SWPort>(),
-		                                      numerics == 2 ? draw::SWFeatureLevel::SSE2 : draw::SWFeatureLevel::SSE)
+		                                      numerics == 1 ? draw::SWFeatureLevel::SSE : draw::SWFeatureLevel::SSE2)
 		          .Cast<client::IRenderer>();
 		Handle<client::IModel> models[2];
 		Handle<VoxelModel> vm = make_model(seed ^ 77u);
-		for (int k = 0; k < 2; k++) {
+		for (int k = k0; k < 2; k++) {
 			client::IRenderer &r = *rs[k];
 			r.Init();
 			r.SetFogColor(MakeVector3(0.8f, 1.f, 1.f));
@@ -133,21 +137,34 @@ __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t v
 		for (int f = 0; f < nScenes; f++) {
 			// edits through the real GameMap::Set: both renderers are listeners of the same map
 			for (int e = 0; e < (f == 0 ? 0 : editsPerFrame); e++) {
-				// near the camera so that the edits are visible in the frame
-				const int x = ((int)scenes[f].origin[0] + (int)(rng() % 41) - 20) & 511;
-				const int y = ((int)scenes[f].origin[1] + (int)(rng() % 41) - 20) & 511;
+				// in front of the camera (10..70 blocks along the view direction, +-15 sideways) so that the edits are
+				// visible in the frame
+				const float along = 10.f + (float)(rng() % 61), side = (float)(rng() % 31) - 15.f;
+				const int x = (int)floorf(scenes[f].origin[0] + scenes[f].axis[2][0] * along + scenes[f].axis[0][0] * side) & 511;
+				const int y = (int)floorf(scenes[f].origin[1] + scenes[f].axis[2][1] * along + scenes[f].axis[0][1] * side) & 511;
 				const uint64_t col = map->GetSolidMapWrapped(x, y);
 				int top = 0;
 				while (top < 63 && !((col >> top) & 1ull))
 					top++;
-				if ((rng() & 1u) && top < 61)
+				int ez = -1, es = 0;
+				uint32_t ec = 0;
+				if ((rng() & 1u) && top < 61) {
+					ez = top;
 					map->Set(x, y, top, false, 0);
-				else if (top > 1)
-					map->Set(x, y, top - 1, true, 0x64000000u | (rng() & 0xffffffu));
+				} else if (top > 1) {
+					ez = top - 1;
+					es = 1;
+					ec = 0x64000000u | (rng() & 0xffffffu);
+					map->Set(x, y, top - 1, true, ec);
+				}
+				if (editsOut) {
+					int32_t *e = editsOut + (size_t)totalEdits * 6;
+					e[0] = f; e[1] = x; e[2] = y; e[3] = ez; e[4] = es; e[5] = (int32_t)ec;
+				}
 				totalEdits++;
 			}
 			const client::SceneDefinition def = make_def(scenes[f], w, h);
-			for (int k = 0; k < 2; k++) {
+			for (int k = k0; k < 2; k++) {
 				client::IRenderer &r = *rs[k];
 				r.StartScene(def);
 				if (withModels) {
@@ -175,13 +192,13 @@ __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t v
 			}
 		}
 		if (info) {
-			info[0] = static_cast<draw::B200Renderer *>(rs[0].GetPointerOrNull())->LastFlushedColumns();
+			info[0] = k0 ? 0 : static_cast<draw::B200Renderer *>(rs[0].GetPointerOrNull())->LastFlushedColumns();
 			info[1] = portB->swaps;
 			info[2] = totalEdits;
 		}
 		// API misuse must raise like SWRenderer does (SWRenderer.cpp:520-547)
 		int raised = 0;
-		for (int k = 0; k < 2; k++) {
+		for (int k = k0; k < 2; k++) {
 			try {
 				rs[k]->EndScene();
 			} catch (const spades::Exception &) {
@@ -190,7 +207,7 @@ __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t v
 		}
 		if (info)
 			info[3] = raised;
-		for (int k = 0; k < 2; k++) {
+		for (int k = k0; k < 2; k++) {
 			models[k] = nullptr;
 			rs[k]->SetGameMap({});
 			rs[k]->Shutdown();

@@ -115,7 +115,7 @@ def test_reference_side_adapter_links_and_fails_loudly_without_a_gpu():
         pass
     L = ctypes.CDLL(lib)
     vp, ci = ctypes.c_void_p, ctypes.c_int
-    L.adapter_run.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci, vp, ci, ci, ci, ctypes.c_uint32, vp, vp, vp]
+    L.adapter_run.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci, vp, ci, ci, ci, ctypes.c_uint32, vp, vp, vp, vp]
     L.adapter_last_error.restype = ctypes.c_char_p
     vxl = np.frombuffer(open(oracles.TITLE_VXL, "rb").read(), np.uint8)
     sc = np.ascontiguousarray(np.atleast_1d(workloads.title_scene(64, 64, 68.0)))
@@ -123,7 +123,7 @@ def test_reference_side_adapter_links_and_fails_loudly_without_a_gpu():
     b = np.zeros((1, 64, 64), np.uint32)
     info = np.zeros(4, np.int32)
     rc = L.adapter_run(vxl.ctypes.data, len(vxl), 64, 64, 2, 4, sc.ctypes.data, 1, 0, 0, 1, a.ctypes.data, b.ctypes.data,
-                       info.ctypes.data)
+                       info.ctypes.data, None)
     assert rc == -1
     msg = L.adapter_last_error().decode()
     assert "no CPU fallback" in msg and "B200Renderer" in msg

@@ -27,7 +27,7 @@ def adapter():
         pytest.skip("oracle/_ref/libadapter_sse2.so not built (needs the reference checkout: make -C oracle adapter)")
     L = ctypes.CDLL(LIB)
     vp, ci = ctypes.c_void_p, ctypes.c_int
-    L.adapter_run.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci, vp, ci, ci, ci, ctypes.c_uint32, vp, vp, vp]
+    L.adapter_run.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci, vp, ci, ci, ci, ctypes.c_uint32, vp, vp, vp, vp]
     L.adapter_last_error.restype = ctypes.c_char_p
     return L
 
@@ -40,7 +40,7 @@ def _run(L, w, h, scenes, edits, with_models, numerics=2, threads=4, seed=1):
     b = np.zeros((n, h, w), np.uint32)
     info = np.zeros(4, np.int32)
     rc = L.adapter_run(vxl.ctypes.data, len(vxl), w, h, numerics, threads, sc.ctypes.data, n, edits, int(with_models), seed,
-                       a.ctypes.data, b.ctypes.data, info.ctypes.data)
+                       a.ctypes.data, b.ctypes.data, info.ctypes.data, None)
     assert rc == 0, L.adapter_last_error().decode()
     return a, b, info
 
