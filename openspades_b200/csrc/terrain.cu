@@ -238,6 +238,59 @@ namespace osb {
 		}
 	}
 
+	// Cooperative walker for small launches: one warp (= one CTA) per yaw line, see CoopLine in terrain_core.cuh.
+	// Tasks are single lines (k_line_compact with taskLines = 1).
+	template <bool kSse, bool kSse2Shade>
+	__global__ void __launch_bounds__(32)
+	  k_walk_coop(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, const uint32_t *__restrict__ tasks,
+	              const uint32_t *__restrict__ counters) {
+		extern __shared__ uint32_t s_coop[]; // CoopShared, then the strip's pixel keys
+		CoopShared &sh = *reinterpret_cast<CoopShared *>(s_coop);
+		uint32_t *key = s_coop + sizeof(CoopShared) / sizeof(uint32_t);
+		const int lane = threadIdx.x;
+		const osbn::Num<kSse> num{tabs};
+		const uint32_t nTasks = counters[0];
+		for (uint32_t t = blockIdx.x; t < nTasks; t += gridDim.x) {
+			const uint32_t slot = __ldg(tasks + t) >> 5;
+			const uint32_t gl = __ldg(active + slot);
+			CoopLine<kSse, kSse2Shade> C;
+			C.begin(io, gl, slot, sh, key, lane);
+			__syncwarp();
+			if (lane == 0)
+				C.path(sh);
+			__syncwarp();
+			const int nSteps = sh.nSteps;
+			bool ended = false;
+			for (int s0 = 0; s0 < nSteps && !ended; s0 += 32) {
+				const int s = s0 + lane;
+				const unsigned cull = __ballot_sync(0xffffffffu, C.culls_after(io, num, sh, s));
+				const int cullAt = cull ? s0 + __ffs((int)cull) - 1 : 0x7fffffff; // the step after which the line ends
+				if (s < nSteps && s <= cullAt)
+					C.emit_step(io, num, sh, key, s);
+				ended = cull != 0u;
+			}
+			__syncwarp();
+			if (sh.nSpans > kCoopMaxSpans) { // too many spans to record: this line goes through the sequential walker
+				if (lane == 0) {
+					LineWalker<kSse, kSse2Shade> W;
+					W.init(io, gl, slot, key, 1);
+					while (W.step(io, num, key, 1)) {
+					}
+				}
+				__syncwarp();
+				continue;
+			}
+			C.resolve_long(sh, key, lane);
+			__syncwarp();
+			int first, last;
+			C.scan_hull(io, key, lane, first, last);
+			first = __reduce_min_sync(0xffffffffu, first);
+			last = __reduce_max_sync(0xffffffffu, last);
+			C.store(io, sh, key, lane, first, last);
+			__syncwarp();
+		}
+	}
+
 	// RenderFinal + ApplyFog, see GatherLane in terrain_core.cuh
 	template <bool kSse, bool kSse2Fog>
 #ifndef OSB_GATHER_MINB
@@ -383,6 +436,14 @@ namespace osb {
 			const char *e = getenv("OSB200_WALK_BLOCKS");
 			const int n = e ? atoi(e) : 0;
 			return n < 0 ? 0 : n;
+		}();
+		return v;
+	}
+	// OSB200_COOP: 1 = always the cooperative walker, 0 = never, unset = by launch size
+	static int coop_mode() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_COOP");
+			return e ? (atoi(e) != 0 ? 1 : 0) : -1;
 		}();
 		return v;
 	}
@@ -586,6 +647,10 @@ namespace osb {
 			while (taskLines > line_min_lanes() && (size_t)totalLines / taskLines < (size_t)c->smCount * 4 * 2) // < 2 warps per scheduler
 				taskLines >>= 1;
 			taskLines = std::max(taskLines, kMinTaskLines);
+			// few lines (a single frame, a handful of views): one WARP per line instead of one lane per line
+			const bool coop = coop_mode() == 1 || (coop_mode() < 0 && (size_t)totalLines < (size_t)c->smCount * 64);
+			if (coop)
+				taskLines = 1;
 			{
 				KLaunch kl(c, K_LINE_SETUP, st);
 				const dim3 grid((maxViewLines + kSetupThreads - 1) / kSetupThreads, nv, 1);
@@ -599,7 +664,18 @@ namespace osb {
 				                                              B.d_lineRecs, B.d_active, B.d_tasks, B.d_counters);
 				c->launches++;
 			}
-			if (!g.noMap) {
+			if (!g.noMap && coop) {
+				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
+				const size_t smem = coop_shared_bytes(lineRes);
+				const unsigned blocks = (unsigned)std::min<size_t>(totalLines, (size_t)c->smCount * 32);
+				KLaunch kl(c, K_WALK_LINES, st);
+				if (num == OSB200_NUM_IEEE)
+					k_walk_coop<false, false><<<blocks, 32, smem, st>>>(io, sse, B.d_active, B.d_tasks, B.d_counters);
+				else if (num == OSB200_NUM_SSE)
+					k_walk_coop<true, false><<<blocks, 32, smem, st>>>(io, sse, B.d_active, B.d_tasks, B.d_counters);
+				else
+					k_walk_coop<true, true><<<blocks, 32, smem, st>>>(io, sse, B.d_active, B.d_tasks, B.d_counters);
+			} else if (!g.noMap) {
 				const size_t wantWarps = ((size_t)totalLines + taskLines - 1) / taskLines;
 				int perSm = T->walkBlocksPerSm[num];
 				if (walk_blocks_cap() && nChunks > 1)
@@ -617,11 +693,17 @@ namespace osb {
 					LAUNCH_WALK(true, true);
 #undef LAUNCH_WALK
 			}
-			const int segs = ((h >> 3) + kSegRows - 1) / kSegRows;
-			const size_t tasks = (size_t)nv * (((w >> 3) + 3) >> 2) * segs;
+			// warp tasks of the gather: 8 block rows each for batches; a single frame is cut finer (2 block rows) so that
+			// its few hundred tasks become enough warps to hide the gather's load latency
+			const size_t colGroupsAll = (size_t)nv * (((w >> 3) + 3) >> 2);
+			int segRows = kSegRows;
+			while (segRows > 2 && colGroupsAll * (((h >> 3) + segRows - 1) / segRows) < (size_t)c->smCount * 32)
+				segRows >>= 1;
+			const int segs = ((h >> 3) + segRows - 1) / segRows;
+			const size_t tasks = colGroupsAll * segs;
 			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
 			GatherIO gio{dV,           nv,      g, B.d_tabs, c->d_solid, T->d_atan, B.d_strips, B.d_lineRecs, B.d_lineTan, B.d_lineMask,
-			             lineRes, d_fb + (size_t)v0 * w * h, d_depth + (size_t)v0 * w * h};
+			             lineRes, d_fb + (size_t)v0 * w * h, d_depth + (size_t)v0 * w * h, segRows};
 			{
 				KLaunch kl(c, K_GATHER_FOG, st);
 				if (num == OSB200_NUM_IEEE)

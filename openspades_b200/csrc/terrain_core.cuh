@@ -399,20 +399,30 @@ namespace osb {
 			nT = tiled_xy((uint32_t)nIrx & 511u, (uint32_t)nIry & 511u);
 		}
 
-		OSB_HDM void init(const WalkIO &io, uint32_t gl, uint32_t slot, uint32_t *filled, int fstride) {
+		// z > icz / z < icz as bit masks (the eye's voxel layer splits a column into floors seen from above and ceilings
+		// seen from below)
+		OSB_HDM void eye_masks(uint32_t m[4]) const {
+			const uint64_t belowEye = icz >= 63 ? 0ull : (icz < 0 ? ~0ull : (~0ull << (icz + 1)));
+			const uint64_t aboveEye = icz <= 0 ? 0ull : (icz >= 64 ? ~0ull : ((1ull << icz) - 1ull));
+			m[0] = (uint32_t)belowEye;
+			m[1] = (uint32_t)(belowEye >> 32);
+			m[2] = (uint32_t)aboveEye;
+			m[3] = (uint32_t)(aboveEye >> 32);
+		}
+
+		// everything of the set-up that does not touch the fill mask or the map (shared with the cooperative walker)
+		OSB_HDM void init_consts(const WalkIO &io, uint32_t gl, uint32_t slot) {
 			using namespace osbc;
 			const LineRec rec = io.lineRecs[gl];
 			const ViewParams &V = io.views[rec.view];
 			const float2 hd = io.lineDirs[gl];
 			const float2 tn = io.lineTan[gl];
-			const int lineRes = io.lineRes, words = lineRes >> 5;
-			for (int w = 0; w < words; w++)
-				filled[w * fstride] = 0;
+			const int lineRes = io.lineRes;
 			stripBase = slot * (uint32_t)lineRes;
 #if OSB_STRIP_HULL
 			maskBase = gl;
 #else
-			maskBase = slot * (uint32_t)words;
+			maskBase = slot * (uint32_t)(lineRes >> 5);
 #endif
 
 			// ---- DDA set-up (:309-351) ----
@@ -432,14 +442,6 @@ namespace osb {
 			const float cx = V.origin[0], cy = V.origin[1];
 			cz = V.origin[2];
 			icz = osbn::x86_f2i(floorf(cz));
-			{ // z > icz / z < icz as bit masks, parked behind the line's fill words (read once per step / per ceiling scan)
-				const uint64_t belowEye = icz >= 63 ? 0ull : (icz < 0 ? ~0ull : (~0ull << (icz + 1)));
-				const uint64_t aboveEye = icz <= 0 ? 0ull : (icz >= 64 ? ~0ull : ((1ull << icz) - 1ull));
-				filled[(words + 0) * fstride] = (uint32_t)belowEye;
-				filled[(words + 1) * fstride] = (uint32_t)(belowEye >> 32);
-				filled[(words + 2) * fstride] = (uint32_t)aboveEye;
-				filled[(words + 3) * fstride] = (uint32_t)(aboveEye >> 32);
-			}
 			const int rx = osbn::x86_f2i(fmul(cx, 512.f)), ry = osbn::x86_f2i(fmul(cy, 512.f));
 			irx = rx >> 9;
 			iry = ry >> 9;
@@ -459,10 +461,21 @@ namespace osb {
 			depthBias = fmul(-cz, heightScale);
 
 			tOld = tiled_xy((uint32_t)irx & 511u, (uint32_t)iry & 511u);
-			sOld = io.solid[tOld];
 			count = 1;
 			cnt2 = 1024; // static_cast<int>(fogDist * 8.f)
 			advance(irx, iry, gx, gy, distance);
+		}
+
+		OSB_HDM void init(const WalkIO &io, uint32_t gl, uint32_t slot, uint32_t *filled, int fstride) {
+			const int words = io.lineRes >> 5;
+			for (int w = 0; w < words; w++)
+				filled[w * fstride] = 0;
+			init_consts(io, gl, slot);
+			uint32_t m[4]; // parked behind the line's fill words (read once per step / per ceiling scan)
+			eye_masks(m);
+			for (int k = 0; k < 4; k++)
+				filled[(words + k) * fstride] = m[k];
+			sOld = io.solid[tOld];
 			sNext = io.solid[nT];
 		}
 
@@ -539,6 +552,68 @@ namespace osb {
 			}
 		}
 
+		// The spans of one DDA step in the reference's order: floor tops of the cell being left (ascending z, :584-603),
+		// its ceilings (descending z, :604-622), then the walls of the cell being entered for the crossed face
+		// (ascending z, :627-657).  Tops and walls share one loop (phase 0 / 1: both walk the lowest set bit first);
+		// ceilings exist only with solid above the eye and run in between.  emit(from, to, cellIsTheEnteredOne, z, zA,
+		// mode, ordinal) is called for every candidate whose strip interval [from, to) is not empty; ordinal counts the
+		// step's candidates (empty ones included) in list order.  aboveEye(k) yields the lo / hi word of the z < icz mask.
+		template <class AboveEye, class Emit>
+		OSB_HDM void spans_of_step(const osbn::Num<kSse> &num, float vmax, uint64_t sOldV, uint64_t sNewV, float iDist, float oldIDist,
+		                           int wallMode, uint32_t belowLo, uint32_t belowHi, AboveEye aboveEye, Emit emit) const {
+			using namespace osbc;
+			const uint32_t oLo = (uint32_t)sOldV, oHi = (uint32_t)(sOldV >> 32);
+			const uint32_t nLo = (uint32_t)sNewV, nHi = (uint32_t)(sNewV >> 32);
+			uint32_t cLo = oLo & ~(oLo << 1) & belowLo;                                 // solid, air above, below the eye
+			uint32_t cHi = oHi & ~((oHi << 1) | (oLo >> 31)) & belowHi;
+			const uint32_t wLo = nLo & ~oLo, wHi = nHi & ~oHi;                          // solid there, air in the cell left
+			int phase = 0; // 0 tops, 1 walls
+			int ordinal = 0;
+			for (;;) {
+				if (!(cLo | cHi)) {
+					if (phase)
+						break;
+					// ceilings: solid, air below, above the eye; z = 63 is never listed (BuildRle :185-190)
+					uint32_t bLo = oLo & ~((oLo >> 1) | (oHi << 31)) & aboveEye(0);
+					uint32_t bHi = oHi & ~(oHi >> 1) & 0x7fffffffu & aboveEye(1);
+					while (bLo | bHi) { // highest z first
+						int z;
+						if (bHi) {
+							z = 63 - clz32(bHi);
+							bHi &= ~(1u << (z - 32));
+						} else {
+							z = 31 - clz32(bLo);
+							bLo &= ~(1u << z);
+						}
+						const int pA = transform(num, iDist, z + 1, vmax);
+						const int pB = transform(num, oldIDist, z + 1, vmax);
+						if (pB < pA)
+							emit(pB, pA, false, z, z + 1, 2, ordinal);
+						ordinal++;
+					}
+					phase = 1;
+					cLo = wLo;
+					cHi = wHi;
+					if (!(cLo | cHi))
+						break;
+				}
+				int z;
+				if (cLo) {
+					z = ffs32(cLo);
+					cLo &= cLo - 1;
+				} else {
+					z = 32 + ffs32(cHi);
+					cHi &= cHi - 1;
+				}
+				OSB_STAT(0, 1); // span candidate
+				const int pA = transform(num, iDist, z, vmax);
+				const int pB = transform(num, phase ? iDist : oldIDist, z + phase, vmax);
+				if (pA < pB)
+					emit(pA, pB, phase != 0, z, z, phase ? wallMode : 0, ordinal);
+				ordinal++;
+			}
+		}
+
 		// One DDA step with all its spans.  Returns false when the line has ended (its mask is published).
 		OSB_HDM bool step(const WalkIO &io, const osbn::Num<kSse> &num, uint32_t *filled, int fstride) {
 			using namespace osbc;
@@ -564,58 +639,13 @@ namespace osb {
 			invDist = num.rcpHotPos(distance); // distance is in [1e-20, ~200]
 			const float medDist = fadd(fmul(distance, zscale), depthBias);
 
-			// ---- spans of this step in the reference's order: floor tops of the cell being left (ascending z,
-			// :584-603), its ceilings (descending z, :604-622), then the walls of the cell being entered for the
-			// crossed face (ascending z, :627-657).  Tops and walls share one loop (phase 0 / 1: both walk the lowest
-			// set bit first); ceilings exist only with solid above the eye and run in between.
-			const uint32_t oLo = (uint32_t)sOld, oHi = (uint32_t)(sOld >> 32);
-			const uint32_t nLo = (uint32_t)sNew, nHi = (uint32_t)(sNew >> 32);
 			const int words = lineRes >> 5;
-			uint32_t cLo = oLo & ~(oLo << 1) & filled[(words + 0) * fstride];          // solid, air above, below the eye
-			uint32_t cHi = oHi & ~((oHi << 1) | (oLo >> 31)) & filled[(words + 1) * fstride];
-			const uint32_t wLo = nLo & ~oLo, wHi = nHi & ~oHi;                          // solid there, air in the cell left
-			int phase = 0; // 0 tops, 1 walls
-			for (;;) {
-				if (!(cLo | cHi)) {
-					if (phase)
-						break;
-					// ceilings: solid, air below, above the eye; z = 63 is never listed (BuildRle :185-190)
-					uint32_t bLo = oLo & ~((oLo >> 1) | (oHi << 31)) & filled[(words + 2) * fstride];
-					uint32_t bHi = oHi & ~(oHi >> 1) & 0x7fffffffu & filled[(words + 3) * fstride];
-					while (bLo | bHi) { // highest z first
-						int z;
-						if (bHi) {
-							z = 63 - clz32(bHi);
-							bHi &= ~(1u << (z - 32));
-						} else {
-							z = 31 - clz32(bLo);
-							bLo &= ~(1u << z);
-						}
-						const int pA = transform(num, invDist, z + 1, vmax);
-						const int pB = transform(num, oldInvDist, z + 1, vmax);
-						if (pB < pA)
-							fill(io, filled, fstride, pB, pA, tOld, z, z + 1, 2, medDist);
-					}
-					phase = 1;
-					cLo = wLo;
-					cHi = wHi;
-					if (!(cLo | cHi))
-						break;
-				}
-				int z;
-				if (cLo) {
-					z = ffs32(cLo);
-					cLo &= cLo - 1;
-				} else {
-					z = 32 + ffs32(cHi);
-					cHi &= cHi - 1;
-				}
-				OSB_STAT(0, 1); // span candidate
-				const int pA = transform(num, invDist, z, vmax);
-				const int pB = transform(num, phase ? invDist : oldInvDist, z + phase, vmax);
-				if (pA < pB)
-					fill(io, filled, fstride, pA, pB, phase ? tNew : tOld, z, z, phase ? wallMode : 0, medDist);
-			}
+			spans_of_step(
+			  num, vmax, sOld, sNew, invDist, oldInvDist, wallMode, filled[(words + 0) * fstride], filled[(words + 1) * fstride],
+			  [&](int k) { return filled[(words + 2 + k) * fstride]; },
+			  [&](int from, int to, bool cellNew, int z, int zA, int mode, int) {
+				  fill(io, filled, fstride, from, to, cellNew ? tNew : tOld, z, zA, mode, medDist);
+			  });
 			sOld = sNew;
 			tOld = tNew;
 			// ---- pitch cull every 4th step (:661-667) ----
@@ -627,6 +657,173 @@ namespace osb {
 				count = 4;
 			}
 			return true;
+		}
+	};
+
+	// ------------------------------------------------------------------------------------------------------------
+	// Cooperative line walker for SMALL launches (a single frame has only a few thousand yaw lines: one lane per line
+	// leaves the GPU empty and a line's ~150 dependent steps set the frame time).  One WARP builds one line:
+	//   path      one lane runs the map-independent DDA (:426-522) and records every step's cell and distance;
+	//   batches   32 steps at a time, one lane per step: column masks, spans (spans_of_step, the same code the
+	//             lane-per-line walker runs), the every-4th-step pitch cull (:661-667) by ballot;
+	//   resolve   "first writer wins" along the strip is order, not time: a span's rank in the reference's sequence is
+	//             (step, ordinal within the step).  Every non-empty span is recorded and does an atomicMin of
+	//             rank << 11 | index on the strip pixels it covers, so a pixel ends up with exactly the span that would
+	//             have written it first, whatever the order the lanes arrive in;
+	//   store     one lane per strip pixel: winner -> colour (one load) + depth, stored as contiguous 256-byte runs;
+	//             hull + LinePixel::Clear holes as LineWalker::finish does.
+	// Same strips, bit for bit (tests/test_terrain_emul.py runs both walkers against the oracle).  A line with more
+	// spans than kCoopMaxSpans falls back to the sequential walker.
+	// ------------------------------------------------------------------------------------------------------------
+	constexpr int kCoopMaxSteps = 1024; // the reference's own limit: cnt2 = fogDist * 8 (:424)
+	constexpr int kCoopMaxSpans = 1024; // non-empty spans per line (measured: <= 160 at 1080p on Title.vxl)
+	constexpr int kCoopShortSpan = 8;   // spans up to this many pixels are resolved by the lane that found them
+	constexpr uint32_t kCoopEmpty = 0xffffffffu;
+
+	struct CoopShared { // per warp; key[] (lineRes words) follows in dynamic shared memory
+		uint32_t cell[kCoopMaxSteps]; // tiled cell entered by the step | wall mode << 31
+		float dist[kCoopMaxSteps];    // distance after the step
+		uint2 span[kCoopMaxSpans];    // x = from | to << 16, y = step << 17 | ordinal << 10 | z << 4 | mode << 2 | kind
+		uint16_t longSpan[kCoopMaxSpans];
+		int nSteps, nSpans, nLong;
+	};
+	OSB_HDI size_t coop_shared_bytes(int lineRes) { return sizeof(CoopShared) + sizeof(uint32_t) * (size_t)lineRes; }
+
+	template <bool kSse, bool kSse2Shade> struct CoopLine {
+		LineWalker<kSse, kSse2Shade> W;
+		uint32_t tStart, eye[4];
+
+		// every lane (uniform): constants of the line; the strip's pixel keys start empty
+		OSB_HDM void begin(const WalkIO &io, uint32_t gl, uint32_t slot, CoopShared &sh, uint32_t *key, int lane) {
+			W.init_consts(io, gl, slot);
+			W.eye_masks(eye);
+			tStart = W.tOld;
+			for (int p = lane; p < io.lineRes; p += 32)
+				key[p] = kCoopEmpty;
+			if (lane == 0)
+				sh.nSpans = sh.nLong = 0;
+		}
+
+		// one lane: the DDA of the whole line (it never looks at the map)
+		OSB_HDM void path(CoopShared &sh) {
+			int s = 0;
+			while (W.distance < W.kFogDist && (--W.cnt2) != 0) { // while (distance < fogDist && --cnt2 > 0) (:423-425)
+				sh.cell[s] = W.nT | ((uint32_t)W.nWallMode << 31);
+				W.irx = W.nIrx;
+				W.iry = W.nIry;
+				W.gx = W.nGx;
+				W.gy = W.nGy;
+				W.distance = W.nDistance;
+				sh.dist[s] = W.distance;
+				W.advance(W.irx, W.iry, W.gx, W.gy, W.distance);
+				s++;
+			}
+			sh.nSteps = s;
+		}
+
+		OSB_HDM float inv_dist_of(const osbn::Num<kSse> &num, const CoopShared &sh, int s) const {
+			return s < 0 ? osbc::fdiv(1.f, 1.e-20f) : num.rcpHotPos(sh.dist[s]);
+		}
+		// does the line end after step s (pitch cull, checked after steps 0, 4, 8, ...)?
+		OSB_HDM bool culls_after(const WalkIO &io, const osbn::Num<kSse> &num, const CoopShared &sh, int s) const {
+			if (s >= sh.nSteps || (s & 3))
+				return false;
+			const float vmax = osbc::fadd((float)io.lineRes, 0.5f);
+			const float iDist = inv_dist_of(num, sh, s);
+			return (W.transform(num, iDist, 0, vmax) >= io.lineRes - 1 && W.icz >= 0) || W.transform(num, iDist, 63, vmax) <= 0;
+		}
+
+		OSB_HDM static uint32_t atomic_min(uint32_t *p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+			return atomicMin(p, v);
+#else
+			const uint32_t o = *p;
+			if (v < o)
+				*p = v;
+			return o;
+#endif
+		}
+		OSB_HDM static int atomic_inc(int *p) {
+#if defined(__CUDA_ARCH__)
+			return atomicAdd(p, 1);
+#else
+			return (*p)++;
+#endif
+		}
+
+		// one lane per step: the spans of step s
+		OSB_HDM void emit_step(const WalkIO &io, const osbn::Num<kSse> &num, CoopShared &sh, uint32_t *key, int s) {
+			using namespace osbc;
+			const float vmax = fadd((float)io.lineRes, 0.5f);
+			const uint32_t tNew = sh.cell[s] & 0x7fffffffu, tOldS = s ? (sh.cell[s - 1] & 0x7fffffffu) : tStart;
+			const int wallMode = (int)(sh.cell[s] >> 31);
+			const uint64_t sOldV = io.solid[tOldS], sNewV = io.solid[tNew];
+			const float iDist = inv_dist_of(num, sh, s), oldIDist = inv_dist_of(num, sh, s - 1);
+			W.spans_of_step(
+			  num, vmax, sOldV, sNewV, iDist, oldIDist, wallMode, eye[0], eye[1], [&](int k) { return eye[2 + k]; },
+			  [&](int from, int to, bool cellNew, int z, int zA, int mode, int ordinal) {
+				  const int idx = atomic_inc(&sh.nSpans);
+				  if (idx >= kCoopMaxSpans)
+					  return; // overflow: the caller falls back to the sequential walker
+				  const uint32_t kind = cellNew ? 2u : (zA != z ? 1u : 0u);
+				  sh.span[idx] = make_uint2((uint32_t)from | ((uint32_t)to << 16),
+				                            ((uint32_t)s << 17) | ((uint32_t)ordinal << 10) | ((uint32_t)z << 4) | ((uint32_t)mode << 2) | kind);
+				  if (to - from <= kCoopShortSpan) {
+					  const uint32_t k = ((((uint32_t)s << 7) | (uint32_t)ordinal) << 11) | (uint32_t)idx;
+					  for (int p = from; p < to; p++)
+						  atomic_min(key + p, k);
+				  } else {
+					  sh.longSpan[atomic_inc(&sh.nLong)] = (uint16_t)idx;
+				  }
+			  });
+		}
+		// all lanes: the long spans, 32 pixels at a time
+		OSB_HDM void resolve_long(const CoopShared &sh, uint32_t *key, int lane) const {
+			for (int i = 0; i < sh.nLong; i++) {
+				const int idx = sh.longSpan[i];
+				const uint2 r = sh.span[idx];
+				const int from = (int)(r.x & 0xffffu), to = (int)(r.x >> 16);
+				const uint32_t k = ((r.y >> 10) << 11) | (uint32_t)idx; // (step << 7 | ordinal) << 11 | index
+				for (int p = from + lane; p < to; p += 32)
+					atomic_min(key + p, k);
+			}
+		}
+		// this lane's share of the hull: lowest / highest written strip pixel among p = lane, lane + 32, ...
+		OSB_HDM void scan_hull(const WalkIO &io, const uint32_t *key, int lane, int &first, int &last) const {
+			first = io.lineRes;
+			last = -1;
+			for (int p = lane; p < io.lineRes; p += 32)
+				if (key[p] != kCoopEmpty) {
+					first = osbc::imin(first, p);
+					last = osbc::imax(last, p);
+				}
+		}
+		// one lane per strip pixel inside the hull [first, last]
+		OSB_HDM void store(const WalkIO &io, const CoopShared &sh, const uint32_t *key, int lane, int first, int last) const {
+			using namespace osbc;
+			const uint2 clearPix = make_uint2(0u, f2u(10000.f)); // LinePixel::Clear (:89-92)
+			for (int p = (first & ~31) + lane; p <= last; p += 32) {
+				if (p < first)
+					continue;
+				const uint32_t k = key[p];
+				uint2 px = clearPix; // a hole inside the hull
+				if (k != kCoopEmpty) {
+					const uint2 r = sh.span[k & (uint32_t)(kCoopMaxSpans - 1)];
+					const int s = (int)(r.y >> 17), z = (int)((r.y >> 4) & 63u), mode = (int)((r.y >> 2) & 3u);
+					const uint32_t kind = r.y & 3u;
+					const uint32_t cellIdx = kind == 2u ? (sh.cell[s] & 0x7fffffffu) : (s ? (sh.cell[s - 1] & 0x7fffffffu) : tStart);
+					const uint32_t rawCol = ldg(io.color + (cellIdx * 64u + (uint32_t)z));
+					const float medDist = fadd(fmul(sh.dist[s], W.zscale), W.depthBias);
+					px = make_uint2(shade<kSse2Shade>(rawCol, mode),
+					                f2u(fadd(medDist, fmul(i2f(z + (kind == 1u ? 1 : 0)), W.heightScale))));
+				}
+				stcs(io.strips + (W.stripBase + (uint32_t)p), px);
+			}
+			if (lane == 0) {
+#if OSB_STRIP_HULL
+				io.lineRecs[W.maskBase].view = last >= first ? (first | ((last - first + 1) << 16)) : 1;
+#endif
+			}
 		}
 	};
 
@@ -694,7 +891,7 @@ namespace osb {
 	//                 every pixel row is one 128-byte run per buffer.
 	// ------------------------------------------------------------------------------------------------------------
 	constexpr int kGatherWarps = 4;
-	constexpr int kSegRows = 8; // 8x8 blocks per warp task (vertical)
+	constexpr int kSegRows = 8; // most 8x8 block rows per warp task (vertical); GatherIO::segRows picks the actual number
 
 	struct GatherShared { // per warp
 		int yaw[32], pit[32]; // [r*16 + b*4 + k]
@@ -716,6 +913,7 @@ namespace osb {
 		int lineRes;
 		uint32_t *fb;
 		float *depth;
+		int segRows; // block rows per warp task, 1..kSegRows (small launches use fewer: more warps in flight)
 	};
 
 	template <bool kSse, bool kSse2Fog> struct GatherLane {
@@ -737,7 +935,7 @@ namespace osb {
 			colBlocks = g.fw >> 3;
 			const int rowBlocks = g.fh >> 3;
 			const int colGroups = (colBlocks + 3) >> 2;
-			const int segs = (rowBlocks + kSegRows - 1) / kSegRows;
+			const int segs = (rowBlocks + io.segRows - 1) / io.segRows;
 			const uint32_t perView = (uint32_t)colGroups * segs;
 			if (task >= perView * (uint32_t)io.nViews)
 				return false;
@@ -746,8 +944,8 @@ namespace osb {
 			const int seg = rem / colGroups;
 			cg = rem - seg * colGroups;
 			V = io.views + vi;
-			by0 = seg * kSegRows;
-			by1 = imin(by0 + kSegRows, rowBlocks);
+			by0 = seg * io.segRows;
+			by1 = imin(by0 + io.segRows, rowBlocks);
 
 			pb = lane >> 3;
 			const int bx = (cg << 2) + pb;     // this lane's block column

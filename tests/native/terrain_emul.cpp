@@ -31,6 +31,8 @@ extern "C" int osb200_calibrate_sse(uint32_t *rcp_table, int *rcp_bits, uint32_t
 
 namespace {
 	using namespace osb;
+	unsigned long long g_coopStats[4]; // lines, fallbacks, max spans, sum spans
+	int g_coop = 0; // 0: lane-per-line walker, 1: cooperative walker (one warp per line), 2: its sequential fallback
 
 	struct Tables {
 		std::vector<uint32_t> rcp, rsqrt;
@@ -155,6 +157,54 @@ namespace {
 			return 0;
 		}
 		unsigned long long steps = 0;
+		if (g_coop) { // k_walk_coop: one warp per line, the phases in kernel order, the lanes one after the other
+			std::vector<uint32_t> shbuf((coop_shared_bytes(lineRes) + 3) / 4);
+			CoopShared &sh = *reinterpret_cast<CoopShared *>(shbuf.data());
+			uint32_t *key = shbuf.data() + sizeof(CoopShared) / 4;
+			for (size_t s = 0; s < active.size(); s++) {
+				CoopLine<kSse, kSse2> C[32];
+				for (int l = 0; l < 32; l++)
+					C[l].begin(wio, active[s], (uint32_t)s, sh, key, l);
+				C[0].path(sh);
+				steps += sh.nSteps;
+				bool ended = false;
+				for (int s0 = 0; s0 < sh.nSteps && !ended; s0 += 32) {
+					int cullAt = 1 << 30;
+					for (int l = 31; l >= 0; l--)
+						if (C[l].culls_after(wio, num, sh, s0 + l))
+							cullAt = s0 + l;
+					for (int l = 31; l >= 0; l--) { // any lane order must give the same strip: run them backwards
+						const int st = s0 + l;
+						if (st < sh.nSteps && st <= cullAt)
+							C[l].emit_step(wio, num, sh, key, st);
+					}
+					ended = cullAt < (1 << 30);
+				}
+				g_coopStats[0]++;
+				g_coopStats[2] = std::max<unsigned long long>(g_coopStats[2], (unsigned long long)sh.nSpans);
+				g_coopStats[3] += sh.nSpans;
+				if (sh.nSpans > kCoopMaxSpans)
+					g_coopStats[1]++;
+				if (sh.nSpans > kCoopMaxSpans || g_coop == 2) { // fallback: the sequential walker (g_coop == 2 forces it)
+					LineWalker<kSse, kSse2> W;
+					W.init(wio, active[s], (uint32_t)s, key, 1);
+					while (W.step(wio, num, key, 1)) {
+					}
+					continue;
+				}
+				for (int l = 0; l < 32; l++)
+					C[l].resolve_long(sh, key, l);
+				int first = lineRes, last = -1;
+				for (int l = 0; l < 32; l++) {
+					int f, la;
+					C[l].scan_hull(wio, key, l, f, la);
+					first = std::min(first, f);
+					last = std::max(last, la);
+				}
+				for (int l = 0; l < 32; l++)
+					C[l].store(wio, sh, key, l, first, last);
+			}
+		} else
 		for (size_t s = 0; s < active.size(); s++) {
 			uint32_t filled[128 + kWalkExtraWords];
 			LineWalker<kSse, kSse2> W;
@@ -168,10 +218,11 @@ namespace {
 			stats->steps = steps;
 		}
 		// ---- k_gather_fog ----
+		const int segRowsArg = (h >> 3) % 3 == 0 ? 2 : ((w >> 3) & 1 ? 4 : kSegRows); // exercise all task heights across the test sizes
 		const std::vector<uint16_t> atanTab = atan_table();
 		GatherIO gio{views.data(), nViews,       g,         tabs.data(), solidT, atanTab.data(), strips.data(), recs.data(),
-		             lineTan.data(), mask.data(), lineRes, fb,          depth};
-		const int colGroups = ((w >> 3) + 3) >> 2, segs = ((h >> 3) + kSegRows - 1) / kSegRows;
+		             lineTan.data(), mask.data(), lineRes, fb,          depth, segRowsArg};
+		const int colGroups = ((w >> 3) + 3) >> 2, segs = ((h >> 3) + segRowsArg - 1) / segRowsArg;
 		const uint32_t tasks = (uint32_t)nViews * colGroups * segs;
 		for (uint32_t task = 0; task < tasks; task++) {
 			GatherLane<kSse, kSse2> L[32];
@@ -288,6 +339,14 @@ __attribute__((visibility("default"))) int emul_render(const uint64_t *solid, co
 		stats3[2] = st.steps;
 	}
 	return rc;
+}
+__attribute__((visibility("default"))) void emul_set_coop(int mode) { g_coop = mode; }
+__attribute__((visibility("default"))) void emul_coop_stats(unsigned long long *out, int reset) {
+	for (int i = 0; i < 4; i++) {
+		out[i] = g_coopStats[i];
+		if (reset)
+			g_coopStats[i] = 0;
+	}
 }
 // lock-step warp statistics of the walker for a batch of views (V-SSE2): out[10], see warp_model
 __attribute__((visibility("default"))) int emul_warp_model(const uint64_t *solid, const uint32_t *color, const osb200_scene *scenes,

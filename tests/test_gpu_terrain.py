@@ -120,8 +120,9 @@ def test_eye_inside_solid_and_bad_size(title_map):
 
 
 def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
-    """k_build_lines deals 4..32 lines to a warp depending on the launch size (OSB200_LINE_MIN_LANES, read once per process):
-    the same views rendered in fresh processes with full warps and with the default give identical frames + depth."""
+    """Small launches are walked differently from batches (OSB200_LINE_MIN_LANES / OSB200_COOP, read once per process): fewer
+    lines per warp task, or the cooperative walker k_walk_coop with a whole warp per yaw line.  The same views rendered in
+    fresh processes under each policy give identical frames + depth."""
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -140,9 +141,11 @@ def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
         "    fb2, dp2 = ctx.render(sc, 1920, 1080, (0.1, 0.1, 0.1), 128.0)\n"
         "np.savez(sys.argv[1], fb=fb, dp=dp, fb2=fb2, dp2=dp2)\n")
     outs = []
-    for lanes in ("32", "4", "1"):
-        out = str(tmp_path / f"lanes{lanes}.npz")
-        env = dict(os.environ, OSB200_LINE_MIN_LANES=lanes)
+    # lane-per-line walker with 32 / 4 / 1 lines per warp task, then the cooperative walker (one warp per line), forced for
+    # the 3-view batch too (by default it serves launches of fewer than 64 lines per SM)
+    for lanes, coop in (("32", "0"), ("4", "0"), ("1", "0"), ("4", "1")):
+        out = str(tmp_path / f"lanes{lanes}_{coop}.npz")
+        env = dict(os.environ, OSB200_LINE_MIN_LANES=lanes, OSB200_COOP=coop)
         subprocess.run([sys.executable, "-c", code, out], check=True, env=env, timeout=300)
         outs.append(np.load(out))
     for other in outs[1:]:

@@ -36,7 +36,12 @@ class Emul:
         self.L = ctypes.CDLL(LIB)
         vp, ci = ctypes.c_void_p, ctypes.c_int
         self.L.emul_render.argtypes = [vp, vp, vp, ci, ci, ci, vp, ctypes.c_float, ci, ci, ci, ci, ci, vp, vp, vp, ci]
+        self.L.emul_set_coop.argtypes = [ci]
         self.key = 0
+
+    def set_walker(self, mode):
+        """0 = lane-per-line walker (k_walk_lines), 1 = cooperative walker (k_walk_coop), 2 = its sequential fallback"""
+        self.L.emul_set_coop(mode)
 
     def render(self, solid, color, scenes, w, h, fog, fog_dist, numerics, threads=4, under=1, no_map=False, depth=None,
                new_map=True):
@@ -55,9 +60,12 @@ class Emul:
         return fb, dp, st
 
 
-@pytest.fixture(scope="module")
-def emul():
-    return Emul()
+@pytest.fixture(scope="module", params=[0, 1], ids=["lane_per_line", "cooperative"])
+def emul(request):
+    e = Emul()
+    e.set_walker(request.param)
+    yield e
+    e.set_walker(0)
 
 
 @pytest.fixture(scope="module")
@@ -169,3 +177,15 @@ def test_ceilings_above_the_eye(emul, port, title_map, numerics):
         assert _same(f"hall {i} num {numerics}", fb[0], dp[0], rfb, rdp) == (1.0, 1.0)
         dark = ((rfb & 0xFFFFFF) != 0).mean()
         assert dark > 0.5
+
+
+def test_cooperative_fallback_path(port, title_map):
+    """a line with more spans than the cooperative walker records falls back to the sequential one inside the same warp"""
+    e = Emul()
+    e.set_walker(2)
+    solid, color = title_map
+    sc = workloads.title_scene(256, 256, 68.0)
+    fb, dp, _ = e.render(solid, color, sc, 256, 256, FOG, 128.0, 2)
+    e.set_walker(0)
+    rfb, rdp = port.render(solid, color, sc, 256, 256, FOG, 128.0, 2, 4, 1)
+    assert _same("coop fallback", fb[0], dp[0], rfb, rdp) == (1.0, 1.0)
