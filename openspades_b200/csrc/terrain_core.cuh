@@ -677,7 +677,7 @@ namespace osb {
 	// ------------------------------------------------------------------------------------------------------------
 	constexpr int kCoopMaxSteps = 1024; // the reference's own limit: cnt2 = fogDist * 8 (:424)
 	constexpr int kCoopMaxSpans = 1024; // non-empty spans per line (measured: <= 160 at 1080p on Title.vxl)
-	constexpr int kCoopShortSpan = 8;   // spans up to this many pixels are resolved by the lane that found them
+	constexpr int kCoopShortSpan = 32;  // spans up to this many pixels are resolved by the lane that found them
 	constexpr uint32_t kCoopEmpty = 0xffffffffu;
 
 	struct CoopShared { // per warp; key[] (lineRes words) follows in dynamic shared memory
@@ -798,26 +798,59 @@ namespace osb {
 					last = osbc::imax(last, p);
 				}
 		}
-		// one lane per strip pixel inside the hull [first, last]
+		// one lane per strip pixel inside the hull [first, last]; kB pixels per lane and pass, stage by stage, so that
+		// the colour loads of a pass (DRAM latency on a cold map) are in flight together
 		OSB_HDM void store(const WalkIO &io, const CoopShared &sh, const uint32_t *key, int lane, int first, int last) const {
 			using namespace osbc;
+			constexpr int kB = 4;
 			const uint2 clearPix = make_uint2(0u, f2u(10000.f)); // LinePixel::Clear (:89-92)
-			for (int p = (first & ~31) + lane; p <= last; p += 32) {
-				if (p < first)
-					continue;
-				const uint32_t k = key[p];
-				uint2 px = clearPix; // a hole inside the hull
-				if (k != kCoopEmpty) {
-					const uint2 r = sh.span[k & (uint32_t)(kCoopMaxSpans - 1)];
-					const int s = (int)(r.y >> 17), z = (int)((r.y >> 4) & 63u), mode = (int)((r.y >> 2) & 3u);
-					const uint32_t kind = r.y & 3u;
-					const uint32_t cellIdx = kind == 2u ? (sh.cell[s] & 0x7fffffffu) : (s ? (sh.cell[s - 1] & 0x7fffffffu) : tStart);
-					const uint32_t rawCol = ldg(io.color + (cellIdx * 64u + (uint32_t)z));
-					const float medDist = fadd(fmul(sh.dist[s], W.zscale), W.depthBias);
-					px = make_uint2(shade<kSse2Shade>(rawCol, mode),
-					                f2u(fadd(medDist, fmul(i2f(z + (kind == 1u ? 1 : 0)), W.heightScale))));
+			for (int p0 = (first & ~31) + lane; p0 <= last; p0 += 32 * kB) {
+				uint32_t spanY[kB], rawCol[kB];
+				bool live[kB];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+				for (int j = 0; j < kB; j++) {
+					const int p = p0 + 32 * j;
+					live[j] = false;
+					spanY[j] = 0u;
+					rawCol[j] = 0u;
+					if (p >= first && p <= last) {
+						const uint32_t k = key[p];
+						if (k != kCoopEmpty) {
+							live[j] = true;
+							spanY[j] = sh.span[k & (uint32_t)(kCoopMaxSpans - 1)].y;
+						}
+					}
 				}
-				stcs(io.strips + (W.stripBase + (uint32_t)p), px);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+				for (int j = 0; j < kB; j++) {
+					if (live[j]) {
+						const int s = (int)(spanY[j] >> 17), z = (int)((spanY[j] >> 4) & 63u);
+						const uint32_t kind = spanY[j] & 3u;
+						const uint32_t cellIdx = kind == 2u ? (sh.cell[s] & 0x7fffffffu) : (s ? (sh.cell[s - 1] & 0x7fffffffu) : tStart);
+						rawCol[j] = ldg(io.color + (cellIdx * 64u + (uint32_t)z));
+					}
+				}
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+				for (int j = 0; j < kB; j++) {
+					const int p = p0 + 32 * j;
+					if (p < first || p > last)
+						continue;
+					uint2 px = clearPix; // a hole inside the hull
+					if (live[j]) {
+						const int s = (int)(spanY[j] >> 17), z = (int)((spanY[j] >> 4) & 63u), mode = (int)((spanY[j] >> 2) & 3u);
+						const uint32_t kind = spanY[j] & 3u;
+						const float medDist = fadd(fmul(sh.dist[s], W.zscale), W.depthBias);
+						px = make_uint2(shade<kSse2Shade>(rawCol[j], mode),
+						                f2u(fadd(medDist, fmul(i2f(z + (kind == 1u ? 1 : 0)), W.heightScale))));
+					}
+					stcs(io.strips + (W.stripBase + (uint32_t)p), px);
+				}
 			}
 			if (lane == 0) {
 #if OSB_STRIP_HULL
