@@ -291,11 +291,20 @@ namespace osb {
 		}
 	}
 
-	// RenderFinal + ApplyFog, see GatherLane in terrain_core.cuh
-	template <bool kSse, bool kSse2Fog>
+	// RenderFinal + ApplyFog, see GatherLane in terrain_core.cuh.
+	// OSB_GATHER_TMA=1 (experiment): the CTA stages its view's line-record table (numLines x 16 B)
+	// in shared memory with ONE bulk asynchronous copy (cp.async.bulk, the 1-D TMA path, completion on an mbarrier) while
+	// the warps run their fog / corner set-up, and the per-pixel record loads become shared-memory loads.
+#ifndef OSB_GATHER_TMA
+#define OSB_GATHER_TMA 0
+#endif
+#if OSB_GATHER_TMA
+	constexpr int kStagedRecs = 1536; // line records a CTA can stage (24 KB): covers 256x256 views (<= 1192 lines)
+#endif
 #ifndef OSB_GATHER_MINB
 #define OSB_GATHER_MINB 8 // <= 64 registers: measured 1.24 ms per 4096 views against 1.29 ms unbounded (72 registers)
 #endif
+	template <bool kSse, bool kSse2Fog>
 	__global__ void __launch_bounds__(kGatherWarps * 32, OSB_GATHER_MINB) k_gather_fog(GatherIO io, osbn::SseTables tabs) {
 		__shared__ GatherShared s_g[kGatherWarps];
 		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -303,10 +312,46 @@ namespace osb {
 		const osbn::Num<kSse> num{tabs};
 		GatherShared &sm = s_g[wid];
 		GatherLane<kSse, kSse2Fog> L;
-		if (!L.init(io, task, lane)) // whole warp
+		const bool mine = L.init(io, task, lane); // false: the task lies outside the launch (whole warp)
+#if OSB_GATHER_TMA
+		__shared__ alignas(128) LineRec s_recs[kStagedRecs];
+		__shared__ alignas(8) unsigned long long s_bar;
+		// the view of the CTA's first task; its table is staged when it fits (warps of another view read global memory)
+		const uint32_t perView = (uint32_t)((((io.g.fw >> 3) + 3) >> 2) * (((io.g.fh >> 3) + io.segRows - 1) / io.segRows));
+		const uint32_t vi0 = (blockIdx.x * kGatherWarps) / perView;
+		const ViewParams *V0 = vi0 < (uint32_t)io.nViews ? io.views + vi0 : nullptr;
+		const bool stage = V0 && V0->numLines <= kStagedRecs;
+		const uint32_t barAddr = (uint32_t)__cvta_generic_to_shared(&s_bar);
+		if (threadIdx.x == 0 && stage) {
+			asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr));
+			asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+		}
+		__syncthreads();
+		if (threadIdx.x == 0 && stage) {
+			const uint32_t bytes = (uint32_t)V0->numLines * (uint32_t)sizeof(LineRec);
+			const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s_recs);
+			const LineRec *src = io.lineRecs + V0->lineBase;
+			asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barAddr), "r"(bytes) : "memory");
+			asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+			             "l"(src), "r"(bytes), "r"(barAddr)
+			             : "memory");
+		}
+#endif
+		if (!mine)
 			return;
 		L.fog_phase(io, num, sm, lane);
 		__syncwarp();
+#if OSB_GATHER_TMA
+		if (stage && L.V == V0) { // wait for the bulk copy (phase 0 of the barrier), then read records from shared memory
+			uint32_t done = 0;
+			while (!done)
+				asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}"
+				             : "=r"(done)
+				             : "r"(barAddr)
+				             : "memory");
+			L.stagedRecs = s_recs;
+		}
+#endif
 		for (int by = L.by0; by < L.by1; by += 2) {
 			L.corner_phase(io, num, sm, lane, by);
 			__syncwarp();

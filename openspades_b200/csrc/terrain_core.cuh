@@ -960,6 +960,8 @@ namespace osb {
 		// corner role
 		int cr, ck, cb;
 		float v2c[3], dRL[3], dDL[3];
+		// line records of this lane's view staged in shared memory by the kernel (bulk copy), or null: read them from global
+		const LineRec *stagedRecs = nullptr;
 
 		// false: the task lies outside the launch (whole warp)
 		OSB_HDM bool init(const GatherIO &io, uint32_t task, int lane) {
@@ -1155,7 +1157,8 @@ namespace osb {
 						yawIndex = (yawIndex * yawScale2) >> 16;
 						yawIndex = (yawIndex * numLines) >> 16;
 						yawIndex = uminu(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
-						lpw[j] = ldg(reinterpret_cast<const int4 *>(lpV + yawIndex));
+						lpw[j] = stagedRecs ? *reinterpret_cast<const int4 *>(stagedRecs + yawIndex)
+						                    : ldg(reinterpret_cast<const int4 *>(lpV + yawIndex));
 					}
 #if defined(__CUDA_ARCH__)
 #pragma unroll
