@@ -5,12 +5,14 @@ Headline workload (BASELINE.json configs[3], the one the north_star's roofline t
 only render workload that shards): a batch of independent 256x256 camera views of the bundled
 Title.vxl map, fovY 68 deg, fog (0.8,1,1)/128, V-SSE2 numerics with r_swNumThreads = 4 -- 4096 views PER
 GPU (weak scaling: views are sharded by view, map replicated, no data-path collective).
-A "step" renders the whole batch once: terrain pass (k_build_lines) + fused gather/fog (k_gather_fog).
+A "step" renders the whole batch once: k_view_prep, k_line_setup, k_line_compact, k_walk_lines (the terrain pass,
+SWMapRenderer::BuildLine) and k_gather_fog (RenderFinal + ApplyFog fused) -- one launch of each per step.
 
   value   Mpixel/s, device-timed, inputs resident in HBM (scene constants upload is part of the call).
   e2e     same metric through the host-pointer C-ABI call osb200_render: host scenes in, frames copied back
           to pinned host memory inside the timed region (depth stays device-resident, as in SWRenderer).
-  extra   configs[1] (1920x1080 single view) and configs[2] (16 Mi CastRay2 rays) measured the same way.
+  extra   configs[0] (800x600 title frame), configs[1] (1920x1080 single view), configs[2] (16 Mi CastRay2 rays),
+          the in-game frame and configs[4] (radiosity) measured the same way, each with its CPU baseline beside it.
 
 `--impl reference` times the reference's own CPU code (oracle/_ref, else the oracle port) on the host cores.
 """
@@ -318,9 +320,8 @@ def run_b200(args):
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     gpu_launches = ctx.launch_count - launches0
     ms_per_step = ms_total / K
-    # per-kernel durations: a second pass of K steps with CUDA events around every launch on the launching stream.
-    # With timing on the library runs its chunks back to back on one stream (in the timed region above, chunk k+1's
-    # line build overlaps chunk k's gather on a second stream, which would smear the per-kernel durations).
+    # per-kernel durations: a second pass of K steps with CUDA events around every launch on the launching stream
+    # (the timed region above runs without them).
     ctx.timing_enable(True)
     ctx.timing_read()
     for _ in range(K):
@@ -329,6 +330,26 @@ def run_b200(args):
     ktimes = ctx.timing_read()
     ctx.timing_enable(False)
     value = world * pixels_per_step / (ms_per_step * 1e-3) / 1e6
+
+    # ---- what the numerics choice costs: the same step with the other two variants (rank-local, not part of `value`) ----
+    numerics_cost = {"V-SSE2": ms_per_step}
+    if not args.no_extra:
+        for name, num in (("V-IEEE", osb.NUM_IEEE), ("V-SSE", osb.NUM_SSE)):
+            with osb.Context(device=local, numerics=num, sw_threads=4) as nc:
+                nc.map_upload(solid, color)
+                nx = torch.cuda.ExternalStream(nc.stream, device=dev)
+                for _ in range(W):
+                    nc.render_device(scenes, S, S, FOG, FOG_DIST, d_fb, d_dp)
+                nc.sync()
+                n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n0.record(nx)
+                for _ in range(K):
+                    nc.render_device(scenes, S, S, FOG, FOG_DIST, d_fb, d_dp)
+                n1.record(nx)
+                n1.synchronize()
+                numerics_cost[name] = n0.elapsed_time(n1) / K
+        step_device()  # leave the V-SSE2 frames in d_fb / d_dp for the parity sample and the checksum
+        ctx.sync()
 
     # ---- e2e through the host-pointer C-ABI call (H2D scenes, D2H frames + depth every step) ----
     # What the reference-facing call returns is the framebuffer (SWPort bitmap); the depth buffer is internal
@@ -468,8 +489,8 @@ def run_b200(args):
                          "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
                          "note": "the whole step (all kernels + gaps) against the same 8 B/pixel"},
                 "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": dms / max(dl, 1),
-                "kernel_timing": "separate pass of the same K steps, chunks serialised on one stream, CUDA events "
-                                 "around every launch (the timed region overlaps chunks on two streams)",
+                "kernel_timing": "separate pass of the same K steps on the context's stream with CUDA events around "
+                                 "every launch (OSB200 kernel timing facility); `value` comes from the untimed-launch pass",
                 "kernel_ms_per_step": {k: v[1] / K for k, v in ktimes.items() if v[0]},
                 "kernel_launches_per_step": {k: v[0] / K for k, v in ktimes.items() if v[0]}}
 
@@ -493,7 +514,7 @@ def run_b200(args):
                              % (pixels_per_step / 1e9, pixels_per_step * 8 / 1e9)},
             "e2e": e2e, "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "parity_sample": parity, "strong": strong, "multi_gpu": multi_gpu,
-            "extra": extra, "result_checksum": checksum,
+            "numerics_ms_per_step": numerics_cost, "extra": extra, "result_checksum": checksum,
         }
         emit_json(line)
     ctx.close()

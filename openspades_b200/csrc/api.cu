@@ -317,6 +317,8 @@ void osb200_destroy(osb200_ctx *c) {
 			cudaEventDestroy(c->rayPipe->computed[i]);
 			cudaEventDestroy(c->rayPipe->downloaded[i]);
 		}
+		if (c->rayPipe->h_ring)
+			cudaFreeHost(c->rayPipe->h_ring);
 		delete c->rayPipe;
 	}
 	cudaFree(c->d_stage);

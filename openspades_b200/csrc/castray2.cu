@@ -5,11 +5,19 @@
 // round-to-nearest intrinsics explicitly; every field of RayCastResult is reproduced bit for bit.
 //
 // Memory: 24 B in + 40 B out per ray (the algorithmic bytes) plus the 2 MiB
-// solid bitmap, which is L2/L1-resident in 4x4-column tiles (ctx.h: tiled_index).  Result records
-// are transposed through shared memory so that each warp writes its 1280 B contiguously.
+// solid bitmap, which is L2/L1-resident in 4x4-column tiles (ctx.h: tiled_index).  Each lane writes its own
+// 40-byte record as five 8-byte stores when its ray ends (rays of a warp end at different steps, so there is no
+// common point at which a warp-wide transposed write could happen; L2 merges the sectors before they reach HBM).
 #include "ctx.h"
 
 #include <algorithm>
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
 
 namespace {
 
@@ -22,17 +30,10 @@ namespace {
 	constexpr int kWordsPerHit = 10;   // sizeof(osb200_rayhit) / 4
 	constexpr int kCtasPerSm = 10;     // persistent grid: 48 registers x 128 threads -> 10 CTAs per SM
 	constexpr int kRefillAt = 8;       // idle lanes that trigger a refill (ray set-up is the divergent part)
-
-	struct RayState {
-		float fx, fy, fz;       // distance to the next boundary per axis (fv in the reference)
-		float ax, ay, az;       // |dir|
-		float invX, invY, invZ; // 1 / |dir|, 0 when the component is 0
-		int ix, iy, iz;         // current cell
-		uint32_t sign;          // bit0..2: dir.x/y/z > 0
-		uint64_t col;           // solid mask of column (ix, iy)
-		int axis, steps;
-		size_t ray;
-	};
+#ifndef OSB_RAY_STEPS_PER_CHECK
+#define OSB_RAY_STEPS_PER_CHECK 8
+#endif
+	constexpr int kStepsPerCheck = OSB_RAY_STEPS_PER_CHECK; // DDA steps between two looks at the warp's idle lanes
 
 	__device__ __forceinline__ void write_hit(uint32_t *__restrict__ out, size_t ray, uint32_t flags, float hx, float hy,
 	                                          float hz, int bx, int by, int bz, int nx, int ny, int nz) {
@@ -53,27 +54,101 @@ namespace {
 		return z >= 64;
 	}
 
+	// The reference's loop as written (GameMap.cpp:413-497), one ray from start to end by one lane.  Only rays whose
+	// normalised direction holds a NaN come here (an infinite or NaN input component): the fast step below folds the
+	// "axis present" tests into the comparisons, which orders NaNs differently.  Garbage in, the reference's garbage out.
+	__device__ __noinline__ void cast_ray_generic(const uint64_t *__restrict__ solid, uint32_t *__restrict__ out, size_t ray,
+	                                              float v0x, float v0y, float v0z, float dx, float dy, float dz, int ix, int iy,
+	                                              int iz, uint64_t col, int maxSteps) {
+		const bool px = dx > 0.f, py = dy > 0.f, pz = dz > 0.f;
+		float fx = px ? __fsub_rn((float)(ix + 1), v0x) : __fsub_rn(v0x, (float)ix);
+		float fy = py ? __fsub_rn((float)(iy + 1), v0y) : __fsub_rn(v0y, (float)iy);
+		float fz = pz ? __fsub_rn((float)(iz + 1), v0z) : __fsub_rn(v0z, (float)iz);
+		const float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
+		const float invX = dx != 0.f ? __fdiv_rn(1.f, ax) : dx;
+		const float invY = dy != 0.f ? __fdiv_rn(1.f, ay) : dy;
+		const float invZ = dz != 0.f ? __fdiv_rn(1.f, az) : dz;
+		const bool hasX = invX != 0.f, hasY = invY != 0.f, hasZ = invZ != 0.f;
+		int axis = 0;
+		bool hit = false;
+		for (int steps = 0; steps < maxSteps && !hit; steps++) {
+			axis = 0;
+			float t = 0.f;
+			const float tx = __fmul_rn(fx, invX), ty = __fmul_rn(fy, invY), tz = __fmul_rn(fz, invZ);
+			if (hasX) {
+				t = tx;
+				axis = 1;
+			}
+			if (hasY && (!axis || ty < t)) {
+				t = ty;
+				axis = 2;
+			}
+			if (hasZ && (!axis || tz < t)) {
+				t = tz;
+				axis = 3;
+			}
+			const float nfx = __fsub_rn(fx, __fmul_rn(ax, t)), nfy = __fsub_rn(fy, __fmul_rn(ay, t)),
+			            nfz = __fsub_rn(fz, __fmul_rn(az, t));
+			fx = axis == 1 ? 1.f : nfx;
+			fy = axis == 2 ? 1.f : nfy;
+			fz = axis == 3 ? 1.f : nfz;
+			ix += axis == 1 ? (px ? 1 : -1) : 0;
+			iy += axis == 2 ? (py ? 1 : -1) : 0;
+			iz += axis == 3 ? (pz ? 1 : -1) : 0;
+			if (axis == 1 || axis == 2)
+				col = solid[osb::tiled_index(ix & 511, iy & 511)];
+			hit = solid_at(col, iz);
+		}
+		const int nx = axis == 1 ? (px ? -1 : 1) : 0, ny = axis == 2 ? (py ? -1 : 1) : 0, nz = axis == 3 ? (pz ? -1 : 1) : 0;
+		float hx = v0x, hy = v0y, hz = v0z;
+		if (hit) {
+			hx = px ? __fsub_rn((float)(ix + 1), fx) : __fadd_rn((float)ix, fx);
+			hy = py ? __fsub_rn((float)(iy + 1), fy) : __fadd_rn((float)iy, fy);
+			hz = pz ? __fsub_rn((float)(iz + 1), fz) : __fadd_rn((float)iz, fz);
+		}
+		write_hit(out, ray, hit ? 1u : 0u, hx, hy, hz, ix, iy, iz, nx, ny, nz);
+	}
+
+	struct RayState {
+		float fx, fy, fz;       // distance to the next boundary per axis (fv in the reference)
+		float ax, ay, az;       // |dir|
+		float invX, invY, invZ; // 1 / |dir|, 0 when the component is 0
+		float bX, bY, bZ;       // 0, or +inf for an axis the ray never crosses (its t must lose every comparison)
+		int ix, iy, iz;         // current cell
+		uint32_t sign;          // bit0..2: dir.x/y/z > 0
+		uint64_t col;           // solid mask of column (ix, iy)
+		int left;               // steps the ray may still take; 0 = this lane has no ray
+		size_t ray;
+	};
+
 	// Persistent grid (one CTA slot per resident CTA).  Every warp keeps its 32 lanes busy: a lane whose ray has
 	// ended (hit, start-solid or step limit) writes its record and waits; once kRefillAt lanes wait, the warp takes
 	// that many rays from the batch-wide cursor (one atomicAdd per refill) and re-arms them.  Ray lengths differ by
 	// two orders of magnitude (start-solid: 0 steps, sky rays: maxSteps), so one-ray-per-thread left two thirds
 	// of the lanes idle, and a static split left whole SMs idle in the tail.
-	__global__ void __launch_bounds__(kThreads)
+	//
+	// The step is bound by the ALU pipe (compares, selects, logic: ncu 84 % of its peak in round 1), so it is written
+	// to need few of those: the reference's "is this axis crossed at all" tests (hasX/Y/Z, :417-419,432-446) are folded
+	// into the t of the axis -- t = fma(f, inv, bias) with bias = +inf for an axis whose direction component is 0
+	// (the product is exact-rounded once and adding 0 does not change it), which then loses both "<" comparisons
+	// exactly where the reference skips the axis; a ray with no axis at all never moves and is answered at set-up.
+	__global__ void __launch_bounds__(kThreads, kCtasPerSm)
 	  k_castray2(const uint64_t *__restrict__ solid, const float *__restrict__ v0s,
 	             const float *__restrict__ dirs, int maxSteps, uint32_t *__restrict__ out, size_t n,
 	             unsigned long long *__restrict__ cursor) {
 		const int lane = threadIdx.x & 31;
 		bool drained = false; // the cursor ran past n: no more refills for this warp
 		RayState r;
-		bool active = false;
-		r.fx = r.fy = r.fz = r.ax = r.ay = r.az = r.invX = r.invY = r.invZ = 0.f;
-		r.ix = r.iy = r.iz = r.axis = r.steps = 0;
+		r.fx = r.fy = r.fz = r.ax = r.ay = r.az = r.invX = r.invY = r.invZ = r.bX = r.bY = r.bZ = 0.f;
+		r.ix = r.iy = r.iz = 0;
+		r.left = 0;
 		r.sign = 0;
 		r.col = 0;
 		r.ray = 0;
+		const float kInf = __int_as_float(0x7f800000);
 
 		for (;;) {
-			const unsigned idle = __ballot_sync(0xffffffffu, !active);
+			const unsigned idle = __ballot_sync(0xffffffffu, r.left == 0);
 			if (idle == 0xffffffffu && drained)
 				break;
 			if (!drained && (idle == 0xffffffffu || __popc(idle) >= kRefillAt)) {
@@ -85,7 +160,7 @@ namespace {
 				const size_t end = n;
 				const size_t mine = (size_t)base + __popc(idle & ((1u << lane) - 1u));
 				drained = base + __popc(idle) >= n;
-				if (!active && mine < end) {
+				if (r.left == 0 && mine < end) {
 					const float v0x = v0s[mine * 3], v0y = v0s[mine * 3 + 1], v0z = v0s[mine * 3 + 2];
 					float dx = dirs[mine * 3], dy = dirs[mine * 3 + 1], dz = dirs[mine * 3 + 2];
 					// dir = dir.Normalize()  (Core/Math.h:369-374; GetLength = sqrtf(x*x + y*y + z*z))
@@ -101,6 +176,12 @@ namespace {
 						write_hit(out, mine, 1u | (1u << 8), v0x, v0y, v0z, ix, iy, iz, 0, 0, 0);
 					} else if (maxSteps <= 0) { // the loop never runs: hit = false, hitPos = v0, rest untouched (:503-506)
 						write_hit(out, mine, 0u, v0x, v0y, v0z, 0, 0, 0, 0, 0, 0);
+					} else if (dx != dx || dy != dy || dz != dz) {
+						cast_ray_generic(solid, out, mine, v0x, v0y, v0z, dx, dy, dz, ix, iy, iz, col, maxSteps);
+					} else if (dx == 0.f && dy == 0.f && dz == 0.f) {
+						// no axis to cross: every one of the maxSteps iterations stays in the (empty) start cell with
+						// t = 0 and the zero normal (:432-446 take no branch), then hit = false, hitPos = v0 (:503-506)
+						write_hit(out, mine, 0u, v0x, v0y, v0z, ix, iy, iz, 0, 0, 0);
 					} else {
 						const bool px = dx > 0.f, py = dy > 0.f, pz = dz > 0.f;
 						r.fx = px ? __fsub_rn((float)(ix + 1), v0x) : __fsub_rn(v0x, (float)ix);
@@ -112,57 +193,52 @@ namespace {
 						r.invX = dx != 0.f ? __fdiv_rn(1.f, r.ax) : dx;
 						r.invY = dy != 0.f ? __fdiv_rn(1.f, r.ay) : dy;
 						r.invZ = dz != 0.f ? __fdiv_rn(1.f, r.az) : dz;
+						// hasX = invX != 0 (:417): a NaN component counts as present, like there
+						r.bX = r.invX != 0.f ? 0.f : kInf;
+						r.bY = r.invY != 0.f ? 0.f : kInf;
+						r.bZ = r.invZ != 0.f ? 0.f : kInf;
 						r.sign = (px ? 1u : 0u) | (py ? 2u : 0u) | (pz ? 4u : 0u);
 						r.ix = ix;
 						r.iy = iy;
 						r.iz = iz;
 						r.col = col;
-						r.steps = 0;
-						r.axis = 0;
+						r.left = maxSteps;
 						r.ray = mine;
-						active = true;
 					}
 				}
 			}
 			// ---- a few DDA steps between idle checks (:413-497) ----
 #pragma unroll 1
-			for (int k = 0; k < 4; k++) {
-				if (active) {
-					const bool hasX = r.invX != 0.f, hasY = r.invY != 0.f, hasZ = r.invZ != 0.f;
-					int axis = 0;
-					float t = 0.f;
-					const float tx = __fmul_rn(r.fx, r.invX), ty = __fmul_rn(r.fy, r.invY), tz = __fmul_rn(r.fz, r.invZ);
-					if (hasX) {
-						t = tx;
-						axis = 1;
-					}
-					if (hasY && (!axis || ty < t)) {
-						t = ty;
-						axis = 2;
-					}
-					if (hasZ && (!axis || tz < t)) {
-						t = tz;
-						axis = 3;
-					}
+			for (int k = 0; k < kStepsPerCheck; k++) {
+				if (r.left != 0) {
+					// the nearest boundary: X unless Y is strictly nearer, then Z if strictly nearer still (:432-446)
+					const float tx = __fmaf_rn(r.fx, r.invX, r.bX), ty = __fmaf_rn(r.fy, r.invY, r.bY),
+					            tz = __fmaf_rn(r.fz, r.invZ, r.bZ);
+					const bool useY = ty < tx;
+					float t = useY ? ty : tx;
+					const bool isZ = tz < t;
+					t = isZ ? tz : t;
+					const bool isX = !useY && !isZ, isY = useY && !isZ;
 					const float nfx = __fsub_rn(r.fx, __fmul_rn(r.ax, t));
 					const float nfy = __fsub_rn(r.fy, __fmul_rn(r.ay, t));
 					const float nfz = __fsub_rn(r.fz, __fmul_rn(r.az, t));
-					r.fx = axis == 1 ? 1.f : nfx;
-					r.fy = axis == 2 ? 1.f : nfy;
-					r.fz = axis == 3 ? 1.f : nfz;
-					r.ix += axis == 1 ? ((r.sign & 1u) ? 1 : -1) : 0;
-					r.iy += axis == 2 ? ((r.sign & 2u) ? 1 : -1) : 0;
-					r.iz += axis == 3 ? ((r.sign & 4u) ? 1 : -1) : 0;
-					r.axis = axis;
-					r.steps++;
-					if (axis == 1 || axis == 2)
+					r.fx = isX ? 1.f : nfx;
+					r.fy = isY ? 1.f : nfy;
+					r.fz = isZ ? 1.f : nfz;
+					const int sx = (int)((r.sign << 1) & 2u) - 1, sy = (int)(r.sign & 2u) - 1, sz = (int)((r.sign >> 1) & 2u) - 1;
+					r.ix += isX ? sx : 0;
+					r.iy += isY ? sy : 0;
+					r.iz += isZ ? sz : 0;
+					r.left--;
+					if (!isZ)
 						r.col = solid[osb::tiled_index(r.ix & 511, r.iy & 511)];
-					const bool hit = solid_at(r.col, r.iz);
-					if (hit || r.steps >= maxSteps) {
-						// normal = iv - next = minus the step just taken; a zero-axis step (all components 0) moves nowhere
-						const int nx = axis == 1 ? ((r.sign & 1u) ? -1 : 1) : 0;
-						const int ny = axis == 2 ? ((r.sign & 2u) ? -1 : 1) : 0;
-						const int nz = axis == 3 ? ((r.sign & 4u) ? -1 : 1) : 0;
+					// IsSolidWrapped (GameMap.h:91-98) as one bit: bit z of the column, 0 above the map, 1 below it
+					uint32_t bit = (uint32_t)(r.col >> (r.iz & 63));
+					bit = (uint32_t)r.iz < 64u ? bit : ~((uint32_t)r.iz >> 31);
+					const bool hit = (bit & 1u) != 0u;
+					if (hit || r.left == 0) {
+						// normal = iv - next = minus the step just taken
+						const int nx = isX ? -sx : 0, ny = isY ? -sy : 0, nz = isZ ? -sz : 0;
 						float hx, hy, hz;
 						if (hit) {
 							hx = (r.sign & 1u) ? __fsub_rn((float)(r.ix + 1), r.fx) : __fadd_rn((float)r.ix, r.fx);
@@ -174,7 +250,7 @@ namespace {
 							hz = v0s[r.ray * 3 + 2];
 						}
 						write_hit(out, r.ray, hit ? 1u : 0u, hx, hy, hz, r.ix, r.iy, r.iz, nx, ny, nz);
-						active = false;
+						r.left = 0;
 					}
 				}
 			}
@@ -211,12 +287,219 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	return 0;
 }
 
-// Host-buffer entry point.  The batch is cut into chunks of kPipeRays rays that flow through three stages on three
-// streams -- H2D of chunk k+1, the kernel of chunk k, D2H of chunk k-1 -- over a ring of kPipeSlots device slots, so the
-// call runs at the speed of the slower PCIe direction (40 B/ray out) instead of copy + kernel + copy in series.
-// With pinned host buffers every copy is truly asynchronous; with pageable buffers the driver stages each copy and
-// blocks the host meanwhile, so the issue order below (upload and launch chunk k+1 BEFORE downloading chunk k) is
-// what keeps the GPU busy during the download.
+// Host-buffer entry point.  The batch is cut into chunks that flow through three stages on three streams -- H2D of
+// chunk k+1, the kernel of chunk k, D2H of chunk k-1 -- over a ring of kPipeSlots device slots, so the call runs at the
+// speed of the slower PCIe direction (40 B/ray out) instead of copy + kernel + copy in series.
+//   pinned caller buffers    (cudaHostAlloc / cudaHostRegister memory): chunks of kPipeRays rays are copied straight
+//                            between the caller's arrays and the device slots, every copy truly asynchronous;
+//   pageable caller buffers  (what the reference's callers hold: std::vector, the stack): a cudaMemcpyAsync from
+//                            pageable memory is staged by the driver on the calling thread at a few GB/s and blocks
+//                            it meanwhile.  Here a few host threads move the data through a pinned ring instead: every
+//                            thread copies its stripe of chunk k+1 into the ring, the last one to finish enqueues that
+//                            chunk's H2D + kernel + D2H, and every thread then copies its stripe of chunk k's results
+//                            out of the ring -- host copies, PCIe in, kernel and PCIe out all overlap.
+namespace {
+	bool is_pinned(const void *p) {
+		cudaPointerAttributes a;
+		if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+			cudaGetLastError(); // pageable memory: older runtimes report an error instead of "unregistered"
+			return false;
+		}
+		return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+	}
+	int copy_threads() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_COPY_THREADS");
+			int n = e ? atoi(e) : 0;
+			if (n <= 0) {
+				const unsigned hw = std::thread::hardware_concurrency();
+				n = hw >= 16 ? 6 : (hw >= 8 ? 4 : (hw >= 4 ? 2 : 1));
+			}
+			return n > 16 ? 16 : n;
+		}();
+		return v;
+	}
+
+	int castray2_pinned(osb200_ctx *c, osb::RayPipe *P, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
+	                    size_t n) {
+		const size_t chunk = osb::kPipeRays;
+		const size_t inPad = (chunk * 12 + 255) & ~(size_t)255, outPad = (chunk * sizeof(osb200_rayhit) + 255) & ~(size_t)255;
+		const size_t slotBytes = 2 * inPad + outPad;
+		if (c->ensure_scratch(slotBytes * osb::kPipeSlots))
+			return -2;
+		char *base = reinterpret_cast<char *>(c->d_scratch);
+		const size_t nChunks = (n + chunk - 1) / chunk;
+		// the scratch area may still be read by earlier work of the context stream
+		OSB_CUDA(cudaEventRecord(P->computed[0], c->stream));
+		OSB_CUDA(cudaStreamWaitEvent(P->in, P->computed[0], 0));
+		auto upload = [&](size_t k) -> int {
+			const int s = (int)(k % osb::kPipeSlots);
+			const size_t lo = k * chunk, m = std::min(chunk, n - lo);
+			char *p = base + slotBytes * s;
+			if (k >= (size_t)osb::kPipeSlots) // the slot's previous results must have left the device
+				OSB_CUDA(cudaStreamWaitEvent(P->in, P->downloaded[s], 0));
+			OSB_CUDA(cudaMemcpyAsync(p, v0 + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
+			OSB_CUDA(cudaMemcpyAsync(p + inPad, dir + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
+			OSB_CUDA(cudaEventRecord(P->uploaded[s], P->in));
+			OSB_CUDA(cudaStreamWaitEvent(c->stream, P->uploaded[s], 0));
+			int rc = osb200_castray2_device(c, reinterpret_cast<float *>(p), reinterpret_cast<float *>(p + inPad), maxSteps,
+			                                reinterpret_cast<osb200_rayhit *>(p + 2 * inPad), m);
+			if (rc)
+				return rc;
+			OSB_CUDA(cudaEventRecord(P->computed[s], c->stream));
+			return 0;
+		};
+		auto download = [&](size_t k) -> int {
+			const int s = (int)(k % osb::kPipeSlots);
+			const size_t lo = k * chunk, m = std::min(chunk, n - lo);
+			char *p = base + slotBytes * s;
+			OSB_CUDA(cudaStreamWaitEvent(P->out, P->computed[s], 0));
+			OSB_CUDA(cudaMemcpyAsync(out + lo, p + 2 * inPad, m * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, P->out));
+			OSB_CUDA(cudaEventRecord(P->downloaded[s], P->out));
+			return 0;
+		};
+		if (int rc = upload(0))
+			return rc;
+		for (size_t k = 0; k < nChunks; k++) {
+			if (k + 1 < nChunks)
+				if (int rc = upload(k + 1))
+					return rc;
+			if (int rc = download(k))
+				return rc;
+		}
+		OSB_CUDA(cudaStreamSynchronize(P->out));
+		// later work on the context stream must not overwrite the scratch area before the last download has read it
+		OSB_CUDA(cudaStreamWaitEvent(c->stream, P->downloaded[(nChunks - 1) % osb::kPipeSlots], 0));
+		return 0;
+	}
+
+	int castray2_staged(osb200_ctx *c, osb::RayPipe *P, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
+	                    size_t n) {
+		const size_t chunk = osb::kStagedRays;
+		const size_t inPad = (chunk * 12 + 255) & ~(size_t)255, outPad = (chunk * sizeof(osb200_rayhit) + 255) & ~(size_t)255;
+		const size_t slotBytes = 2 * inPad + outPad;
+		if (c->ensure_scratch(slotBytes * osb::kPipeSlots))
+			return -2;
+		if (P->h_ring_bytes < slotBytes * osb::kPipeSlots) {
+			if (P->h_ring)
+				cudaFreeHost(P->h_ring);
+			P->h_ring = nullptr;
+			P->h_ring_bytes = 0;
+			OSB_CUDA(cudaHostAlloc(&P->h_ring, slotBytes * osb::kPipeSlots, cudaHostAllocDefault));
+			P->h_ring_bytes = slotBytes * osb::kPipeSlots;
+		}
+		char *dBase = reinterpret_cast<char *>(c->d_scratch);
+		char *hBase = reinterpret_cast<char *>(P->h_ring);
+		const size_t nChunks = (n + chunk - 1) / chunk;
+		const int T = (int)std::min<size_t>((size_t)copy_threads(), std::max<size_t>(1, n >> 14));
+		OSB_CUDA(cudaEventRecord(P->computed[0], c->stream));
+		OSB_CUDA(cudaStreamWaitEvent(P->in, P->computed[0], 0));
+
+		std::vector<std::atomic<int>> arrived(nChunks);
+		for (auto &a : arrived)
+			a.store(0, std::memory_order_relaxed);
+		std::atomic<size_t> launched{0}; // chunks whose GPU work has been enqueued
+		std::atomic<int> failed{0};
+		std::string failText;
+		std::mutex failLock;
+
+		// enqueue chunk k: ring -> device, kernel, device -> ring (called by exactly one thread per chunk, in chunk order)
+		auto launch = [&](size_t k) -> int {
+			const int s = (int)(k % osb::kPipeSlots);
+			const size_t m = std::min(chunk, n - k * chunk);
+			char *d = dBase + slotBytes * s, *h = hBase + slotBytes * s;
+			if (k >= (size_t)osb::kPipeSlots)
+				OSB_CUDA(cudaStreamWaitEvent(P->in, P->downloaded[s], 0));
+			OSB_CUDA(cudaMemcpyAsync(d, h, m * 12, cudaMemcpyHostToDevice, P->in));
+			OSB_CUDA(cudaMemcpyAsync(d + inPad, h + inPad, m * 12, cudaMemcpyHostToDevice, P->in));
+			OSB_CUDA(cudaEventRecord(P->uploaded[s], P->in));
+			OSB_CUDA(cudaStreamWaitEvent(c->stream, P->uploaded[s], 0));
+			int rc = osb200_castray2_device(c, reinterpret_cast<float *>(d), reinterpret_cast<float *>(d + inPad), maxSteps,
+			                                reinterpret_cast<osb200_rayhit *>(d + 2 * inPad), m);
+			if (rc)
+				return rc;
+			OSB_CUDA(cudaEventRecord(P->computed[s], c->stream));
+			OSB_CUDA(cudaStreamWaitEvent(P->out, P->computed[s], 0));
+			OSB_CUDA(cudaMemcpyAsync(h + 2 * inPad, d + 2 * inPad, m * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, P->out));
+			OSB_CUDA(cudaEventRecord(P->downloaded[s], P->out));
+			return 0;
+		};
+		auto fail = [&](int rc) {
+			std::lock_guard<std::mutex> g(failLock);
+			if (!failed.load()) {
+				failText = osb200_last_error();
+				failed.store(rc ? rc : -2);
+			}
+		};
+		// bytes [lo, hi) of a chunk-sized copy that thread t of T moves (64-byte granules)
+		auto stripe = [&](size_t bytes, int t, size_t &lo, size_t &hi) {
+			const size_t g = (bytes + 63) / 64;
+			lo = std::min(bytes, (g * (size_t)t / (size_t)T) * 64);
+			hi = std::min(bytes, (g * (size_t)(t + 1) / (size_t)T) * 64);
+		};
+		auto worker = [&](int t) {
+			if (cudaSetDevice(c->device) != cudaSuccess) {
+				fail(-2);
+				return;
+			}
+			auto copy_out = [&](size_t k) -> bool {
+				while (launched.load(std::memory_order_acquire) <= k) { // its events must have been recorded first
+					if (failed.load())
+						return false;
+					std::this_thread::yield();
+				}
+				const int s = (int)(k % osb::kPipeSlots);
+				if (cudaEventSynchronize(P->downloaded[s]) != cudaSuccess) {
+					osb::set_error("osb200_castray2: waiting for chunk %zu failed: %s", k, cudaGetErrorString(cudaGetLastError()));
+					fail(-2);
+					return false;
+				}
+				const size_t m = std::min(chunk, n - k * chunk);
+				size_t lo, hi;
+				stripe(m * sizeof(osb200_rayhit), t, lo, hi);
+				memcpy(reinterpret_cast<char *>(out + k * chunk) + lo, hBase + slotBytes * s + 2 * inPad + lo, hi - lo);
+				return true;
+			};
+			for (size_t k = 0; k < nChunks; k++) {
+				if (failed.load())
+					return;
+				// the ring slot is free: this thread copied chunk k - kPipeSlots out of it in an earlier iteration, and
+				// the chunk's H2D had finished long before its results came back
+				const int s = (int)(k % osb::kPipeSlots);
+				const size_t m = std::min(chunk, n - k * chunk);
+				size_t lo, hi;
+				stripe(m * 12, t, lo, hi);
+				char *h = hBase + slotBytes * s;
+				memcpy(h + lo, reinterpret_cast<const char *>(v0 + k * chunk * 3) + lo, hi - lo);
+				memcpy(h + inPad + lo, reinterpret_cast<const char *>(dir + k * chunk * 3) + lo, hi - lo);
+				if (arrived[k].fetch_add(1, std::memory_order_acq_rel) == T - 1) { // the last stripe of the chunk is in
+					if (int rc = launch(k)) {
+						fail(rc);
+						return;
+					}
+					launched.store(k + 1, std::memory_order_release);
+				}
+				if (k >= 1 && !copy_out(k - 1))
+					return;
+			}
+			copy_out(nChunks - 1);
+		};
+		std::vector<std::thread> pool;
+		for (int t = 1; t < T; t++)
+			pool.emplace_back(worker, t);
+		worker(0);
+		for (auto &th : pool)
+			th.join();
+		if (int rc = failed.load()) {
+			osb::set_error("%s", failText.c_str());
+			cudaStreamSynchronize(P->out);
+			return rc;
+		}
+		OSB_CUDA(cudaStreamWaitEvent(c->stream, P->downloaded[(nChunks - 1) % osb::kPipeSlots], 0));
+		return 0;
+	}
+} // namespace
+
 int osb200_castray2(osb200_ctx *c, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out,
                     size_t n) {
 	if (!c || !c->mapLoaded) {
@@ -241,56 +524,10 @@ int osb200_castray2(osb200_ctx *c, const float *v0, const float *dir, int maxSte
 			OSB_CUDA(cudaEventCreateWithFlags(&P->downloaded[i], cudaEventDisableTiming));
 		}
 	}
-	osb::RayPipe *P = c->rayPipe;
-	const size_t chunk = osb::kPipeRays;
-	const size_t inPad = (chunk * 12 + 255) & ~(size_t)255, outPad = (chunk * sizeof(osb200_rayhit) + 255) & ~(size_t)255;
-	const size_t slotBytes = 2 * inPad + outPad;
-	if (c->ensure_scratch(slotBytes * osb::kPipeSlots))
-		return -2;
-	char *base = reinterpret_cast<char *>(c->d_scratch);
-	const size_t nChunks = (n + chunk - 1) / chunk;
-	// the scratch area may still be read by earlier work of the context stream
-	OSB_CUDA(cudaEventRecord(P->computed[0], c->stream));
-	OSB_CUDA(cudaStreamWaitEvent(P->in, P->computed[0], 0));
-	auto upload = [&](size_t k) -> int {
-		const int s = (int)(k % osb::kPipeSlots);
-		const size_t lo = k * chunk, m = std::min(chunk, n - lo);
-		char *p = base + slotBytes * s;
-		if (k >= (size_t)osb::kPipeSlots) // the slot's previous results must have left the device
-			OSB_CUDA(cudaStreamWaitEvent(P->in, P->downloaded[s], 0));
-		OSB_CUDA(cudaMemcpyAsync(p, v0 + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
-		OSB_CUDA(cudaMemcpyAsync(p + inPad, dir + lo * 3, m * 12, cudaMemcpyHostToDevice, P->in));
-		OSB_CUDA(cudaEventRecord(P->uploaded[s], P->in));
-		OSB_CUDA(cudaStreamWaitEvent(c->stream, P->uploaded[s], 0));
-		int rc = osb200_castray2_device(c, reinterpret_cast<float *>(p), reinterpret_cast<float *>(p + inPad), maxSteps,
-		                                reinterpret_cast<osb200_rayhit *>(p + 2 * inPad), m);
-		if (rc)
-			return rc;
-		OSB_CUDA(cudaEventRecord(P->computed[s], c->stream));
-		return 0;
-	};
-	auto download = [&](size_t k) -> int {
-		const int s = (int)(k % osb::kPipeSlots);
-		const size_t lo = k * chunk, m = std::min(chunk, n - lo);
-		char *p = base + slotBytes * s;
-		OSB_CUDA(cudaStreamWaitEvent(P->out, P->computed[s], 0));
-		OSB_CUDA(cudaMemcpyAsync(out + lo, p + 2 * inPad, m * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, P->out));
-		OSB_CUDA(cudaEventRecord(P->downloaded[s], P->out));
-		return 0;
-	};
-	if (int rc = upload(0))
-		return rc;
-	for (size_t k = 0; k < nChunks; k++) {
-		if (k + 1 < nChunks)
-			if (int rc = upload(k + 1))
-				return rc;
-		if (int rc = download(k))
-			return rc;
-	}
-	OSB_CUDA(cudaStreamSynchronize(P->out));
-	// later work on the context stream must not overwrite the scratch area before the last download has read it
-	OSB_CUDA(cudaStreamWaitEvent(c->stream, P->downloaded[(nChunks - 1) % osb::kPipeSlots], 0));
-	return 0;
+	// a small batch is one chunk either way: the driver's own staging is as good and needs no threads
+	const bool direct = n <= ((size_t)1 << 15) || (is_pinned(v0) && is_pinned(dir) && is_pinned(out));
+	return direct ? castray2_pinned(c, c->rayPipe, v0, dir, maxSteps, out, n)
+	              : castray2_staged(c, c->rayPipe, v0, dir, maxSteps, out, n);
 }
 
 } // extern "C"

@@ -61,9 +61,12 @@ namespace osb {
 	// osb200_castray2's chunk pipeline (castray2.cu)
 	constexpr int kPipeSlots = 3;
 	constexpr size_t kPipeRays = (size_t)1 << 20; // rays per chunk: 64 MB per slot
+	constexpr size_t kStagedRays = (size_t)1 << 18; // rays per chunk when the caller's buffers are pageable: 16 MB per slot
 	struct RayPipe {
 		cudaStream_t in = nullptr, out = nullptr;
 		cudaEvent_t uploaded[kPipeSlots] = {}, computed[kPipeSlots] = {}, downloaded[kPipeSlots] = {};
+		void *h_ring = nullptr; // pinned staging ring of the pageable path (kPipeSlots slots of kStagedRays rays)
+		size_t h_ring_bytes = 0;
 	};
 	struct TerrainState;   // terrain.cu
 	struct RadiosityState; // radiosity.cu

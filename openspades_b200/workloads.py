@@ -87,13 +87,16 @@ def random_rays(n, seed=1234, zmax=62.0):
 
 def edge_rays():
     """Axis-aligned directions, zero components, origins on integer boundaries, rays leaving through
-    z < 0 and z >= 64, x/y wrap, tiny and huge directions."""
+    z < 0 and z >= 64, x/y wrap, tiny and huge directions, zero / underflowing / infinite / NaN directions."""
     v0, d = [], []
     origins = [(10.0, 20.0, 5.0), (0.0, 0.0, 0.0), (511.999, 511.999, 1.5), (256.5, 256.5, 0.25), (100.0, 200.5, 30.0),
                (-3.5, 700.25, 10.5), (511.5, 0.5, -2.5), (12.25, 13.75, 62.9), (300.0, 300.0, 63.5), (5.5, 5.5, 70.0)]
     dirs = [(1, 0, 0), (-1, 0, 0), (0, 1, 0), (0, -1, 0), (0, 0, 1), (0, 0, -1), (1, 1, 0), (1, -1, 0), (0, 1, 1),
             (1, 0, -1), (1, 1, 1), (-1, -1, -1), (1e-3, 1, 0), (1, 1e-6, 1e-6), (1e-20, 1e-20, 1), (3e5, -2e5, 1e4),
-            (-0.0, 1, 0), (0.5, 0.25, -0.125), (1, 2, 3), (-3, 2, -1)]
+            (-0.0, 1, 0), (0.5, 0.25, -0.125), (1, 2, 3), (-3, 2, -1),
+            # no direction at all (never moves), a length that underflows to 0, infinite / NaN components
+            (0, 0, 0), (1e-30, -1e-30, 1e-30), (float("inf"), 1, 0), (float("nan"), 1, 0), (0, float("nan"), 1),
+            (0, 1, float("-inf")), (1, float("nan"), float("nan"))]
     for o in origins:
         for dd in dirs:
             v0.append(o)

@@ -249,7 +249,9 @@ namespace {
 	// step together until the last one ends.  Reports where lanes idle: out[0] warp-steps, [1] lane-steps, [2] sum over
 	// warp-steps of the MAX span candidates of a lane (= iterations of the span loop), [3] sum of candidates, [4] warp-level
 	// fill events (iterations with >= 1 landing lane) approximated per step by max landing words, [5] landing words,
-	// [6] sum of max stored pixels, [7] stored pixels, [8] tasks, [9] lines.
+	// [6] sum of max stored pixels, [7] stored pixels, [8] tasks, [9] lines.  For a candidate-at-a-time loop (each lane
+	// either processes one candidate or, having none, takes its next DDA step): [10] sum over tasks of the MAX over lanes
+	// of the lane's iterations (sum over its steps of max(1, candidates)), [11] sum over lanes of the same.
 	template <bool kSse, bool kSse2> void warp_model(WalkIO wio, const osbn::Num<kSse> &num, const std::vector<ViewParams> &views,
 	                                                 const std::vector<LineRec> &recs, const std::vector<uint32_t> &active,
 	                                                 unsigned long long *out) {
@@ -263,6 +265,7 @@ namespace {
 			std::vector<LineWalker<kSse, kSse2>> W(n);
 			std::vector<std::vector<uint32_t>> filled(n, std::vector<uint32_t>(128 + kWalkExtraWords));
 			std::vector<char> alive(n, 1);
+			std::vector<unsigned long long> iters(n, 0);
 			for (int i = 0; i < n; i++)
 				W[i].init(wio, active[a + i], (uint32_t)(a + i), filled[i].data(), 1);
 			out[8]++;
@@ -277,6 +280,7 @@ namespace {
 					lanes++;
 					maxC = std::max(maxC, g_stat[0]);
 					sumC += g_stat[0];
+					iters[i] += std::max(1u, g_stat[0]);
 					maxW = std::max(maxW, g_stat[1]);
 					sumW += g_stat[1];
 					maxP = std::max(maxP, g_stat[2]);
@@ -293,6 +297,12 @@ namespace {
 				out[6] += maxP;
 				out[7] += sumP;
 			}
+			unsigned long long mx = 0;
+			for (int i = 0; i < n; i++) {
+				mx = std::max(mx, iters[i]);
+				out[11] += iters[i];
+			}
+			out[10] += mx;
 			a = b;
 		}
 	}
@@ -360,7 +370,7 @@ __attribute__((visibility("default"))) int emul_warp_model(const uint64_t *solid
 			std::memcpy(&colorT[(size_t)t * 64], &color[((size_t)x * 512 + y) * 64], 64 * 4);
 		}
 	const float fog[3] = {0.8f, 1.f, 1.f};
-	for (int i = 0; i < 10; i++)
+	for (int i = 0; i < 12; i++)
 		out[i] = 0;
 	return run<true, true>(solidT.data(), colorT.data(), scenes, nViews, w, h, fog, 128.f, 4, 1, 0, 0, nullptr, nullptr, nullptr, out);
 }

@@ -62,13 +62,32 @@ def test_castray2_title_bit_exact(ctx, port, title_map, max_steps):
 
 def test_castray2_edges_and_ragged(ctx, port, title_map):
     ctx.map_upload(title_map.solid, title_map.color)
-    v0, d = workloads.edge_rays()
-    keep = np.any(d != 0, axis=1)
-    v0, d = v0[keep], d[keep]
+    v0, d = workloads.edge_rays()  # includes zero, underflowing, infinite and NaN directions
     for n in (0, 1, 31, 33, 255, 257, len(v0)):
         got = ctx.castray2(v0[:n], d[:n], 300)
         want = port.castray2(title_map.solid.copy(), v0[:n], d[:n], 300)
         assert _same(got, want), n
+
+
+def test_castray2_pageable_and_pinned_paths_agree(ctx, port, title_map):
+    """osb200_castray2 moves pageable caller buffers through a pinned ring with a few host threads and pinned ones
+    directly; both must return the same records (ragged sizes: not a multiple of either chunk size)."""
+    import torch
+    ctx.map_upload(title_map.solid, title_map.color)
+    n = (1 << 20) + 12345
+    v0, d = workloads.random_rays(n, seed=77)
+    ev0, ed = workloads.edge_rays()
+    v0[1000:1000 + len(ev0)], d[1000:1000 + len(ed)] = ev0, ed
+    pageable = ctx.castray2(v0, d, 200)
+    pv0, pd = torch.from_numpy(v0).pin_memory(), torch.from_numpy(d).pin_memory()
+    pout = torch.zeros(n * 40, dtype=torch.uint8).pin_memory()
+    ctx.castray2(pv0, pd, 200, out=pout)
+    pinned = pout.numpy().view(pageable.dtype)
+    assert pageable.tobytes() == pinned.tobytes()
+    k = 1 << 18
+    lo = n - k
+    assert _same(pageable[lo:], port.castray2(title_map.solid.copy(), v0[lo:], d[lo:], 200, threads=8))
+    assert _same(pageable[:k], port.castray2(title_map.solid.copy(), v0[:k], d[:k], 200, threads=8))
 
 
 def test_castray2_synthetic_and_edit(ctx, port):
