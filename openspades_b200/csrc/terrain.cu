@@ -30,6 +30,19 @@ namespace osb {
 
 	// lower bound of lanes per warp for small k_walk_lines launches (OSB200_LINE_MIN_LANES, default 4; 32 = off).
 	// One 1080p frame (3.8 k lines) with the round-1 kernel: 32 / 16 / 8 / 4 / 2 lanes -> 0.338 / 0.285 / 0.240 / 0.207 / 0.203 ms
+	// OSB200_TASK_ORDER=1: walker tasks queued by estimated length, longest first (predict_steps, 16 queues) instead of
+	// view order.  A list-scheduling model of the launch (tests/native: emul_task_costs) puts view order 10.6 % above the
+	// ideal makespan and this order 2.9 % above it; on the B200 it is SLOWER (k_walk_lines 2.35 -> 2.59 ms per 4096
+	// views, profiles/r02_ab_task_order.json): a view's neighbouring tasks no longer run side by side and stop sharing
+	// their map columns and colours in L1 / L2, and the tail the model charges in full is mostly absorbed by the
+	// remaining warps issuing faster.  Off by default; kept as the measured answer.
+	static int task_order() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_TASK_ORDER");
+			return e ? atoi(e) : 0;
+		}();
+		return v;
+	}
 	static int line_min_lanes() {
 		static const int v = [] {
 			const char *e = getenv("OSB200_LINE_MIN_LANES");
@@ -47,7 +60,9 @@ namespace osb {
 		uint32_t *d_active = nullptr;   // strip slot -> line: the surviving lines of every view, compacted in yaw order
 		uint32_t *d_liveBits = nullptr; // per view, per 32 lines: ballot of the lines that survived the pitch cull
 		uint32_t *d_tasks = nullptr;    // walker tasks: (first slot << 5) | (lines - 1)
-		uint32_t *d_counters = nullptr; // [0] number of tasks, [1] work cursor of k_walk_lines
+		uint32_t *d_counters = nullptr; // [0] number of tasks, [1] work cursor of k_walk_lines, [2..] fill + cursor per task queue
+		uint32_t *d_bucketTasks = nullptr; // kTaskBuckets queues of bucketCap walker tasks (ordered mode)
+		size_t bucketTaskCap = 0;
 		uint2 *d_strips = nullptr;
 		uint32_t *d_lineMask = nullptr; // lineRes bits per strip slot: strip pixels the line wrote
 		float *d_tabs = nullptr;
@@ -85,6 +100,7 @@ namespace osb {
 	constexpr int kWalkThreads = OSB_WALK_THREADS; // lanes (= lines in flight) per CTA of k_walk_lines
 	constexpr int kSetupThreads = 128;
 	constexpr int kMinTaskLines = 1; // smallest walker task (OSB200_LINE_MIN_LANES)
+	constexpr int kCounterWords = 2 + 2 * kTaskBuckets;
 
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
 	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs, float *tabs) {
@@ -141,10 +157,15 @@ namespace osb {
 	__global__ void __launch_bounds__(kCompactThreads)
 	  k_line_compact(const ViewParams *__restrict__ views, const float2 *__restrict__ lineTan, const uint32_t *__restrict__ liveBits,
 	                 int wordsPerView, int taskLines, LineRec *__restrict__ lineRecs, uint32_t *__restrict__ active,
-	                 uint32_t *__restrict__ tasks, uint32_t *__restrict__ counters) {
+	                 uint32_t *__restrict__ tasks, uint32_t *__restrict__ counters, const float2 *__restrict__ lineDirs, int lineRes,
+	                 uint32_t *__restrict__ bucketTasks, uint32_t bucketCap) {
 		__shared__ uint32_t s_prefix[kMaxLineWords]; // exclusive prefix of the survivor counts per 32-line word
 		__shared__ uint32_t s_warpSum[kCompactThreads / 32];
 		__shared__ uint32_t s_base, s_taskBase;
+		// ordered mode (bucketTasks != nullptr, tasks of 32 lines): longest estimated line per task, bucket fill counts
+		__shared__ int s_taskSteps[kMaxLineWords];
+		__shared__ uint32_t s_hist[kTaskBuckets], s_bucketBase[kTaskBuckets];
+		const bool ordered = bucketTasks != nullptr;
 		const int vi = blockIdx.x;
 		const ViewParams &V = views[vi];
 		const int nWords = (V.numLines + 31) >> 5;
@@ -177,6 +198,13 @@ namespace osb {
 			__syncthreads();
 		}
 		const uint32_t nLive = s_base;
+		if (ordered) {
+			for (int i = threadIdx.x; i < nWords; i += kCompactThreads)
+				s_taskSteps[i] = 0;
+			if (threadIdx.x < kTaskBuckets)
+				s_hist[threadIdx.x] = 0;
+			__syncthreads();
+		}
 		for (int j = wid; j < nWords; j += kCompactThreads / 32) { // one warp per word: lane = line
 			const uint32_t b = bits[j];
 			const int l = (j << 5) + lane;
@@ -190,8 +218,11 @@ namespace osb {
 			o.culled = !((b >> lane) & 1u);
 			int slot = -1;
 			if (!o.culled) {
-				slot = (int)(V.lineBase + s_prefix[j] + (uint32_t)__popc(b & ((1u << lane) - 1u)));
+				const uint32_t rank = s_prefix[j] + (uint32_t)__popc(b & ((1u << lane) - 1u));
+				slot = (int)(V.lineBase + rank);
 				active[slot] = gl;
+				if (ordered)
+					atomicMax(&s_taskSteps[rank >> 5], (int)predict_steps(tn.x, tn.y, lineRes, V.origin[2], lineDirs[gl]));
 			}
 			// (a culled line never reaches the walker: its record carries the empty hull from the start)
 			lineRecs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : vi);
@@ -200,10 +231,39 @@ namespace osb {
 		if (threadIdx.x == 0)
 			s_taskBase = nTasks ? atomicAdd(counters, nTasks) : 0u;
 		__syncthreads();
-		for (uint32_t i = threadIdx.x; i < nTasks; i += kCompactThreads) {
-			const uint32_t first = i * (uint32_t)taskLines;
-			const uint32_t n = min((uint32_t)taskLines, nLive - first);
-			tasks[s_taskBase + i] = ((V.lineBase + first) << 5) | (n - 1u); // slot of the first line, lines - 1
+		if (!ordered) {
+			for (uint32_t i = threadIdx.x; i < nTasks; i += kCompactThreads) {
+				const uint32_t first = i * (uint32_t)taskLines;
+				const uint32_t n = min((uint32_t)taskLines, nLive - first);
+				tasks[s_taskBase + i] = ((V.lineBase + first) << 5) | (n - 1u); // slot of the first line, lines - 1
+			}
+			return;
+		}
+		// ordered: the view's tasks go into the batch-wide queues by estimated length (one global atomic per non-empty
+		// bucket per view)
+		for (uint32_t i0 = 0; i0 < nTasks; i0 += kCompactThreads) { // nTasks <= 2048: a few rounds at most
+			const uint32_t i = i0 + threadIdx.x;
+			int bkt = 0;
+			uint32_t pos = 0;
+			if (i < nTasks) {
+				bkt = task_bucket((float)s_taskSteps[i]);
+				pos = atomicAdd(&s_hist[bkt], 1u);
+			}
+			__syncthreads();
+			if (threadIdx.x < kTaskBuckets) {
+				const uint32_t cnt = s_hist[threadIdx.x];
+				s_bucketBase[threadIdx.x] = cnt ? atomicAdd(counters + 2 + threadIdx.x, cnt) : 0u;
+			}
+			__syncthreads();
+			if (i < nTasks) {
+				const uint32_t first = i * 32u;
+				const uint32_t n = min(32u, nLive - first);
+				bucketTasks[(size_t)bkt * bucketCap + s_bucketBase[bkt] + pos] = ((V.lineBase + first) << 5) | (n - 1u);
+			}
+			__syncthreads();
+			if (threadIdx.x < kTaskBuckets)
+				s_hist[threadIdx.x] = 0;
+			__syncthreads();
 		}
 	}
 
@@ -212,20 +272,40 @@ namespace osb {
 	template <bool kSse, bool kSse2Shade>
 	__global__ void __launch_bounds__(kWalkThreads, OSB_WALK_MINB)
 	  k_walk_lines(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, const uint32_t *__restrict__ tasks,
-	               uint32_t *__restrict__ counters) {
+	               uint32_t *__restrict__ counters, uint32_t bucketCap) {
 		extern __shared__ uint32_t s_filled[]; // (lineRes/32 + kWalkExtraWords) words x kWalkThreads, word-major: bank = lane
 		uint32_t *filled = s_filled + threadIdx.x;
 		const int lane = threadIdx.x & 31;
 		const osbn::Num<kSse> num{tabs};
 		const uint32_t nTasks = counters[0]; // written by k_line_compact, earlier on this stream
+		// bucketCap != 0: `tasks` holds kTaskBuckets queues of bucketCap entries, filled to counters[2 + b], taken from
+		// counters[2 + kTaskBuckets + b]; the warp drains the queue of the longest lines first (longest-processing-time
+		// order: the launch ends with short tasks, not with one warp in the middle of a 180-step line)
+		int bucket = kTaskBuckets - 1;
 		LineWalker<kSse, kSse2Shade> W;
 		for (;;) {
 			uint32_t t = 0;
-			if (lane == 0)
-				t = atomicAdd(counters + 1, 1u);
-			t = __shfl_sync(0xffffffffu, t, 0);
-			if (t >= nTasks)
-				break;
+			if (bucketCap) {
+				if (lane == 0) {
+					for (;;) {
+						t = atomicAdd(counters + 2 + kTaskBuckets + bucket, 1u);
+						if (t < counters[2 + bucket])
+							break;
+						if (--bucket < 0)
+							break;
+					}
+				}
+				bucket = __shfl_sync(0xffffffffu, bucket, 0);
+				if (bucket < 0)
+					break;
+				t = __shfl_sync(0xffffffffu, t, 0) + (uint32_t)bucket * bucketCap;
+			} else {
+				if (lane == 0)
+					t = atomicAdd(counters + 1, 1u);
+				t = __shfl_sync(0xffffffffu, t, 0);
+				if (t >= nTasks)
+					break;
+			}
 			const uint32_t task = __ldg(tasks + t);
 			const uint32_t slot = (task >> 5) + (uint32_t)lane;
 			bool alive = (uint32_t)lane <= (task & 31u);
@@ -408,6 +488,7 @@ namespace osb {
 			cudaFree(b.d_liveBits);
 			cudaFree(b.d_tasks);
 			cudaFree(b.d_counters);
+			cudaFree(b.d_bucketTasks);
 			cudaFree(b.d_strips);
 			cudaFree(b.d_lineMask);
 			cudaFree(b.d_tabs);
@@ -622,11 +703,12 @@ namespace osb {
 			    grow(B.d_lineRecs, B.recCap, maxLines) || grow(B.d_active, B.activeCap, maxLines) ||
 			    grow(B.d_liveBits, B.liveCap, maxViews * (size_t)maxWordsPerView) ||
 			    grow(B.d_tasks, B.taskCap, maxLines / kMinTaskLines + maxViews) ||
+			    grow(B.d_bucketTasks, B.bucketTaskCap, (size_t)kTaskBuckets * (maxLines / 32 + maxViews)) ||
 			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) ||
 			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)words) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
 				return -2;
 			if (!B.d_counters)
-				OSB_CUDA(cudaMalloc(&B.d_counters, 2 * sizeof(uint32_t)));
+				OSB_CUDA(cudaMalloc(&B.d_counters, kCounterWords * sizeof(uint32_t)));
 		}
 		OSB_CUDA(cudaMemcpyAsync(T->d_views, T->h_views, sizeof(ViewParams) * nViews, cudaMemcpyHostToDevice,
 		                         c->stream));
@@ -667,7 +749,7 @@ namespace osb {
 			int maxViewLines = 0;
 			for (int i = 0; i < nv; i++)
 				maxViewLines = std::max(maxViewLines, T->h_views[v0 + i].numLines);
-			OSB_CUDA(cudaMemsetAsync(B.d_counters, 0, 2 * sizeof(uint32_t), st));
+			OSB_CUDA(cudaMemsetAsync(B.d_counters, 0, kCounterWords * sizeof(uint32_t), st));
 			if (hostPrep) {
 				for (int i = 0; i < nv; i++) {
 					const ViewParams &V = T->h_views[v0 + i];
@@ -696,6 +778,9 @@ namespace osb {
 			const bool coop = coop_mode() == 1 || (coop_mode() < 0 && (size_t)totalLines < (size_t)c->smCount * 64);
 			if (coop)
 				taskLines = 1;
+			// batches (tasks of 32 lines, many more tasks than resident warps): tasks queued longest-first
+			const bool ordered = task_order() && !coop && taskLines == 32;
+			const uint32_t bucketCap = ordered ? (uint32_t)(totalLines / 32 + nv) : 0u;
 			{
 				KLaunch kl(c, K_LINE_SETUP, st);
 				const dim3 grid((maxViewLines + kSetupThreads - 1) / kSetupThreads, nv, 1);
@@ -706,7 +791,8 @@ namespace osb {
 					k_line_setup<true><<<grid, kSetupThreads, 0, st>>>(dV, B.d_lineDirs, sse, lineRes, g.noMap, B.d_lineTan,
 					                                                   B.d_liveBits, maxWordsPerView);
 				k_line_compact<<<nv, kCompactThreads, 0, st>>>(dV, B.d_lineTan, B.d_liveBits, maxWordsPerView, taskLines,
-				                                              B.d_lineRecs, B.d_active, B.d_tasks, B.d_counters);
+				                                              B.d_lineRecs, B.d_active, B.d_tasks, B.d_counters, B.d_lineDirs, lineRes,
+				                                              ordered ? B.d_bucketTasks : nullptr, bucketCap);
 				c->launches++;
 			}
 			if (!g.noMap && coop) {
@@ -729,7 +815,9 @@ namespace osb {
 				const unsigned blocks = (unsigned)std::min<size_t>((wantWarps + kWalkThreads / 32 - 1) / (kWalkThreads / 32), resident);
 				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
 				KLaunch kl(c, K_WALK_LINES, st);
-#define LAUNCH_WALK(SSE, SH) k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, B.d_tasks, B.d_counters)
+#define LAUNCH_WALK(SSE, SH)                                                                                                      \
+	k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, ordered ? B.d_bucketTasks : B.d_tasks,    \
+	                                                              B.d_counters, bucketCap)
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_WALK(false, false);
 				else if (num == OSB200_NUM_SSE)

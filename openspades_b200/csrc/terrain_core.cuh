@@ -295,6 +295,36 @@ namespace osb {
 		return r;
 	}
 
+	// How many DDA steps a line will take, estimated at set-up -- ORDER of the walker's work only, no effect on any
+	// result.  A line ends at the fog distance (128) or where the every-4th-step pitch cull fires (:661-667): once the
+	// map's top layer (z = 0) projects at or above the last strip pixel, or its bottom layer (z = 63) at or below the
+	// first.  Both projections are monotonic in the distance, so the distance of the cull has a closed form (the inverse
+	// of ToSpecialTan, :59-66); steps = distance x cell crossings per unit distance (|dx| + |dy| of the unit direction).
+	constexpr int kTaskBuckets = 16;      // walker tasks are queued by estimated length, longest first
+	constexpr float kStepsPerBucket = 12.f; // 128 * sqrt(2) = 181 steps at most
+	OSB_HDI float predict_steps(float minTan, float pitchScale, int lineRes, float cz, float2 hd) {
+		float dEnd = 128.f;
+		if (pitchScale > 0.f) {
+			const float inv = 1.f / pitchScale;
+			const float tA = (float)(lineRes - 1) * inv + minTan, tB = inv + minTan;
+			if (fabsf(tA) < 2.f && cz > 0.f) { // z = 0 lies above the eye: v = -cz / d rises towards 0
+				const float vA = fabsf(tA) <= 1.f ? tA : 1.f / ((tA < 0.f ? -2.f : 2.f) - tA);
+				if (vA < 0.f)
+					dEnd = fminf(dEnd, cz / -vA);
+			}
+			if (fabsf(tB) < 2.f && cz < 63.f) { // z = 63 lies below the eye: v = (63 - cz) / d falls towards 0
+				const float vB = fabsf(tB) <= 1.f ? tB : 1.f / ((tB < 0.f ? -2.f : 2.f) - tB);
+				if (vB > 0.f)
+					dEnd = fminf(dEnd, (63.f - cz) / vB);
+			}
+		}
+		return dEnd * (fabsf(hd.x) + fabsf(hd.y));
+	}
+	OSB_HDI int task_bucket(float steps) {
+		const int b = (int)(steps * (1.f / kStepsPerBucket));
+		return b < 0 ? 0 : (b >= kTaskBuckets ? kTaskBuckets - 1 : b);
+	}
+
 	// BuildLinePixel colour (SWMapRenderer.cpp:532-576). col = 0xHHBBGGRR from the map; mode 0 = NegY walls and
 	// tops (NegZ), 1 = PosX/PosY/NegX walls, 2 = undersides (PosZ).  All four 8-bit lanes are shaded in one
 	// register: (x>>1)+(x>>2) <= 190 never carries into the neighbouring lane.

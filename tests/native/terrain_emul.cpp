@@ -9,6 +9,7 @@
 // g++ -O2 -ffp-contract=off -shared -fPIC terrain_emul.cpp ../../openspades_b200/csrc/sse_calibrate.cpp
 #include <cstdarg>
 #include <cstdio>
+#include <algorithm>
 #include <vector>
 
 // per-lane counters of the current step (span candidates, landing words, stored pixels): the warp model below turns them
@@ -244,6 +245,9 @@ namespace {
 	}
 } // namespace
 
+static std::vector<float> g_taskCost; // per walker task: modelled warp instructions (see warp_model)
+static std::vector<int> g_taskView;
+static std::vector<int> g_taskSteps, g_taskPred; // per task: max DDA steps of a line, and their prediction at set-up
 namespace {
 	// Lock-step model of k_walk_lines' warps on one view batch: tasks of 32 adjacent surviving lines of a view, all lanes
 	// step together until the last one ends.  Reports where lanes idle: out[0] warp-steps, [1] lane-steps, [2] sum over
@@ -266,10 +270,31 @@ namespace {
 			std::vector<std::vector<uint32_t>> filled(n, std::vector<uint32_t>(128 + kWalkExtraWords));
 			std::vector<char> alive(n, 1);
 			std::vector<unsigned long long> iters(n, 0);
-			for (int i = 0; i < n; i++)
+			std::vector<int> nsteps(n, 0);
+			int pred = 0;
+			for (int i = 0; i < n; i++) {
 				W[i].init(wio, active[a + i], (uint32_t)(a + i), filled[i].data(), 1);
+				// prediction: distance at which the every-4th-step pitch cull fires (or the fog distance), times the cell
+				// crossings per unit distance
+				const float vmax = (float)wio.lineRes + 0.5f;
+				float dEnd = 128.f;
+				for (float dd = 0.5f; dd < 128.f; dd *= 1.09f) {
+					const float id = 1.f / dd;
+					if ((W[i].transform(num, id, 0, vmax) >= wio.lineRes - 1 && W[i].icz >= 0) || W[i].transform(num, id, 63, vmax) <= 0) {
+						dEnd = dd;
+						break;
+					}
+				}
+				const float2 hd = wio.lineDirs[active[a + i]];
+				if (getenv("EMUL_PRED_SCAN"))
+					pred = std::max(pred, (int)(dEnd * (fabsf(hd.x) + fabsf(hd.y))));
+				else
+					pred = std::max(pred, (int)predict_steps(wio.lineTan[active[a + i]].x, wio.lineTan[active[a + i]].y, wio.lineRes,
+					                                         views[view].origin[2], hd));
+			}
 			out[8]++;
 			out[9] += n;
+			double cost = 0;
 			for (;;) {
 				unsigned maxC = 0, sumC = 0, maxW = 0, sumW = 0, maxP = 0, sumP = 0, lanes = 0;
 				for (int i = 0; i < n; i++) {
@@ -278,6 +303,7 @@ namespace {
 					g_stat[0] = g_stat[1] = g_stat[2] = 0;
 					alive[i] = W[i].step(wio, num, filled[i].data(), 1);
 					lanes++;
+					nsteps[i]++;
 					maxC = std::max(maxC, g_stat[0]);
 					sumC += g_stat[0];
 					iters[i] += std::max(1u, g_stat[0]);
@@ -290,6 +316,8 @@ namespace {
 					break;
 				out[0]++;
 				out[1] += lanes;
+				cost += 112 + 96 * maxC + 60 * maxW + 14 * maxP; // step + candidates + landing words + stored pixels
+
 				out[2] += maxC;
 				out[3] += sumC;
 				out[4] += maxW;
@@ -303,6 +331,10 @@ namespace {
 				out[11] += iters[i];
 			}
 			out[10] += mx;
+			g_taskCost.push_back((float)cost);
+			g_taskView.push_back(view);
+			g_taskSteps.push_back(*std::max_element(nsteps.begin(), nsteps.end()));
+			g_taskPred.push_back(pred);
 			a = b;
 		}
 	}
@@ -350,6 +382,25 @@ __attribute__((visibility("default"))) int emul_render(const uint64_t *solid, co
 	}
 	return rc;
 }
+// costs of the tasks of the last emul_warp_model call (returns their number; cost / view may be null)
+__attribute__((visibility("default"))) int emul_task_steps(int *steps, int *pred, int cap) {
+	const int n = (int)g_taskSteps.size();
+	for (int i = 0; i < n && i < cap; i++) {
+		steps[i] = g_taskSteps[i];
+		pred[i] = g_taskPred[i];
+	}
+	return n;
+}
+__attribute__((visibility("default"))) int emul_task_costs(float *cost, int *view, int cap) {
+	const int n = (int)g_taskCost.size();
+	for (int i = 0; i < n && i < cap; i++) {
+		if (cost)
+			cost[i] = g_taskCost[i];
+		if (view)
+			view[i] = g_taskView[i];
+	}
+	return n;
+}
 __attribute__((visibility("default"))) void emul_set_coop(int mode) { g_coop = mode; }
 __attribute__((visibility("default"))) void emul_coop_stats(unsigned long long *out, int reset) {
 	for (int i = 0; i < 4; i++) {
@@ -372,6 +423,10 @@ __attribute__((visibility("default"))) int emul_warp_model(const uint64_t *solid
 	const float fog[3] = {0.8f, 1.f, 1.f};
 	for (int i = 0; i < 12; i++)
 		out[i] = 0;
+	g_taskCost.clear();
+	g_taskView.clear();
+	g_taskSteps.clear();
+	g_taskPred.clear();
 	return run<true, true>(solidT.data(), colorT.data(), scenes, nViews, w, h, fog, 128.f, 4, 1, 0, 0, nullptr, nullptr, nullptr, out);
 }
 }
