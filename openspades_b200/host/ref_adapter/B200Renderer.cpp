@@ -10,11 +10,26 @@
 #include <Core/Exception.h>
 #include <Core/VoxelModel.h>
 #include <Core/VoxelModelLoader.h>
+#include <Draw/SWFeatureLevel.h>
 
 namespace spades {
 	namespace draw {
 
 		B200Model::~B200Model() { osb200_model_destroy(model); }
+
+		int B200Renderer::NumericsOfThisBuild() {
+			const int level = static_cast<int>(DetectFeatureLevel());
+#if ENABLE_SSE2
+			if (level >= static_cast<int>(SWFeatureLevel::SSE2))
+				return OSB200_NUM_SSE2;
+#endif
+#if ENABLE_SSE
+			if (level >= static_cast<int>(SWFeatureLevel::SSE))
+				return OSB200_NUM_SSE;
+#endif
+			(void)level;
+			return OSB200_NUM_IEEE;
+		}
 
 		B200Renderer::B200Renderer(Handle<SWPort> port, int numerics, int device) : port(port) {
 			SPADES_MARK_FUNCTION();

@@ -100,6 +100,10 @@ namespace spades {
 			 * OSB200_NUM_SSE / OSB200_NUM_IEEE the other two builds (SWFeatureLevel.h:25-121). */
 			B200Renderer(Handle<SWPort> port, int numerics = OSB200_NUM_SSE2, int device = 0);
 
+			/** the variant whose frames equal what SWRenderer draws in THIS binary on THIS host: the feature level
+			 * SWRenderer's own constructor defaults to (DetectFeatureLevel, SWFeatureLevel.cpp:30-41) */
+			static int NumericsOfThisBuild();
+
 			void Init() override;
 			void Shutdown() override;
 

@@ -94,6 +94,7 @@ __attribute__((visibility("default"))) const char *adapter_last_error(void) { re
  * the shared map.  withModels: every frame also submits 3 RenderModel calls and 2 AddLight calls.
  * outB200 / outSW: nScenes x h x w RGBA words as ReadBitmap returns them.  info: [0] listener calls seen by the B200
  * renderer's last flush (columns), [1] port swaps of the B200 port, [2] total edits applied.
+ * numerics == 100: B200Renderer::NumericsOfThisBuild() against SWRenderer at its own default feature level (DetectFeatureLevel);
  * numerics < 0: only SWRenderer runs (usable without a GPU: the harness then serves to pin the oracle port on edited maps). */
 __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t vxlLen, int w, int h, int numerics, int threads,
                                                        const void *scenesRaw, int nScenes, int editsPerFrame, int withModels,
@@ -117,9 +118,12 @@ __attribute__((visibility("default"))) int adapter_run(const void *vxl, size_t v
 		Handle<client::IRenderer> rs[2];
 		const int k0 = numerics < 0 ? 1 : 0;
 		if (!k0)
-			rs[0] = Handle<draw::B200Renderer>::New(portB.Cast<draw::SWPort>(), numerics, 0).Cast<client::IRenderer>();
+			rs[0] = Handle<draw::B200Renderer>::New(portB.Cast<draw::SWPort>(),
+			                                        numerics == 100 ? draw::B200Renderer::NumericsOfThisBuild() : numerics, 0)
+			          .Cast<client::IRenderer>();
 		rs[1] = Handle<draw::SWRenderer>::New(portS.Cast<draw::SWPort>(),
-		                                      numerics == 1 ? draw::SWFeatureLevel::SSE : draw::SWFeatureLevel::SSE2)
+		                                      numerics == 100 ? draw::DetectFeatureLevel()
+		                                                      : (numerics == 1 ? draw::SWFeatureLevel::SSE : draw::SWFeatureLevel::SSE2))
 		          .Cast<client::IRenderer>();
 		Handle<client::IModel> models[2];
 		Handle<VoxelModel> vm = make_model(seed ^ 77u);

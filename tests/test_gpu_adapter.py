@@ -63,6 +63,15 @@ def test_same_frames_as_swrenderer_through_irenderer(adapter, with_models):
     assert info[3] == 2                        # EndScene outside a scene raises in both renderers
 
 
+def test_numerics_of_this_build(adapter):
+    """the selection a maintainer would ship: B200Renderer::NumericsOfThisBuild() against SWRenderer at the feature level
+    its own constructor detects on this host"""
+    w, h = 256, 256
+    scenes = np.stack([workloads.title_scene(w, h, 68.0)] * 2)
+    a, b, _ = _run(adapter, w, h, scenes, edits=20, with_models=True, numerics=100)
+    assert np.array_equal(a, b)
+
+
 def test_edits_change_the_frame(adapter):
     """the same pose before and after digging next to the camera: the second frame differs from the first and still
     equals SWRenderer's (i.e. the listener path really re-uploaded the columns)"""
