@@ -12,6 +12,8 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 namespace osb {
 	static thread_local std::string g_err;
@@ -200,19 +202,38 @@ int osb200_create(const osb200_opts *opts, osb200_ctx **out) {
 		osb::set_error("osb200_create: bad numerics mode %d", opts->numerics);
 		return -1;
 	}
-	std::vector<uint32_t> calRcp, calRsqrt;
 	const uint32_t *rcpTab = opts->rcp_table, *rsqrtTab = opts->rsqrt_table;
 	int rcpBits = opts->rcp_bits, rsqrtBits = opts->rsqrt_bits;
 	if (opts->numerics != OSB200_NUM_IEEE) {
 		if (!rcpTab || !rsqrtTab) {
-			// measure this host's RCPSS/RSQRTSS (the CPU the reference SWRenderer would run on)
-			calRcp.resize(1u << 16);
-			calRsqrt.resize(2u << 16);
-			int rc = osb200_calibrate_sse(calRcp.data(), &rcpBits, calRsqrt.data(), &rsqrtBits, 16);
-			if (rc)
-				return rc;
-			rcpTab = calRcp.data();
-			rsqrtTab = calRsqrt.data();
+			// measure this host's RCPSS/RSQRTSS (the CPU the reference SWRenderer would run on): an exhaustive scan of
+			// ~10^8 evaluations, done ONCE per process and shared by every context (ranks, groups, tests)
+			struct Cal {
+				std::vector<uint32_t> rcp, rsqrt;
+				int rcpBits = 0, rsqrtBits = 0, rc = 0;
+				std::string err;
+			};
+			static Cal cal;
+			static std::once_flag once;
+			std::call_once(once, [] {
+				cal.rcp.resize(1u << 16);
+				cal.rsqrt.resize(2u << 16);
+				cal.rc = osb200_calibrate_sse(cal.rcp.data(), &cal.rcpBits, cal.rsqrt.data(), &cal.rsqrtBits, 16);
+				if (cal.rc)
+					cal.err = osb200_last_error();
+			});
+			if (cal.rc) {
+				osb::set_error("osb200_create: the host's RCPSS/RSQRTSS could not be modelled (%s); the SSE / SSE2 numerics "
+				               "variants reproduce the reference as it runs on THIS CPU and need that model -- pass tables "
+				               "measured elsewhere in osb200_opts, or use numerics = OSB200_NUM_IEEE (the reference built "
+				               "without SSE), which needs none",
+				               cal.err.c_str());
+				return cal.rc;
+			}
+			rcpTab = cal.rcp.data();
+			rsqrtTab = cal.rsqrt.data();
+			rcpBits = cal.rcpBits;
+			rsqrtBits = cal.rsqrtBits;
 		}
 		if (rcpBits < 1 || rcpBits > 16 || rsqrtBits < 1 || rsqrtBits > 16) {
 			osb::set_error("osb200_create: bad rcpss/rsqrtss table sizes");

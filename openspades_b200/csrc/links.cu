@@ -68,6 +68,19 @@ namespace osb {
 		reach[i] = vfill(w, r);
 	}
 
+	// AddBlock (:104-193): seeds of the incremental flood = everything that is linked already (and still solid) plus
+	// the solid voxels of z = 62, which link to Root below them (:141-144).  Rebuild's (0,0,0) quirk is NOT re-applied:
+	// AddBlock has no such path, a voxel added at (1,0,0) / (0,1,0) / (0,0,1) next to nothing linked stays Invalid.
+	__global__ void k_links_add_seeds(const uint64_t *__restrict__ solidT, const uint64_t *__restrict__ linked,
+	                                  uint64_t *__restrict__ within, uint64_t *__restrict__ reach) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= OSB200_MAP_W * OSB200_MAP_H)
+			return;
+		const uint64_t w = solidT[i] & kBelowRoot;
+		within[i] = w;
+		reach[i] = vfill(w, (linked[i] & w) | (w & (1ull << 62)));
+	}
+
 	__global__ void __launch_bounds__(kLinkTile *kLinkTile)
 	  k_links_flood(const uint64_t *__restrict__ within, uint64_t *__restrict__ reach, int *__restrict__ changed) {
 		__shared__ uint64_t sR[kLinkTile + 2][kLinkTile + 2]; // [x][y] with a one-column halo
@@ -403,9 +416,26 @@ int osb200_links_rebuild(osb200_ctx *c) {
 int osb200_links_blocks_added(osb200_ctx *c) {
 	// AddBlock links a new voxel next to a linked one and walks on into never-linked neighbours (:127-192): after any
 	// number of additions the linked set is again "connected to the ground"
-	if (int rc = osb::links_ready(c, "osb200_links_blocks_added", true))
+	// The linked set is closed under solid adjacency (Rebuild and RemoveBlocks leave it so), hence flooding from the
+	// whole linked set through the solid voxels reaches exactly what the per-voxel walks of AddBlock would link: new
+	// voxels that touch a linked one, and on through never-linked neighbours.  Usually one flood launch (nothing moves
+	// outside the tiles that hold the new voxels).
+	using namespace osb;
+	if (int rc = links_ready(c, "osb200_links_blocks_added", true))
 		return rc;
-	return osb200_links_rebuild(c);
+	OSB_CUDA(cudaSetDevice(c->device));
+	LinksState *S = c->links;
+	S->lastRounds = 0;
+	const int nCols = OSB200_MAP_W * OSB200_MAP_H;
+	k_links_add_seeds<<<nCols / 256, 256, 0, c->stream>>>(c->d_solid, S->d_linked, S->d_within, S->d_reach);
+	c->launches++;
+	if (int rc = flood(c, S->d_within, S->d_reach))
+		return rc;
+	k_links_finish<<<nCols / 256, 256, 0, c->stream>>>(S->d_reach, S->d_linked);
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	OSB_CUDA(cudaStreamSynchronize(c->stream));
+	return S->lastRounds;
 }
 
 int osb200_links_remove_blocks(osb200_ctx *c, const int16_t *cells, int n, int16_t *floating, int cap) {

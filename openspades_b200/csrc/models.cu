@@ -31,7 +31,8 @@ struct osb200_model {
 	std::vector<uint32_t> renderData, renderDataAddr; // host copies (test hook)
 	uint32_t *d_data = nullptr, *d_addr = nullptr;
 	uint32_t voxels = 0; // splat candidates = (renderData.size() - columns) / 2
-	osb200_ctx *owner = nullptr;
+	osb200_ctx *owner = nullptr; // identity check only (osb200_render_scene); never dereferenced through a model
+	int device = 0;              // the owner's device, kept here so that a model may outlive its context
 };
 
 namespace osb {
@@ -622,6 +623,7 @@ int osb200_model_create(osb200_ctx *c, int w, int h, int d, const float origin[3
 	M->h = h;
 	M->d = d;
 	M->owner = c;
+	M->device = c->device;
 	for (int k = 0; k < 3; k++)
 		M->origin[k] = origin[k];
 	// SWModel.cpp:28-32: center = (w, h, d) * 0.5, radius = |center|
@@ -660,8 +662,7 @@ int osb200_model_create(osb200_ctx *c, int w, int h, int d, const float origin[3
 void osb200_model_destroy(osb200_model *m) {
 	if (!m)
 		return;
-	if (m->owner)
-		cudaSetDevice(m->owner->device);
+	cudaSetDevice(m->device);
 	cudaDeviceSynchronize();
 	cudaFree(m->d_data);
 	cudaFree(m->d_addr);

@@ -147,7 +147,7 @@ namespace osb200 {
 		duringSceneRendering_ = true;
 	}
 
-	Model::~Model() { osb200_model_destroy(m_); }
+	Model::~Model() = default; // the device copy goes with the last reference (this one, or the open scene's queue)
 
 	std::unique_ptr<Model> B200Renderer::CreateModel(const VoxelModelData &vm) {
 		EnsureInitialized();
@@ -185,7 +185,8 @@ namespace osb200 {
 		if (model.owner_ != this)
 			throw RendererError("model"); // SPInvalidArgument("model"): the dynamic_cast<SWModel&> of a foreign model
 		osb200_model_instance inst;
-		inst.model = model.m_;
+		inst.model = model.m_.get();
+		modelRefs_.push_back(model.m_);
 		for (int i = 0; i < 16; i++)
 			inst.matrix[i] = param.matrix[i];
 		inst.customColor[0] = param.customColor.x;
@@ -242,7 +243,9 @@ namespace osb200 {
 		// models.clear() / lights.clear() of the reference (:731,737) happen whether or not the draw succeeds
 		std::vector<osb200_model_instance> models;
 		std::vector<osb200_light> lights;
+		std::vector<std::shared_ptr<osb200_model>> refs;
 		models.swap(models_);
+		refs.swap(modelRefs_);
 		lights.swap(lights_);
 		if (osb200_render_scene(ctx_, &sc, w, h, fog, fogDistance_, models.data(), (int)models.size(), lights.data(),
 		                        (int)lights.size(), fb_->GetPixels(), nullptr) != 0)

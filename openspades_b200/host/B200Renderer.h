@@ -125,8 +125,10 @@ namespace osb200 {
 
 	private:
 		friend class B200Renderer;
-		Model(osb200_model *m, const B200Renderer *owner) : m_(m), owner_(owner) {}
-		osb200_model *m_;
+		Model(osb200_model *m, const B200Renderer *owner) : m_(m, osb200_model_destroy), owner_(owner) {}
+		// shared with the renderer's queue: a model destroyed between RenderModel and EndScene stays alive until the
+		// scene has been drawn, like the Handle<SWModel> SWRenderer keeps (SWRenderer.h:87-91)
+		std::shared_ptr<osb200_model> m_;
 		const B200Renderer *owner_;
 	};
 
@@ -209,6 +211,7 @@ namespace osb200 {
 		Vector3 fogColor_{0.f, 0.f, 0.f};
 		int lastFlushed_ = 0;
 		std::vector<osb200_model_instance> models_; // RenderModel calls of the open scene
+		std::vector<std::shared_ptr<osb200_model>> modelRefs_; // ... and what keeps their models alive until EndScene
 		std::vector<osb200_light> lights_;          // AddLight calls of the open scene (point lights)
 		std::mutex dirtyMutex_; // GameMapChanged may arrive from another thread (SWFlatMapRenderer.cpp:107-111)
 	};

@@ -48,6 +48,13 @@ def script(solid, seed=0, n_random=150):
     for c in fl:
         ops.append(("add",) + c + (col(),))
     ops.append(("remove", [fl[1]]))
+    # voxels added at the three cells Rebuild links through its value-initialised queue (GameMapWrapper.cpp:62): AddBlock
+    # has no such path, so in mid-air they stay unlinked; removing one of them then reports nothing else
+    quirk = [c for c in ((1, 0, 0), (0, 1, 0), (0, 0, 1)) if top_of(solid, c[0], c[1]) > 3 and top_of(solid, 0, 0) > 3]
+    for c in quirk:
+        ops.append(("add",) + c + (col(),))
+    if quirk:
+        ops.append(("remove", [quirk[0]]))
     # random digs of surface voxels (usually nothing falls) and undercuts one below the surface
     for _ in range(n_random):
         x, y = (int(v) for v in rng.integers(0, 512, 2))

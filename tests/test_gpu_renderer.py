@@ -176,9 +176,21 @@ def test_renderer_draws_models_and_lights_like_the_reference():
     wfb2, _ = rr.render_scene(sc)
     assert np.array_equal(r.framebuffer() & 0xFFFFFF, wfb2 & 0xFFFFFF)
     assert not np.array_equal(wfb2 & 0xFFFFFF, wfb & 0xFFFFFF)
+    # a model destroyed between RenderModel and EndScene is still drawn: the queue holds a reference until the scene
+    # has been rendered (Handle<SWModel> in SWRenderer::Model, SWRenderer.h:87-91)
+    r.start_scene(sc)
+    for _, mat, cc in pl:
+        r.render_model(gmod, mat, cc)
+    for o, rad, col in lrows:
+        r.add_light(o, rad, col)
     r.free_model(gmod)
+    r.end_scene()
+    assert np.array_equal(r.framebuffer() & 0xFFFFFF, wfb & 0xFFFFFF)
+    # ... and a model may outlive its renderer
+    late = r.create_model(vm.w, vm.hgt, vm.d, vm.origin, s, c)
     r.set_game_map(None)
     r.close()
+    r.free_model(late)
     rr.free_model(rmod)
     vm.close()
     rr.set_map(None)
