@@ -31,6 +31,8 @@ def _rays(n, seed):
     v0[: n // 8, 2] -= 40.0           # origins above the map
     v0[n // 8: n // 4, 2] += 30.0     # and below the water floor
     ev0, ed = workloads.edge_rays()
+    keep = np.isfinite(ed).all(axis=1)  # GameMap::CastRay asserts its arguments are not NaN (GameMap.cpp:212-218) and an
+    ev0, ed = ev0[keep], ed[keep]       # infinite direction makes v1 NaN / infinite: outside the function's contract
     return np.concatenate([v0, ev0]).astype(np.float32), np.concatenate([d.astype(np.float32), ed])
 
 
