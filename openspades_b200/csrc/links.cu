@@ -53,17 +53,20 @@ namespace osb {
 	// within = solid below the root layer; reach = the seeds of a flood from the ground: every solid voxel of z = 62
 	// (they link to Root, :65-70) and the three neighbours of voxel (0,0,0) that Rebuild links through the
 	// value-initialised cells its queue starts with (:62)
+	// linkedOld == nullptr: Rebuild.  Otherwise (RemoveBlocks) the three quirk cells count as ground only while they
+	// still carry the link Rebuild gave them: a voxel ADDED there later went through AddBlock, which knows no such link.
 	__global__ void k_links_ground_seeds(const uint64_t *__restrict__ solidT, uint64_t *__restrict__ within,
-	                                     uint64_t *__restrict__ reach) {
+	                                     uint64_t *__restrict__ reach, const uint64_t *__restrict__ linkedOld) {
 		const int i = blockIdx.x * blockDim.x + threadIdx.x;
 		if (i >= OSB200_MAP_W * OSB200_MAP_H)
 			return;
 		const uint64_t w = solidT[i] & kBelowRoot;
+		const uint64_t quirk = linkedOld ? w & linkedOld[i] : w;
 		uint64_t r = w & (1ull << 62);
 		if (i == (int)tiled_index(1, 0) || i == (int)tiled_index(0, 1))
-			r |= w & 1ull;
+			r |= quirk & 1ull;
 		if (i == (int)tiled_index(0, 0))
-			r |= w & 2ull;
+			r |= quirk & 2ull;
 		within[i] = w;
 		reach[i] = vfill(w, r);
 	}
@@ -364,10 +367,10 @@ namespace osb {
 		S->lastRounds += rounds;
 		return 0;
 	}
-	static int ground_flood(osb200_ctx *c) {
+	static int ground_flood(osb200_ctx *c, bool rebuild) {
 		LinksState *S = c->links;
 		const int n = OSB200_MAP_W * OSB200_MAP_H;
-		k_links_ground_seeds<<<n / 256, 256, 0, c->stream>>>(c->d_solid, S->d_within, S->d_reach);
+		k_links_ground_seeds<<<n / 256, 256, 0, c->stream>>>(c->d_solid, S->d_within, S->d_reach, rebuild ? nullptr : S->d_linked);
 		c->launches++;
 		return flood(c, S->d_within, S->d_reach);
 	}
@@ -403,7 +406,7 @@ int osb200_links_rebuild(osb200_ctx *c) {
 		return -2;
 	LinksState *S = c->links;
 	S->lastRounds = 0;
-	if (int rc = ground_flood(c))
+	if (int rc = ground_flood(c, true))
 		return rc;
 	k_links_finish<<<OSB200_MAP_W * OSB200_MAP_H / 256, 256, 0, c->stream>>>(S->d_reach, S->d_linked);
 	c->launches++;
@@ -467,7 +470,7 @@ int osb200_links_remove_blocks(osb200_ctx *c, const int16_t *cells, int n, int16
 		S->cellCap = (size_t)n + 1024;
 	}
 	OSB_CUDA(cudaMemcpyAsync(S->d_cells, cells, (size_t)n * 3 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream));
-	if (int rc = ground_flood(c))
+	if (int rc = ground_flood(c, false))
 		return rc;
 	OSB_CUDA(cudaMemsetAsync(S->d_flags, 0, 4 * sizeof(int), c->stream));
 	OSB_CUDA(cudaMemsetAsync(S->d_reach2, 0, (size_t)nCols * 8, c->stream));

@@ -1,7 +1,7 @@
 #!/bin/bash
 # full GPU suite + both bench arms + smoke after the castray2 / links / lifetime changes
 mkdir -p gpurun_out
-timeout 2400 python -m pytest tests -m gpu -x -q 2>&1 | tail -6 | tee gpurun_out/r2_pytest_full.log
+timeout 2400 python -m pytest tests -m gpu -x -q 2>&1 | tail -60 | tee gpurun_out/r2_pytest_full.log | tail -8
 timeout 600 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/r2_smoke.log
 timeout 900 python bench.py --impl reference > gpurun_out/r2_bench_ref_final.json 2> gpurun_out/r2_bench_ref_final.err; tail -c 600 gpurun_out/r2_bench_ref_final.json
 timeout 1200 python bench.py > gpurun_out/r2_bench_final.json 2> gpurun_out/r2_bench_final.err; tail -3 gpurun_out/r2_bench_final.err
