@@ -123,6 +123,15 @@ OSB200_API int osb200_castray2(osb200_ctx *ctx, const float *v0, const float *di
                                osb200_rayhit *out, size_t n);
 OSB200_API int osb200_castray2_device(osb200_ctx *ctx, const float *d_v0, const float *d_dir,
                                       int maxSteps, osb200_rayhit *d_out, size_t n);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * osb200_castray2 (host pointers in and out), but the call allocates nothing: the device staging of the batch and the
+ * kernel's work cursor live in a static device array that every GPU loading the library holds until exit (4 MiB + 256 B).
+ * n > OSB200_CASTRAY2_STATIC_MAX_RAYS is rejected (-1, text via osb200_last_error).  The array is shared by all calls on a
+ * GPU: calls that overlap there (other contexts, streams or host threads) race -- serialise them. */
+#define OSB200_CASTRAY2_STATIC_MAX_RAYS 65536
+OSB200_API int osb200_castray2_static(osb200_ctx *ctx, const float *v0, const float *dir, int maxSteps,
+                                      osb200_rayhit *out, size_t n);
 
 /* ---- terrain pass + fog: SWRenderer::StartScene + EndScene for the map (SWRenderer.cpp:549-563,709-745;
  *      SWMapRenderer::Render SWMapRenderer.cpp:1176-1194; SWRenderer::ApplyFog SWRenderer.cpp:341-516) ----

@@ -90,6 +90,7 @@ def load_library():
     lib.osb200_map_read_solid.argtypes = [vp, vp]
     lib.osb200_castray2.argtypes = [vp, vp, vp, ci, vp, sz]
     lib.osb200_castray2_device.argtypes = [vp, vp, vp, ci, vp, sz]
+    lib.osb200_castray2_static.argtypes = [vp, vp, vp, ci, vp, sz]
     fp = ctypes.c_float
     lib.osb200_render.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
     lib.osb200_render_device.argtypes = [vp, vp, ci, ci, ci, vp, fp, vp, vp]
@@ -307,6 +308,20 @@ class Context:
         if out is None:
             out = np.zeros(n, RAYHIT_DTYPE)
         self._check(self._lib.osb200_castray2(self._h, pv, pd, int(max_steps), _ptr(out), n))
+        return out
+
+    CASTRAY2_STATIC_MAX_RAYS = 65536  # OSB200_CASTRAY2_STATIC_MAX_RAYS (include/osb200.h)
+
+    def castray2_static(self, v0, dirs, max_steps, out=None):
+        """osb200_castray2_static: same arguments and results as castray2, no allocation inside the call (static device
+        scratch, at most CASTRAY2_STATIC_MAX_RAYS rays per call; calls that overlap on one GPU race)."""
+        v0 = np.ascontiguousarray(v0, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        n = v0.shape[0]
+        assert v0.shape == (n, 3) and dirs.shape == (n, 3)
+        if out is None:
+            out = np.zeros(n, RAYHIT_DTYPE)
+        self._check(self._lib.osb200_castray2_static(self._h, v0.ctypes.data, dirs.ctypes.data, int(max_steps), _ptr(out), n))
         return out
 
     def castray2_device(self, d_v0, d_dir, max_steps, d_out, n):

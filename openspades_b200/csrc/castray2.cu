@@ -530,4 +530,87 @@ int osb200_castray2(osb200_ctx *c, const float *v0, const float *dir, int maxSte
 	              : castray2_staged(c, c->rayPipe, v0, dir, maxSteps, out, n);
 }
 
+// ---- CastRay2 without any allocation -------------------------------------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// osb200_castray2 stages the caller's host buffers in device scratch that it allocates on demand (ensure_scratch, the ray
+// cursor, the pipeline's streams and events).  This variant runs the same kernel with that scratch in a file-scope device
+// array of fixed size: the batch cursor, the two input arrays and the result records of up to
+// OSB200_CASTRAY2_STATIC_MAX_RAYS rays.  Every GPU that loads the library holds the array (4 MiB + 256 B) until exit.
+//   * the array is shared by every call on a device and keeps the last call's contents: the cursor is cleared per call,
+//     the input slots are overwritten by this call's copies, and the kernel writes every field of records 0 .. n-1;
+//   * calls that overlap on one GPU (two contexts / streams / host threads) race on it -- serialise them.
+namespace {
+	constexpr size_t kStaticMaxRays = OSB200_CASTRAY2_STATIC_MAX_RAYS;
+	constexpr size_t kStaticCursorBytes = 256;
+	constexpr size_t kStaticInBytes = kStaticMaxRays * 3 * sizeof(float);       // per input array; a multiple of 256
+	constexpr size_t kStaticOutBytes = kStaticMaxRays * sizeof(osb200_rayhit);  // a multiple of 256
+	static_assert(kStaticInBytes % 256 == 0 && kStaticOutBytes % 256 == 0, "slots of the static scratch stay 256-byte aligned");
+	static __device__ __align__(256) unsigned char g_rayScratch[kStaticCursorBytes + 2 * kStaticInBytes + kStaticOutBytes];
+
+	// In host code `g_rayScratch` is a host-side stand-in, not a device address: the address a kernel may use comes from
+	// cudaGetSymbolAddress, asked once per device with that device current.
+	constexpr int kMaxDevices = 64;
+	std::mutex g_rayScratchLock;
+	unsigned char *g_rayScratchAddr[kMaxDevices] = {};
+
+	int ray_scratch_of(int device, unsigned char **out) {
+		if (device < 0 || device >= kMaxDevices) {
+			osb::set_error("osb200_castray2_static: device %d beyond the %d devices this entry point keeps an address for", device,
+			               kMaxDevices);
+			return -1;
+		}
+		std::lock_guard<std::mutex> g(g_rayScratchLock);
+		if (!g_rayScratchAddr[device]) {
+			OSB_CUDA(cudaSetDevice(device));
+			void *p = nullptr;
+			OSB_CUDA(cudaGetSymbolAddress(&p, g_rayScratch));
+			if (!p) {
+				osb::set_error("osb200_castray2_static: cudaGetSymbolAddress returned a null address on device %d", device);
+				return -2;
+			}
+			g_rayScratchAddr[device] = static_cast<unsigned char *>(p);
+		}
+		*out = g_rayScratchAddr[device];
+		return 0;
+	}
+} // namespace
+
+int osb200_castray2_static(osb200_ctx *c, const float *v0, const float *dir, int maxSteps, osb200_rayhit *out, size_t n) {
+	if (!c || !c->mapLoaded) {
+		osb::set_error("osb200_castray2_static: no context or no map uploaded");
+		return -1;
+	}
+	if (n == 0)
+		return 0;
+	if (!v0 || !dir || !out) {
+		osb::set_error("osb200_castray2_static: null buffer");
+		return -1;
+	}
+	if (n > kStaticMaxRays) {
+		osb::set_error("osb200_castray2_static: %zu rays exceed OSB200_CASTRAY2_STATIC_MAX_RAYS = %zu, the capacity of the static "
+		               "device scratch; split the batch or use osb200_castray2 (which allocates)",
+		               n, kStaticMaxRays);
+		return -1;
+	}
+	OSB_CUDA(cudaSetDevice(c->device));
+	unsigned char *base = nullptr;
+	if (int rc = ray_scratch_of(c->device, &base))
+		return rc;
+	auto *cursor = reinterpret_cast<unsigned long long *>(base);
+	auto *d_v0 = reinterpret_cast<float *>(base + kStaticCursorBytes);
+	auto *d_dir = reinterpret_cast<float *>(base + kStaticCursorBytes + kStaticInBytes);
+	auto *d_out = reinterpret_cast<uint32_t *>(base + kStaticCursorBytes + 2 * kStaticInBytes);
+	cudaStream_t st = c->stream;
+	OSB_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st)); // the one thing that must start at zero
+	OSB_CUDA(cudaMemcpyAsync(d_v0, v0, n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+	OSB_CUDA(cudaMemcpyAsync(d_dir, dir, n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+	const size_t blocks = std::min<size_t>((size_t)c->smCount * kCtasPerSm, (n + kThreads - 1) / kThreads);
+	k_castray2<<<(unsigned)blocks, kThreads, 0, st>>>(c->d_solid, d_v0, d_dir, maxSteps, d_out, n, cursor);
+	c->launches++;
+	OSB_CUDA(cudaGetLastError());
+	OSB_CUDA(cudaMemcpyAsync(out, d_out, n * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, st));
+	OSB_CUDA(cudaStreamSynchronize(st));
+	return 0;
+}
+
 } // extern "C"
