@@ -29,7 +29,7 @@ namespace osb {
 		static const char *names[K_COUNT] = {"k_map_repack", "k_map_scatter", "k_view_prep", "k_walk_lines",
 		                                     "k_gather_fog", "k_castray2", "k_shadow_update", "k_radiosity",
 		                                     "k_rad_select", "k_castray", "k_ao_chunk", "k_scene_finish", "k_model_setup", "k_model_splat",
-		                                     "k_line_setup", "k_light_prep", "k_vxl_index", "k_vxl_decode", "k_vxl_encode", "k_links_flood", "k_minimap", "k_cluster_union"};
+		                                     "k_line_setup", "k_light_prep", "k_vxl_index", "k_vxl_decode", "k_vxl_encode", "k_links_flood", "k_minimap", "k_cluster_union", "k_view_pipeline"};
 		return id >= 0 && id < K_COUNT ? names[id] : "?";
 	}
 	KLaunch::KLaunch(osb200_ctx *ctx, int kid, cudaStream_t stream) : c(ctx), slot(-1), st(stream ? stream : ctx->stream) {

@@ -54,6 +54,7 @@ namespace osb {
 		K_LINKS_FLOOD,
 		K_MINIMAP,
 		K_CLUSTER_UNION,
+		K_VIEW_PIPELINE,
 		K_COUNT
 	};
 	const char *kernel_name(int id);

@@ -77,6 +77,7 @@ namespace osbc {
 	OSB_HDI uint32_t byte_perm(uint32_t a, uint32_t b, uint32_t s) { return __byte_perm(a, b, s); }
 	OSB_HDI int mulhi(int a, int b) { return __mulhi(a, b); }
 	template <class T> OSB_HDI T ldg(const T *p) { return __ldg(p); }
+	template <class T> OSB_HDI T ldcg(const T *p) { return __ldcg(p); } // L2 only: data another SM wrote in this kernel
 	template <class T> OSB_HDI void stcs(T *p, T v) { __stcs(p, v); }
 	OSB_HDI float fminf_(float a, float b) { return fminf(a, b); }
 	OSB_HDI float fmaxf_(float a, float b) { return fmaxf(a, b); }
@@ -117,6 +118,7 @@ namespace osbc {
 	}
 	OSB_HDI int mulhi(int a, int b) { return (int)(((int64_t)a * (int64_t)b) >> 32); }
 	template <class T> OSB_HDI T ldg(const T *p) { return *p; }
+	template <class T> OSB_HDI T ldcg(const T *p) { return *p; }
 	template <class T> OSB_HDI void stcs(T *p, T v) { *p = v; }
 	// x86 minss / maxss semantics are not needed here: callers never pass NaN (asserted by the parity runs)
 	OSB_HDI float fminf_(float a, float b) { return fminf(a, b); }

@@ -23,6 +23,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -40,6 +41,23 @@ namespace osb {
 		static const int v = [] {
 			const char *e = getenv("OSB200_TASK_ORDER");
 			return e ? atoi(e) : 0;
+		}();
+		return v;
+	}
+	// OSB200_PIPELINE=W: batches run k_view_pipeline (walk + gather of a view back to back in one persistent kernel, at most
+	// W views between the first line walked and the last pixel gathered) instead of k_walk_lines + k_gather_fog.  0 = off.
+	static int pipeline_window() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_PIPELINE");
+			return e ? std::max(0, atoi(e)) : 0;
+		}();
+		return v;
+	}
+	// OSB200_PIPE_SPLIT=k: of every 16 SMs, k walk and 16 - k gather (0 = every warp takes whatever is there)
+	static int pipeline_split() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_PIPE_SPLIT");
+			return e ? std::min(15, std::max(0, atoi(e))) : 0;
 		}();
 		return v;
 	}
@@ -63,6 +81,9 @@ namespace osb {
 		uint32_t *d_counters = nullptr; // [0] number of tasks, [1] work cursor of k_walk_lines, [2..] fill + cursor per task queue
 		uint32_t *d_bucketTasks = nullptr; // kTaskBuckets queues of bucketCap walker tasks (ordered mode)
 		size_t bucketTaskCap = 0;
+		uint32_t *d_tasksPV = nullptr; // k_view_pipeline: walker tasks in per-view regions of maxWordsPerView entries
+		uint32_t *d_pipe = nullptr;    // ... and its counters: head | nTasks | taken | walked | gathered | ready queue (per view)
+		size_t tasksPVCap = 0, pipeCap = 0;
 		uint2 *d_strips = nullptr;
 		uint32_t *d_lineMask = nullptr; // lineRes bits per strip slot: strip pixels the line wrote
 		float *d_tabs = nullptr;
@@ -158,7 +179,8 @@ namespace osb {
 	  k_line_compact(const ViewParams *__restrict__ views, const float2 *__restrict__ lineTan, const uint32_t *__restrict__ liveBits,
 	                 int wordsPerView, int taskLines, LineRec *__restrict__ lineRecs, uint32_t *__restrict__ active,
 	                 uint32_t *__restrict__ tasks, uint32_t *__restrict__ counters, const float2 *__restrict__ lineDirs, int lineRes,
-	                 uint32_t *__restrict__ bucketTasks, uint32_t bucketCap) {
+	                 uint32_t *__restrict__ bucketTasks, uint32_t bucketCap, uint32_t *__restrict__ tasksPV,
+	                 uint32_t *__restrict__ nTasksPV, int maxTasksPV) {
 		__shared__ uint32_t s_prefix[kMaxLineWords]; // exclusive prefix of the survivor counts per 32-line word
 		__shared__ uint32_t s_warpSum[kCompactThreads / 32];
 		__shared__ uint32_t s_base, s_taskBase;
@@ -231,6 +253,16 @@ namespace osb {
 		if (threadIdx.x == 0)
 			s_taskBase = nTasks ? atomicAdd(counters, nTasks) : 0u;
 		__syncthreads();
+		if (tasksPV) { // k_view_pipeline: the view's tasks in a region of their own, taken view by view
+			for (uint32_t i = threadIdx.x; i < nTasks; i += kCompactThreads) {
+				const uint32_t first = i * (uint32_t)taskLines;
+				const uint32_t n = min((uint32_t)taskLines, nLive - first);
+				tasksPV[(size_t)vi * maxTasksPV + i] = ((V.lineBase + first) << 5) | (n - 1u);
+			}
+			if (threadIdx.x == 0)
+				nTasksPV[vi] = nTasks;
+			return;
+		}
 		if (!ordered) {
 			for (uint32_t i = threadIdx.x; i < nTasks; i += kCompactThreads) {
 				const uint32_t first = i * (uint32_t)taskLines;
@@ -442,6 +474,177 @@ namespace osb {
 		}
 	}
 
+	// ------------------------------------------------------------------------------------------------------------------
+	// View-granular pipeline: ONE persistent kernel walks the lines of a view and gathers + fogs that view as soon as its
+	// last line is done, so that the view's strips are read back while they are still in L2 instead of making the round
+	// trip through HBM that two batch-wide kernels force (walker writes 1.8 GB of strips, gather reads 1.6 GB back).
+	// A warp is a walker or a gatherer task by task:
+	//   gather first   a ticket of the oldest walked view (ready queue, in the order the views' walks completed; the
+	//                  tickets on offer are counted by a semaphore);
+	//   else walk      the next task of the current view -- views are admitted in index order, and view v only once view
+	//                  v - window has been gathered completely: the strips in flight stay within `window` views;
+	//   else           back off and look again.
+	// Hand-over of a view from its walker warps to its gatherer warps: every lane fences its strip / hull stores, lane 0
+	// counts the task done with an atomic; the warp that counts the last one publishes the view in the ready queue; the
+	// taker reads the queue entry, fences, and reads strips and line records with ld.global.cg (L1 is not coherent).
+	// ------------------------------------------------------------------------------------------------------------------
+	constexpr int kPipeCur = 0, kPipeReady = 32, kPipeGather = 64, kPipeAvail = 16; // hot counters on separate lines / sectors
+	constexpr int kPipeHead = 128;                                 // words before the per-view arrays
+	__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t *p) {
+		uint32_t v;
+		asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+		return v;
+	}
+	template <bool kSse, bool kSse2>
+	__global__ void __launch_bounds__(kWalkThreads, OSB_WALK_MINB)
+	  k_view_pipeline(WalkIO wio, GatherIO gio, osbn::SseTables tabs, const uint32_t *__restrict__ active,
+	                  const uint32_t *__restrict__ tasksPV, int maxTasksPV, uint32_t *__restrict__ pipe, uint32_t window,
+	                  uint32_t perView, uint32_t split) {
+		extern __shared__ uint32_t s_filled[]; // the walker's fill masks, as in k_walk_lines
+		__shared__ GatherShared s_g[kWalkThreads / 32];
+		uint32_t *filled = s_filled + threadIdx.x;
+		const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+		const osbn::Num<kSse> num{tabs};
+		const uint32_t nViews = (uint32_t)gio.nViews, totalG = nViews * perView;
+		const uint32_t *nTasksPV = pipe + kPipeHead;
+		uint32_t *viewTaken = pipe + kPipeHead + nViews, *walkDone = viewTaken + nViews, *gatherDone = walkDone + nViews,
+		         *readyQ = gatherDone + nViews;
+		// split != 0: roles per SM instead of per warp -- SMs with smid % 16 < split walk (and gather only once every walk task
+		// is handed out), the others gather (and walk only until the first view is ready): an SM then runs ONE of the two
+		// instruction streams at a time (together they do not fit the instruction cache)
+		uint32_t smid = 0;
+		asm("mov.u32 %0, %%smid;" : "=r"(smid));
+		const bool mayGatherFirst = split == 0 || (smid & 15u) >= split;
+		const bool walkerSm = split == 0 || (smid & 15u) < split;
+		auto publish = [&](uint32_t v) { // lane 0, after its fence
+			const uint32_t idx = atomicAdd(pipe + kPipeReady, 1u);
+			asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(readyQ + idx), "r"(v) : "memory");
+			__threadfence();
+			atomicAdd(reinterpret_cast<int *>(pipe + kPipeAvail), (int)perView); // perView more gather tickets
+		};
+#ifdef OSB_PIPE_STATS
+		unsigned long long tDisp = 0, tWalk = 0, tGather = 0, nPoll = 0, nSleep = 0, nCasFail = 0;
+#define PIPE_T0 const long long t0_ = clock64()
+#define PIPE_ACC(x) x += (unsigned long long)(clock64() - t0_)
+#else
+#define PIPE_T0
+#define PIPE_ACC(x)
+#endif
+		for (;;) {
+			uint32_t kind = 0, a = 0, b = 0; // 1 walk (view a, task b), 2 gather (ticket a), 3 all work handed out
+			if (lane == 0) {
+				PIPE_T0;
+				uint32_t backoff = 64;
+				for (;;) {
+					if (ld_relaxed(pipe + kPipeGather) >= totalG) {
+						kind = 3;
+						break;
+					}
+					// gather tickets are a semaphore (fetch-and-add only: a compare-and-swap ticket collapses to one success
+					// per L2 round trip once a few thousand warps contend -- measured, 90x slower)
+					const uint32_t cur = ld_relaxed(pipe + kPipeCur);
+					if ((mayGatherFirst || cur >= nViews) && (int)ld_relaxed(pipe + kPipeAvail) > 0) {
+						if (atomicSub(reinterpret_cast<int *>(pipe + kPipeAvail), 1) > 0) {
+							kind = 2;
+							a = atomicAdd(pipe + kPipeGather, 1u);
+							break;
+						}
+						atomicAdd(reinterpret_cast<int *>(pipe + kPipeAvail), 1); // none left after all: give it back
+					}
+					const uint32_t v = cur;
+					if ((walkerSm || ld_relaxed(pipe + kPipeReady) == 0u) && v < nViews && (v < window || ld_relaxed(gatherDone + (v - window)) >= perView)) {
+						const uint32_t nt = nTasksPV[v];
+						if (ld_relaxed(viewTaken + v) < nt) { // (looked at first: a herd of idle warps must not pile atomics on it)
+							const uint32_t t = atomicAdd(viewTaken + v, 1u);
+							if (t < nt) {
+								kind = 1;
+								a = v;
+								b = t;
+								break;
+							}
+						}
+						// the view's tasks are all handed out: move on (a view without surviving lines is ready at once)
+						if (atomicCAS(pipe + kPipeCur, v, v + 1u) == v && nt == 0u)
+							publish(v);
+						continue;
+					}
+#ifdef OSB_PIPE_STATS
+					nSleep++;
+#endif
+					__nanosleep(backoff);
+					if (backoff < 2048)
+						backoff <<= 1;
+				}
+				PIPE_ACC(tDisp);
+			}
+			kind = __shfl_sync(0xffffffffu, kind, 0);
+			a = __shfl_sync(0xffffffffu, a, 0);
+			b = __shfl_sync(0xffffffffu, b, 0);
+			if (kind == 3)
+				break;
+			if (kind == 1) {
+				PIPE_T0;
+				const uint32_t task = __ldg(tasksPV + (size_t)a * maxTasksPV + b);
+				const uint32_t slot = (task >> 5) + (uint32_t)lane;
+				bool alive = (uint32_t)lane <= (task & 31u);
+				LineWalker<kSse, kSse2> W;
+				if (alive)
+					W.init(wio, __ldg(active + slot), slot, filled, kWalkThreads);
+				while (__any_sync(0xffffffffu, alive)) {
+					if (alive)
+						alive = W.step(wio, num, filled, kWalkThreads);
+				}
+				__threadfence(); // this lane's strip pixels and hull, before the task is counted
+				__syncwarp();
+				if (lane == 0) {
+					__threadfence();
+					if (atomicAdd(walkDone + a, 1u) + 1u == nTasksPV[a]) {
+						__threadfence();
+						publish(a);
+					}
+					PIPE_ACC(tWalk);
+				}
+			} else {
+				PIPE_T0;
+				const uint32_t ridx = a / perView, sub = a - ridx * perView;
+				uint32_t v = 0;
+				if (lane == 0) {
+					do
+						v = ld_relaxed(readyQ + ridx); // reserved before it was written: a few cycles at most
+					while (v == 0xffffffffu);
+					__threadfence();
+				}
+				v = __shfl_sync(0xffffffffu, v, 0);
+				GatherShared &sm = s_g[wid];
+				GatherLane<kSse, kSse2, true> L;
+				L.init(gio, v * perView + sub, lane);
+				L.fog_phase(gio, num, sm, lane);
+				__syncwarp();
+				for (int by = L.by0; by < L.by1; by += 2) {
+					L.corner_phase(gio, num, sm, lane, by);
+					__syncwarp();
+					OSB_PRAGMA(unroll 1)
+					for (int r = 0; r < 2; r++)
+						L.pixel_phase(gio, num, sm, r, by);
+					__syncwarp();
+				}
+				if (lane == 0) {
+					atomicAdd(gatherDone + v, 1u);
+					PIPE_ACC(tGather);
+				}
+			}
+		}
+#ifdef OSB_PIPE_STATS
+		if (lane == 0) {
+			unsigned long long *st = reinterpret_cast<unsigned long long *>(pipe + 96);
+			atomicAdd(st + 0, tDisp);
+			atomicAdd(st + 1, tWalk);
+			atomicAdd(st + 2, tGather);
+			atomicAdd(st + 3, nSleep);
+		}
+#endif
+	}
+
 	static int terrain_init(osb200_ctx *c) {
 		if (c->terrain)
 			return 0;
@@ -489,6 +692,8 @@ namespace osb {
 			cudaFree(b.d_tasks);
 			cudaFree(b.d_counters);
 			cudaFree(b.d_bucketTasks);
+			cudaFree(b.d_tasksPV);
+			cudaFree(b.d_pipe);
 			cudaFree(b.d_strips);
 			cudaFree(b.d_lineMask);
 			cudaFree(b.d_tabs);
@@ -704,6 +909,8 @@ namespace osb {
 			    grow(B.d_liveBits, B.liveCap, maxViews * (size_t)maxWordsPerView) ||
 			    grow(B.d_tasks, B.taskCap, maxLines / kMinTaskLines + maxViews) ||
 			    grow(B.d_bucketTasks, B.bucketTaskCap, (size_t)kTaskBuckets * (maxLines / 32 + maxViews)) ||
+			    (pipeline_window() &&
+			     (grow(B.d_tasksPV, B.tasksPVCap, maxViews * (size_t)maxWordsPerView) || grow(B.d_pipe, B.pipeCap, kPipeHead + 5 * maxViews))) ||
 			    grow(B.d_strips, B.stripCap, maxLines * (size_t)lineRes) ||
 			    grow(B.d_lineMask, B.maskCap, maxLines * (size_t)words) || grow(B.d_tabs, B.tabCap, maxViews * tabF))
 				return -2;
@@ -750,6 +957,10 @@ namespace osb {
 			for (int i = 0; i < nv; i++)
 				maxViewLines = std::max(maxViewLines, T->h_views[v0 + i].numLines);
 			OSB_CUDA(cudaMemsetAsync(B.d_counters, 0, kCounterWords * sizeof(uint32_t), st));
+			if (pipeline_window() && B.d_pipe) {
+				OSB_CUDA(cudaMemsetAsync(B.d_pipe, 0, (kPipeHead + 4 * (size_t)nv) * sizeof(uint32_t), st));
+				OSB_CUDA(cudaMemsetAsync(B.d_pipe + kPipeHead + 4 * (size_t)nv, 0xff, (size_t)nv * sizeof(uint32_t), st));
+			}
 			if (hostPrep) {
 				for (int i = 0; i < nv; i++) {
 					const ViewParams &V = T->h_views[v0 + i];
@@ -779,7 +990,8 @@ namespace osb {
 			if (coop)
 				taskLines = 1;
 			// batches (tasks of 32 lines, many more tasks than resident warps): tasks queued longest-first
-			const bool ordered = task_order() && !coop && taskLines == 32;
+			const bool pipeline = pipeline_window() > 0 && !coop && taskLines == 32 && !hostPrep && !g.noMap;
+			const bool ordered = task_order() && !coop && taskLines == 32 && !pipeline;
 			const uint32_t bucketCap = ordered ? (uint32_t)(totalLines / 32 + nv) : 0u;
 			{
 				KLaunch kl(c, K_LINE_SETUP, st);
@@ -792,10 +1004,40 @@ namespace osb {
 					                                                   B.d_liveBits, maxWordsPerView);
 				k_line_compact<<<nv, kCompactThreads, 0, st>>>(dV, B.d_lineTan, B.d_liveBits, maxWordsPerView, taskLines,
 				                                              B.d_lineRecs, B.d_active, B.d_tasks, B.d_counters, B.d_lineDirs, lineRes,
-				                                              ordered ? B.d_bucketTasks : nullptr, bucketCap);
+				                                              ordered ? B.d_bucketTasks : nullptr, bucketCap,
+				                                              pipeline ? B.d_tasksPV : nullptr, pipeline ? B.d_pipe + kPipeHead : nullptr,
+				                                              maxWordsPerView);
 				c->launches++;
 			}
-			if (!g.noMap && coop) {
+			if (pipeline) {
+				// walk + gather of a view back to back in one persistent kernel (see k_view_pipeline)
+				const int segsP = ((h >> 3) + kSegRows - 1) / kSegRows;
+				const uint32_t perView = (uint32_t)((((w >> 3) + 3) >> 2) * segsP);
+				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
+				GatherIO gioP{dV,      nv,          g, B.d_tabs, c->d_solid, T->d_atan, B.d_strips, B.d_lineRecs, B.d_lineTan, B.d_lineMask,
+				              lineRes, d_fb + (size_t)v0 * w * h, d_depth + (size_t)v0 * w * h, kSegRows};
+				const unsigned blocks = (unsigned)((size_t)c->smCount * T->walkBlocksPerSm[num]);
+				const uint32_t window = (uint32_t)pipeline_window();
+				KLaunch kl(c, K_VIEW_PIPELINE, st);
+				if (num == OSB200_NUM_IEEE)
+					k_view_pipeline<false, false><<<blocks, kWalkThreads, walkSmem, st>>>(io, gioP, sse, B.d_active, B.d_tasksPV, maxWordsPerView,
+					                                                                   B.d_pipe, window, perView, (uint32_t)pipeline_split());
+				else if (num == OSB200_NUM_SSE)
+					k_view_pipeline<true, false><<<blocks, kWalkThreads, walkSmem, st>>>(io, gioP, sse, B.d_active, B.d_tasksPV, maxWordsPerView,
+					                                                                  B.d_pipe, window, perView, (uint32_t)pipeline_split());
+				else
+					k_view_pipeline<true, true><<<blocks, kWalkThreads, walkSmem, st>>>(io, gioP, sse, B.d_active, B.d_tasksPV, maxWordsPerView,
+					                                                                 B.d_pipe, window, perView, (uint32_t)pipeline_split());
+#ifdef OSB_PIPE_STATS
+				{
+					unsigned long long hs[4];
+					cudaMemcpyAsync(hs, B.d_pipe + 96, sizeof(hs), cudaMemcpyDeviceToHost, st);
+					cudaStreamSynchronize(st);
+					fprintf(stderr, "pipe stats: blocks %u  dispatch %.3f  walk %.3f  gather %.3f Gcycles (lane 0 of every warp), sleeps %llu\n", blocks,
+					        hs[0] * 1e-9, hs[1] * 1e-9, hs[2] * 1e-9, hs[3]);
+				}
+#endif
+			} else if (!g.noMap && coop) {
 				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
 				const size_t smem = coop_shared_bytes(lineRes);
 				const unsigned blocks = (unsigned)std::min<size_t>(totalLines, (size_t)c->smCount * 32);
@@ -837,7 +1079,7 @@ namespace osb {
 			const unsigned gBlocks = (unsigned)((tasks + kGatherWarps - 1) / kGatherWarps);
 			GatherIO gio{dV,           nv,      g, B.d_tabs, c->d_solid, T->d_atan, B.d_strips, B.d_lineRecs, B.d_lineTan, B.d_lineMask,
 			             lineRes, d_fb + (size_t)v0 * w * h, d_depth + (size_t)v0 * w * h, segRows};
-			{
+			if (!pipeline) {
 				KLaunch kl(c, K_GATHER_FOG, st);
 				if (num == OSB200_NUM_IEEE)
 					k_gather_fog<false, false><<<gBlocks, kGatherWarps * 32, 0, st>>>(gio, sse);

@@ -979,7 +979,10 @@ namespace osb {
 		int segRows; // block rows per warp task, 1..kSegRows (small launches use fewer: more warps in flight)
 	};
 
-	template <bool kSse, bool kSse2Fog> struct GatherLane {
+	// kCg: strips and line records are read with ld.global.cg (L2 only).  Needed when the SAME kernel wrote them on another
+	// SM (k_view_pipeline): L1 is not coherent, and this SM's L1 may still hold a record line its walker warps read before
+	// the line's hull was published.
+	template <bool kSse, bool kSse2Fog, bool kCg = false> struct GatherLane {
 		// task
 		int by0, by1, colBlocks, cg;
 		const ViewParams *V;
@@ -1105,8 +1108,10 @@ namespace osb {
 		OSB_HDM uint2 fetch_pixel(const GatherIO &io, int slot, int pitchIndex, uint32_t hull) const {
 			uint2 pix = make_uint2(0u, osbc::f2u(10000.f)); // LinePixel::Clear (:89-92)
 			// first <= pitchIndex < first + count as one unsigned compare; a culled line carries count = 0
-			if ((uint32_t)(pitchIndex - (int)(hull & 0xffffu)) < (hull >> 16))
-				pix = osbc::ldg(io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex));
+			if ((uint32_t)(pitchIndex - (int)(hull & 0xffffu)) < (hull >> 16)) {
+				const uint2 *p = io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex);
+				pix = kCg ? osbc::ldcg(p) : osbc::ldg(p);
+			}
 			return pix;
 		}
 #else
@@ -1188,7 +1193,8 @@ namespace osb {
 						yawIndex = (yawIndex * numLines) >> 16;
 						yawIndex = uminu(yawIndex, numLines - 1); // memory safety; the reference would read a stale line
 						lpw[j] = stagedRecs ? *reinterpret_cast<const int4 *>(stagedRecs + yawIndex)
-						                    : ldg(reinterpret_cast<const int4 *>(lpV + yawIndex));
+						                    : (kCg ? ldcg(reinterpret_cast<const int4 *>(lpV + yawIndex))
+						                           : ldg(reinterpret_cast<const int4 *>(lpV + yawIndex)));
 					}
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -1241,7 +1247,16 @@ namespace osb {
 					yawIndex = (yawIndex * yawScale2) >> 16;
 					yawIndex = (yawIndex * numLines) >> 16;
 					yawIndex = osbc::uminu(yawIndex, numLines - 1);
-					const LineRec lp = lpV[yawIndex];
+					LineRec lp;
+					if (kCg) {
+						const int4 w4 = ldcg(reinterpret_cast<const int4 *>(lpV + yawIndex));
+						lp.pitchTanMinI = w4.x;
+						lp.pitchScaleI = w4.y;
+						lp.slot = w4.z;
+						lp.view = w4.w;
+					} else {
+						lp = lpV[yawIndex];
+					}
 					const float2 lt = ltV[yawIndex];
 					float pitch = fmul(v4[2], num.rsqrt(fadd(fmul(v4[0], v4[0]), fmul(v4[1], v4[1]))));
 					pitch = num.toSpecialTan(pitch);

@@ -153,6 +153,46 @@ def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
             assert np.array_equal(outs[0][k].view(np.uint32), other[k].view(np.uint32)), k
 
 
+def test_view_pipeline_gives_the_same_frames(tmp_path, port, title_map):
+    """k_view_pipeline (OSB200_PIPELINE = window in views, off by default: measured slower) walks and
+    gathers a view back to back inside one persistent kernel.  A batch large enough to take that path, rendered in fresh
+    processes with the pipeline off, with an unlimited window, with a window of 8 views (admission waits) and with roles
+    per SM, gives identical frames + depth; a few of them are checked against the oracle port."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, numpy as np\n"
+        f"sys.path.insert(0, {root!r})\n"
+        "import openspades_b200 as osb\n"
+        "from openspades_b200 import workloads\n"
+        "from openspades_b200.hostlib import VoxelMap\n"
+        "m = VoxelMap.load_file(workloads.TITLE_VXL)\n"
+        "with osb.Context(0, osb.NUM_SSE2, sw_threads=4) as ctx:\n"
+        "    ctx.map_upload(m.solid.copy(), m.color.copy())\n"
+        "    S = workloads.random_scenes(96, m.solid, 256, 256, seed=31)\n"
+        "    S[5]['origin'] = (256.5, 256.5, 62.5)\n"  # a view with the eye inside the ground
+        "    ctx.timing_enable(True)\n"
+        "    fb, dp = ctx.render(S, 256, 256, (0.8, 1.0, 1.0), 128.0)\n"
+        "    names = sorted(k for k, v in ctx.timing_read().items() if v[0])\n"
+        "np.savez(sys.argv[1], fb=fb, dp=dp, names=np.array(names))\n")
+    outs = []
+    for window, split in (("0", "0"), ("4096", "0"), ("8", "0"), ("4096", "10")):
+        out = str(tmp_path / f"pipe{window}_{split}.npz")
+        env = dict(os.environ, OSB200_PIPELINE=window, OSB200_PIPE_SPLIT=split)
+        subprocess.run([sys.executable, "-c", code, out], check=True, env=env, timeout=300)
+        outs.append(np.load(out))
+        assert ("k_view_pipeline" in list(outs[-1]["names"])) == (window != "0"), list(outs[-1]["names"])
+    for other in outs[1:]:
+        for k in ("fb", "dp"):
+            assert np.array_equal(outs[0][k].view(np.uint32), other[k].view(np.uint32)), k
+    solid, color = title_map.solid.copy(), title_map.color.copy()
+    S = workloads.random_scenes(96, solid, 256, 256, seed=31)
+    for i in (0, 40, 95):
+        pfb, pdp = port.render(solid, color, S[i], 256, 256, (0.8, 1.0, 1.0), 128.0, osb.NUM_SSE2, 4, 1)
+        assert _report(f"pipeline view {i} vs port", outs[1]["fb"][i], outs[1]["dp"][i], pfb, pdp) == (1.0, 1.0)
+
+
 @pytest.mark.parametrize("under", [2, 4])
 @pytest.mark.parametrize("size", [(800, 600, 30.0), (256, 256, 68.0)])
 def test_undersampling_matches_reference(port, title_map, under, size):
