@@ -247,7 +247,7 @@ namespace osb {
 					atomicMax(&s_taskSteps[rank >> 5], (int)predict_steps(tn.x, tn.y, lineRes, V.origin[2], lineDirs[gl]));
 			}
 			// (a culled line never reaches the walker: its record carries the empty hull from the start)
-			lineRecs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : vi);
+			lineRecs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : vi, lineRes);
 		}
 		const uint32_t nTasks = (nLive + (uint32_t)taskLines - 1) / (uint32_t)taskLines;
 		if (threadIdx.x == 0)

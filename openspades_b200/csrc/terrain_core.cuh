@@ -199,7 +199,8 @@ namespace osb {
 	struct alignas(16) LineRec {
 		int pitchTanMinI; // static_cast<int>(minTan * 65536.f)        (SWMapRenderer.cpp:305)
 		int pitchScaleI;  // static_cast<int>(pitchScale * 65536.f)    (:306)
-		int slot;         // strip slot (index in the active list), -1 = culled line: its strip is all LinePixel::Clear
+		int slot;         // strip slot (index in the active list), -1 = culled line: its strip is all LinePixel::Clear;
+		                  // hull scheme: slot * lineRes, the index of the line's first strip pixel (make_line_rec)
 		int view;         // view index inside the chunk until the walker has finished the line; then (OSB_STRIP_HULL)
 		                  // first | count << 16: the hull [first, first + count) of the strip pixels the line wrote
 	};
@@ -286,11 +287,13 @@ namespace osb {
 		o.culled = minPitch >= maxPitch; // the strip stays cleared (:387-389)
 		return o;
 	}
-	OSB_HDI LineRec make_line_rec(const LineSetupOut &o, int slot, int view) {
+	// lineRes > 0 (hull scheme): the record carries the index of the line's first strip pixel, slot * lineRes, instead of
+	// the slot -- the gather adds the pitch index and is done (one multiply and one constant load less per pixel)
+	OSB_HDI LineRec make_line_rec(const LineSetupOut &o, int slot, int view, int lineRes = 0) {
 		LineRec r;
 		r.pitchTanMinI = osbn::x86_f2i(osbc::fmul(o.minTan, 65536.f));
 		r.pitchScaleI = osbn::x86_f2i(osbc::fmul(o.pitchScale, 65536.f));
-		r.slot = slot;
+		r.slot = (OSB_STRIP_HULL && lineRes > 0 && slot >= 0) ? (int)((uint32_t)slot * (uint32_t)lineRes) : slot;
 		r.view = view;
 		return r;
 	}
@@ -896,21 +899,23 @@ namespace osb {
 		int idx, base;
 		if (v < 0.f) {
 			if (v > -1.f) {
-				idx = osbn::x86_f2i(fmul(v, -4096.f));
+				idx = f2i_rz(fmul(v, -4096.f));
 				base = 10000;
 			} else {
-				idx = osbn::x86_f2i(num.div(-4096.f, v));
+				idx = f2i_rz(num.div(-4096.f, v));
 				base = 15000;
 			}
 		} else {
 			if (v < 1.f) {
-				idx = osbn::x86_f2i(fmul(v, 4096.f));
+				idx = f2i_rz(fmul(v, 4096.f));
 				base = 0;
 			} else {
-				idx = osbn::x86_f2i(num.div(4096.f, v));
+				idx = f2i_rz(num.div(4096.f, v));
 				base = 5000;
 			}
 		}
+		// |v| < 1 -> |v| * 4096 < 4096, |v| >= 1 -> 4096 / |v| <= 4096: cvttss2si's out-of-range case cannot occur, and a NaN
+		// (index "indefinite" in the reference, an out-of-bounds read there) ends as entry 0 here
 		idx = imin(imax(idx, 0), 4999); // memory safety only; in range for every finite input
 		return ldg(tab + base + idx);
 	}
@@ -930,18 +935,18 @@ namespace osb {
 		if (kSse2Fog) {
 			float d = dist > 0.f ? dist : 0.f; // maxps / minps return the 2nd operand on NaN
 			d = d < 256.f ? d : 256.f;
-			factor = osbn::x86_f2i_rn(d);
+			factor = osbc::f2i_rn(d); // d is in [0, 256]: cvtps2dq's out-of-range case cannot occur
 		} else {
 			factor = osbc::imin(osbn::x86_f2i(dist), 256);
 			factor = osbc::imax(0, factor);
 		}
 		const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
-		const uint32_t br = (((col & 0x00ff00ffu) * f2 + fogBR * f1) >> 8) & 0x00ff00ffu;
-		const uint32_t gg = (((col & 0x0000ff00u) * f2 + fogG8 * f1) >> 8) & 0x0000ff00u;
-		uint32_t out = br | gg;
-		if (kSse2Fog) // lane 3 of the SSE2 path keeps (X * f2) >> 8
-			out |= (((col >> 24) * f2) << 16) & 0xff000000u;
-		return out;
+		const uint32_t br = ((col & 0x00ff00ffu) * f2 + fogBR * f1) >> 8;
+		// G and X (bytes 1 and 3) share the second multiply like B and R the first: low half G * f2 + fogG * f1, high half
+		// X * f2, both below 2^16; their bits 8..15 are the result bytes and already sit where they belong
+		const uint32_t gx = ((col >> 8) & 0x00ff00ffu) * f2 + (fogG8 >> 8) * f1;
+		// lane 3 of the SSE2 path keeps (X * f2) >> 8, the scalar path writes 0 there
+		return (br & 0x00ff00ffu) | (gx & (kSse2Fog ? 0xff00ff00u : 0x0000ff00u));
 	}
 
 	// ------------------------------------------------------------------------------------------------------------
@@ -986,6 +991,8 @@ namespace osb {
 		// task
 		int by0, by1, colBlocks, cg;
 		const ViewParams *V;
+		uint32_t *fbLane;  // frame pixel (row 0 of the task's first block row, this lane's column) of this lane's view
+		ptrdiff_t dbDelta; // depth pixel - frame pixel, in 4-byte elements (both buffers hold one 4-byte word per pixel)
 		// pixel role
 		int pb, px, xs, hSh;
 		uint32_t o; // pixel offset inside the view of this lane's column at block row by0
@@ -1021,6 +1028,8 @@ namespace osb {
 			const int bxc = colValid ? bx : colBlocks - 1;
 			px = lane & 7;                     // pixel column inside the block
 			o = (uint32_t)(by0 * 8) * (uint32_t)g.fw + (uint32_t)((bxc << 3) + px);
+			fbLane = io.fb + (size_t)vi * g.fw * g.fh + o;
+			dbDelta = reinterpret_cast<const uint32_t *>(io.depth) - io.fb;
 			const int under = g.under;
 			hSh = under == 1 ? 3 : (under == 2 ? 2 : 1); // log2(8 / under)
 			xs = (px - (px % under)) / under;            // undersampling: pixels share their group leader's sample
@@ -1109,7 +1118,7 @@ namespace osb {
 			uint2 pix = make_uint2(0u, osbc::f2u(10000.f)); // LinePixel::Clear (:89-92)
 			// first <= pitchIndex < first + count as one unsigned compare; a culled line carries count = 0
 			if ((uint32_t)(pitchIndex - (int)(hull & 0xffffu)) < (hull >> 16)) {
-				const uint2 *p = io.strips + ((uint32_t)slot * (uint32_t)io.lineRes + (uint32_t)pitchIndex);
+				const uint2 *p = io.strips + ((uint32_t)slot + (uint32_t)pitchIndex); // slot = first strip pixel of the line
 				pix = kCg ? osbc::ldcg(p) : osbc::ldg(p);
 			}
 			return pix;
@@ -1138,9 +1147,10 @@ namespace osb {
 			const int row = by + r;
 			if (row >= by1)
 				return;
-			uint32_t *fbV = io.fb + (size_t)(V - io.views) * g.fw * g.fh;
-			float *dbV = io.depth + (size_t)(V - io.views) * g.fw * g.fh;
-			uint32_t oo = o + (uint32_t)((row - by0) * 8) * (uint32_t)g.fw;
+			// one 64-bit pixel pointer per lane; the depth pixel lies a constant distance behind it
+			uint32_t *fbV = fbLane;
+			float *dbV = reinterpret_cast<float *>(fbLane + dbDelta);
+			uint32_t oo = (uint32_t)((row - by0) * 8) * (uint32_t)g.fw;
 			const float fog0 = sm.fog[(row - by0) * 2][px >> 2 | (pb << 1)], fog1 = sm.fog[(row - by0) * 2 + 1][px >> 2 | (pb << 1)];
 			const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
 			if (skip) {

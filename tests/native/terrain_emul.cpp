@@ -137,7 +137,7 @@ namespace {
 						slot = (int)active.size();
 						active.push_back(gl);
 					}
-					recs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : i);
+					recs[gl] = make_line_rec(o, slot, (OSB_STRIP_HULL && slot < 0) ? kEmptyHull : i, lineRes);
 				}
 			}
 		} else {
