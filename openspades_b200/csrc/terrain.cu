@@ -341,12 +341,14 @@ namespace osb {
 			const uint32_t task = __ldg(tasks + t);
 			const uint32_t slot = (task >> 5) + (uint32_t)lane;
 			bool alive = (uint32_t)lane <= (task & 31u);
-			if (alive)
+			if (alive) {
 				W.init(io, __ldg(active + slot), slot, filled, kWalkThreads);
-			while (__any_sync(0xffffffffu, alive)) {
-				if (alive)
-					alive = W.step(io, num, filled, kWalkThreads);
+				// every lane walks its own line to the end; the warp meets again behind the loop (a warp-wide vote per step
+				// cost a dozen instructions of votes and register shuffles per DDA step)
+				while (W.step(io, num, filled, kWalkThreads)) {
+				}
 			}
+			__syncwarp();
 		}
 	}
 

@@ -574,12 +574,14 @@ namespace osb {
 					px = make_uint2(shade<kSse2Shade>(rawCol, mode), f2u(fadd(medDist, fmul(i2f(zA), heightScale))));
 					havePx = true;
 				}
-				uint2 *dst = io.strips + (stripBase + ((uint32_t)w << 5));
+				// (unsigned 32-bit pixel index: a chunk stays below 2^32 strip pixels, and the address is then one wide
+				// multiply-add instead of a sign-extended 64-bit sum per store)
+				const uint32_t wordBase = stripBase + ((uint32_t)w << 5);
 				OSB_STAT(1, 1); // word with landing pixels
 				do {
-					const int b = ffs32(todo);
+					const uint32_t b = (uint32_t)ffs32(todo);
 					todo &= todo - 1;
-					stcs(dst + b, px);
+					stcs(io.strips + (uint32_t)(wordBase + b), px);
 					OSB_STAT(2, 1); // strip pixel stored
 				} while (todo);
 			}
