@@ -69,6 +69,7 @@ namespace osbc {
 	OSB_HDI float fsqrt(float a) { return __fsqrt_rn(a); }
 	OSB_HDI int f2i_rz(float f) { return __float2int_rz(f); } // in-range inputs only
 	OSB_HDI int f2i_rn(float f) { return __float2int_rn(f); }
+	OSB_HDI uint32_t f2u_rz_sat(float f) { return __float2uint_rz(f); } // negative and NaN -> 0, >= 2^32 -> 0xffffffff
 	OSB_HDI float i2f(int i) { return __int2float_rn(i); }
 	OSB_HDI float u2flt(uint32_t i) { return __uint2float_rn(i); }
 	OSB_HDI int ffs32(uint32_t x) { return __ffs((int)x) - 1; } // index of the lowest set bit, x != 0
@@ -94,6 +95,7 @@ namespace osbc {
 	OSB_HDI float fsqrt(float a) { return sqrtf(a); }
 	OSB_HDI int f2i_rz(float f) { return (int)f; }
 	OSB_HDI int f2i_rn(float f) { return (int)lrintf(f); } // default rounding mode: nearest even
+	OSB_HDI uint32_t f2u_rz_sat(float f) { return !(f > 0.f) ? 0u : (f >= 4294967296.f ? 0xffffffffu : (uint32_t)f); }
 	OSB_HDI float i2f(int i) { return (float)i; }
 	OSB_HDI float u2flt(uint32_t i) { return (float)i; }
 	OSB_HDI int ffs32(uint32_t x) { return __builtin_ctz(x); }

@@ -94,6 +94,20 @@ namespace osbn {
 			}
 			return osbc::fdiv(1.f, b);
 		}
+		// ToSpecialTan for |v| > 1 (SWMapRenderer.cpp:59-66): -2 - rcp(v) for v < -1, 2 - rcp(v) for v > 1.  Both are
+		// sign(v) * (2 - rcp(|v|)) -- the reciprocal (table or division) and the subtraction are odd functions under
+		// round-to-nearest -- so the sign is dealt with once, by copying it onto the positive result.
+		OSB_HDM float specialTanTail(float v) const {
+			const uint32_t u = osbc::f2u(v);
+			float ra;
+			if (kSse) {
+				const uint32_t r = osbc::ldg(t.rcp + ((u & 0x7fffffu) >> (23 - t.rcpBits)));
+				ra = osbc::u2f(r + 0x3f800000u - (u & 0x7f800000u));
+			} else {
+				ra = osbc::fdiv(1.f, osbc::u2f(u & 0x7fffffffu));
+			}
+			return osbc::u2f(osbc::f2u(osbc::fsub(2.f, ra)) | (u & 0x80000000u));
+		}
 		OSB_HDM float rcpHotPos(float b) const { // b > 0
 			if (kSse) {
 				const uint32_t u = osbc::f2u(b);

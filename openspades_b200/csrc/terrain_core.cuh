@@ -405,12 +405,13 @@ namespace osb {
 			const float v = fmul(iDist, zv);
 			float t = v;
 			if (fabsf(v) > 1.f) // |v| <= 64e20: a normal number, the table path needs no range test
-				t = fsub(v < 0.f ? -2.f : 2.f, num.rcpHot(v));
+				t = num.specialTanTail(v);
 			float p = fadd(fmul(t, transScale), transOffset);
 			// p < 0 ? 0 : p;  vmax < p ? vmax : p;  truncation.  p is never NaN here (finite * finite), and a NaN
 			// would end as 0 either way (cvttss2si of the clamp result vs fmaxf dropping the NaN).
-			p = fminf_(fmaxf_(p, 0.f), vmax);
-			return f2i_rz(p);
+			// vmax = lineRes + 0.5: trunc(min(max(p, 0), vmax)) == min(trunc_sat_unsigned(p), lineRes) -- the saturating
+			// unsigned conversion is the lower clamp, and an integer min the upper one
+			return (int)uminu(f2u_rz_sat(p), (uint32_t)vmax);
 		}
 
 		// one DDA step from (irx0, iry0, gx0, gy0, dist0) into the n* members (:426-522)
