@@ -944,12 +944,15 @@ namespace osb {
 			factor = osbc::imax(0, factor);
 		}
 		const uint32_t f1 = (uint32_t)factor, f2 = (uint32_t)(256 - factor);
-		const uint32_t br = ((col & 0x00ff00ffu) * f2 + fogBR * f1) >> 8;
+		const uint32_t br = (col & 0x00ff00ffu) * f2 + fogBR * f1; // B' and R' are bytes 1 and 3
 		// G and X (bytes 1 and 3) share the second multiply like B and R the first: low half G * f2 + fogG * f1, high half
 		// X * f2, both below 2^16; their bits 8..15 are the result bytes and already sit where they belong
 		const uint32_t gx = ((col >> 8) & 0x00ff00ffu) * f2 + (fogG8 >> 8) * f1;
 		// lane 3 of the SSE2 path keeps (X * f2) >> 8, the scalar path writes 0 there
-		return (br & 0x00ff00ffu) | (gx & (kSse2Fog ? 0xff00ff00u : 0x0000ff00u));
+		// result bytes: B' R' = bytes 1 and 3 of the first sum, G' X' = bytes 1 and 3 of the second: one byte permute picks
+		// all four (instead of a shift, two masks and an or)
+		const uint32_t out = osbc::byte_perm(br, gx, 0x7351);
+		return kSse2Fog ? out : (out & 0x00ffffffu);
 	}
 
 	// ------------------------------------------------------------------------------------------------------------
@@ -994,8 +997,9 @@ namespace osb {
 		// task
 		int by0, by1, colBlocks, cg;
 		const ViewParams *V;
-		uint32_t *fbLane;  // frame pixel (row 0 of the task's first block row, this lane's column) of this lane's view
-		ptrdiff_t dbDelta; // depth pixel - frame pixel, in 4-byte elements (both buffers hold one 4-byte word per pixel)
+		uint32_t *fbLane;      // frame pixel (row 0 of the task's first block row, this lane's column) of this lane's view
+		float *dbLane;         // ... and its depth pixel: an address is then one 32-bit offset away (one wide multiply-add)
+		const LineRec *lpLane; // line records of the view
 		// pixel role
 		int pb, px, xs, hSh;
 		uint32_t o; // pixel offset inside the view of this lane's column at block row by0
@@ -1032,7 +1036,8 @@ namespace osb {
 			px = lane & 7;                     // pixel column inside the block
 			o = (uint32_t)(by0 * 8) * (uint32_t)g.fw + (uint32_t)((bxc << 3) + px);
 			fbLane = io.fb + (size_t)vi * g.fw * g.fh + o;
-			dbDelta = reinterpret_cast<const uint32_t *>(io.depth) - io.fb;
+			dbLane = io.depth + (size_t)vi * g.fw * g.fh + o;
+			lpLane = io.lineRecs + V->lineBase;
 			const int under = g.under;
 			hSh = under == 1 ? 3 : (under == 2 ? 2 : 1); // log2(8 / under)
 			xs = (px - (px % under)) / under;            // undersampling: pixels share their group leader's sample
@@ -1152,7 +1157,7 @@ namespace osb {
 				return;
 			// one 64-bit pixel pointer per lane; the depth pixel lies a constant distance behind it
 			uint32_t *fbV = fbLane;
-			float *dbV = reinterpret_cast<float *>(fbLane + dbDelta);
+			float *dbV = dbLane;
 			uint32_t oo = (uint32_t)((row - by0) * 8) * (uint32_t)g.fw;
 			const float fog0 = sm.fog[(row - by0) * 2][px >> 2 | (pb << 1)], fog1 = sm.fog[(row - by0) * 2 + 1][px >> 2 | (pb << 1)];
 			const uint32_t fogBR = g.fogB | (g.fogR << 16), fogG8 = g.fogG << 8;
@@ -1172,7 +1177,7 @@ namespace osb {
 			const uint32_t numLines = (uint32_t)V->numLines;
 			const uint32_t yawScale2 = (uint32_t)V->yawScale2;
 			const int lineRes = io.lineRes;
-			const LineRec *lpV = io.lineRecs + V->lineBase;
+			const LineRec *lpV = lpLane;
 			if (!slow) {
 				const int ci = r * 16 + pb * 4;
 				const int yaw1 = sm.yaw[ci], yaw2 = sm.yaw[ci + 1], yaw3 = sm.yaw[ci + 2], yaw4 = sm.yaw[ci + 3];
