@@ -125,21 +125,24 @@ namespace osb {
 
 	// Device-side recurrences for large batches: one warp per view, one lane per role.
 	__global__ void k_view_prep(const ViewParams *__restrict__ views, int nViews, FrameGeom g, float2 *lineDirs, float *tabs) {
-		const int vi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-		const int lane = threadIdx.x & 31;
+		// Every job is a sequential float recurrence (that is what makes the reference's tables what they are): one THREAD per
+		// (job, view), the job in blockIdx.y, so that the 32 lanes of a warp run the same recurrence for 32 views.  (One warp
+		// per view with a lane per job spent a whole warp instruction on every step of one lane's recurrence: 56 us.)
+		//   job 0: line directions, 1: fog vx, 2 .. 2 + T - 1: fog vy band of emulated thread t, then T jobs: v1 columns
+		const int vi = blockIdx.x * blockDim.x + threadIdx.x;
 		if (vi >= nViews)
 			return;
+		const int job = blockIdx.y;
 		const ViewParams &V = views[vi];
 		float *vx = tabs + V.tabBase, *vy = vx + (g.fw >> 2), *v1 = vy + (g.fh >> 2);
-		if (lane == 0)
+		if (job == 0)
 			prep_line_dirs(V, lineDirs + V.lineBase);
-		else if (lane == 1)
+		else if (job == 1)
 			prep_fog_vx(V, g, vx);
-		// the emulated SW threads (<= 32) are spread over the lanes for the vy bands and v1 columns
-		for (int t = lane; t < g.swThreads; t += 32)
-			prep_fog_vy(V, g, t, vy);
-		for (int t = 31 - lane; t < g.swThreads; t += 32)
-			prep_v1(V, g, t, v1);
+		else if (job < 2 + g.swThreads)
+			prep_fog_vy(V, g, job - 2, vy);
+		else
+			prep_v1(V, g, job - 2 - g.swThreads, v1);
 	}
 
 	// One thread per yaw line (blockIdx.y = view): pitch cull against the frustum side planes.  Writes the line's
@@ -979,7 +982,7 @@ namespace osb {
 				OSB_CUDA(cudaMemcpyAsync(B.d_tabs, T->h_tabs, sizeof(float) * tabF * nv, cudaMemcpyHostToDevice, st));
 			} else {
 				KLaunch kl(c, K_VIEW_PREP, st);
-				k_view_prep<<<(nv + 3) / 4, 128, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
+				k_view_prep<<<dim3((nv + 31) / 32, 2 + 2 * g.swThreads, 1), 32, 0, st>>>(dV, nv, g, B.d_lineDirs, B.d_tabs);
 			}
 			// small launches cut a view's lines into smaller tasks (a line is one long dependent chain: what counts is
 			// how many warps run side by side and how little each warp diverges)
