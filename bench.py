@@ -37,7 +37,8 @@ BYTES_PER_PIXEL = 8  # 4 B BGRX + 4 B f32 depth written once per
 BYTES_PER_RAY = 64   # 24 B in + 40 B RayCastResult out
 CPU_VIEWS_PER_WORKER = 256  # CPU sample of both arms: views per worker process per step
 STRONG_VIEWS_TOTAL = 4096   # BASELINE.json configs[3]: 4096 views sharded by view across 1/2/4/8 GPUs
-FLOP_PER_TAP = 42           # one executed radiosity tap (GLRadiosityRenderer.cpp:216-262), sqrt and each divide counted as 1
+FLOP_PER_TAP = 32           # float operations one executed radiosity tap issues (GLRadiosityRenderer.cpp:216-262) now that its
+                            # square root and two divisions come from a table (round 1 / early round 2: 42 with those counted as 1 each)
 
 
 def parse_args():

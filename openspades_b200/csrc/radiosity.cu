@@ -46,6 +46,7 @@ namespace osb {
 		ChunkBox *d_boxes = nullptr;      // kNumChunks
 		int *d_list = nullptr;            // selected chunk ids + [kNumChunks] = count
 		uint32_t *d_words = nullptr;      // dirty word list for the shadow update
+		float2 *d_tapTab = nullptr;       // {1 / len, 1 / (len + 0.4)} of a tap by 4 * len^2 (k_rad_tap_table)
 		std::vector<uint32_t> markWords;  // host dirty bitset, 16 words per row (GLMapShadowRenderer.cpp:57-58)
 		bool allDirty = true;             // initial state: every pixel + every chunk dirty
 		bool anyMarked = false;
@@ -142,8 +143,22 @@ namespace osb {
 
 	// Evaluate for voxel (vx,vy,vz).  tile = bitmap window in shared memory, tile(0,0) = bitmap pixel
 	// (tx0, ty0) (unwrapped coordinates; wrapped when the tile was loaded), row pitch kTileW.
+	// The distance terms of a tap without the square root and the two divisions.  A tap's offset (fx, fy, fz) is made of
+	// two integers and one half-integer (voxel centres against the face a bitmap pixel stands for), so 4 * len^2 is an
+	// integer n, computed exactly, and {1 / len, 1 / (len + 0.4)} are functions of n alone: a table, filled once with the
+	// very same IEEE operations (k_rad_tap_table), gives the same bits for 1 load instead of ~55 instructions.  n beyond
+	// the table (a depth byte no valid bitmap holds) takes the arithmetic path.
+	constexpr int kTapTabMax = 36863; // 4 * (6^2 + 69.5^2 + 64^2) = 35849 for depth bytes <= 64; 288 KB of float2
+	__global__ void k_rad_tap_table(float2 *tab) {
+		const int n = blockIdx.x * blockDim.x + threadIdx.x;
+		if (n > kTapTabMax)
+			return;
+		const float len = __fsqrt_rn(__fmul_rn((float)n, 0.25f));
+		tab[n] = make_float2(__fdiv_rn(1.f, len), __fdiv_rn(1.f, __fadd_rn(len, .4f)));
+	}
+
 	__device__ __forceinline__ void evaluate_voxel(const uint32_t *tile, int tx0, int ty0, int vx, int vy, int vz,
-	                                               float acc[12]) {
+	                                               float acc[12], const float2 *__restrict__ tapTab) {
 #pragma unroll
 		for (int i = 0; i < 12; i++)
 			acc[i] = 0.f;
@@ -160,22 +175,36 @@ namespace osb {
 				const int depth = (int)(pixel >> 24);
 				const int wy = cy + dy + depth, wz = depth;
 				float fy, fz, facing;
+				int a2, b2; // 2 fy, 2 fz
 				if (pixel & 0x80u) {
 					if (wy <= vy)
 						continue;
 					fy = __fsub_rn(py, (float)wy);
 					fz = __fsub_rn(pz, __fsub_rn((float)wz, .5f));
 					facing = -fy;
+					a2 = 2 * (vy - wy) + 1;
+					b2 = 2 * (vz - wz + 1);
 				} else {
 					if (wz <= vz)
 						continue;
 					fy = __fsub_rn(py, __fadd_rn((float)wy, .5f));
 					fz = __fsub_rn(pz, (float)wz);
 					facing = -fz;
+					a2 = 2 * (vy - wy);
+					b2 = 2 * (vz - wz) + 1;
 				}
-				const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(fx2, __fmul_rn(fy, fy)), __fmul_rn(fz, fz)));
-				const float invLen = __fdiv_rn(1.f, len);
-				const float invSmooth = __fdiv_rn(1.f, __fadd_rn(len, .4f));
+				// 4 * len^2 in integers: (2 fx)^2 + (2 fy)^2 + (2 fz)^2 (every term of the float sum is exact as well)
+				const int n = 4 * dx * dx + a2 * a2 + b2 * b2;
+				float invLen, invSmooth;
+				if (n <= kTapTabMax) {
+					const float2 t = __ldg(tapTab + n);
+					invLen = t.x;
+					invSmooth = t.y;
+				} else {
+					const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(fx2, __fmul_rn(fy, fy)), __fmul_rn(fz, fz)));
+					invLen = __fdiv_rn(1.f, len);
+					invSmooth = __fdiv_rn(1.f, __fadd_rn(len, .4f));
+				}
 				float intensity = __fmul_rn(facing, invLen);
 				intensity = __fmul_rn(intensity, invSmooth);
 				intensity = __fmul_rn(intensity, invSmooth);
@@ -267,7 +296,7 @@ namespace osb {
 	__global__ void __launch_bounds__(256) k_radiosity(const uint32_t *__restrict__ bitmap, ChunkBox *boxes,
 	                                                   const int *__restrict__ list, uint32_t *__restrict__ vFlat,
 	                                                   uint32_t *__restrict__ vX, uint32_t *__restrict__ vY,
-	                                                   uint32_t *__restrict__ vZ, int mode) {
+	                                                   uint32_t *__restrict__ vZ, int mode, const float2 *__restrict__ tapTab) {
 		__shared__ uint32_t tile[kTileW * kTileH];
 		__shared__ ChunkBox s_box;
 		if ((int)blockIdx.x >= list[kNumChunks])
@@ -287,7 +316,7 @@ namespace osb {
 			const int lx = i % nx, t = i / nx, ly = t % ny, lz = t / ny;
 			const int x = X0 + b.lo[0] + lx, y = Y0 + b.lo[1] + ly, z = Z0 + b.lo[2] + lz;
 			float acc[12];
-			evaluate_voxel(tile, tx0, ty0, x, y, z, acc);
+			evaluate_voxel(tile, tx0, ty0, x, y, z, acc, tapTab);
 			const size_t o = ((size_t)z * 512 + y) * 512 + x;
 			vFlat[o] = encode_value(acc, mode);
 			vX[o] = encode_value(acc + 3, mode);
@@ -306,7 +335,8 @@ namespace osb {
 	// Test hook: un-encoded Evaluate results of an arbitrary box (<= 16 per axis per CTA), 12 floats/voxel,
 	// box-ordered [z][y][x].  Grid = blocks of 16^3 covering the box.
 	__global__ void __launch_bounds__(256) k_radiosity_f32(const uint32_t *__restrict__ bitmap, int x0, int y0, int z0,
-	                                                       int nx, int ny, int nz, float *__restrict__ out) {
+	                                                       int nx, int ny, int nz, float *__restrict__ out,
+	                                                       const float2 *__restrict__ tapTab) {
 		__shared__ uint32_t tile[kTileW * kTileH];
 		const int bxn = (nx + 15) >> 4, byn = (ny + 15) >> 4;
 		const int bx = blockIdx.x % bxn, by = (blockIdx.x / bxn) % byn, bz = blockIdx.x / (bxn * byn);
@@ -320,7 +350,7 @@ namespace osb {
 			if (gx >= nx || gy >= ny || gz >= nz)
 				continue;
 			float acc[12];
-			evaluate_voxel(tile, tx0, ty0, X0 + lx, Y0 + ly, Z0 + lz, acc);
+			evaluate_voxel(tile, tx0, ty0, X0 + lx, Y0 + ly, Z0 + lz, acc, tapTab);
 			float *o = out + (((size_t)gz * ny + gy) * nx + gx) * 12;
 #pragma unroll
 			for (int k = 0; k < 12; k++)
@@ -414,6 +444,9 @@ namespace osb {
 		OSB_CUDA(cudaMalloc(&R->d_boxes, sizeof(ChunkBox) * kNumChunks));
 		OSB_CUDA(cudaMalloc(&R->d_list, sizeof(int) * (kNumChunks + 1)));
 		OSB_CUDA(cudaMalloc(&R->d_words, 512 * 16 * 4));
+		OSB_CUDA(cudaMalloc(&R->d_tapTab, sizeof(float2) * (kTapTabMax + 1)));
+		k_rad_tap_table<<<(kTapTabMax + 256) / 256, 256, 0, c->stream>>>(R->d_tapTab);
+		c->launches++;
 		OSB_CUDA(cudaMallocHost(&R->h_count, sizeof(int)));
 		OSB_CUDA(cudaMallocHost(&R->h_words, 512 * 16 * 4));
 		return radiosity_reset(c);
@@ -429,6 +462,7 @@ namespace osb {
 		cudaFree(R->d_boxes);
 		cudaFree(R->d_list);
 		cudaFree(R->d_words);
+		cudaFree(R->d_tapTab);
 		cudaFreeHost(R->h_count);
 		cudaFreeHost(R->h_words);
 		delete R;
@@ -533,7 +567,7 @@ int osb200_radiosity_update(osb200_ctx *c, int maxChunks, const float *eye) {
 	{
 		osb::KLaunch kl(c, osb::K_RADIOSITY);
 		osb::k_radiosity<<<maxChunks, 256, 0, c->stream>>>(R->d_bitmap, R->d_boxes, R->d_list, R->d_vol[0], R->d_vol[1],
-		                                                  R->d_vol[2], R->d_vol[3], c->opts.radiosity_mode);
+		                                                  R->d_vol[2], R->d_vol[3], c->opts.radiosity_mode, R->d_tapTab);
 	}
 	OSB_CUDA(cudaGetLastError());
 	OSB_CUDA(cudaMemcpyAsync(R->h_count, R->d_list + osb::kNumChunks, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -601,7 +635,7 @@ int osb200_radiosity_evaluate_box(osb200_ctx *c, int x0, int y0, int z0, int x1,
 		return -2;
 	const int blocks = ((nx + 15) >> 4) * ((ny + 15) >> 4) * ((nz + 15) >> 4);
 	osb::k_radiosity_f32<<<blocks, 256, 0, c->stream>>>(c->radiosity->d_bitmap, x0, y0, z0, nx, ny, nz,
-	                                                   reinterpret_cast<float *>(c->d_scratch));
+	                                                   reinterpret_cast<float *>(c->d_scratch), c->radiosity->d_tapTab);
 	c->launches++;
 	OSB_CUDA(cudaGetLastError());
 	OSB_CUDA(cudaMemcpyAsync(out, c->d_scratch, bytes, cudaMemcpyDeviceToHost, c->stream));
