@@ -63,6 +63,7 @@ namespace osb {
 		std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
 		c->anyDirty = false;
 		c->mapLoaded = true;
+		c->mapVersion++;
 		radiosity_map_replaced(c);
 		ambient_map_replaced(c);
 		links_map_replaced(c);
@@ -166,6 +167,7 @@ namespace osb {
 			KLaunch kl(c, K_MAP_SCATTER);
 			k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n, c->d_solid,
 			                                                    c->d_color);
+			c->mapVersion++;
 		}
 		std::fill(c->dirtyWords.begin(), c->dirtyWords.end(), 0u);
 		c->anyDirty = false;
@@ -279,6 +281,7 @@ int osb200_create(const osb200_opts *opts, osb200_ctx **out) {
 		TRY(cudaMalloc(&base, sb + cb));
 		c->d_solid = reinterpret_cast<uint64_t *>(base);
 		c->d_color = reinterpret_cast<uint32_t *>(reinterpret_cast<char *>(base) + sb);
+		TRY(cudaMalloc(&c->d_solidXY, sb)); // the ray kernel's copy of the solid map (castray2.cu); here, so that no ray call allocates
 		const char *env = getenv("OSB200_L2_PERSIST");
 		const bool want = env && atoi(env) != 0; // measured on B200: the carve-out costs more (strip write-combining capacity) than it saves -> opt-in only
 		if (want && prop.persistingL2CacheMaxSize > 0 && prop.accessPolicyMaxWindowSize > 0) {
@@ -330,6 +333,7 @@ void osb200_destroy(osb200_ctx *c) {
 	cudaFree(c->d_rsqrt);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_rayCursor);
+	cudaFree(c->d_solidXY);
 	if (c->rayPipe) {
 		cudaStreamDestroy(c->rayPipe->in);
 		cudaStreamDestroy(c->rayPipe->out);
@@ -490,6 +494,7 @@ int osb200_map_flush(osb200_ctx *c, const uint64_t *solid, const uint32_t *color
 		osb::KLaunch kl(c, osb::K_MAP_SCATTER);
 		k_map_scatter<<<(n + 15) / 16, 256, 0, c->stream>>>(reinterpret_cast<DirtyColumn *>(c->d_stage), n,
 		                                                    c->d_solid, c->d_color);
+		c->mapVersion++;
 	}
 	OSB_CUDA(cudaGetLastError());
 	return n;

@@ -26,6 +26,22 @@ namespace {
 		return (f >= -2147483648.f && f < 2147483648.f) ? __float2int_rz(f) : (int)0x80000000;
 	}
 
+#ifndef OSB_RAY_LINEAR
+#define OSB_RAY_LINEAR 1
+#endif
+	// column of the map copy the ray kernel reads: GameMap's own [x][y] order (wrapped), or the renderer's 4x4 tiles
+	__device__ __forceinline__ uint32_t ray_index(int x, int y) {
+#if OSB_RAY_LINEAR
+		return ((uint32_t)(x & 511) << 9) | (uint32_t)(y & 511);
+#else
+		return osb::tiled_index(x & 511, y & 511);
+#endif
+	}
+	__global__ void k_ray_map_xy(const uint64_t *__restrict__ solidT, uint64_t *__restrict__ solidXY) {
+		const int i = blockIdx.x * blockDim.x + threadIdx.x; // [x][y]
+		solidXY[i] = solidT[osb::tiled_index(i >> 9, i & 511)];
+	}
+
 	constexpr int kThreads = 128;
 	constexpr int kWordsPerHit = 10;   // sizeof(osb200_rayhit) / 4
 	constexpr int kCtasPerSm = 10;     // persistent grid: 48 registers x 128 threads -> 10 CTAs per SM
@@ -96,7 +112,7 @@ namespace {
 			iy += axis == 2 ? (py ? 1 : -1) : 0;
 			iz += axis == 3 ? (pz ? 1 : -1) : 0;
 			if (axis == 1 || axis == 2)
-				col = solid[osb::tiled_index(ix & 511, iy & 511)];
+				col = solid[ray_index(ix, iy)];
 			hit = solid_at(col, iz);
 		}
 		const int nx = axis == 1 ? (px ? -1 : 1) : 0, ny = axis == 2 ? (py ? -1 : 1) : 0, nz = axis == 3 ? (pz ? -1 : 1) : 0;
@@ -171,7 +187,7 @@ namespace {
 					dy = __fmul_rn(dy, scale);
 					dz = __fmul_rn(dz, scale);
 					const int ix = x86_f2i(floorf(v0x)), iy = x86_f2i(floorf(v0y)), iz = x86_f2i(floorf(v0z));
-					const uint64_t col = solid[osb::tiled_index(ix & 511, iy & 511)];
+					const uint64_t col = solid[ray_index(ix, iy)];
 					if (solid_at(col, iz)) { // startSolid (:375-384)
 						write_hit(out, mine, 1u | (1u << 8), v0x, v0y, v0z, ix, iy, iz, 0, 0, 0);
 					} else if (maxSteps <= 0) { // the loop never runs: hit = false, hitPos = v0, rest untouched (:503-506)
@@ -231,7 +247,7 @@ namespace {
 					r.iz += isZ ? sz : 0;
 					r.left--;
 					if (!isZ)
-						r.col = solid[osb::tiled_index(r.ix & 511, r.iy & 511)];
+						r.col = solid[ray_index(r.ix, r.iy)];
 					// IsSolidWrapped (GameMap.h:91-98) as one bit: bit z of the column, 0 above the map, 1 below it
 					uint32_t bit = (uint32_t)(r.col >> (r.iz & 63));
 					bit = (uint32_t)r.iz < 64u ? bit : ~((uint32_t)r.iz >> 31);
@@ -256,6 +272,22 @@ namespace {
 			}
 		}
 	}
+	// the solid map as the ray kernel reads it; brought up to date (one 2 MiB pass, no allocation) when the resident map
+	// changed since the last ray call of this context
+	int ray_map(osb200_ctx *c, const uint64_t **out) {
+#if OSB_RAY_LINEAR
+		if (c->solidXYVersion != c->mapVersion) {
+			k_ray_map_xy<<<OSB200_MAP_W * OSB200_MAP_H / 256, 256, 0, c->stream>>>(c->d_solid, c->d_solidXY);
+			c->launches++;
+			OSB_CUDA(cudaGetLastError());
+			c->solidXYVersion = c->mapVersion;
+		}
+		*out = c->d_solidXY;
+#else
+		*out = c->d_solid;
+#endif
+		return 0;
+	}
 } // namespace
 
 extern "C" {
@@ -277,10 +309,13 @@ int osb200_castray2_device(osb200_ctx *c, const float *d_v0, const float *d_dir,
 	if (!c->d_rayCursor)
 		OSB_CUDA(cudaMalloc(&c->d_rayCursor, sizeof(unsigned long long)));
 	OSB_CUDA(cudaMemsetAsync(c->d_rayCursor, 0, sizeof(unsigned long long), c->stream));
+	const uint64_t *solidMap = nullptr;
+	if (int rc = ray_map(c, &solidMap))
+		return rc;
 	size_t blocks = std::min<size_t>((size_t)c->smCount * kCtasPerSm, (n + kThreads - 1) / kThreads);
 	{
 		osb::KLaunch kl(c, osb::K_CASTRAY2);
-		k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(c->d_solid, d_v0, d_dir, maxSteps,
+		k_castray2<<<(unsigned)blocks, kThreads, 0, c->stream>>>(solidMap, d_v0, d_dir, maxSteps,
 		                                                       reinterpret_cast<uint32_t *>(d_out), n, c->d_rayCursor);
 	}
 	OSB_CUDA(cudaGetLastError());
@@ -605,7 +640,10 @@ int osb200_castray2_static(osb200_ctx *c, const float *v0, const float *dir, int
 	OSB_CUDA(cudaMemcpyAsync(d_v0, v0, n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
 	OSB_CUDA(cudaMemcpyAsync(d_dir, dir, n * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
 	const size_t blocks = std::min<size_t>((size_t)c->smCount * kCtasPerSm, (n + kThreads - 1) / kThreads);
-	k_castray2<<<(unsigned)blocks, kThreads, 0, st>>>(c->d_solid, d_v0, d_dir, maxSteps, d_out, n, cursor);
+	const uint64_t *solidMap = nullptr;
+	if (int rc = ray_map(c, &solidMap))
+		return rc;
+	k_castray2<<<(unsigned)blocks, kThreads, 0, st>>>(solidMap, d_v0, d_dir, maxSteps, d_out, n, cursor);
 	c->launches++;
 	OSB_CUDA(cudaGetLastError());
 	OSB_CUDA(cudaMemcpyAsync(out, d_out, n * sizeof(osb200_rayhit), cudaMemcpyDeviceToHost, st));

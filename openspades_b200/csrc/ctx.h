@@ -153,6 +153,10 @@ struct osb200_ctx {
 	int rsqrtBits = 0;
 
 	unsigned long long *d_rayCursor = nullptr; // batch-wide work cursor of k_castray2
+	// the solid map once more in GameMap's own [x][y] order, for the ray kernel (its address is three instructions instead
+	// of eight for the tiled one, and the kernel is bound by exactly that kind of instruction); rebuilt when mapVersion moved
+	uint64_t *d_solidXY = nullptr;
+	uint64_t mapVersion = 0, solidXYVersion = ~0ull;
 	osb::RayPipe *rayPipe = nullptr;           // streams / events of the host-buffer ray pipeline
 
 	// ---- scratch for host-pointer convenience entry points ----
