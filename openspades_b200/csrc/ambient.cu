@@ -52,6 +52,10 @@ namespace osb {
 		const uint64_t *solid;
 		__device__ __forceinline__ uint64_t operator()(int x, int y) const { return solid[tiled_index(x & 511, y & 511)]; }
 	};
+	struct LinearColumns { // the [x][y] copy of the map (ctx.h: ray_map): a cheaper address for the batch ray kernel
+		const uint64_t *solidXY;
+		__device__ __forceinline__ uint64_t operator()(int x, int y) const { return solidXY[((uint32_t)(x & 511) << 9) | (uint32_t)(y & 511)]; }
+	};
 	struct PatchColumns {
 		const uint64_t *patch; // [kAoPatch][kAoPatch], origin (px0, py0) in world columns (unwrapped)
 		int px0, py0;
@@ -239,7 +243,7 @@ namespace osb {
 	__global__ void __launch_bounds__(256) k_castray(const uint64_t *__restrict__ solid, const float *__restrict__ v0,
 	                                                const float *__restrict__ dir, float length, int4 *__restrict__ out,
 	                                                size_t n, unsigned long long *__restrict__ cursor) {
-		const GlobalColumns col{solid};
+		const LinearColumns col{solid}; // `solid` is the [x][y] copy here
 		const unsigned lane = threadIdx.x & 31;
 		RayWalk w;
 		size_t idx = 0;
@@ -632,9 +636,12 @@ int osb200_castray_device(osb200_ctx *c, const float *d_v0, const float *d_dir, 
 	if (!c->d_rayCursor)
 		OSB_CUDA(cudaMalloc(&c->d_rayCursor, sizeof(unsigned long long)));
 	OSB_CUDA(cudaMemsetAsync(c->d_rayCursor, 0, sizeof(unsigned long long), c->stream));
+	const uint64_t *solidXY = nullptr;
+	if (int rc = osb::ray_map(c, &solidXY))
+		return rc;
 	{
 		osb::KLaunch kl(c, osb::K_CASTRAY);
-		osb::k_castray<<<(unsigned)blocks, 256, 0, c->stream>>>(c->d_solid, d_v0, d_dir, length,
+		osb::k_castray<<<(unsigned)blocks, 256, 0, c->stream>>>(solidXY, d_v0, d_dir, length,
 		                                                       reinterpret_cast<int4 *>(d_out), n, c->d_rayCursor);
 	}
 	OSB_CUDA(cudaGetLastError());

@@ -26,17 +26,9 @@ namespace {
 		return (f >= -2147483648.f && f < 2147483648.f) ? __float2int_rz(f) : (int)0x80000000;
 	}
 
-#ifndef OSB_RAY_LINEAR
-#define OSB_RAY_LINEAR 1
-#endif
-	// column of the map copy the ray kernel reads: GameMap's own [x][y] order (wrapped), or the renderer's 4x4 tiles
-	__device__ __forceinline__ uint32_t ray_index(int x, int y) {
-#if OSB_RAY_LINEAR
-		return ((uint32_t)(x & 511) << 9) | (uint32_t)(y & 511);
-#else
-		return osb::tiled_index(x & 511, y & 511);
-#endif
-	}
+	// column of the map copy the ray kernel reads: GameMap's own [x][y] order, wrapped (measured against the renderer's
+	// 4x4 tiles: 5.62 against 5.99 ms per 16 Mi rays -- three address instructions instead of eight in an ALU-bound step)
+	__device__ __forceinline__ uint32_t ray_index(int x, int y) { return ((uint32_t)(x & 511) << 9) | (uint32_t)(y & 511); }
 	__global__ void k_ray_map_xy(const uint64_t *__restrict__ solidT, uint64_t *__restrict__ solidXY) {
 		const int i = blockIdx.x * blockDim.x + threadIdx.x; // [x][y]
 		solidXY[i] = solidT[osb::tiled_index(i >> 9, i & 511)];
@@ -272,10 +264,12 @@ namespace {
 			}
 		}
 	}
+} // namespace
+
+namespace osb {
 	// the solid map as the ray kernel reads it; brought up to date (one 2 MiB pass, no allocation) when the resident map
 	// changed since the last ray call of this context
-	int ray_map(osb200_ctx *c, const uint64_t **out) {
-#if OSB_RAY_LINEAR
+	int ray_map(osb200_ctx *c, const uint64_t **out) { // declared in ctx.h: k_castray (ambient.cu) reads the same copy
 		if (c->solidXYVersion != c->mapVersion) {
 			k_ray_map_xy<<<OSB200_MAP_W * OSB200_MAP_H / 256, 256, 0, c->stream>>>(c->d_solid, c->d_solidXY);
 			c->launches++;
@@ -283,12 +277,10 @@ namespace {
 			c->solidXYVersion = c->mapVersion;
 		}
 		*out = c->d_solidXY;
-#else
-		*out = c->d_solid;
-#endif
 		return 0;
 	}
-} // namespace
+} // namespace osb
+using osb::ray_map;
 
 extern "C" {
 

@@ -80,6 +80,8 @@ namespace osb {
 struct osb200_ctx;
 namespace osb {
 	// terrain.cu, shared with models.cu (the full EndScene: terrain -> models -> lights -> fog)
+	// castray2.cu: the solid map in [x][y] order (index (x & 511) << 9 | (y & 511)), up to date with the resident map
+	int ray_map(osb200_ctx *c, const uint64_t **out);
 	int render_impl(osb200_ctx *c, const osb200_scene *scenes, int nViews, int w, int h, const float fogColor[3],
 	                float fogDist, uint32_t *d_fb, float *d_depth, uint32_t *host_fb, float *host_depth, bool deferFog);
 	int terrain_out_buffers(osb200_ctx *c, size_t n, uint32_t **fb, float **depth);
