@@ -396,7 +396,11 @@ def run_b200(args):
     else:
         sc_all = workloads.random_scenes(sv, solid, S, S, 68.0, seed=4321)
         mine = np.ascontiguousarray(sc_all[lo:hi])
-        s_fb, s_dp = d_fb[:hi - lo], d_dp[:hi - lo]
+        if hi - lo <= nv:
+            s_fb, s_dp = d_fb[:hi - lo], d_dp[:hi - lo]
+        else:  # --views smaller than this rank's share of the strong-scaling batch: buffers of their own
+            s_fb = torch.empty((hi - lo, S, S), dtype=torch.int32, device=dev)
+            s_dp = torch.zeros((hi - lo, S, S), dtype=torch.float32, device=dev)
         for _ in range(W):
             ctx.render_device(mine, S, S, FOG, FOG_DIST, s_fb, s_dp)
         ctx.sync()
