@@ -101,7 +101,7 @@ namespace osbn {
 			const uint32_t u = osbc::f2u(v);
 			float ra;
 			if (kSse) {
-				const uint32_t r = osbc::ldg(t.rcp + ((u & 0x7fffffu) >> (23 - t.rcpBits)));
+				const uint32_t r = t.rcp[(u & 0x7fffffu) >> (23 - t.rcpBits)]; // (plain load: k_walk_lines keeps the table in shared memory)
 				ra = osbc::u2f(r + 0x3f800000u - (u & 0x7f800000u));
 			} else {
 				ra = osbc::fdiv(1.f, osbc::u2f(u & 0x7fffffffu));
@@ -111,7 +111,7 @@ namespace osbn {
 		OSB_HDM float rcpHotPos(float b) const { // b > 0
 			if (kSse) {
 				const uint32_t u = osbc::f2u(b);
-				const uint32_t r = osbc::ldg(t.rcp + ((u & 0x7fffffu) >> (23 - t.rcpBits)));
+				const uint32_t r = t.rcp[(u & 0x7fffffu) >> (23 - t.rcpBits)];
 				return osbc::u2f(r + 0x3f800000u - (u & 0x7f800000u));
 			}
 			return osbc::fdiv(1.f, b);

@@ -61,6 +61,14 @@ namespace osb {
 		}();
 		return v;
 	}
+	// OSB200_RCP_SHARED=0: k_walk_lines reads the rcpss table from global memory (A/B knob)
+	static int rcp_shared() {
+		static const int v = [] {
+			const char *e = getenv("OSB200_RCP_SHARED");
+			return e ? atoi(e) : 1;
+		}();
+		return v;
+	}
 	static int line_min_lanes() {
 		static const int v = [] {
 			const char *e = getenv("OSB200_LINE_MIN_LANES");
@@ -304,13 +312,23 @@ namespace osb {
 
 	// Persistent line walker.  A warp takes one task (<= 32 adjacent surviving lines of one view) at a time from the
 	// chunk-wide cursor; lane = one yaw line.
-	template <bool kSse, bool kSse2Shade>
+	// kRcpS: the rcpss table (<= kRcpSharedEntries entries) is copied to shared memory once per CTA -- the walker looks it
+	// up once per DDA step and twice per span candidate, each time with an immediately dependent use
+	constexpr int kRcpSharedBits = 11, kRcpSharedEntries = 1 << kRcpSharedBits;
+	template <bool kSse, bool kSse2Shade, bool kRcpS = false>
 	__global__ void __launch_bounds__(kWalkThreads, OSB_WALK_MINB)
 	  k_walk_lines(WalkIO io, osbn::SseTables tabs, const uint32_t *__restrict__ active, const uint32_t *__restrict__ tasks,
 	               uint32_t *__restrict__ counters, uint32_t bucketCap) {
 		extern __shared__ uint32_t s_filled[]; // (lineRes/32 + kWalkExtraWords) words x kWalkThreads, word-major: bank = lane
+		__shared__ uint32_t s_rcp[kRcpS ? kRcpSharedEntries : 1];
 		uint32_t *filled = s_filled + threadIdx.x;
 		const int lane = threadIdx.x & 31;
+		if (kRcpS) {
+			for (int i = threadIdx.x; i < (1 << tabs.rcpBits); i += kWalkThreads)
+				s_rcp[i] = __ldg(tabs.rcp + i);
+			__syncthreads();
+			tabs.rcp = s_rcp;
+		}
 		const osbn::Num<kSse> num{tabs};
 		const uint32_t nTasks = counters[0]; // written by k_line_compact, earlier on this stream
 		// bucketCap != 0: `tasks` holds kTaskBuckets queues of bucketCap entries, filled to counters[2 + b], taken from
@@ -1063,8 +1081,16 @@ namespace osb {
 				WalkIO io{dV, B.d_lineDirs, B.d_lineTan, B.d_lineRecs, c->d_solid, c->d_color, B.d_strips, B.d_lineMask, lineRes};
 				KLaunch kl(c, K_WALK_LINES, st);
 #define LAUNCH_WALK(SSE, SH)                                                                                                      \
-	k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active, ordered ? B.d_bucketTasks : B.d_tasks,    \
-	                                                              B.d_counters, bucketCap)
+	do {                                                                                                                      \
+		if (SSE && sse.rcpBits <= kRcpSharedBits && rcp_shared())                                                              \
+			k_walk_lines<SSE, SH, SSE><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active,                              \
+			                                                                 ordered ? B.d_bucketTasks : B.d_tasks, B.d_counters, \
+			                                                                 bucketCap);                                          \
+		else                                                                                                                  \
+			k_walk_lines<SSE, SH><<<blocks, kWalkThreads, walkSmem, st>>>(io, sse, B.d_active,                                   \
+			                                                              ordered ? B.d_bucketTasks : B.d_tasks, B.d_counters,    \
+			                                                              bucketCap);                                             \
+	} while (0)
 				if (num == OSB200_NUM_IEEE)
 					LAUNCH_WALK(false, false);
 				else if (num == OSB200_NUM_SSE)
