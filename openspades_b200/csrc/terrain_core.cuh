@@ -262,6 +262,13 @@ namespace osb {
 				}
 			}
 		}
+		if (minPitch >= maxPitch) { // culled (:387-389): the strip stays cleared and nothing reads the line's pitch mapping --
+			LineSetupOut c;         // its record carries the empty hull, so the two tanf below would be computed for nobody
+			c.minTan = 0.f;
+			c.pitchScale = 0.f;
+			c.culled = true;
+			return c;
+		}
 		// SpecialTan (:43-57)
 		auto specialTan = [&](float v) -> float {
 			if (v <= -pi * 0.5f)
