@@ -528,6 +528,10 @@ def run_b200(args):
     return 0
 
 
+def rank_is_zero():
+    return int(os.environ.get("RANK", "0")) == 0
+
+
 def run_extras(args, ctx, ext, solid, color, dev, world, barrier, max_over_ranks, peak):
     """configs[1] (1920x1080 single view; replicas only, rank-local) and configs[2] (CastRay2 batch,
     rays sharded by ray, aggregate over ranks).  Same timing rules: warm-up, events on the context stream."""
@@ -658,6 +662,37 @@ def run_extras(args, ctx, ext, solid, color, dev, world, barrier, max_over_ranks
                                "ms_per_frame": g_ms, "e2e_ms_per_frame": g_e2e, "fps_device": 1e3 / g_ms, "fps_e2e": 1e3 / g_e2e,
                                "surface_voxels_of_the_3_models": vox, "kernel_ms": g_kt}
     del fb, dp, hfb, hdp, flush
+
+    # ---- the batched views once more on SURVEY.md 8(d)'s synthetic map (height field + caves + floating slabs, hashed
+    # colours: more ceilings and overhangs per column than Title.vxl), rank-local ----
+    if rank_is_zero():
+        S2, nv2 = 256, 1024
+        syn_solid, syn_color = workloads.synthetic_map(7)
+        with osb.Context(device=dev.index, numerics=osb.NUM_SSE2, sw_threads=4) as sc_ctx:
+            sc_ctx.map_upload(syn_solid, syn_color)
+            sx = torch.cuda.ExternalStream(sc_ctx.stream, device=dev)
+            scenes2 = workloads.random_scenes(nv2, syn_solid, S2, S2, 68.0, seed=99)
+            fb2 = torch.empty((nv2, S2, S2), dtype=torch.int32, device=dev)
+            dp2 = torch.zeros((nv2, S2, S2), dtype=torch.float32, device=dev)
+            for _ in range(3):
+                sc_ctx.render_device(scenes2, S2, S2, FOG, FOG_DIST, fb2, dp2)
+            sc_ctx.sync()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(sx)
+            for _ in range(5):
+                sc_ctx.render_device(scenes2, S2, S2, FOG, FOG_DIST, fb2, dp2)
+            a1.record(sx)
+            a1.synchronize()
+            syn_ms = a0.elapsed_time(a1) / 5
+            sc_ctx.timing_enable(True)
+            sc_ctx.timing_read()
+            sc_ctx.render_device(scenes2, S2, S2, FOG, FOG_DIST, fb2, dp2)
+            sc_ctx.sync()
+            syn_kt = {k: v[1] for k, v in sc_ctx.timing_read().items() if v[0]}
+        out["views_synthetic_map"] = {"workload": f"{nv2} views of {S2}x{S2}, fovY 68, fog, workloads.synthetic_map(7) (SURVEY.md 8d), V-SSE2; "
+                                                  "1024 x 65536 x 8 B = 537 MB per step > L2",
+                                      "ms_per_step": syn_ms, "mpixel_s": nv2 * S2 * S2 / syn_ms / 1e3, "kernel_ms": syn_kt}
+        del fb2, dp2, syn_solid, syn_color
 
     # ---- CastRay2, args.rays rays per GPU, maxSteps 256 ----
     n = args.rays
