@@ -9,14 +9,18 @@
 // (colour, depth) built by a 2-D DDA through map columns, then gathers every screen pixel from (line, pitch index).
 // The per-lane arithmetic lives in terrain_core.cuh (shared with the CPU emulation of tests/native); this file is
 // the launch structure around it:
-//   k_view_prep    one warp per view: the reference's sequential float recurrences (line directions, fog / v1 tables)
-//   k_line_setup   one thread per yaw line: pitch cull against the frustum (glibc-exact atanf / tanf), line records,
-//                  and warp-aggregated COMPACTION of the surviving lines into the chunk's active list -- a line's
-//                  position in that list is its strip slot, culled lines own no strip memory at all
-//   k_walk_lines   persistent grid; a lane walks one active line (DDA + spans), and when enough lanes of a warp have
-//                  finished, the warp fetches the next lines from the chunk-wide cursor with one atomic (ballot +
-//                  prefix rank) -- no launch tail per chunk, no lanes parked on culled or short lines
-//   k_gather_fog   one warp per (view, 32-pixel column group, 8 block rows): RenderFinal + ApplyFog, frame written once
+//   k_view_prep    one thread per (job, view): the reference's sequential float recurrences (line directions, fog / v1
+//                  tables); a warp runs one recurrence for 32 views
+//   k_line_setup   one thread per yaw line: pitch cull against the frustum (glibc-exact atanf / tanf), the line's pitch
+//                  mapping, and per warp the ballot of the lines that survive
+//   k_line_compact one CTA per view: order-preserving compaction of the survivors (a line's rank is its strip slot; culled
+//                  lines own no strip memory), line records, and the walker's tasks: <= 32 adjacent lines of one view
+//   k_walk_lines   persistent grid; a warp takes one task at a time from a batch-wide cursor, a lane walks one line (DDA +
+//                  spans) in a loop of its own -- no launch tail per chunk, no lanes parked on culled lines
+//   k_walk_coop    small launches (a single frame): one warp per line, see CoopLine in terrain_core.cuh
+//   k_gather_fog   one warp per (view, 32-pixel column group, <= 8 block rows): RenderFinal + ApplyFog, frame written once
+//   k_view_pipeline  optional (OSB200_PIPELINE): walk + gather of a view back to back in one persistent kernel; measured
+//                  slower than the two kernels above
 // All float arithmetic is separate IEEE mul/add (--fmad=false) in the reference's evaluation order.
 #include "ctx.h"
 #include "terrain_core.cuh"
