@@ -441,7 +441,7 @@ namespace osb {
 	constexpr int kStagedRecs = 1536; // line records a CTA can stage (24 KB): covers 256x256 views (<= 1192 lines)
 #endif
 #ifndef OSB_GATHER_MINB
-#define OSB_GATHER_MINB 8 // <= 64 registers: measured 1.24 ms per 4096 views against 1.29 ms unbounded (72 registers)
+#define OSB_GATHER_MINB 9 // <= 56 registers, no spills: 1.15 ms per 4096 views; 8 CTAs (62 registers) 1.17, 10 CTAs (48) 1.25
 #endif
 	template <bool kSse, bool kSse2Fog>
 	__global__ void __launch_bounds__(kGatherWarps * 32, OSB_GATHER_MINB) k_gather_fog(GatherIO io, osbn::SseTables tabs) {
