@@ -153,6 +153,22 @@ def test_small_launch_lane_dealing_does_not_change_the_frame(tmp_path):
             assert np.array_equal(outs[0][k].view(np.uint32), other[k].view(np.uint32)), k
 
 
+@pytest.mark.parametrize("threads,under", [(1, 1), (32, 1), (7, 2)])
+def test_batch_with_device_side_tables(port, title_map, threads, under):
+    """More than 8 views take the device-side recurrences (k_view_prep: one thread per (job, view), 2 + 2 T jobs) instead of
+    the host loop the small tests above go through: the same r_swNumThreads / r_swUndersampling dependence, checked on a
+    batch of 24 views against the oracle port."""
+    solid, color = title_map.solid.copy(), title_map.color.copy()
+    w = h = 256
+    scenes = workloads.random_scenes(24, solid, w, h, 68.0, seed=77)
+    with osb.Context(0, osb.NUM_SSE2, sw_threads=threads, undersampling=under) as ctx:
+        ctx.map_upload(solid, color)
+        fbs, dps = ctx.render(scenes, w, h, (0.8, 1.0, 1.0), 128.0)
+    for i in (0, 7, 16, 23):
+        pfb, pdp = port.render(solid, color, scenes[i], w, h, (0.8, 1.0, 1.0), 128.0, osb.NUM_SSE2, threads, under)
+        assert _report(f"batch threads {threads} under {under} #{i}", fbs[i], dps[i], pfb, pdp) == (1.0, 1.0)
+
+
 def test_view_pipeline_gives_the_same_frames(tmp_path, port, title_map):
     """k_view_pipeline (OSB200_PIPELINE = window in views, off by default: measured slower) walks and
     gathers a view back to back inside one persistent kernel.  A batch large enough to take that path, rendered in fresh
